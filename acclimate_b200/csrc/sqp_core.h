@@ -1,0 +1,352 @@
+// sqp_core.h -- sequential quadratic programming core for problems with box bounds and
+// at most ONE general constraint (equality or inequality).
+//
+// This is the solver that replaces the reference's per-agent NLopt(SLSQP) calls
+// (reference include/optimization.h:123-190; call sites src/model/PurchasingManager.cpp:690-702
+// and src/model/Consumer.cpp:381-433).  It keeps the skeleton of Kraft's SLSQP as NLopt drives
+// it: Hessian model started at the identity, one QP sub-problem per iteration, L1 merit function
+// with Kraft's inexact line search (Armijo factor 0.1, quadratic interpolation floored at 0.1, at
+// most 10 backtracks), at most 5 Hessian resets on a non-descent direction (then "roundoff
+// limited"), NLopt's stopping rules (xtol_abs between completed iterations, maxeval) and NLopt's
+// best-point bookkeeping.  One thing is deliberately different: the Hessian model is DIAGONAL,
+// updated by the per-coordinate secant  b_i = dgradL_i / dx_i.  The purchasing objective is
+// separable (each term depends on its own D_r only, PurchasingManager.cpp:220-241) and its
+// constraint is linear, so the Lagrangian's Hessian IS diagonal and the secant is exact for it;
+// the QP sub-problem then collapses to a monotone one-dimensional root-find in the constraint
+// multiplier, which a warp solves exactly out of shared memory.  The first iteration (identity
+// Hessian) coincides with SLSQP's.
+//
+// The file compiles as plain C++ (host, used by oracle/nlopt_shim so that the reference's own
+// CPU run and the device run execute the same arithmetic) and as CUDA device code.  All
+// reductions go through Ctx::sum / Ctx::vmin / Ctx::vmax; Ctx::sum is defined to accumulate
+// element i into partial (i mod 32) in increasing i and then combine the 32 partials by an
+// xor-butterfly, so host and device produce bit-identical results.
+#pragma once
+
+#include <math.h>
+
+#if defined(__CUDACC__)
+#define SQP_HD __host__ __device__ __forceinline__
+#else
+#define SQP_HD inline
+#endif
+
+// Shared limits (host shim and device kernel must agree so that both sides stop alike).
+#ifndef ACCSQP_MAX_ITER
+#define ACCSQP_MAX_ITER 200  // SQP iterations per call before "more than iter SQP iterations"
+#endif
+#define ACCSQP_BMIN 1e-12
+#define ACCSQP_BMAX 1e+15
+
+namespace accsqp {
+
+enum : int {
+    SQP_SUCCESS = 1,
+    SQP_XTOL_REACHED = 4,
+    SQP_MAXEVAL_REACHED = 5,
+    SQP_ROUNDOFF_LIMITED = -4,
+    SQP_FAILURE = -1,
+};
+
+enum : int { CON_NONE = 0, CON_EQ = 1, CON_INEQ = 2 };  // CON_INEQ: c(x) >= 0 (Kraft's convention)
+
+struct Params {
+    int n;
+    int ctype;
+    double ctol;      // feasibility tolerance on the constraint (NLopt's per-constraint tol)
+    int maxeval;      // <=0: unlimited
+    int max_iter;     // cap on SQP iterations (<=0: unlimited)
+};
+
+struct Work {
+    // length-n vectors
+    double *x, *x0, *g, *a, *d, *b, *lo, *hi, *gl, *xbest, *xprev;
+    const double *xl, *xu, *xtol;
+};
+#define ACCSQP_NVEC 11  // number of length-n work vectors above
+
+struct Stats {
+    int iters;
+    int evals;
+    int qp_iters;
+    int qp_inexact;
+    int resets;
+    double minf;
+    int feasible;
+};
+
+// ---------------------------------------------------------------------------------------
+// QP sub-problem:  min 1/2 d^T diag(b) d + g^T d   s.t.  a^T d + c (=|>=) 0,  lo <= d <= hi.
+// Solution d_i(lambda) = clamp((-g_i + lambda a_i)/b_i, lo_i, hi_i); psi(lambda) = a^T d + c is
+// non-decreasing and piecewise linear, its root is found by Newton steps kept inside a bracket.
+// Returns lambda (gradient condition  B d + g = lambda a + z); *cres = a^T d + c at the solution.
+// ---------------------------------------------------------------------------------------
+template <class Ctx>
+SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, Work& w, Stats& st, double* cres) {
+    if (ctype == CON_NONE) {
+        cx.foreach(n, [&](int i) {
+            const double t = -w.g[i] / w.b[i];
+            w.d[i] = t < w.lo[i] ? w.lo[i] : (t > w.hi[i] ? w.hi[i] : t);
+        });
+        *cres = 0.0;
+        return 0.0;
+    }
+    const double target = -c;  // want a^T d = target
+    // attainable range of a^T d over the box
+    const double smin = cx.sum(n, [&](int i) { const double p = w.a[i] * w.lo[i], q = w.a[i] * w.hi[i]; return p < q ? p : q; });
+    const double smax = cx.sum(n, [&](int i) { const double p = w.a[i] * w.lo[i], q = w.a[i] * w.hi[i]; return p > q ? p : q; });
+    int forced = 0;  // -1: push a^T d to its minimum, +1: to its maximum
+    if (ctype == CON_EQ && target <= smin) forced = -1;
+    else if (target >= smax) forced = 1;
+    if (forced != 0) {
+        // vertex of the box; multiplier = the extreme ratio that keeps every bound multiplier sign-feasible
+        cx.foreach(n, [&](int i) {
+            const double p = w.a[i] * w.lo[i], q = w.a[i] * w.hi[i];
+            w.d[i] = (forced > 0) ? (p >= q ? w.lo[i] : w.hi[i]) : (p <= q ? w.lo[i] : w.hi[i]);
+        });
+        const double big = 1e300;
+        // need  (b d + g)_i - lambda a_i <= 0 where d sits at hi,  >= 0 where it sits at lo
+        const double lmin = cx.vmax(n, [&](int i) {
+            if (w.a[i] == 0.0 || w.lo[i] == w.hi[i]) return -big;
+            const bool at_hi = (w.d[i] == w.hi[i]);
+            const double r = (w.b[i] * w.d[i] + w.g[i]) / w.a[i];
+            if (at_hi) return (w.a[i] > 0.0) ? r : -big;
+            return (w.a[i] < 0.0) ? r : -big;
+        });
+        const double lmax = cx.vmin(n, [&](int i) {
+            if (w.a[i] == 0.0 || w.lo[i] == w.hi[i]) return big;
+            const bool at_hi = (w.d[i] == w.hi[i]);
+            const double r = (w.b[i] * w.d[i] + w.g[i]) / w.a[i];
+            if (at_hi) return (w.a[i] < 0.0) ? r : big;
+            return (w.a[i] > 0.0) ? r : big;
+        });
+        double lambda;
+        if (lmin > -big && lmax < big) lambda = (fabs(lmin) < fabs(lmax)) ? lmin : lmax;
+        else if (lmin > -big) lambda = lmin;
+        else if (lmax < big) lambda = lmax;
+        else lambda = 0.0;
+        if (ctype == CON_INEQ && lambda < 0.0) lambda = 0.0;
+        *cres = c + cx.sum(n, [&](int i) { return w.a[i] * w.d[i]; });
+        return lambda;
+    }
+
+    const double psi_tol = 4e-16 * (fabs(c) + (fabs(smin) > fabs(smax) ? fabs(smin) : fabs(smax)));
+    double lambda = 0.0;
+    double lamL = 0.0, lamR = 0.0;
+    bool haveL = false, haveR = false;
+    double step = 1.0;
+    double prev_lambda = 0.0;
+    bool prev_valid = false;
+    bool converged = false;
+    int it = 0;
+    for (; it < 200; ++it) {
+        // psi and its slope at lambda
+        const double psi = c + cx.sum(n, [&](int i) {
+            const double t = (-w.g[i] + lambda * w.a[i]) / w.b[i];
+            const double di = t < w.lo[i] ? w.lo[i] : (t > w.hi[i] ? w.hi[i] : t);
+            return w.a[i] * di;
+        });
+        if (it == 0 && ctype == CON_INEQ && psi >= 0.0) { converged = true; break; }  // constraint inactive
+        const double slope = cx.sum(n, [&](int i) {
+            const double t = (-w.g[i] + lambda * w.a[i]) / w.b[i];
+            return (t > w.lo[i] && t < w.hi[i]) ? w.a[i] * w.a[i] / w.b[i] : 0.0;
+        });
+        if (fabs(psi) <= psi_tol) { converged = true; break; }
+        if (psi < 0.0) { lamL = lambda; haveL = true; } else { lamR = lambda; haveR = true; }
+        if (prev_valid && lambda == prev_lambda) { converged = true; break; }
+        prev_lambda = lambda; prev_valid = true;
+        double next;
+        bool ok = false;
+        if (slope > 0.0) {
+            next = lambda - psi / slope;
+            ok = (!haveL || next > lamL) && (!haveR || next < lamR);
+        }
+        if (!ok) {
+            if (haveL && haveR) {
+                next = 0.5 * (lamL + lamR);
+                if (next == lamL || next == lamR) { converged = true; break; }
+            } else {
+                next = (psi < 0.0) ? lambda + step : lambda - step;
+                step *= 4.0;
+            }
+        }
+        lambda = next;
+    }
+    st.qp_iters += it;
+    if (!converged) st.qp_inexact += 1;
+    cx.foreach(n, [&](int i) {
+        const double t = (-w.g[i] + lambda * w.a[i]) / w.b[i];
+        w.d[i] = t < w.lo[i] ? w.lo[i] : (t > w.hi[i] ? w.hi[i] : t);
+    });
+    *cres = c + cx.sum(n, [&](int i) { return w.a[i] * w.d[i]; });
+    return lambda;
+}
+
+// ---------------------------------------------------------------------------------------
+// Main driver.  Eval is a callable:  ev(const double* x, bool want_grad, double* F, double* c)
+// returning the objective to MINIMISE in *F and the constraint value in *c (Kraft's convention:
+// equality c == 0, inequality c >= 0), and -- when want_grad -- filling w.g (objective gradient)
+// and w.a (constraint gradient).  On return w.xbest holds the best point found (NLopt's rule:
+// best feasible objective, else least infeasible) and st.minf its objective.
+// ---------------------------------------------------------------------------------------
+SQP_HD double con_violation(int ctype, double c) {
+    if (ctype == CON_EQ) return fabs(c);
+    if (ctype == CON_INEQ) return c < 0.0 ? -c : 0.0;
+    return 0.0;
+}
+
+template <class Ctx, class Eval>
+SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, Work& w, const Params& p, Stats& st) {
+    const int n = p.n;
+    st.iters = 0; st.evals = 0; st.qp_iters = 0; st.qp_inexact = 0; st.resets = 0; st.minf = 0.0; st.feasible = 0;
+
+    // NLopt clips the start point into the box
+    cx.foreach(n, [&](int i) {
+        double xi = w.x[i];
+        if (xi < w.xl[i]) xi = w.xl[i];
+        if (xi > w.xu[i]) xi = w.xu[i];
+        w.x[i] = xi;
+        w.b[i] = 1.0;
+    });
+    double F = 0.0, c = 0.0;
+    ev(w.x, true, &F, &c);
+    st.evals = 1;
+    double viol = con_violation(p.ctype, c);
+    bool feasible = viol <= p.ctol;
+    double infeas = viol;
+    st.minf = F;
+    cx.foreach(n, [&](int i) { w.xbest[i] = w.x[i]; w.xprev[i] = w.x[i]; });
+
+    bool b_identity = true;
+    double mu = 0.0;      // merit penalty parameter
+    int ireset = 0;
+    int ret = SQP_SUCCESS;
+
+    while (ret == SQP_SUCCESS) {
+        ++st.iters;
+        if (p.max_iter > 0 && st.iters > p.max_iter) { ret = SQP_FAILURE; break; }
+        // bounds on the step
+        cx.foreach(n, [&](int i) { w.lo[i] = w.xl[i] - w.x[i]; w.hi[i] = w.xu[i] - w.x[i]; });
+        double cres = 0.0;
+        const double lambda = qp_solve(cx, n, p.ctype, c, w, st, &cres);
+        // gradient of the Lagrangian at the old point with the new multiplier (Kraft: v)
+        cx.foreach(n, [&](int i) { w.gl[i] = w.g[i] - lambda * w.a[i]; w.x0[i] = w.x[i]; });
+        const double f0 = F;
+        const double gs = cx.sum(n, [&](int i) { return w.g[i] * w.d[i]; });
+        const double al = fabs(lambda);
+        mu = (al > 0.5 * (mu + al)) ? al : 0.5 * (mu + al);
+        const double viol0 = con_violation(p.ctype, c);
+        const double viol_lin = con_violation(p.ctype, cres);
+        const double t0 = f0 + mu * viol0;
+        double h3 = gs - mu * (viol0 - viol_lin);
+#ifdef ACCSQP_DEBUG
+        printf("iter %d lambda %g gs %g mu %g viol0 %g viol_lin %g h3 %g F %.12g c %g\n", st.iters, lambda, gs, mu, viol0, viol_lin, h3, F, c);
+#endif
+        if (!(h3 < 0.0)) {
+            // not a descent direction for the merit function: reset the Hessian model (Kraft L110), at most 5 times
+            ++ireset; ++st.resets;
+            if (ireset > 5 || b_identity) { ret = SQP_ROUNDOFF_LIMITED; break; }
+            cx.foreach(n, [&](int i) { w.b[i] = 1.0; });
+            b_identity = true;
+            continue;
+        }
+        // Kraft's inexact line search
+        int line = 0;
+        double alpha = 1.0;
+        for (;;) {
+            ++line;
+            h3 = alpha * h3;
+            cx.foreach(n, [&](int i) {
+                const double si = alpha * w.d[i];
+                w.d[i] = si;
+                double xi = w.x0[i] + si;
+                if (xi < w.xl[i]) xi = w.xl[i];
+                if (xi > w.xu[i]) xi = w.xu[i];
+                w.x[i] = xi;
+            });
+            ev(w.x, false, &F, &c);
+            ++st.evals;
+            {   // NLopt: keep the best point seen at every evaluation
+                const double vi = con_violation(p.ctype, c);
+                const bool fc = vi <= p.ctol;
+                if ((F < st.minf && (fc || !feasible)) || (!feasible && vi < infeas)) {
+                    feasible = fc; infeas = vi; st.minf = F;
+                    cx.foreach(n, [&](int i) { w.xbest[i] = w.x[i]; });
+                }
+            }
+            if (p.maxeval > 0 && st.evals >= p.maxeval) { ret = SQP_MAXEVAL_REACHED; break; }
+            const double tt = F + mu * con_violation(p.ctype, c);
+            const double h1 = tt - t0;
+            if (h1 <= h3 / 10.0 || line > 10) break;
+            const double cand = h3 / (2.0 * (h3 - h1));
+            alpha = cand > 0.1 ? cand : 0.1;
+        }
+        if (ret != SQP_SUCCESS) break;
+        // completed iteration: gradients at the new point (NLopt re-evaluates f with gradient)
+        ev(w.x, true, &F, &c);
+        ++st.evals;
+        {
+            const double vi = con_violation(p.ctype, c);
+            const bool fc = vi <= p.ctol;
+            if ((F < st.minf && (fc || !feasible)) || (!feasible && vi < infeas)) {
+                feasible = fc; infeas = vi; st.minf = F;
+                cx.foreach(n, [&](int i) { w.xbest[i] = w.x[i]; });
+            }
+        }
+        // NLopt's xtol test between completed iterations
+        const double moved = cx.sum(n, [&](int i) { return (fabs(w.x[i] - w.xprev[i]) < w.xtol[i]) ? 0.0 : 1.0; });
+        cx.foreach(n, [&](int i) { w.xprev[i] = w.x[i]; });
+        if (moved == 0.0) { ret = SQP_XTOL_REACHED; break; }
+        if (p.maxeval > 0 && st.evals >= p.maxeval) { ret = SQP_MAXEVAL_REACHED; break; }
+        // per-coordinate secant update of the diagonal Hessian model
+        cx.foreach(n, [&](int i) {
+            const double si = w.x[i] - w.x0[i];
+            if (si != 0.0) {
+                const double ui = (w.g[i] - lambda * w.a[i]) - w.gl[i];
+                const double r = ui / si;
+                if (r > 0.0 && r < 1e300) {
+                    w.b[i] = r < ACCSQP_BMIN ? ACCSQP_BMIN : (r > ACCSQP_BMAX ? ACCSQP_BMAX : r);
+                }
+            }
+        });
+        b_identity = false;
+    }
+    st.feasible = feasible ? 1 : 0;
+    return ret;
+}
+
+// ---------------------------------------------------------------------------------------
+// Host execution context: one logical lane that reproduces the 32-lane reduction order.
+// ---------------------------------------------------------------------------------------
+struct HostCtx {
+    inline int lane() const { return 0; }
+    inline void sync() const {}
+    template <class Fn>
+    inline void foreach(int n, Fn f) const { for (int i = 0; i < n; ++i) f(i); }
+    template <class Fn>
+    inline double sum(int n, Fn f) const {
+        double p[32];
+        for (int l = 0; l < 32; ++l) p[l] = 0.0;
+        for (int i = 0; i < n; ++i) p[i & 31] += f(i);
+        for (int off = 16; off >= 1; off >>= 1) {
+            double q[32];
+            for (int l = 0; l < 32; ++l) q[l] = p[l] + p[l ^ off];
+            for (int l = 0; l < 32; ++l) p[l] = q[l];
+        }
+        return p[0];
+    }
+    template <class Fn>
+    inline double vmax(int n, Fn f) const {
+        double r = -1e308;
+        for (int i = 0; i < n; ++i) { const double val = f(i); if (val > r) r = val; }
+        return r;
+    }
+    template <class Fn>
+    inline double vmin(int n, Fn f) const {
+        double r = 1e308;
+        for (int i = 0; i < n; ++i) { const double val = f(i); if (val < r) r = val; }
+        return r;
+    }
+};
+
+}  // namespace accsqp

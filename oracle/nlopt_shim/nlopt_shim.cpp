@@ -1,0 +1,165 @@
+/* TEST INFRASTRUCTURE (oracle). Not part of the product path.
+ *
+ * NLopt provider for the oracle build of the reference (the reference downloads NLopt at build
+ * time, reference cmake/libraries.cmake:49-97; it is not available offline).  Implements the 14
+ * entry points the reference binds (reference include/optimization.h:137-186,
+ * src/model/Consumer.cpp:422).  Only NLOPT_LD_SLSQP -- the reference's default for both the
+ * purchasing and the utility optimisation (src/input/ModelInitializer.cpp:1034,1048) -- is
+ * provided; every other algorithm id returns NLOPT_INVALID_ARGS with a message.
+ *
+ * The SLSQP iteration itself is acclimate_b200/csrc/sqp_core.h, run through its HostCtx, which
+ * reproduces the device solver's reduction order so that the reference's CPU run and the CUDA
+ * run execute the same floating-point sequence (see DESIGN.md "Optimiser").  Its optima are
+ * cross-checked against scipy's SLSQP (Kraft's Fortran) in tests/test_sqp_vs_scipy.py.
+ * PARITY WITH UPSTREAM NLopt IS UNPINNED.
+ */
+#include "nlopt.h"
+
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../../acclimate_b200/csrc/sqp_core.h"
+
+struct nlopt_opt_s {
+    nlopt_algorithm algorithm;
+    unsigned n;
+    nlopt_func f = nullptr;
+    void* f_data = nullptr;
+    bool maximize = false;
+    nlopt_func con = nullptr;
+    void* con_data = nullptr;
+    int ctype = accsqp::CON_NONE;
+    double ctol = 0.0;
+    std::vector<double> lb, ub, xtol;
+    int maxeval = 0;
+    double maxtime = 0.0;
+    const char* errmsg = nullptr;
+    int last_iters = 0;
+    int last_evals = 0;
+};
+
+extern "C" {
+
+nlopt_opt nlopt_create(nlopt_algorithm algorithm, unsigned n) {
+    auto* o = new nlopt_opt_s;
+    o->algorithm = algorithm;
+    o->n = n;
+    o->lb.assign(n, -1e300);
+    o->ub.assign(n, 1e300);
+    o->xtol.assign(n, 0.0);
+    return o;
+}
+
+void nlopt_destroy(nlopt_opt opt) { delete opt; }
+
+nlopt_result nlopt_set_max_objective(nlopt_opt opt, nlopt_func f, void* f_data) {
+    opt->f = f; opt->f_data = f_data; opt->maximize = true;
+    return NLOPT_SUCCESS;
+}
+nlopt_result nlopt_set_min_objective(nlopt_opt opt, nlopt_func f, void* f_data) {
+    opt->f = f; opt->f_data = f_data; opt->maximize = false;
+    return NLOPT_SUCCESS;
+}
+nlopt_result nlopt_set_lower_bounds(nlopt_opt opt, const double* lb) {
+    opt->lb.assign(lb, lb + opt->n);
+    return NLOPT_SUCCESS;
+}
+nlopt_result nlopt_set_upper_bounds(nlopt_opt opt, const double* ub) {
+    opt->ub.assign(ub, ub + opt->n);
+    return NLOPT_SUCCESS;
+}
+nlopt_result nlopt_add_inequality_constraint(nlopt_opt opt, nlopt_func fc, void* fc_data, double tol) {
+    if (opt->con != nullptr) { opt->errmsg = "shim supports a single constraint"; return NLOPT_INVALID_ARGS; }
+    opt->con = fc; opt->con_data = fc_data; opt->ctype = accsqp::CON_INEQ; opt->ctol = tol;
+    return NLOPT_SUCCESS;
+}
+nlopt_result nlopt_add_equality_constraint(nlopt_opt opt, nlopt_func h, void* h_data, double tol) {
+    if (opt->con != nullptr) { opt->errmsg = "shim supports a single constraint"; return NLOPT_INVALID_ARGS; }
+    opt->con = h; opt->con_data = h_data; opt->ctype = accsqp::CON_EQ; opt->ctol = tol;
+    return NLOPT_SUCCESS;
+}
+nlopt_result nlopt_set_xtol_abs(nlopt_opt opt, const double* tol) {
+    opt->xtol.assign(tol, tol + opt->n);
+    return NLOPT_SUCCESS;
+}
+nlopt_result nlopt_set_maxeval(nlopt_opt opt, int maxeval) { opt->maxeval = maxeval; return NLOPT_SUCCESS; }
+nlopt_result nlopt_set_maxtime(nlopt_opt opt, double maxtime) { opt->maxtime = maxtime; return NLOPT_SUCCESS; }
+nlopt_result nlopt_set_local_optimizer(nlopt_opt opt, const nlopt_opt) {
+    opt->errmsg = "nlopt_shim: subsidiary optimizers are not provided";
+    return NLOPT_INVALID_ARGS;
+}
+nlopt_result nlopt_set_population(nlopt_opt, unsigned) { return NLOPT_SUCCESS; }
+const char* nlopt_get_errmsg(nlopt_opt opt) { return opt->errmsg; }
+int nlopt_shim_last_iterations(nlopt_opt opt) { return opt->last_iters; }
+int nlopt_shim_last_evals(nlopt_opt opt) { return opt->last_evals; }
+
+}  // extern "C"
+
+namespace {
+
+struct CallbackEval {
+    nlopt_opt o;
+    accsqp::Work* w;
+    std::vector<double> tmp;
+    void operator()(const double* x, bool want_grad, double* F, double* c) {
+        const unsigned n = o->n;
+        const double sgn = o->maximize ? -1.0 : 1.0;
+        if (want_grad) {
+            const double fv = o->f(n, x, tmp.data(), o->f_data);
+            *F = sgn * fv;
+            for (unsigned i = 0; i < n; ++i) w->g[i] = sgn * tmp[i];
+        } else {
+            *F = sgn * o->f(n, x, nullptr, o->f_data);
+        }
+        if (o->con != nullptr) {
+            const double cs = (o->ctype == accsqp::CON_INEQ) ? -1.0 : 1.0;  // NLopt: fc(x) <= 0
+            if (want_grad) {
+                const double cv = o->con(n, x, tmp.data(), o->con_data);
+                *c = cs * cv;
+                for (unsigned i = 0; i < n; ++i) w->a[i] = cs * tmp[i];
+            } else {
+                *c = cs * o->con(n, x, nullptr, o->con_data);
+            }
+        } else {
+            *c = 0.0;
+            if (want_grad) for (unsigned i = 0; i < n; ++i) w->a[i] = 0.0;
+        }
+    }
+};
+
+}  // namespace
+
+extern "C" nlopt_result nlopt_optimize(nlopt_opt opt, double* x, double* opt_f) {
+    if (opt->algorithm != NLOPT_LD_SLSQP) {
+        opt->errmsg = "nlopt_shim: only NLOPT_LD_SLSQP is provided";
+        return NLOPT_INVALID_ARGS;
+    }
+    if (opt->f == nullptr) return NLOPT_INVALID_ARGS;
+    const int n = (int)opt->n;
+    std::vector<double> buf((size_t)ACCSQP_NVEC * n);
+    double* q = buf.data();
+    accsqp::Work w;
+    w.x = q; q += n; w.x0 = q; q += n; w.g = q; q += n; w.a = q; q += n; w.d = q; q += n; w.b = q; q += n;
+    w.lo = q; q += n; w.hi = q; q += n; w.gl = q; q += n; w.xbest = q; q += n; w.xprev = q; q += n;
+    w.xl = opt->lb.data();
+    w.xu = opt->ub.data();
+    w.xtol = opt->xtol.data();
+    std::memcpy(w.x, x, sizeof(double) * n);
+
+    accsqp::Params p;
+    p.n = n; p.ctype = opt->ctype; p.ctol = opt->ctol; p.maxeval = opt->maxeval; p.max_iter = ACCSQP_MAX_ITER;
+    accsqp::Stats st;
+    accsqp::HostCtx cx;
+    CallbackEval ev{opt, &w, std::vector<double>((size_t)n)};
+    const int ret = accsqp::sqp_minimize(cx, ev, w, p, st);
+    std::memcpy(x, w.xbest, sizeof(double) * n);
+    *opt_f = opt->maximize ? -st.minf : st.minf;
+    opt->last_iters = st.iters;
+    opt->last_evals = st.evals;
+    if (ret == accsqp::SQP_FAILURE) {
+        opt->errmsg = "bug: more than iter SQP iterations";  // NLopt's message for Kraft's mode 9
+        return NLOPT_FAILURE;
+    }
+    return (nlopt_result)ret;
+}
