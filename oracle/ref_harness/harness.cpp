@@ -1,0 +1,523 @@
+/* TEST INFRASTRUCTURE (oracle). Not part of the product path.
+ *
+ * Driver that runs the REFERENCE's own model code (compiled from /root/reference/src/model/*.cpp
+ * where it lies, see oracle/Makefile) on a flat network snapshot and dumps per-step state.
+ * It replaces exactly the three reference files that cannot be built offline:
+ *   - src/ModelRun.cpp          (includes NetCDF output)        -> ModelRun members below,
+ *                                                                  same phase order as ModelRun.cpp:153-229
+ *   - src/input/ModelInitializer.cpp (NetCDF + yaml-cpp input)  -> class ModelInitializer below, calling the
+ *                                                                  same model mutators in the same order as
+ *                                                                  ModelInitializer.cpp:73-213,689-700,1081-1085
+ *   - src/scenario/Scenario.cpp (settings tree)                 -> forcing table applied with the rule of
+ *                                                                  Scenario.cpp:161-174
+ * No arithmetic of the hot path lives here: every number dumped is computed by reference code.
+ */
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "ModelRun.h"
+#include "acclimate.h"
+#include "accio.h"
+#include "model/BusinessConnection.h"
+#include "model/CapacityManager.h"
+#include "model/Consumer.h"
+#include "model/EconomicAgent.h"
+#include "model/Firm.h"
+#include "model/GeoConnection.h"
+#include "model/GeoRoute.h"
+#include "model/Model.h"
+#include "model/PurchasingManager.h"
+#include "model/Region.h"
+#include "model/SalesManager.h"
+#include "model/Sector.h"
+#include "model/Storage.h"
+#include "nlopt.h"
+#include "openmp.h"
+
+// index of each entry in the "model_f64" array of the network file (acclimate_b200/netfile.py)
+enum ModelParamIdx {
+    MP_TRANSPORT_PENALTY_SMALL = 0,
+    MP_TRANSPORT_PENALTY_LARGE,
+    MP_MIN_STORAGE,
+    MP_CHEAPEST_PRICE_RANGE_WIDTH,  // < 0: "auto"
+    MP_OPTIMIZATION_MAXITER,
+    MP_OPTIMIZATION_PRECISION_ADJUSTMENT,
+    MP_QUADRATIC_TRANSPORT_PENALTY,
+    MP_RELATIVE_TRANSPORT_PENALTY,
+    MP_MAX_DECREASE_RESERVATION_PRICE_LIMITED_BY_MARKUP,
+    MP_DEVIATION_PENALTY,
+    MP_CHEAPEST_PRICE_RANGE_PRESERVE_SELLER_PRICE,
+    MP_NO_SELF_SUPPLY,
+    MP_UTILITARIAN,
+    MP_DELTA_T,
+    MP_COUNT
+};
+// per-sector parameters in "sector_f64" (row-major, SP_COUNT per sector)
+enum SectorParamIdx {
+    SP_UPPER_STORAGE_LIMIT = 0,
+    SP_INITIAL_STORAGE_FILL_FACTOR,
+    SP_TRANSPORT_TYPE,  // 0 aviation, 1 immediate, 2 roadsea
+    SP_SUPPLY_ELASTICITY,
+    SP_PRICE_INCREASE_PRODUCTION_EXTENSION,
+    SP_ESTIMATED_PRICE_INCREASE_PRODUCTION_EXTENSION,
+    SP_INITIAL_MARKUP,
+    SP_TARGET_STORAGE_REFILL_TIME,
+    SP_TARGET_STORAGE_WITHDRAW_TIME,
+    SP_COUNT
+};
+
+struct HarnessConfig {
+    std::map<std::string, accio::Array> net;
+    int steps = 1;
+    std::string dump_path;
+    int dump_every = 1;
+    bool dump_edges = true;
+    const std::vector<std::int64_t>& I(const char* n) const { return net.at(n).i; }
+    const std::vector<double>& F(const char* n) const { return net.at(n).f; }
+};
+
+namespace settings {
+class SettingsNode {  // stand-in: the harness passes its own config through the reference's constructor signature
+  public:
+    const HarnessConfig* cfg;
+};
+}  // namespace settings
+
+struct EventRec {
+    std::int64_t step, type, a, b;
+    double value;
+};
+static std::vector<EventRec> g_events;
+static std::int64_t g_step = 0;
+
+namespace acclimate {
+
+class Scenario {};  // complete types for ModelRun's unique_ptr members (unused)
+class Output {};
+
+const std::array<options::Option, 10> options::options = {{{"BASED_ON_INT", true},
+                                                           {"BANKERS_ROUNDING", true},
+                                                           {"CHECKPOINTING", false},
+                                                           {"CLEANUP_INFO", false},
+                                                           {"FATAL_FLOATING_POINT_EXCEPTIONS", false},
+                                                           {"FLOATING_POINT_EXCEPTIONS", false},
+                                                           {"OPTIMIZATION_PROBLEMS_FATAL", false},
+                                                           {"OPTIMIZATION_WARNINGS", false},
+                                                           {"STRICT_MIN_DERIVATIVE", false},
+                                                           {"USE_MIN_PASSAGE_IN_EXPECTATION", true}}};
+
+// ---- network construction (follows src/input/ModelInitializer.cpp) ------------------------------
+class ModelInitializer {
+  public:
+    Model* model;
+    const HarnessConfig& cfg;
+    std::vector<EconomicAgent*> agents;
+    std::vector<std::shared_ptr<BusinessConnection>> edges;  // file order
+    std::vector<Storage*> storages;                          // creation order
+    std::vector<std::shared_ptr<GeoConnection>> connections; // unordered region pairs, (i, j<i) order
+    std::vector<std::int64_t> conn_a, conn_b;
+
+    ModelInitializer(Model* m, const HarnessConfig& c) : model(m), cfg(c) {}
+
+    void run() {
+        const auto& meta = cfg.I("meta");
+        const std::size_t n_sectors = meta[0], n_regions = meta[1], n_agents = meta[2], n_edges = meta[3];
+        const auto& mp = cfg.F("model_f64");
+        const auto& sp = cfg.F("sector_f64");
+        // ModelInitializer.cpp:58-62
+        model->set_delta_t(Time(mp[MP_DELTA_T]));
+        model->no_self_supply(mp[MP_NO_SELF_SUPPLY] != 0.0);
+        // pre_initialize, ModelInitializer.cpp:1015-1079 (defaults of the reference for everything not in the file)
+        auto& P = model->parameters_writable();
+        P.transport_penalty_small = Price(mp[MP_TRANSPORT_PENALTY_SMALL]);
+        P.transport_penalty_large = Price(mp[MP_TRANSPORT_PENALTY_LARGE]);
+        P.optimization_maxiter = int(mp[MP_OPTIMIZATION_MAXITER]);
+        P.optimization_timeout = 3600;
+        P.quadratic_transport_penalty = mp[MP_QUADRATIC_TRANSPORT_PENALTY] != 0.0;
+        P.maximal_decrease_reservation_price_limited_by_markup = mp[MP_MAX_DECREASE_RESERVATION_PRICE_LIMITED_BY_MARKUP] != 0.0;
+        P.always_extend_expected_demand_curve = false;
+        P.naive_expectations = true;
+        P.deviation_penalty = mp[MP_DEVIATION_PENALTY] != 0.0;
+        P.min_storage = mp[MP_MIN_STORAGE];
+        P.cheapest_price_range_preserve_seller_price = mp[MP_CHEAPEST_PRICE_RANGE_PRESERVE_SELLER_PRICE] != 0.0;
+        P.cheapest_price_range_generic_size = mp[MP_CHEAPEST_PRICE_RANGE_WIDTH] < 0.0;
+        if (!P.cheapest_price_range_generic_size) P.cheapest_price_range_width = Price(mp[MP_CHEAPEST_PRICE_RANGE_WIDTH]);
+        P.relative_transport_penalty = mp[MP_RELATIVE_TRANSPORT_PENALTY] != 0.0;
+        P.respect_markup_in_production_extension = false;  // never assigned by the reference (parameters.h:46); pinned
+        P.optimization_algorithm = NLOPT_LD_SLSQP;
+        P.utility_optimization_algorithm = NLOPT_LD_SLSQP;
+        P.global_optimization_algorithm = NLOPT_GN_CRS2_LM;
+        P.lagrangian_algorithm = NLOPT_AUGLAG;
+        P.global_utility_optimization_algorithm = NLOPT_G_MLSL_LDS;
+        P.global_purchasing_optimization = false;
+        P.local_purchasing_optimization = true;
+        P.optimization_restart_baseline = false;
+        P.start_purchasing_at_baseline = false;
+        P.purchasing_halfway_baseline = false;
+        P.global_utility_optimization = false;
+        P.budget_inequality_constrained = false;
+        P.elastic_budget = false;
+        P.global_utility_optimization_random_points = 64;
+        P.utility_optimization_maxiter = P.optimization_maxiter;
+        P.utility_optimization_timeout = P.optimization_timeout;
+        P.global_optimization_maxiter = P.optimization_maxiter;
+        P.global_optimization_timeout = P.optimization_timeout;
+        P.global_utility_optimization_maxiter = P.optimization_maxiter;
+        P.global_utility_optimization_timeout = P.optimization_timeout;
+        P.optimization_precision_adjustment = int(mp[MP_OPTIMIZATION_PRECISION_ADJUSTMENT]);
+        P.utility_optimization_precision_adjustment = 1;
+        P.global_optimization_precision_adjustment = 1;
+        P.global_utility_optimization_precision_adjustment = 1;
+
+        // sectors: add_sector, ModelInitializer.cpp:159-185
+        for (std::size_t s = 0; s < n_sectors; ++s) {
+            const double* q = &sp[s * SP_COUNT];
+            char name[32];
+            if (s + 1 == n_sectors) std::snprintf(name, sizeof(name), "FCON");
+            else std::snprintf(name, sizeof(name), "SEC%02zu", s);
+            const int tt = int(q[SP_TRANSPORT_TYPE]);
+            auto* sector = model->sectors.add(model, id_t(name), Ratio(q[SP_UPPER_STORAGE_LIMIT]), q[SP_INITIAL_STORAGE_FILL_FACTOR] * model->delta_t(),
+                                              tt == 0   ? Sector::transport_type_t::AVIATION
+                                              : tt == 1 ? Sector::transport_type_t::IMMEDIATE
+                                                        : Sector::transport_type_t::ROADSEA);
+            sector->parameters_writable().supply_elasticity = q[SP_SUPPLY_ELASTICITY];
+            sector->parameters_writable().price_increase_production_extension = Price(q[SP_PRICE_INCREASE_PRODUCTION_EXTENSION]);
+            sector->parameters_writable().estimated_price_increase_production_extension = Price(q[SP_ESTIMATED_PRICE_INCREASE_PRODUCTION_EXTENSION]);
+            sector->parameters_writable().initial_markup = Price(q[SP_INITIAL_MARKUP]);
+            sector->parameters_writable().target_storage_refill_time = q[SP_TARGET_STORAGE_REFILL_TIME] * model->delta_t();
+            sector->parameters_writable().target_storage_withdraw_time = q[SP_TARGET_STORAGE_WITHDRAW_TIME] * model->delta_t();
+        }
+        for (std::size_t r = 0; r < n_regions; ++r) {
+            char name[32];
+            std::snprintf(name, sizeof(name), "RG%03zu", r);
+            model->regions.add(model, id_t(name));
+        }
+        // agents: add_firm / add_consumer, ModelInitializer.cpp:94-142
+        const auto& at = cfg.I("agent_type");
+        const auto& as = cfg.I("agent_sector");
+        const auto& ar = cfg.I("agent_region");
+        const auto& ab = cfg.F("agent_beta");
+        const bool utilitarian = mp[MP_UTILITARIAN] != 0.0;
+        for (std::size_t a = 0; a < n_agents; ++a) {
+            Sector* sector = model->sectors[as[a]];
+            Region* region = model->regions[ar[a]];
+            const std::string name = sector->name() + ":" + region->name();
+            if (at[a] == 1) {
+                auto* firm = model->economic_agents.add<Firm>(id_t(name), sector, region, Ratio(ab[a]));
+                sector->firms.add(firm);
+                region->economic_agents.add(firm);
+                agents.push_back(firm);
+            } else {
+                std::vector<std::pair<std::vector<Sector*>, FloatType>> baskets;
+                std::vector<Sector*> all;
+                for (std::size_t s = 0; s + 1 < n_sectors; ++s) all.push_back(model->sectors[s]);
+                baskets.emplace_back(all, 2.0);
+                auto* consumer = model->economic_agents.add<Consumer>(id_t(name), region, 1.5, baskets, utilitarian);
+                region->economic_agents.add(consumer);
+                agents.push_back(consumer);
+            }
+        }
+        // transport: one simple connection per unordered region pair (create_simple_transport_connection,
+        // ModelInitializer.cpp:689-700; loop order of build_transport_network "const", :985-992)
+        const auto& delay = cfg.I("delay");
+        for (std::size_t i = 0; i < n_regions; ++i) {
+            for (std::size_t j = 0; j < i; ++j) {
+                Region* from = model->regions[i];
+                Region* to = model->regions[j];
+                auto inf = std::make_shared<GeoConnection>(model, TransportDelay(delay[i * n_regions + j]), GeoConnection::type_t::UNSPECIFIED, from, to);
+                from->connections.push_back(inf);
+                to->connections.push_back(inf);
+                GeoRoute route;
+                route.path.add(inf.get());
+                from->routes.emplace(std::make_pair(IndexType(to->id.index()), Sector::transport_type_t::AVIATION), route);
+                from->routes.emplace(std::make_pair(IndexType(to->id.index()), Sector::transport_type_t::ROADSEA), route);
+                to->routes.emplace(std::make_pair(IndexType(from->id.index()), Sector::transport_type_t::AVIATION), route);
+                to->routes.emplace(std::make_pair(IndexType(from->id.index()), Sector::transport_type_t::ROADSEA), route);
+                connections.push_back(inf);
+                conn_a.push_back(i);
+                conn_b.push_back(j);
+            }
+        }
+        // connections: initialize_connection, ModelInitializer.cpp:187-213
+        const auto& ef = cfg.I("edge_from");
+        const auto& et = cfg.I("edge_to");
+        const auto& ez = cfg.I("edge_zq");
+        const auto& cel = cfg.F("consumer_elasticity");
+        edges.reserve(n_edges);
+        for (std::size_t e = 0; e < n_edges; ++e) {
+            Firm* firm_from = agents[ef[e]]->as_firm();
+            EconomicAgent* to = agents[et[e]];
+            if (model->no_self_supply() && static_cast<void*>(firm_from) == static_cast<void*>(to)) {
+                throw std::runtime_error("network file contains a self-supply edge although no_self_supply is set");
+            }
+            Sector* sector_from = firm_from->sector;
+            auto* input_storage = to->input_storages.find(sector_from->name() + "->" + to->name());
+            if (input_storage == nullptr) {
+                input_storage = to->input_storages.add(sector_from, to);
+                if (to->is_consumer()) input_storage->parameters_writable().consumption_price_elasticity = cel[sector_from->id.index()];
+                storages.push_back(input_storage);
+            }
+            const Flow flow = Flow(FlowQuantity(double(ez[e]) * FlowQuantity::precision), Price(1.0));
+            if (iround(to_float(flow.get_quantity()) / FlowQuantity::precision) != ez[e]) throw std::runtime_error("flow quantisation mismatch");
+            input_storage->add_initial_flow_Z_star(flow);
+            firm_from->add_initial_production_X_star(flow);
+            auto bc = std::make_shared<BusinessConnection>(input_storage->purchasing_manager.get(), firm_from->sales_manager.get(), flow);
+            firm_from->sales_manager->business_connections.emplace_back(bc);
+            input_storage->purchasing_manager->business_connections.emplace_back(bc);
+            if (static_cast<void*>(firm_from) == static_cast<void*>(to)) firm_from->self_supply_connection(bc);
+            edges.push_back(bc);
+        }
+        check_clean();
+        // post_initialize, ModelInitializer.cpp:1081-1085
+        for (auto& agent : model->economic_agents) agent->initialize();
+    }
+
+    // clean_network (ModelInitializer.cpp:215-299) must be a no-op for a valid snapshot: the generator guarantees it.
+    void check_clean() {
+        for (auto& ea : model->economic_agents) {
+            if (ea->is_firm()) {
+                Firm* firm = ea->as_firm();
+                FlowQuantity input(0.0);
+                for (const auto& is : firm->input_storages) input = input + is->initial_input_flow_I_star().get_quantity();
+                const FloatType value_added = to_float(firm->initial_production_X_star().get_quantity() - input);
+                if (value_added <= 0.0 || firm->sales_manager->business_connections.empty() || firm->input_storages.empty()) {
+                    throw std::runtime_error("network snapshot is not clean: " + firm->name() + " would be removed by clean_network");
+                }
+            } else if (ea->input_storages.empty()) {
+                throw std::runtime_error("network snapshot is not clean: consumer without inputs");
+            }
+        }
+    }
+};
+
+}  // namespace acclimate
+
+// ---- ModelRun members (replacement for src/ModelRun.cpp) -------------------------------------------
+namespace acclimate {
+
+static ModelInitializer* g_init = nullptr;
+static const HarnessConfig* g_cfg = nullptr;
+static double g_phase_seconds = 0.0;
+
+static inline std::int64_t qi(const FlowQuantity& q) { return iround(to_float(q) / FlowQuantity::precision); }
+static inline std::int64_t qi(const Quantity& q) { return iround(to_float(q) / Quantity::precision); }
+static inline std::int64_t pi(const Price& p) { return iround(to_float(p) / Price::precision); }
+
+ModelRun::ModelRun(const settings::SettingsNode& settings) {
+    step(IterationStep::INITIALIZATION);
+    fesetround(FE_TONEAREST);  // ModelRun.cpp:80-82
+    g_cfg = settings.cfg;
+    start_time_m = Time(0.0);
+    stop_time_m = Time(double(g_cfg->steps - 1) * g_cfg->F("model_f64")[MP_DELTA_T]);
+    auto model = new Model(this);
+    g_init = new ModelInitializer(model, *g_cfg);
+    g_init->run();
+    model_m.reset(model);
+}
+
+ModelRun::~ModelRun() {
+    outputs_m.clear();
+    model_m.reset();
+}
+
+bool ModelRun::done() const { return model_m->time() > stop_time_m; }
+
+unsigned int ModelRun::thread_count() const { return openmp::get_thread_count(); }
+
+std::string ModelRun::timeinfo() const { return std::to_string(time_m); }
+
+static void record_event(EventType type, std::int64_t a, std::int64_t b, FloatType value) {
+#pragma omp critical(harness_events)
+    g_events.push_back(EventRec{g_step, std::int64_t(type), a, b, value});
+}
+
+void ModelRun::event(EventType type, const Sector* sector, const EconomicAgent* economic_agent, FloatType value) {
+    record_event(type, std::int64_t(sector->id.index()), std::int64_t(economic_agent->id.index()), value);
+}
+void ModelRun::event(EventType type, const EconomicAgent* economic_agent, FloatType value) {
+    record_event(type, std::int64_t(economic_agent->id.index()), -1, value);
+}
+void ModelRun::event(EventType type, const EconomicAgent* economic_agent_from, const EconomicAgent* economic_agent_to, FloatType value) {
+    record_event(type, std::int64_t(economic_agent_from->id.index()), economic_agent_to ? std::int64_t(economic_agent_to->id.index()) : -1, value);
+}
+
+// forcing table applied with the rule of Scenario::iterate (src/scenario/Scenario.cpp:161-174)
+static void apply_scenario(Model* model) {
+    const auto it_f = g_cfg->net.find("forcing");
+    if (it_f != g_cfg->net.end()) {
+        const auto& f = it_f->second.f;
+        for (std::size_t k = 0; k + 3 < f.size(); k += 4) {
+            const Time from(f[k]), to(f[k + 1]);
+            EconomicAgent* agent = g_init->agents[std::size_t(f[k + 2])];
+            if (model->time() >= from && model->time() <= to) agent->set_forcing(f[k + 3]);
+            else if (model->time() == to + model->delta_t()) agent->set_forcing(1.0);
+        }
+    }
+    const auto it_p = g_cfg->net.find("passage");
+    if (it_p != g_cfg->net.end()) {
+        const auto& f = it_p->second.f;
+        for (std::size_t k = 0; k + 3 < f.size(); k += 4) {
+            const Time from(f[k]), to(f[k + 1]);
+            GeoConnection* conn = g_init->connections[std::size_t(f[k + 2])].get();
+            if (model->time() >= from && model->time() <= to) conn->set_forcing_nu(f[k + 3]);
+            else if (model->time() == to + model->delta_t()) conn->set_forcing_nu(-1.);
+        }
+    }
+}
+
+static void dump_step(accio::Writer& out, Model* model, std::int64_t t, bool with_edges) {
+    char pre[32];
+    std::snprintf(pre, sizeof(pre), "t%05ld/", long(t));
+    const std::string P(pre);
+    std::vector<std::int64_t> vi;
+    std::vector<double> vf;
+    auto put_i = [&](const char* name, std::size_t n, auto fn) {
+        vi.resize(n);
+        for (std::size_t k = 0; k < n; ++k) vi[k] = fn(k);
+        out.put(P + name, vi);
+    };
+    auto put_f = [&](const char* name, std::size_t n, auto fn) {
+        vf.resize(n);
+        for (std::size_t k = 0; k < n; ++k) vf[k] = fn(k);
+        out.put(P + name, vf);
+    };
+    const auto& E = g_init->edges;
+    if (with_edges) {
+        put_i("edge_D_q", E.size(), [&](std::size_t k) { return qi(E[k]->last_demand_request_D().get_quantity()); });
+        put_i("edge_D_p", E.size(), [&](std::size_t k) { return pi(E[k]->last_demand_request_D().get_price()); });
+        put_i("edge_ship_q", E.size(), [&](std::size_t k) { return qi(E[k]->last_shipment_Z().get_quantity()); });
+        put_f("edge_ship_v", E.size(), [&](std::size_t k) { return to_float(E[k]->last_shipment_Z().get_value()); });
+        put_i("edge_deliv_q", E.size(), [&](std::size_t k) { return qi(E[k]->last_delivery_Z().get_quantity()); });
+        put_f("edge_deliv_v", E.size(), [&](std::size_t k) { return to_float(E[k]->last_delivery_Z().get_value()); });
+        put_i("edge_deficit_q", E.size(), [&](std::size_t k) { return qi(E[k]->get_flow_deficit()); });
+        put_i("edge_transit_q", E.size(), [&](std::size_t k) { return qi(E[k]->get_transport_flow().get_quantity()); });
+        put_f("edge_transit_v", E.size(), [&](std::size_t k) { return to_float(E[k]->get_transport_flow().get_value()); });
+    }
+    const auto& S = g_init->storages;
+    put_i("sto_S_q", S.size(), [&](std::size_t k) { return qi(S[k]->content_S().get_quantity()); });
+    put_f("sto_S_v", S.size(), [&](std::size_t k) { return to_float(S[k]->content_S().get_value()); });
+    put_i("sto_I_q", S.size(), [&](std::size_t k) { return qi(S[k]->last_input_flow_I().get_quantity()); });
+    put_f("sto_I_v", S.size(), [&](std::size_t k) { return to_float(S[k]->last_input_flow_I().get_value()); });
+    put_i("sto_Inext_q", S.size(), [&](std::size_t k) { return qi(S[k]->current_input_flow_I().get_quantity()); });  // register "other" == filled this step? see DESIGN
+    put_i("sto_U_q", S.size(), [&](std::size_t k) { return qi(S[k]->used_flow_U().get_quantity()); });
+    put_f("sto_U_v", S.size(), [&](std::size_t k) { return to_float(S[k]->used_flow_U().get_value()); });
+    put_i("sto_Ut_q", S.size(), [&](std::size_t k) { return qi(S[k]->desired_used_flow_U_tilde().get_quantity()); });
+    put_f("sto_Ut_v", S.size(), [&](std::size_t k) { return to_float(S[k]->desired_used_flow_U_tilde().get_value()); });
+    put_i("sto_demand_q", S.size(), [&](std::size_t k) { return qi(S[k]->purchasing_manager->demand_D().get_quantity()); });
+    put_f("sto_demand_v", S.size(), [&](std::size_t k) { return to_float(S[k]->purchasing_manager->demand_D().get_value()); });
+    put_f("sto_expected_costs", S.size(), [&](std::size_t k) { return to_float(S[k]->purchasing_manager->expected_costs()); });
+    put_f("sto_optimized_value", S.size(), [&](std::size_t k) { return S[k]->purchasing_manager->optimized_value(); });
+    put_f("sto_transport_penalty", S.size(), [&](std::size_t k) { return to_float(S[k]->purchasing_manager->total_transport_penalty()); });
+    const auto& A = g_init->agents;
+    auto firm = [&](std::size_t k) -> const Firm* { return A[k]->is_firm() ? A[k]->as_firm() : nullptr; };
+    put_f("agent_forcing", A.size(), [&](std::size_t k) { return A[k]->forcing(); });
+    put_i("firm_X_q", A.size(), [&](std::size_t k) { return firm(k) ? qi(firm(k)->production_X().get_quantity()) : 0; });
+    put_f("firm_X_v", A.size(), [&](std::size_t k) { return firm(k) ? to_float(firm(k)->production_X().get_value()) : 0.0; });
+    put_i("firm_Xhat_q", A.size(), [&](std::size_t k) { return firm(k) ? qi(firm(k)->sales_manager->communicated_parameters().possible_production_X_hat.get_quantity()) : 0; });
+    put_i("firm_Xhat_p", A.size(), [&](std::size_t k) { return firm(k) ? pi(firm(k)->sales_manager->communicated_parameters().possible_production_X_hat.get_price()) : 0; });
+    put_i("firm_Xexp_q", A.size(), [&](std::size_t k) { return firm(k) ? qi(firm(k)->sales_manager->communicated_parameters().expected_production_X.get_quantity()) : 0; });
+    put_f("firm_Xexp_v", A.size(), [&](std::size_t k) { return firm(k) ? to_float(firm(k)->sales_manager->communicated_parameters().expected_production_X.get_value()) : 0.0; });
+    put_i("firm_nbar", A.size(), [&](std::size_t k) { return firm(k) ? pi(firm(k)->sales_manager->communicated_parameters().offer_price_n_bar) : 0; });
+    put_f("firm_costs_C", A.size(), [&](std::size_t k) { return firm(k) ? to_float(firm(k)->sales_manager->total_production_costs_C()) : 0.0; });
+    put_f("firm_revenue_R", A.size(), [&](std::size_t k) { return firm(k) ? to_float(firm(k)->sales_manager->total_revenue_R()) : 0.0; });
+    put_i("firm_desired_q", A.size(), [&](std::size_t k) { return firm(k) ? qi(firm(k)->capacity_manager->desired_production_X_tilde().get_quantity()) : 0; });
+    put_i("firm_possible_q", A.size(), [&](std::size_t k) { return firm(k) ? qi(firm(k)->capacity_manager->possible_production_X_hat().get_quantity()) : 0; });
+    const std::size_t ns = model->sectors.size(), nr = model->regions.size();
+    put_i("sector_production_q", ns, [&](std::size_t k) { return qi(model->sectors[k]->total_production_X().get_quantity()); });
+    put_f("sector_production_v", ns, [&](std::size_t k) { return to_float(model->sectors[k]->total_production_X().get_value()); });
+    put_i("sector_demand_q", ns, [&](std::size_t k) { return qi(model->sectors[k]->total_demand_D().get_quantity()); });
+    put_f("sector_demand_v", ns, [&](std::size_t k) { return to_float(model->sectors[k]->total_demand_D().get_value()); });
+    put_i("region_import_q", nr, [&](std::size_t k) { return qi(model->regions[k]->import_flow_Z().get_quantity()); });
+    put_f("region_import_v", nr, [&](std::size_t k) { return to_float(model->regions[k]->import_flow_Z().get_value()); });
+    put_i("region_export_q", nr, [&](std::size_t k) { return qi(model->regions[k]->export_flow_Z().get_quantity()); });
+    put_f("region_export_v", nr, [&](std::size_t k) { return to_float(model->regions[k]->export_flow_Z().get_value()); });
+    put_i("region_consumption_q", nr, [&](std::size_t k) { return qi(model->regions[k]->consumption_C().get_quantity()); });
+    put_f("region_consumption_v", nr, [&](std::size_t k) { return to_float(model->regions[k]->consumption_C().get_value()); });
+    put_f("region_gdp_v", nr, [&](std::size_t k) { return to_float(model->regions[k]->get_gdp().get_value()); });
+}
+
+// the time loop: same order of calls as src/ModelRun.cpp:153-229
+void ModelRun::run() {
+    if (has_run) throw log::error(this, "Model has already run");
+    has_run = true;
+    step(IterationStep::INITIALIZATION);
+    model_m->time_m = start_time_m;
+    model_m->start();
+    time_m = 0;
+    step(IterationStep::SCENARIO);
+    std::unique_ptr<accio::Writer> out;
+    if (!g_cfg->dump_path.empty()) out = std::make_unique<accio::Writer>(g_cfg->dump_path);
+    while (!done()) {
+        g_step = time_m;
+        apply_scenario(model_m.get());
+        const auto t0 = std::chrono::high_resolution_clock::now();
+        model_m->switch_registers();
+        step(IterationStep::CONSUMPTION_AND_PRODUCTION);
+        model_m->iterate_consumption_and_production();
+        step(IterationStep::EXPECTATION);
+        model_m->iterate_expectation();
+        step(IterationStep::PURCHASE);
+        model_m->iterate_purchase();
+        step(IterationStep::INVESTMENT);
+        model_m->iterate_investment();
+        const auto t1 = std::chrono::high_resolution_clock::now();
+        g_phase_seconds += std::chrono::duration<double>(t1 - t0).count();
+        duration_m = std::chrono::duration_cast<std::chrono::milliseconds>(t1 - t0).count();
+        step(IterationStep::OUTPUT);
+        if (out && (time_m % g_cfg->dump_every == 0 || time_m + 1 == unsigned(g_cfg->steps))) {
+            dump_step(*out, model_m.get(), time_m, g_cfg->dump_edges);
+        }
+        step(IterationStep::SCENARIO);
+        model_m->tick();
+        ++time_m;
+    }
+    if (out) {
+        std::vector<std::int64_t> ev;
+        std::vector<double> evv;
+        for (const auto& e : g_events) {
+            ev.push_back(e.step); ev.push_back(e.type); ev.push_back(e.a); ev.push_back(e.b);
+            evv.push_back(e.value);
+        }
+        out->put("events", ev);
+        out->put("event_values", evv);
+    }
+}
+
+}  // namespace acclimate
+
+int main(int argc, char** argv) {
+    if (argc < 3) {
+        std::fprintf(stderr, "usage: %s <network.acc> <steps> [dump.acc] [--every k] [--no-edges]\n", argv[0]);
+        return 1;
+    }
+    try {
+        HarnessConfig cfg;
+        cfg.net = accio::read_file(argv[1]);
+        cfg.steps = std::atoi(argv[2]);
+        for (int i = 3; i < argc; ++i) {
+            const std::string a = argv[i];
+            if (a == "--every" && i + 1 < argc) cfg.dump_every = std::atoi(argv[++i]);
+            else if (a == "--no-edges") cfg.dump_edges = false;
+            else cfg.dump_path = a;
+        }
+        settings::SettingsNode node;
+        node.cfg = &cfg;
+        const auto t0 = std::chrono::high_resolution_clock::now();
+        acclimate::ModelRun run(node);
+        const auto t1 = std::chrono::high_resolution_clock::now();
+        run.run();
+        const double init_s = std::chrono::duration<double>(t1 - t0).count();
+        std::printf("{\"edges\": %zu, \"steps\": %d, \"threads\": %u, \"init_seconds\": %.6f, \"phase_seconds\": %.6f, \"events\": %zu}\n",
+                    acclimate::g_init->edges.size(), cfg.steps, run.thread_count(), init_s, acclimate::g_phase_seconds, g_events.size());
+        return 0;
+    } catch (const std::exception& ex) {
+        std::fprintf(stderr, "oracle harness: %s\n", ex.what());
+        return 255;
+    }
+}
