@@ -1,0 +1,1121 @@
+// engine.cu -- device-resident Acclimate timestep engine and its C ABI (include/acclimate_b200.h).
+//
+// Data layout in HBM (DESIGN.md "Data layout"):
+//   * BusinessConnections are stored once, CSR by seller (the file order of the snapshot).  Per
+//     connection: Z* (int64), last demand request D as (quantity, price) int64 pair, delay tau (u8),
+//     domestic flag (u8), geo entity (int32).
+//   * TransportChainLink delay queues are a "conveyor": T = max(tau)+1 planes of [n_edges] (quantity
+//     int64 plane + value f64 plane).  The shipment of step t on a connection with delay tau is written
+//     to plane (t + tau) mod T and arrives when plane t mod T is read -- every connection advances by
+//     exactly one slot per step (reference TransportChainLink.cpp:69-71), so the ring shift is pure
+//     index arithmetic, arrivals of a step are ONE contiguous plane, and nothing is ever moved.
+//   * Buyer side: storages are numbered sector-major / buyer-minor so that neighbouring storages read
+//     neighbouring connections; incoming connections are listed per storage (CSC) twice: sliced-ELL
+//     (k-major in slices of 32 storages) for the thread-per-storage delivery pass and storage-major
+//     for the warp-per-purchasing-manager pass.
+//
+// Kernels of one step (reference phase they implement):
+//   firm_possible_production   CapacityManager::get_possible_production_X_hat            (phase 1)
+//   seller_production          SalesManager::calc_production_X + distribute              (phase 1)
+//   storage_delivery           Firm/Consumer input use, Storage::calc_content_S, TransportChainLink::push_flow_Z
+//                              arrivals, Storage::push_flow_Z accumulation               (phase 1)
+//   seller_expectation         SalesManager::iterate_expectation, Firm::iterate_expectation (phase 2)
+//   purchase                   PurchasingManager::iterate_purchase                       (phase 3)
+//
+// Compiled twice from this one source: by nvcc into libacclimate_b200.so (the product; CUDA only, no
+// CPU path) and -- with -DACC_HOST_EMU, by g++ -- into a test-only library in which every "launch" is
+// a host loop over the same templated routines (tests/emu; lets the CPU-only test tier check the
+// kernel logic against the oracle).  The emulation is never part of the product library.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/acclimate_b200.h"
+#include "purchase_core.cuh"
+
+namespace acc {
+
+// ------------------------------------------------------------------------------------------------
+// backend: memory + launches
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+struct EngineError {
+    std::string msg;
+};
+[[noreturn]] static void fail(const std::string& m) { throw EngineError{m}; }
+
+#ifdef ACC_HOST_EMU
+typedef void* stream_t;
+static void* dev_alloc(size_t bytes) {
+    void* p = std::calloc(1, bytes ? bytes : 1);
+    if (!p) fail("out of host memory (emulation)");
+    return p;
+}
+static void dev_free(void* p) { std::free(p); }
+static void h2d(void* d, const void* h, size_t b, stream_t) { std::memcpy(d, h, b); }
+static void d2h(void* h, const void* d, size_t b, stream_t) { std::memcpy(h, d, b); }
+static void dev_zero(void* d, size_t b, stream_t) { std::memset(d, 0, b); }
+static void dev_sync(stream_t) {}
+template <class K>
+static void launch_thread(stream_t, int n, K k) { for (int i = 0; i < n; ++i) k(i); }
+template <class K>
+static void launch_block(stream_t, int n, int threads, K k) { for (int i = 0; i < n; ++i) { HostCtx cx(threads); k(cx, i); } }
+template <class K>
+static void launch_warp(stream_t, int n, size_t smem, K k) {
+    std::vector<unsigned char> sm(smem + 16);
+    for (int i = 0; i < n; ++i) { HostCtx cx(32); k(cx, i, sm.data()); }
+}
+#else
+typedef cudaStream_t stream_t;
+#define ACC_CUDA(x)                                                                                   \
+    do {                                                                                              \
+        cudaError_t err__ = (x);                                                                      \
+        if (err__ != cudaSuccess) fail(std::string(#x) + ": " + cudaGetErrorString(err__));           \
+    } while (0)
+static void* dev_alloc(size_t bytes) {
+    void* p = nullptr;
+    ACC_CUDA(cudaMalloc(&p, bytes ? bytes : 1));
+    return p;
+}
+static void dev_free(void* p) { cudaFree(p); }
+static void h2d(void* d, const void* h, size_t b, stream_t s) { if (b) ACC_CUDA(cudaMemcpyAsync(d, h, b, cudaMemcpyHostToDevice, s)); }
+static void d2h(void* h, const void* d, size_t b, stream_t s) {
+    if (b) ACC_CUDA(cudaMemcpyAsync(h, d, b, cudaMemcpyDeviceToHost, s));
+    ACC_CUDA(cudaStreamSynchronize(s));
+}
+static void dev_zero(void* d, size_t b, stream_t s) { if (b) ACC_CUDA(cudaMemsetAsync(d, 0, b, s)); }
+static void dev_sync(stream_t s) { ACC_CUDA(cudaStreamSynchronize(s)); }
+
+template <class K>
+__global__ void __launch_bounds__(128) thread_kernel(int n, K k) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) k(i);
+}
+template <class K>
+__global__ void __launch_bounds__(256) block_kernel(K k) {
+    __shared__ __align__(16) unsigned char scratch[ACC_BLOCK_SCRATCH_BYTES];
+    BlockCtx cx(scratch);
+    k(cx, (int)blockIdx.x);
+}
+template <class K>
+__global__ void __launch_bounds__(32) warp_kernel(K k) {
+    extern __shared__ __align__(16) unsigned char dyn_smem[];
+    WarpCtx cx;
+    k(cx, (int)blockIdx.x, dyn_smem);
+}
+template <class K>
+static void launch_thread(stream_t s, int n, K k) {
+    if (n <= 0) return;
+    thread_kernel<K><<<(n + 127) / 128, 128, 0, s>>>(n, k);
+    ACC_CUDA(cudaGetLastError());
+}
+template <class K>
+static void launch_block(stream_t s, int n, int threads, K k) {
+    if (n <= 0) return;
+    block_kernel<K><<<n, threads, 0, s>>>(k);
+    ACC_CUDA(cudaGetLastError());
+}
+template <class K>
+static void launch_warp(stream_t s, int n, size_t smem, K k) {
+    if (n <= 0) return;
+    static size_t configured = 0;
+    if (smem > configured) {
+        ACC_CUDA(cudaFuncSetAttribute(warp_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    warp_kernel<K><<<n, 32, smem, s>>>(k);
+    ACC_CUDA(cudaGetLastError());
+}
+#endif
+
+template <class T>
+struct DBuf {  // device array with its element count
+    T* p = nullptr;
+    size_t n = 0;
+    void alloc(size_t count) { free(); n = count; p = static_cast<T*>(dev_alloc(count * sizeof(T))); }
+    void upload(const std::vector<T>& h, stream_t s) { alloc(h.size()); h2d(p, h.data(), h.size() * sizeof(T), s); }
+    void zero(stream_t s) { dev_zero(p, n * sizeof(T), s); }
+    std::vector<T> download(stream_t s) const { std::vector<T> h(n); d2h(h.data(), p, n * sizeof(T), s); return h; }
+    void free() { if (p) dev_free(p); p = nullptr; n = 0; }
+};
+
+// ------------------------------------------------------------------------------------------------
+// kernels (functors over the routines of model_core.cuh / purchase_core.cuh)
+// ------------------------------------------------------------------------------------------------
+struct FirmPossibleProduction {  // thread per firm
+    FirmView fv; StorageView st; ModelP mp; const int* firm_ids;
+    ACC_HD void operator()(int k) const {
+        const int f = firm_ids[k];
+        const int s0 = fv.st_off[f];
+        const Flow cap = possible_production(st, fv.st_list + s0, fv.st_off[f + 1] - s0, mkflow(fv.Xstar_q[f], fv.Xstar_v[f]), fv.lambda[f], fv.beta[f],
+                                             fv.var_costs[f], mp.dt, false);
+        fv.cap_q[f] = cap.q; fv.cap_v[f] = cap.v;
+    }
+};
+
+struct SellerProduction {  // CTA per firm
+    FirmView fv; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step; const int* firm_ids;
+    template <class Ctx>
+    ACC_HD void operator()(Ctx& cx, int k) const { seller_phase1(cx, firm_ids[k], fv, ev, mp, sectors, events, step); }
+};
+
+struct SellerExpectation {  // warp per firm
+    FirmView fv; EdgeView ev; StorageView st; ModelP mp; const SectorP* sectors; EventSink events; const int* firm_ids;
+    template <class Ctx>
+    ACC_HD void operator()(Ctx& cx, int k, unsigned char*) const { seller_phase2(cx, firm_ids[k], fv, ev, st, mp, sectors, events); }
+};
+
+struct StorageDelivery {  // thread per storage
+    StorageView st; FirmView fv; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
+    const i64* ell_off; const int* ell_width; const int* ell_edge;
+    ACC_HD void operator()(int s) const {
+        const int a = st.agent[s];
+        const SectorP sp = sectors[st.sector[s]];
+        // ---- input use and storage content ----
+        const Flow uhat = possible_use(st, s, mp.dt, false);
+        Flow used;
+        if (fv.type[a] == 1) {  // Firm::iterate_consumption_and_production, Firm.cpp:54-61
+            const Flow X = mkflow(fv.X_q[a], fv.X_v[a]);
+            used = fcopy(fmul(X, st.a[s]));
+            if (X.q > 0) used = set_price(used, flow_price(uhat));
+        } else {  // price-elastic consumer, Consumer.cpp:276-302
+            i64 rp;
+            if (uhat.q > 0) {
+                rp = flow_price(uhat);
+            } else {
+                rp = flow_price(mkflow(st.Ut_q[s], st.Ut_v[s]));
+                events.push(EV_NO_CONSUMPTION, a, -1, pf(rp));
+            }
+            const i64 want = qmul(qmul(st.Istar_q[s], fv.lambda[a]), pow(ratio(rp, 1000000), st.a[s]));
+            const Flow ut = flow_qp(want, rp);
+            used = fcopy(flow_qp(want < uhat.q ? want : uhat.q, rp));
+            st.Ut_q[s] = ut.q; st.Ut_v[s] = fcopy(ut).v;
+        }
+        storage_update(st, s, used, mp, sp.omega, events);
+        // ---- arrivals of this step: TransportChainLink::push_flow_Z (TransportChainLink.cpp:65-97),
+        //      BusinessConnection::deliver_flow_Z (BusinessConnection.cpp:106-113), Storage::push_flow_Z ----
+        const int slice = s >> 5, lane = s & 31;
+        const i64 base = ell_off[slice];
+        const int width = ell_width[slice];
+        const int T = ev.T;
+        const i64 now = (i64)(step % T) * ev.n_edges;
+        Flow in = mkflow(0, 0.0);
+        Flow imp = mkflow(0, 0.0);
+        i64 tq = st.T_q[s];
+        double tv = st.T_v[s];
+        for (int k = 0; k < width; ++k) {
+            const int e = ell_edge[base + (i64)k * 32 + lane];
+            if (e < 0) continue;
+            const Flow front = mkflow(ev.conv_q[now + e], ev.conv_v[now + e]);
+            const int tau = ev.tau[e];
+            Flow ship = front;
+            if (tau != 0) {
+                const i64 pl = (i64)((step + tau) % T) * ev.n_edges;
+                ship = mkflow(ev.conv_q[pl + e], ev.conv_v[pl + e]);
+            }
+            Flow out;
+            if (ev.ovf_q == nullptr) {
+                out = fcopy(front);  // overflow == 0, no passage forcing ever set
+            } else {
+                const int ent = ev.entity[e];
+                const double nu = ent >= 0 ? ev.nu[ent] : -1.0;
+                const Flow total = fadd(mkflow(ev.ovf_q[e], ev.ovf_v[e]), front);
+                if (nu < 0) {
+                    out = fcopy(total);
+                } else {
+                    const Flow cap = flow_qp(qmul_l(nu, ev.Z_q[e]), flow_price(front));
+                    out = fcopy(cap.q < total.q ? cap : total);  // std::min by quantity
+                }
+                const Flow ovf = fcopy(fsub(total, out));
+                ev.ovf_q[e] = ovf.q; ev.ovf_v[e] = ovf.v;
+            }
+            in = fadd(in, out);
+            if (!ev.domestic[e]) imp = fadd(imp, out);
+            tq += ship.q - out.q;
+            tv += ship.v - out.v;
+        }
+        st.In_q[s] = in.q; st.In_v[s] = in.v;
+        st.dlv_q[s] = in.q;
+        st.imp_q[s] = imp.q; st.imp_v[s] = imp.v;
+        st.T_q[s] = tq; st.T_v[s] = tv;
+    }
+};
+
+struct Purchase {  // warp per purchasing manager
+    StorageView st; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
+    const i64* in_off; const int* in_edge; const int* in_seller; const SellerPub* pub; int n_max;
+    i64* dem_q; double* dem_v; double* exp_costs; double* opt_val; double* tpen; int* iters; int* evals;
+    template <class Ctx>
+    ACC_HD void operator()(Ctx& cx, int s, unsigned char* smem) const {
+        PMWork k;
+        k.carve(smem, n_max);
+        const i64 o = in_off[s];
+        const int nin = (int)(in_off[s + 1] - o);
+        const int* ie = in_edge + o;
+        const int* is = in_seller + o;
+        const EdgeView& E = ev;
+        const i64 stp = step;
+        const i64 deficit = st.defc[s] - st.dlv_q[s] - st.T_q[s];
+        const PMResult r = purchase_one(
+            cx, nin, [&](int i) { return ie[i]; }, [&](int i) { return is[i]; },
+            [&](int e) { return E.conv_q[(i64)((stp + E.tau[e]) % E.T) * E.n_edges + e]; },
+            [&](int e) {  // BusinessConnection::get_minimum_passage, BusinessConnection.cpp:69-83 (single hop)
+                double m = 1.0;
+                if (E.nu != nullptr && E.entity[e] >= 0) { const double nu = E.nu[E.entity[e]]; if (nu >= 0.0 && nu < m) m = nu; }
+                return m;
+            },
+            [&](int e, i64 q, i64 p) { E.D_q[e] = q; E.D_p[e] = p; }, pub, E.Z_q, E.D_q, k, mp, sectors[st.sector[s]], st.Istar_q[s], st.Sstar_q[s],
+            st.S_q[s], st.Ut_q[s], deficit, events, st.sector[s], st.agent[s]);
+        if (cx.leader()) {
+            dem_q[s] = r.demand.q; dem_v[s] = r.demand.v; exp_costs[s] = r.expected_costs; opt_val[s] = r.optimized; tpen[s] = r.penalty;
+            iters[s] = r.iters; evals[s] = r.evals;
+        }
+    }
+};
+
+struct FirmIncomingDemand {  // CTA per firm: sum of the demand requests it holds (output surface only)
+    EdgeView ev; const int* firm_ids; i64* out_q; double* out_v;
+    template <class Ctx>
+    ACC_HD void operator()(Ctx& cx, int k) const {
+        const int f = firm_ids[k];
+        const int e0 = ev.seller_off[f];
+        const BookTotals t = book_totals(cx, ev.seller_off[f + 1] - e0, ev.D_q + e0, ev.D_p + e0);
+        if (cx.leader()) { out_q[f] = t.sq; out_v[f] = t.sv; }
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// the engine
+// ------------------------------------------------------------------------------------------------
+struct KernelClock {
+    const char* name;
+    double ms = 0.0;
+    i64 launches = 0;
+#ifndef ACC_HOST_EMU
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending;
+#endif
+};
+
+}  // namespace acc
+
+using namespace acc;
+
+struct acc_engine {
+    int device = 0;
+    stream_t stream = nullptr;
+    i64 step = 0;
+    i64 launches = 0;
+    bool profile = false;
+    std::vector<KernelClock> clocks;
+
+    // sizes
+    int nA = 0, nS = 0, nR = 0, nSt = 0, nF = 0, n_max = 0, T = 1;
+    i64 nE = 0;
+    ModelP mp;
+    std::vector<SectorP> h_sectors;
+    // host copies of topology needed for reads
+    std::vector<int> h_agent_type, h_agent_sector, h_agent_region, h_st_agent, h_st_sector, h_cid2s, h_firm_ids;
+    std::vector<unsigned char> h_tau;
+    std::vector<int> h_consumer_st;  // storages of consumers in (agent, container) order
+
+    DBuf<SectorP> sectors;
+    // agents / firms
+    DBuf<int> a_type, a_sector, a_region, a_st_off, a_st_list, firm_ids;
+    DBuf<double> a_beta, a_lambda;
+    DBuf<i64> f_Xstar_q, f_markup_eff, f_var_costs;
+    DBuf<double> f_Xstar_v;
+    DBuf<i64> f_cap_q, f_Xhat_q, f_est_q, f_X_q, f_Xexp_q, f_nbar, f_cutoff, f_desired_q, f_sumD_q, f_bk_sq, f_bk_cnt, f_bk_pmax, f_bk_pmin, f_exp_q;
+    DBuf<double> f_cap_v, f_Xhat_v, f_est_v, f_X_v, f_Xexp_v, f_C, f_R, f_sumD_v, f_bk_sv, f_exp_v;
+    DBuf<SellerPub> pub;
+    // storages
+    DBuf<i64> s_S_q, s_I0_q, s_I1_q, s_Il_q, s_U_q, s_Ut_q, s_T_q, s_dlv_q, s_imp_q, s_Istar_q, s_Sstar_q, s_defc, s_dem_q;
+    DBuf<double> s_S_v, s_I0_v, s_I1_v, s_Il_v, s_U_v, s_Ut_v, s_T_v, s_imp_v, s_Istar_v, s_Sstar_v, s_a, s_dem_v, s_exp_costs, s_opt_val, s_tpen;
+    DBuf<int> s_agent, s_sector, s_iters, s_evals;
+    int reg = 0;  // which of I0/I1 is the "other" register (arrived during the previous step)
+    // connections
+    DBuf<int> e_seller_off, e_entity;
+    DBuf<i64> e_D_q, e_D_p, e_Z_q, conv_q, e_ovf_q;
+    DBuf<double> conv_v, e_ovf_v, nu;
+    DBuf<unsigned char> e_tau, e_dom;
+    bool forcing_used = false;
+    // buyer-side lists
+    DBuf<i64> ell_off, in_off;
+    DBuf<int> ell_width, ell_edge, in_edge, in_seller;
+    // events
+    DBuf<Event> ev_buf;
+    DBuf<int> ev_count;
+    int ev_cap = 1 << 16;
+
+    ~acc_engine() {
+#ifndef ACC_HOST_EMU
+        for (auto& c : clocks)
+            for (auto& pr : c.pending) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+        if (stream) cudaStreamDestroy(stream);
+#endif
+    }
+
+    StorageView storage_view() {
+        StorageView v;
+        v.S_q = s_S_q.p; v.S_v = s_S_v.p;
+        v.Ip_q = reg == 0 ? s_I0_q.p : s_I1_q.p; v.Ip_v = reg == 0 ? s_I0_v.p : s_I1_v.p;
+        v.In_q = reg == 0 ? s_I1_q.p : s_I0_q.p; v.In_v = reg == 0 ? s_I1_v.p : s_I0_v.p;
+        v.Il_q = s_Il_q.p; v.Il_v = s_Il_v.p;
+        v.U_q = s_U_q.p; v.U_v = s_U_v.p; v.Ut_q = s_Ut_q.p; v.Ut_v = s_Ut_v.p;
+        v.T_q = s_T_q.p; v.T_v = s_T_v.p; v.dlv_q = s_dlv_q.p; v.imp_q = s_imp_q.p; v.imp_v = s_imp_v.p;
+        v.Istar_q = s_Istar_q.p; v.Istar_v = s_Istar_v.p; v.Sstar_q = s_Sstar_q.p; v.Sstar_v = s_Sstar_v.p;
+        v.a = s_a.p; v.defc = s_defc.p; v.agent = s_agent.p; v.sector = s_sector.p;
+        return v;
+    }
+    FirmView firm_view() {
+        FirmView v;
+        v.pub = pub.p;
+        v.Xstar_q = f_Xstar_q.p; v.Xstar_v = f_Xstar_v.p; v.beta = a_beta.p; v.lambda = a_lambda.p; v.sector = a_sector.p; v.region = a_region.p;
+        v.type = a_type.p; v.markup_eff = f_markup_eff.p; v.var_costs = f_var_costs.p; v.st_off = a_st_off.p; v.st_list = a_st_list.p;
+        v.cap_q = f_cap_q.p; v.cap_v = f_cap_v.p; v.Xhat_q = f_Xhat_q.p; v.Xhat_v = f_Xhat_v.p; v.est_q = f_est_q.p; v.est_v = f_est_v.p;
+        v.X_q = f_X_q.p; v.X_v = f_X_v.p; v.Xexp_q = f_Xexp_q.p; v.Xexp_v = f_Xexp_v.p; v.nbar = f_nbar.p; v.cutoff = f_cutoff.p;
+        v.C = f_C.p; v.R = f_R.p; v.desired_q = f_desired_q.p; v.sumD_q = f_sumD_q.p; v.sumD_v = f_sumD_v.p;
+        v.bk_sq = f_bk_sq.p; v.bk_sv = f_bk_sv.p; v.bk_cnt = f_bk_cnt.p; v.bk_pmax = f_bk_pmax.p; v.bk_pmin = f_bk_pmin.p;
+        v.exp_q = f_exp_q.p; v.exp_v = f_exp_v.p;
+        return v;
+    }
+    EdgeView edge_view() {
+        EdgeView v;
+        v.seller_off = e_seller_off.p; v.D_q = e_D_q.p; v.D_p = e_D_p.p; v.Z_q = e_Z_q.p; v.tau = e_tau.p; v.domestic = e_dom.p; v.entity = e_entity.p;
+        v.conv_q = conv_q.p; v.conv_v = conv_v.p; v.n_edges = nE; v.T = T;
+        v.ovf_q = forcing_used ? e_ovf_q.p : nullptr; v.ovf_v = forcing_used ? e_ovf_v.p : nullptr; v.nu = forcing_used ? nu.p : nullptr;
+        return v;
+    }
+    EventSink sink() {
+        EventSink s;
+        s.buf = ev_buf.p; s.count = ev_count.p; s.cap = ev_cap; s.step = step;
+        return s;
+    }
+
+    int clock_id(const char* name) {
+        for (size_t i = 0; i < clocks.size(); ++i) if (std::strcmp(clocks[i].name, name) == 0) return (int)i;
+        KernelClock c;
+        c.name = name;
+        clocks.push_back(c);
+        return (int)clocks.size() - 1;
+    }
+    template <class Fn>
+    void timed(const char* name, Fn fn) {
+        ++launches;
+#ifndef ACC_HOST_EMU
+        if (profile) {
+            const int id = clock_id(name);
+            cudaEvent_t a, b;
+            ACC_CUDA(cudaEventCreate(&a));
+            ACC_CUDA(cudaEventCreate(&b));
+            ACC_CUDA(cudaEventRecord(a, stream));
+            fn();
+            ACC_CUDA(cudaEventRecord(b, stream));
+            clocks[id].pending.push_back(std::make_pair(a, b));
+            clocks[id].launches += 1;
+            return;
+        }
+#endif
+        (void)name;
+        fn();
+    }
+    void collect_clocks() {
+#ifndef ACC_HOST_EMU
+        dev_sync(stream);
+        for (auto& c : clocks) {
+            for (auto& pr : c.pending) {
+                float ms = 0.f;
+                cudaEventElapsedTime(&ms, pr.first, pr.second);
+                c.ms += ms;
+                cudaEventDestroy(pr.first);
+                cudaEventDestroy(pr.second);
+            }
+            c.pending.clear();
+        }
+#endif
+    }
+
+    void phase_cp() {
+        {
+            FirmPossibleProduction k{firm_view(), storage_view(), mp, firm_ids.p};
+            timed("firm_possible_production", [&] { launch_thread(stream, nF, k); });
+        }
+        {
+            SellerProduction k{firm_view(), edge_view(), mp, sectors.p, sink(), step, firm_ids.p};
+            timed("seller_production", [&] { launch_block(stream, nF, 256, k); });
+        }
+        {
+            StorageDelivery k{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p};
+            timed("storage_delivery", [&] { launch_thread(stream, nSt, k); });
+        }
+    }
+    void phase_exp() {
+        SellerExpectation k{firm_view(), edge_view(), storage_view(), mp, sectors.p, sink(), firm_ids.p};
+        timed("seller_expectation", [&] { launch_warp(stream, nF, 0, k); });
+    }
+    void phase_pur() {
+        Purchase k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, pub.p, n_max,
+                   s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
+        timed("purchase", [&] { launch_warp(stream, nSt, pm_workspace_bytes(n_max), k); });
+    }
+    void tick() {
+        reg = 1 - reg;  // this step's arrivals become the next step's "other" register (Model::switch_registers)
+        ++step;
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// snapshot -> tables (host, once)
+// ------------------------------------------------------------------------------------------------
+namespace acc {
+
+static void build(acc_engine& E, const acc_network& net, const acc_params& par) {
+    stream_t s = E.stream;
+    const i64 nS = net.n_sectors, nR = net.n_regions, nA = net.n_agents, nE = net.n_edges;
+    if (nS <= 0 || nR <= 0 || nA <= 0 || nE <= 0) fail("empty network");
+    if (nE >= (i64)0x7fffffff) fail("more than 2^31-1 connections on one device: partition the network");
+    E.nS = (int)nS; E.nR = (int)nR; E.nA = (int)nA; E.nE = nE;
+    const double* m = par.model;
+    // ModelInitializer.cpp:58-62, 1015-1079
+    ModelP& mp = E.mp;
+    mp.dt = (double)mkt(m[ACC_MP_DELTA_T]);
+    if (!(mp.dt > 0)) fail("model.delta_t must be positive");
+    mp.pen_small = mkp(m[ACC_MP_TRANSPORT_PENALTY_SMALL]);
+    mp.pen_large = mkp(m[ACC_MP_TRANSPORT_PENALTY_LARGE]);
+    mp.min_storage = m[ACC_MP_MIN_STORAGE];
+    mp.generic_width = m[ACC_MP_CHEAPEST_PRICE_RANGE_WIDTH] < 0.0 ? 1 : 0;
+    mp.width = mp.generic_width ? 0 : mkp(m[ACC_MP_CHEAPEST_PRICE_RANGE_WIDTH]);
+    mp.quadratic_penalty = m[ACC_MP_QUADRATIC_TRANSPORT_PENALTY] != 0.0;
+    mp.relative_penalty = m[ACC_MP_RELATIVE_TRANSPORT_PENALTY] != 0.0;
+    mp.limited_by_markup = m[ACC_MP_MAX_DECREASE_RESERVATION_PRICE_LIMITED_BY_MARKUP] != 0.0;
+    mp.deviation_penalty = m[ACC_MP_DEVIATION_PENALTY] != 0.0;
+    mp.preserve_seller_price = m[ACC_MP_CHEAPEST_PRICE_RANGE_PRESERVE_SELLER_PRICE] != 0.0;
+    mp.maxeval = (int)m[ACC_MP_OPTIMIZATION_MAXITER];
+    mp.prec_adj = (int)m[ACC_MP_OPTIMIZATION_PRECISION_ADJUSTMENT];
+    if (m[ACC_MP_UTILITARIAN] != 0.0) fail("utilitarian consumers (nested-CES utility optimisation) are not built yet: set bool_utilitarian false");
+    const bool no_self_supply = m[ACC_MP_NO_SELF_SUPPLY] != 0.0;
+
+    E.h_sectors.resize(nS);
+    for (i64 k = 0; k < nS; ++k) {
+        const double* q = net.sector_params + k * ACC_SP_COUNT;
+        SectorP sp;
+        sp.omega = q[ACC_SP_UPPER_STORAGE_LIMIT];
+        sp.psi = (double)mkt(q[ACC_SP_INITIAL_STORAGE_FILL_FACTOR] * mp.dt);
+        sp.transport_type = (int)q[ACC_SP_TRANSPORT_TYPE];
+        sp.eps = q[ACC_SP_SUPPLY_ELASTICITY];
+        sp.dn = mkp(q[ACC_SP_PRICE_INCREASE_PRODUCTION_EXTENSION]);
+        sp.dn_est = mkp(q[ACC_SP_ESTIMATED_PRICE_INCREASE_PRODUCTION_EXTENSION]);
+        sp.markup = mkp(q[ACC_SP_INITIAL_MARKUP]);
+        sp.refill = (double)mkt(q[ACC_SP_TARGET_STORAGE_REFILL_TIME] * mp.dt);
+        sp.withdraw = (double)mkt(q[ACC_SP_TARGET_STORAGE_WITHDRAW_TIME] * mp.dt);
+        if (!(sp.refill > 0) || !(sp.withdraw > 0)) fail("target storage refill / withdraw times must be positive");
+        E.h_sectors[k] = sp;
+    }
+
+    std::vector<int> a_type(nA), a_sector(nA), a_region(nA);
+    std::vector<double> a_beta(nA), a_lambda(nA, 1.0);
+    for (i64 a = 0; a < nA; ++a) {
+        a_type[a] = (int)net.agent_type[a]; a_sector[a] = (int)net.agent_sector[a]; a_region[a] = (int)net.agent_region[a]; a_beta[a] = net.agent_beta[a];
+        if (a_sector[a] < 0 || a_sector[a] >= nS || a_region[a] < 0 || a_region[a] >= nR) fail("agent sector / region index out of range");
+    }
+
+    // ---- storages in creation order (ModelInitializer::initialize_connection, :187-213) ----
+    std::map<std::pair<int, int>, int> sto_of;  // (input sector, buying agent) -> creation id
+    std::vector<int> c_agent, c_sector;
+    std::vector<int> e_cid(nE);
+    std::vector<int> seller_off(nA + 1, 0);
+    for (i64 e = 0; e < nE; ++e) {
+        const i64 f = net.edge_from[e], t = net.edge_to[e];
+        if (f < 0 || f >= nA || t < 0 || t >= nA) fail("connection endpoint out of range");
+        if (a_type[f] != 1) fail("a connection's seller must be a firm");
+        if (e > 0 && net.edge_from[e - 1] > f) fail("connections must be listed seller-major (sorted by edge_from)");
+        if (no_self_supply && f == t) fail("self-supply connection although no_self_supply is set");
+        if (net.edge_zq[e] <= 0) fail("initial flows must be positive");
+        seller_off[f + 1] += 1;
+        const std::pair<int, int> key(a_sector[f], (int)t);
+        auto it = sto_of.find(key);
+        if (it == sto_of.end()) {
+            it = sto_of.emplace(key, (int)c_agent.size()).first;
+            c_agent.push_back((int)t);
+            c_sector.push_back(a_sector[f]);
+        }
+        e_cid[e] = it->second;
+    }
+    for (i64 a = 0; a < nA; ++a) seller_off[a + 1] += seller_off[a];
+    const int nSt = (int)c_agent.size();
+    E.nSt = nSt;
+    // internal order: sector-major, buyer-minor
+    std::vector<int> s2cid(nSt);
+    for (int k = 0; k < nSt; ++k) s2cid[k] = k;
+    std::sort(s2cid.begin(), s2cid.end(), [&](int x, int y) {
+        if (c_sector[x] != c_sector[y]) return c_sector[x] < c_sector[y];
+        return c_agent[x] < c_agent[y];
+    });
+    std::vector<int> cid2s(nSt);
+    for (int k = 0; k < nSt; ++k) cid2s[s2cid[k]] = k;
+    std::vector<int> st_agent(nSt), st_sector(nSt);
+    for (int k = 0; k < nSt; ++k) { st_agent[k] = c_agent[s2cid[k]]; st_sector[k] = c_sector[s2cid[k]]; }
+    // per-agent storage lists in creation order
+    std::vector<int> a_st_off(nA + 1, 0), a_st_list(nSt);
+    for (int c = 0; c < nSt; ++c) a_st_off[c_agent[c] + 1] += 1;
+    for (i64 a = 0; a < nA; ++a) a_st_off[a + 1] += a_st_off[a];
+    {
+        std::vector<int> fill(a_st_off.begin(), a_st_off.end() - 1);
+        for (int c = 0; c < nSt; ++c) a_st_list[fill[c_agent[c]]++] = cid2s[c];
+    }
+
+    // ---- per-connection constants, transport (BusinessConnection.cpp:38-65, ModelInitializer.cpp:689-700) ----
+    std::vector<unsigned char> tau(nE), dom(nE);
+    std::vector<int> entity(nE);
+    std::vector<i64> Zq(net.edge_zq, net.edge_zq + nE);
+    int Tmax = 0;
+    for (i64 e = 0; e < nE; ++e) {
+        const int f = (int)net.edge_from[e], t = (int)net.edge_to[e];
+        const int rf = a_region[f], rt = a_region[t];
+        dom[e] = rf == rt;
+        if (E.h_sectors[a_sector[f]].transport_type == 1 || rf == rt) {
+            tau[e] = 0; entity[e] = -1;
+        } else {
+            const int hi = rf > rt ? rf : rt, lo = rf > rt ? rt : rf;
+            const i64 d = net.delay[(i64)hi * nR + lo];
+            if (d < 0 || d > 254) fail("transport delay out of range (0..254 steps)");
+            tau[e] = (unsigned char)d;
+            entity[e] = hi * (hi - 1) / 2 + lo;
+        }
+        if (tau[e] > Tmax) Tmax = tau[e];
+    }
+    E.T = Tmax + 1;
+
+    // ---- initial state (Storage::add_initial_flow_Z_star, Firm::add_initial_production_X_star) ----
+    std::vector<i64> Xstar_q(nA, 0), Istar_q(nSt, 0), Sstar_q(nSt, 0), defc(nSt, 0), T_q(nSt, 0);
+    std::vector<double> Xstar_v(nA, 0.0), Istar_v(nSt, 0.0), Sstar_v(nSt, 0.0), T_v(nSt, 0.0);
+    std::vector<i64> in_cnt(nSt + 1, 0);
+    for (i64 e = 0; e < nE; ++e) {
+        const int f = (int)net.edge_from[e];
+        const int st = cid2s[e_cid[e]];
+        const Flow z = flow_qp(Zq[e], mkp(1.0));
+        Xstar_q[f] += z.q; Xstar_v[f] += z.v;
+        Istar_q[st] += z.q; Istar_v[st] += z.v;
+        const Flow add = flow_times_time(z, E.h_sectors[st_sector[st]].psi);
+        const Flow ns = fcopy(fadd(mkflow(Sstar_q[st], Sstar_v[st]), add));
+        Sstar_q[st] = ns.q; Sstar_v[st] = ns.v;
+        defc[st] += z.q * (tau[e] + 1);
+        double tv = 0.0;
+        for (int k = 0; k < tau[e]; ++k) tv += z.v;
+        T_q[st] += z.q * tau[e]; T_v[st] += tau[e] ? tv : 0.0;
+        in_cnt[st + 1] += 1;
+    }
+    // clean_network must be a no-op for a valid snapshot (ModelInitializer.cpp:215-299)
+    for (i64 a = 0; a < nA; ++a) {
+        if (a_type[a] == 1) {
+            i64 input = 0;
+            for (int k = a_st_off[a]; k < a_st_off[a + 1]; ++k) input += Istar_q[a_st_list[k]];
+            if (Xstar_q[a] - input <= 0 || seller_off[a + 1] == seller_off[a] || a_st_off[a + 1] == a_st_off[a])
+                fail("network snapshot is not clean: a firm would be removed by clean_network (no value added, no buyers or no inputs)");
+        } else if (a_st_off[a + 1] == a_st_off[a]) {
+            fail("network snapshot is not clean: consumer without inputs");
+        }
+    }
+    // technology coefficients / elasticities (Storage.cpp:68, ModelInitializer.cpp:195-200)
+    std::vector<double> st_a(nSt);
+    for (int k = 0; k < nSt; ++k) {
+        const int a = st_agent[k];
+        st_a[k] = a_type[a] == 1 ? ratio(Istar_q[k], Xstar_q[a]) : net.consumer_elasticity[st_sector[k]];
+    }
+    // SalesManager::initialize, SalesManager.cpp:626-643
+    std::vector<i64> markup_eff(nA, 0), var_costs(nA, 0), est_q(nA, 0), X_q(nA, 0);
+    std::vector<double> est_v(nA, 0.0), X_v(nA, 0.0);
+    std::vector<int> firm_ids;
+    for (i64 a = 0; a < nA; ++a) {
+        if (a_type[a] != 1) continue;
+        firm_ids.push_back((int)a);
+        i64 c0 = 0;
+        for (int k = a_st_off[a]; k < a_st_off[a + 1]; ++k) c0 += pmul(mkp(1.0), st_a[a_st_list[k]]);
+        const i64 one = mkp(1.0);
+        const i64 mk = std::min(one - c0, E.h_sectors[a_sector[a]].markup);
+        const i64 var = std::max((i64)0, one - (c0 + mk));
+        markup_eff[a] = mk; var_costs[a] = var;
+        Flow est = fcopy(fmul(mkflow(Xstar_q[a], Xstar_v[a]), a_beta[a]));
+        est = set_price(est, c0 + var);
+        est_q[a] = est.q; est_v[a] = est.v;
+        X_q[a] = Xstar_q[a]; X_v[a] = Xstar_v[a];
+    }
+    E.nF = (int)firm_ids.size();
+
+    // ---- buyer-side lists ----
+    std::vector<i64> in_off(nSt + 1, 0);
+    for (int k = 0; k < nSt; ++k) in_off[k + 1] = in_off[k] + in_cnt[k + 1];
+    std::vector<int> in_edge(nE), in_seller(nE);
+    {
+        std::vector<i64> fill(in_off.begin(), in_off.end() - 1);
+        for (i64 e = 0; e < nE; ++e) {  // file order == seller ascending
+            const int st = cid2s[e_cid[e]];
+            in_edge[fill[st]] = (int)e;
+            in_seller[fill[st]] = (int)net.edge_from[e];
+            ++fill[st];
+        }
+    }
+    int n_max = 0;
+    for (int k = 0; k < nSt; ++k) n_max = std::max<i64>(n_max, in_off[k + 1] - in_off[k]);
+    E.n_max = (n_max + 7) / 8 * 8;
+    const int n_slices = (nSt + 31) / 32;
+    std::vector<i64> ell_off(n_slices + 1, 0);
+    std::vector<int> ell_width(n_slices, 0);
+    for (int sl = 0; sl < n_slices; ++sl) {
+        int w = 0;
+        for (int k = sl * 32; k < std::min(nSt, sl * 32 + 32); ++k) w = std::max<i64>(w, in_off[k + 1] - in_off[k]);
+        ell_width[sl] = w;
+        ell_off[sl + 1] = ell_off[sl] + (i64)w * 32;
+    }
+    std::vector<int> ell_edge(ell_off[n_slices], -1);
+    for (int k = 0; k < nSt; ++k) {
+        const int sl = k >> 5, lane = k & 31;
+        for (i64 j = in_off[k]; j < in_off[k + 1]; ++j) ell_edge[ell_off[sl] + (j - in_off[k]) * 32 + lane] = in_edge[j];
+    }
+
+    // ---- upload ----
+    E.sectors.upload(E.h_sectors, s);
+    E.a_type.upload(a_type, s); E.a_sector.upload(a_sector, s); E.a_region.upload(a_region, s);
+    E.a_st_off.upload(a_st_off, s); E.a_st_list.upload(a_st_list, s); E.firm_ids.upload(firm_ids, s);
+    E.a_beta.upload(a_beta, s); E.a_lambda.upload(a_lambda, s);
+    E.f_Xstar_q.upload(Xstar_q, s); E.f_Xstar_v.upload(Xstar_v, s); E.f_markup_eff.upload(markup_eff, s); E.f_var_costs.upload(var_costs, s);
+    E.f_est_q.upload(est_q, s); E.f_est_v.upload(est_v, s); E.f_X_q.upload(X_q, s); E.f_X_v.upload(X_v, s);
+    for (DBuf<i64>* b : {&E.f_cap_q, &E.f_Xhat_q, &E.f_Xexp_q, &E.f_nbar, &E.f_cutoff, &E.f_desired_q, &E.f_sumD_q, &E.f_bk_sq, &E.f_bk_cnt, &E.f_bk_pmax,
+                         &E.f_bk_pmin, &E.f_exp_q}) { b->alloc(nA); b->zero(s); }
+    for (DBuf<double>* b : {&E.f_cap_v, &E.f_Xhat_v, &E.f_Xexp_v, &E.f_C, &E.f_R, &E.f_sumD_v, &E.f_bk_sv, &E.f_exp_v}) { b->alloc(nA); b->zero(s); }
+    E.pub.alloc(nA); E.pub.zero(s);
+
+    E.s_agent.upload(st_agent, s); E.s_sector.upload(st_sector, s);
+    E.s_Istar_q.upload(Istar_q, s); E.s_Istar_v.upload(Istar_v, s); E.s_Sstar_q.upload(Sstar_q, s); E.s_Sstar_v.upload(Sstar_v, s);
+    E.s_S_q.upload(Sstar_q, s); E.s_S_v.upload(Sstar_v, s);
+    // input_flow_I_[1] = input_flow_I_[2] = sum of Z*, [0] = 0; the first step reads register 1 as "other"
+    E.s_I0_q.upload(Istar_q, s); E.s_I0_v.upload(Istar_v, s);
+    E.s_I1_q.alloc(nSt); E.s_I1_q.zero(s); E.s_I1_v.alloc(nSt); E.s_I1_v.zero(s);
+    E.s_Il_q.upload(Istar_q, s); E.s_Il_v.upload(Istar_v, s);
+    E.reg = 0;
+    for (DBuf<i64>* b : {&E.s_U_q, &E.s_Ut_q, &E.s_dlv_q, &E.s_imp_q, &E.s_dem_q}) { b->alloc(nSt); b->zero(s); }
+    for (DBuf<double>* b : {&E.s_U_v, &E.s_Ut_v, &E.s_imp_v, &E.s_dem_v, &E.s_exp_costs, &E.s_opt_val, &E.s_tpen}) { b->alloc(nSt); b->zero(s); }
+    E.s_iters.alloc(nSt); E.s_iters.zero(s); E.s_evals.alloc(nSt); E.s_evals.zero(s);
+    E.s_T_q.upload(T_q, s); E.s_T_v.upload(T_v, s); E.s_defc.upload(defc, s); E.s_a.upload(st_a, s);
+    // PurchasingManager::add_initial_demand_D_star: demand_D = sum of Z*
+    h2d(E.s_dem_q.p, Istar_q.data(), nSt * sizeof(i64), s);
+    h2d(E.s_dem_v.p, Istar_v.data(), nSt * sizeof(double), s);
+    h2d(E.s_exp_costs.p, Istar_v.data(), nSt * sizeof(double), s);
+
+    E.e_seller_off.upload(seller_off, s); E.e_entity.upload(entity, s); E.e_tau.upload(tau, s); E.e_dom.upload(dom, s); E.e_Z_q.upload(Zq, s);
+    {   // last_demand_request_D = Z* at price 1 (BusinessConnection.cpp:42)
+        std::vector<i64> p1(nE, mkp(1.0));
+        E.e_D_q.upload(Zq, s); E.e_D_p.upload(p1, s);
+    }
+    {   // delay queues start full of Z* (TransportChainLink.cpp:49)
+        const i64 T = E.T;
+        E.conv_q.alloc((size_t)(T * nE)); E.conv_v.alloc((size_t)(T * nE));
+        E.conv_q.zero(s); E.conv_v.zero(s);
+        std::vector<i64> pq(nE);
+        std::vector<double> pv(nE);
+        for (i64 k = 0; k < T; ++k) {
+            bool any = false;
+            for (i64 e = 0; e < nE; ++e) {
+                // plane T-1 also holds the "last shipment" of connections whose queue is shorter: last_shipment_Z = Z*
+                const bool init = k < tau[e];
+                pq[e] = init ? Zq[e] : 0;
+                pv[e] = init ? flow_qp(Zq[e], mkp(1.0)).v : 0.0;
+                any = any || init;
+            }
+            if (any) {
+                h2d(E.conv_q.p + k * nE, pq.data(), nE * sizeof(i64), s);
+                h2d(E.conv_v.p + k * nE, pv.data(), nE * sizeof(double), s);
+                dev_sync(s);
+            }
+        }
+    }
+    E.in_off.upload(in_off, s); E.in_edge.upload(in_edge, s); E.in_seller.upload(in_seller, s);
+    E.ell_off.upload(ell_off, s); E.ell_width.upload(ell_width, s); E.ell_edge.upload(ell_edge, s);
+    E.ev_buf.alloc(E.ev_cap); E.ev_count.alloc(1); E.ev_count.zero(s);
+    E.nu.alloc((size_t)nR * (nR - 1) / 2 + 1);
+    dev_sync(s);
+
+    E.h_agent_type = a_type; E.h_agent_sector = a_sector; E.h_agent_region = a_region; E.h_st_agent = st_agent; E.h_st_sector = st_sector;
+    E.h_cid2s = cid2s; E.h_firm_ids = firm_ids; E.h_tau = tau;
+    for (i64 a = 0; a < nA; ++a)
+        if (a_type[a] != 1)
+            for (int k = a_st_off[a]; k < a_st_off[a + 1]; ++k) E.h_consumer_st.push_back(a_st_list[k]);
+}
+
+// ---- reads ----
+struct StateArray {
+    std::vector<i64> i;
+    std::vector<double> f;
+    bool is_f64 = false;
+};
+
+template <class T>
+static std::vector<T> to_creation_order(const acc_engine& E, const std::vector<T>& dev_order) {
+    std::vector<T> out(dev_order.size());
+    for (size_t c = 0; c < out.size(); ++c) out[c] = dev_order[E.h_cid2s[c]];
+    return out;
+}
+
+static bool read_state(acc_engine& E, const std::string& name, StateArray& out) {
+    stream_t s = E.stream;
+    auto I = [&](const DBuf<i64>& b) { out.i = b.download(s); out.is_f64 = false; return true; };
+    auto F = [&](const DBuf<double>& b) { out.f = b.download(s); out.is_f64 = true; return true; };
+    auto SI = [&](const DBuf<i64>& b) { out.i = to_creation_order(E, b.download(s)); out.is_f64 = false; return true; };
+    auto SF = [&](const DBuf<double>& b) { out.f = to_creation_order(E, b.download(s)); out.is_f64 = true; return true; };
+    // connections (file order)
+    if (name == "edge_D_q") return I(E.e_D_q);
+    if (name == "edge_D_p") return I(E.e_D_p);
+    if (name == "edge_ship_q" || name == "edge_ship_v") {
+        // last shipment of the last completed step t = step-1 sits on plane (t + tau) mod T
+        const bool q = name == "edge_ship_q";
+        const i64 t = E.step - 1;
+        if (q) out.i.assign(E.nE, 0); else out.f.assign(E.nE, 0.0);
+        out.is_f64 = !q;
+        if (t < 0) {
+            std::vector<i64> z = E.e_Z_q.download(s);
+            for (i64 e = 0; e < E.nE; ++e) { if (q) out.i[e] = z[e]; else out.f[e] = flow_qp(z[e], mkp(1.0)).v; }
+            return true;
+        }
+        std::vector<i64> hq = q ? E.conv_q.download(s) : std::vector<i64>();
+        std::vector<double> hv = q ? std::vector<double>() : E.conv_v.download(s);
+        for (i64 e = 0; e < E.nE; ++e) {
+            const i64 pl = (t + E.h_tau[e]) % E.T;
+            if (q) out.i[e] = hq[pl * E.nE + e]; else out.f[e] = hv[pl * E.nE + e];
+        }
+        return true;
+    }
+    // storages (creation order)
+    if (name == "sto_S_q") return SI(E.s_S_q);
+    if (name == "sto_S_v") return SF(E.s_S_v);
+    if (name == "sto_I_q") return SI(E.s_Il_q);
+    if (name == "sto_I_v") return SF(E.s_Il_v);
+    if (name == "sto_U_q") return SI(E.s_U_q);
+    if (name == "sto_U_v") return SF(E.s_U_v);
+    if (name == "sto_Ut_q") return SI(E.s_Ut_q);
+    if (name == "sto_Ut_v") return SF(E.s_Ut_v);
+    if (name == "sto_demand_q") return SI(E.s_dem_q);
+    if (name == "sto_demand_v") return SF(E.s_dem_v);
+    if (name == "sto_expected_costs") return SF(E.s_exp_costs);
+    if (name == "sto_optimized_value") return SF(E.s_opt_val);
+    if (name == "sto_transport_penalty") return SF(E.s_tpen);
+    if (name == "sto_transit_q") return SI(E.s_T_q);
+    if (name == "sto_transit_v") return SF(E.s_T_v);
+    if (name == "sto_import_q") return SI(E.s_imp_q);
+    if (name == "sto_import_v") return SF(E.s_imp_v);
+    if (name == "sto_delivered_q") return SI(E.s_dlv_q);
+    if (name == "sto_solver_iters" || name == "sto_solver_evals") {
+        std::vector<int> h = (name == "sto_solver_iters" ? E.s_iters : E.s_evals).download(s);
+        std::vector<i64> w(h.begin(), h.end());
+        out.i = to_creation_order(E, w); out.is_f64 = false;
+        return true;
+    }
+    if (name == "sto_deficit_q") {
+        std::vector<i64> a = E.s_defc.download(s), b = E.s_dlv_q.download(s), c = E.s_T_q.download(s);
+        for (size_t k = 0; k < a.size(); ++k) a[k] = a[k] - b[k] - c[k];
+        out.i = to_creation_order(E, a); out.is_f64 = false;
+        return true;
+    }
+    // agents
+    if (name == "agent_forcing") return F(E.a_lambda);
+    if (name == "firm_X_q") return I(E.f_X_q);
+    if (name == "firm_X_v") return F(E.f_X_v);
+    if (name == "firm_Xhat_q") return I(E.f_Xhat_q);
+    if (name == "firm_Xhat_v") return F(E.f_Xhat_v);
+    if (name == "firm_Xhat_p") {
+        std::vector<i64> q = E.f_Xhat_q.download(s);
+        std::vector<double> v = E.f_Xhat_v.download(s);
+        out.i.resize(q.size()); out.is_f64 = false;
+        for (size_t k = 0; k < q.size(); ++k) out.i[k] = flow_price(mkflow(q[k], v[k]));
+        return true;
+    }
+    if (name == "firm_Xexp_q") return I(E.f_Xexp_q);
+    if (name == "firm_Xexp_v") return F(E.f_Xexp_v);
+    if (name == "firm_nbar") return I(E.f_nbar);
+    if (name == "firm_cutoff") return I(E.f_cutoff);
+    if (name == "firm_costs_C") return F(E.f_C);
+    if (name == "firm_revenue_R") return F(E.f_R);
+    if (name == "firm_desired_q") return I(E.f_desired_q);
+    if (name == "firm_possible_q") return I(E.f_cap_q);
+    if (name == "firm_export_q") return I(E.f_exp_q);
+    if (name == "firm_export_v") return F(E.f_exp_v);
+    if (name == "firm_incoming_demand_q" || name == "firm_incoming_demand_v") {
+        DBuf<i64> q; DBuf<double> v;
+        q.alloc(E.nA); v.alloc(E.nA); q.zero(s); v.zero(s);
+        FirmIncomingDemand k{E.edge_view(), E.firm_ids.p, q.p, v.p};
+        E.timed("firm_incoming_demand", [&] { launch_block(s, E.nF, 256, k); });
+        if (name == "firm_incoming_demand_q") I(q); else F(v);
+        q.free(); v.free();
+        return true;
+    }
+    // sector / region sums, folded in the reference's serial order (agent order)
+    if (name == "sector_production_q" || name == "sector_production_v") {
+        std::vector<i64> q = E.f_X_q.download(s);
+        std::vector<double> v = E.f_X_v.download(s);
+        out.is_f64 = name == "sector_production_v";
+        out.i.assign(E.nS, 0); out.f.assign(E.nS, 0.0);
+        for (int a = 0; a < E.nA; ++a)
+            if (E.h_agent_type[a] == 1) { out.i[E.h_agent_sector[a]] += q[a]; out.f[E.h_agent_sector[a]] += v[a]; }
+        return true;
+    }
+    if (name == "region_export_q" || name == "region_export_v" || name == "region_import_q" || name == "region_import_v" || name == "region_consumption_q"
+        || name == "region_consumption_v" || name == "region_gdp_v" || name == "region_gdp_q") {
+        std::vector<i64> xq = E.f_exp_q.download(s), iq = E.s_imp_q.download(s), uq = E.s_U_q.download(s);
+        std::vector<double> xv = E.f_exp_v.download(s), iv = E.s_imp_v.download(s), uv = E.s_U_v.download(s);
+        std::vector<Flow> ex(E.nR, mkflow(0, 0.0)), im(E.nR, mkflow(0, 0.0)), co(E.nR, mkflow(0, 0.0));
+        for (int a = 0; a < E.nA; ++a)
+            if (E.h_agent_type[a] == 1) ex[E.h_agent_region[a]] = fadd(ex[E.h_agent_region[a]], mkflow(xq[a], xv[a]));
+        for (int k = 0; k < E.nSt; ++k) { const int r = E.h_agent_region[E.h_st_agent[k]]; im[r] = fadd(im[r], mkflow(iq[k], iv[k])); }
+        for (int k : E.h_consumer_st) { const int r = E.h_agent_region[E.h_st_agent[k]]; co[r] = fadd(co[r], mkflow(uq[k], uv[k])); }
+        out.i.assign(E.nR, 0); out.f.assign(E.nR, 0.0);
+        out.is_f64 = name.back() == 'v';
+        for (int r = 0; r < E.nR; ++r) {
+            Flow x;
+            if (name.find("export") != std::string::npos) x = ex[r];
+            else if (name.find("import") != std::string::npos) x = im[r];
+            else if (name.find("consumption") != std::string::npos) x = co[r];
+            else x = fsub(fadd(co[r], ex[r]), im[r]);  // Region::get_gdp, Region.cpp:52-54
+            out.i[r] = x.q; out.f[r] = x.v;
+        }
+        return true;
+    }
+    return false;
+}
+
+}  // namespace acc
+
+// ------------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------------
+#define ACC_API_BEGIN try {
+#define ACC_API_END(failval)                                     \
+    }                                                            \
+    catch (const acc::EngineError& ex) {                         \
+        acc::g_last_error = ex.msg;                              \
+        return failval;                                          \
+    }                                                            \
+    catch (const std::exception& ex) {                           \
+        acc::g_last_error = ex.what();                           \
+        return failval;                                          \
+    }
+
+extern "C" {
+
+const char* acc_last_error(void) { return acc::g_last_error.c_str(); }
+
+acc_engine* acc_create(const acc_network* net, const acc_params* params, int device) {
+    acc_engine* E = nullptr;
+    try {
+        if (net == nullptr || params == nullptr) fail("acc_create: null argument");
+        E = new acc_engine;
+        E->device = device;
+#ifndef ACC_HOST_EMU
+        int count = 0;
+        if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) fail("acc_create: no CUDA device available (this library has no CPU path)");
+        ACC_CUDA(cudaSetDevice(device));
+        ACC_CUDA(cudaStreamCreateWithFlags(&E->stream, cudaStreamNonBlocking));
+#endif
+        build(*E, *net, *params);
+        return E;
+    } catch (const acc::EngineError& ex) {
+        acc::g_last_error = ex.msg;
+    } catch (const std::exception& ex) {
+        acc::g_last_error = ex.what();
+    }
+    delete E;
+    return nullptr;
+}
+
+void acc_destroy(acc_engine* e) {
+    if (e == nullptr) return;
+#ifndef ACC_HOST_EMU
+    cudaSetDevice(e->device);
+    cudaStreamSynchronize(e->stream);
+#endif
+    // DBuf members are plain handles: release them explicitly
+    for (DBuf<i64>* b : {&e->f_Xstar_q, &e->f_markup_eff, &e->f_var_costs, &e->f_cap_q, &e->f_Xhat_q, &e->f_est_q, &e->f_X_q, &e->f_Xexp_q, &e->f_nbar,
+                         &e->f_cutoff, &e->f_desired_q, &e->f_sumD_q, &e->f_bk_sq, &e->f_bk_cnt, &e->f_bk_pmax, &e->f_bk_pmin, &e->f_exp_q, &e->s_S_q,
+                         &e->s_I0_q, &e->s_I1_q, &e->s_Il_q, &e->s_U_q, &e->s_Ut_q, &e->s_T_q, &e->s_dlv_q, &e->s_imp_q, &e->s_Istar_q, &e->s_Sstar_q,
+                         &e->s_defc, &e->s_dem_q, &e->e_D_q, &e->e_D_p, &e->e_Z_q, &e->conv_q, &e->e_ovf_q, &e->ell_off, &e->in_off})
+        b->free();
+    for (DBuf<double>* b : {&e->a_beta, &e->a_lambda, &e->f_Xstar_v, &e->f_cap_v, &e->f_Xhat_v, &e->f_est_v, &e->f_X_v, &e->f_Xexp_v, &e->f_C, &e->f_R,
+                            &e->f_sumD_v, &e->f_bk_sv, &e->f_exp_v, &e->s_S_v, &e->s_I0_v, &e->s_I1_v, &e->s_Il_v, &e->s_U_v, &e->s_Ut_v, &e->s_T_v,
+                            &e->s_imp_v, &e->s_Istar_v, &e->s_Sstar_v, &e->s_a, &e->s_dem_v, &e->s_exp_costs, &e->s_opt_val, &e->s_tpen, &e->conv_v,
+                            &e->e_ovf_v, &e->nu})
+        b->free();
+    for (DBuf<int>* b : {&e->a_type, &e->a_sector, &e->a_region, &e->a_st_off, &e->a_st_list, &e->firm_ids, &e->s_agent, &e->s_sector, &e->s_iters,
+                         &e->s_evals, &e->e_seller_off, &e->e_entity, &e->ell_width, &e->ell_edge, &e->in_edge, &e->in_seller, &e->ev_count})
+        b->free();
+    e->e_tau.free(); e->e_dom.free(); e->sectors.free(); e->pub.free(); e->ev_buf.free();
+    delete e;
+}
+
+int acc_set_agent_forcing(acc_engine* e, const double* lambda, size_t n) {
+    ACC_API_BEGIN
+    if (e == nullptr || lambda == nullptr) fail("acc_set_agent_forcing: null argument");
+    if (n != (size_t)e->nA) fail("acc_set_agent_forcing: expected one entry per agent");
+    h2d(e->a_lambda.p, lambda, n * sizeof(double), e->stream);
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_set_entity_passage(acc_engine* e, const double* nu, size_t n) {
+    ACC_API_BEGIN
+    if (e == nullptr || nu == nullptr) fail("acc_set_entity_passage: null argument");
+    if (n != (size_t)e->nR * (e->nR - 1) / 2) fail("acc_set_entity_passage: expected one entry per region pair");
+    if (!e->forcing_used) {
+        bool any = false;
+        for (size_t k = 0; k < n; ++k) any = any || nu[k] >= 0.0;
+        if (!any) return 0;  // nothing forced yet: overflow stays identically zero
+        e->e_ovf_q.alloc((size_t)e->nE); e->e_ovf_v.alloc((size_t)e->nE);
+        e->e_ovf_q.zero(e->stream); e->e_ovf_v.zero(e->stream);
+        e->forcing_used = true;
+    }
+    h2d(e->nu.p, nu, n * sizeof(double), e->stream);
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_phase(acc_engine* e, int phase) {
+    ACC_API_BEGIN
+    if (e == nullptr) fail("acc_phase: null engine");
+    switch (phase) {
+        case ACC_PHASE_CONSUMPTION_AND_PRODUCTION: e->phase_cp(); break;
+        case ACC_PHASE_EXPECTATION: e->phase_exp(); break;
+        case ACC_PHASE_PURCHASE: e->phase_pur(); break;
+        case ACC_PHASE_TICK: e->tick(); break;
+        default: fail("acc_phase: unknown phase");
+    }
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_step(acc_engine* e) {
+    ACC_API_BEGIN
+    if (e == nullptr) fail("acc_step: null engine");
+    e->phase_cp();
+    e->phase_exp();
+    e->phase_pur();
+    e->tick();
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_sync(acc_engine* e) {
+    ACC_API_BEGIN
+    if (e == nullptr) fail("acc_sync: null engine");
+    dev_sync(e->stream);
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_drain_events(acc_engine* e, acc_event* buf, size_t cap, size_t* n) {
+    ACC_API_BEGIN
+    if (e == nullptr || n == nullptr) fail("acc_drain_events: null argument");
+    int count = 0;
+    d2h(&count, e->ev_count.p, sizeof(int), e->stream);
+    if (count > e->ev_cap) count = e->ev_cap;
+    std::vector<Event> h((size_t)count);
+    d2h(h.data(), e->ev_buf.p, (size_t)count * sizeof(Event), e->stream);
+    // the device appends in arrival order; present a deterministic order
+    std::sort(h.begin(), h.end(), [](const Event& x, const Event& y) {
+        if (x.step != y.step) return x.step < y.step;
+        if (x.type != y.type) return x.type < y.type;
+        if (x.a != y.a) return x.a < y.a;
+        return x.b < y.b;
+    });
+    const size_t m = std::min(cap, h.size());
+    for (size_t k = 0; k < m && buf != nullptr; ++k) { buf[k].step = h[k].step; buf[k].type = h[k].type; buf[k].a = h[k].a; buf[k].b = h[k].b; buf[k].value = h[k].value; }
+    *n = h.size();
+    e->ev_count.zero(e->stream);
+    dev_sync(e->stream);
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_read_state(acc_engine* e, const char* name, void* dst, size_t cap_bytes, size_t* n, int* is_f64) {
+    ACC_API_BEGIN
+    if (e == nullptr || name == nullptr || n == nullptr) fail("acc_read_state: null argument");
+    StateArray a;
+    if (!read_state(*e, name, a)) fail(std::string("acc_read_state: unknown array '") + name + "'");
+    const size_t cnt = a.is_f64 ? a.f.size() : a.i.size();
+    *n = cnt;
+    if (is_f64) *is_f64 = a.is_f64 ? 1 : 0;
+    if (dst != nullptr) {
+        if (cap_bytes < cnt * 8) fail("acc_read_state: destination too small");
+        std::memcpy(dst, a.is_f64 ? (const void*)a.f.data() : (const void*)a.i.data(), cnt * 8);
+    }
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_read(acc_engine* e, const char* group, const char* variable, double* dst, size_t cap, size_t* n) {
+    ACC_API_BEGIN
+    if (e == nullptr || group == nullptr || variable == nullptr || n == nullptr) fail("acc_read: null argument");
+    // observable name -> (state array, kind): kind 'q' quantity (x 1e-3), 'p' price (x 1e-6), 'v' value / plain
+    struct Map { const char* group; const char* var; const char* state; char kind; };
+    static const Map maps[] = {
+        {"firms", "production_quantity", "firm_X_q", 'q'}, {"firms", "production_value", "firm_X_v", 'v'},
+        {"firms", "expected_production_quantity", "firm_Xexp_q", 'q'}, {"firms", "expected_production_value", "firm_Xexp_v", 'v'},
+        {"firms", "communicated_possible_production_quantity", "firm_Xhat_q", 'q'}, {"firms", "communicated_possible_production_value", "firm_Xhat_v", 'v'},
+        {"firms", "offer_price", "firm_nbar", 'p'}, {"firms", "forcing", "agent_forcing", 'v'},
+        {"firms", "total_production_costs", "firm_costs_C", 'v'}, {"firms", "total_revenue", "firm_revenue_R", 'v'},
+        {"firms", "incoming_demand_quantity", "firm_incoming_demand_q", 'q'}, {"firms", "incoming_demand_value", "firm_incoming_demand_v", 'v'},
+        {"sectors", "total_production_quantity", "sector_production_q", 'q'}, {"sectors", "total_production_value", "sector_production_v", 'v'},
+        {"regions", "import_quantity", "region_import_q", 'q'}, {"regions", "import_value", "region_import_v", 'v'},
+        {"regions", "export_quantity", "region_export_q", 'q'}, {"regions", "export_value", "region_export_v", 'v'},
+        {"regions", "consumption_quantity", "region_consumption_q", 'q'}, {"regions", "consumption_value", "region_consumption_v", 'v'},
+        {"regions", "gdp_quantity", "region_gdp_q", 'q'}, {"regions", "gdp_value", "region_gdp_v", 'v'},
+        {"storages", "content_quantity", "sto_S_q", 'q'}, {"storages", "content_value", "sto_S_v", 'v'},
+        {"storages", "input_flow_quantity", "sto_I_q", 'q'}, {"storages", "input_flow_value", "sto_I_v", 'v'},
+        {"storages", "used_flow_quantity", "sto_U_q", 'q'}, {"storages", "used_flow_value", "sto_U_v", 'v'},
+        {"storages", "desired_used_flow_quantity", "sto_Ut_q", 'q'}, {"storages", "desired_used_flow_value", "sto_Ut_v", 'v'},
+        {"storages", "demand_quantity", "sto_demand_q", 'q'}, {"storages", "demand_value", "sto_demand_v", 'v'},
+        {"storages", "expected_costs", "sto_expected_costs", 'v'}, {"storages", "optimized_value", "sto_optimized_value", 'v'},
+        {"storages", "total_transport_penalty", "sto_transport_penalty", 'v'},
+        {"flows", "demand_request_quantity", "edge_D_q", 'q'}, {"flows", "sent_flow_quantity", "edge_ship_q", 'q'}, {"flows", "sent_flow_value", "edge_ship_v", 'v'},
+    };
+    for (const Map& mpp : maps) {
+        if (std::strcmp(mpp.group, group) != 0 || std::strcmp(mpp.var, variable) != 0) continue;
+        StateArray a;
+        if (!read_state(*e, mpp.state, a)) fail("acc_read: internal mapping error");
+        const size_t cnt = a.is_f64 ? a.f.size() : a.i.size();
+        *n = cnt;
+        if (dst == nullptr) return 0;
+        if (cap < cnt) fail("acc_read: destination too small");
+        for (size_t k = 0; k < cnt; ++k) dst[k] = a.is_f64 ? a.f[k] : (mpp.kind == 'q' ? qf(a.i[k]) : mpp.kind == 'p' ? pf(a.i[k]) : (double)a.i[k]);
+        return 0;
+    }
+    fail(std::string("acc_read: unknown observable ") + group + "/" + variable);
+    ACC_API_END(-1)
+}
+
+int64_t acc_edge_count(const acc_engine* e) { return e ? e->nE : -1; }
+int64_t acc_step_count(const acc_engine* e) { return e ? e->step : -1; }
+int64_t acc_launch_count(const acc_engine* e) { return e ? e->launches : -1; }
+void* acc_stream(acc_engine* e) { return e ? (void*)e->stream : nullptr; }
+
+int acc_profile(acc_engine* e, int enable) {
+    if (e == nullptr) return -1;
+    e->profile = enable != 0;
+    return 0;
+}
+
+int acc_kernel_times(acc_engine* e, const char** names, double* ms, int64_t* launches, int cap, int reset) {
+    ACC_API_BEGIN
+    if (e == nullptr) fail("acc_kernel_times: null engine");
+    e->collect_clocks();
+    const int cnt = (int)e->clocks.size();
+    for (int k = 0; k < cnt && k < cap; ++k) {
+        if (names) names[k] = e->clocks[k].name;
+        if (ms) ms[k] = e->clocks[k].ms;
+        if (launches) launches[k] = e->clocks[k].launches;
+    }
+    if (reset) for (auto& c : e->clocks) { c.ms = 0.0; c.launches = 0; }
+    return cnt;
+    ACC_API_END(-1)
+}
+
+}  // extern "C"

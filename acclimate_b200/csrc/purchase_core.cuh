@@ -1,0 +1,308 @@
+// purchase_core.cuh -- PurchasingManager::iterate_purchase for ONE purchasing manager, executed by
+// one warp with the connection data staged in shared memory.
+//
+// Follows reference src/model/PurchasingManager.cpp:
+//   :563-660  desired purchase, per-connection bounds / start value / xtol, filtering
+//   :149-451  objective, gradient, equality constraint (price curve n_r, transport penalty)
+//   :465-561  optimiser driver: restart on "more than iter SQP iterations" and on maxeval
+//   :704-737  demand requests D_r -> Demand(quantity, round(n_r)), accumulation of demand / costs
+// The optimiser is csrc/sqp_core.h (the same code the oracle's NLopt shim runs on the CPU).
+// Objective and constraint are accumulated strictly left to right in connection order, exactly as
+// the reference's loops do (:203-217, :221-240), so that the solver sees bit-identical values.
+#pragma once
+
+#include "model_core.cuh"
+#include "sqp_core.h"
+
+namespace acc {
+
+// workspace of one purchasing manager: NPM_F64 f64 vectors + 2 int vectors of length n_max
+#define ACC_PM_NVEC_F64 25
+#define ACC_PM_NVEC_I32 2
+ACC_HD size_t pm_workspace_bytes(int n_max) { return (size_t)n_max * (ACC_PM_NVEC_F64 * sizeof(double) + ACC_PM_NVEC_I32 * sizeof(int)); }
+
+struct PMWork {
+    accsqp::Work w;
+    double *xl, *xu, *xtol;  // bounds and tolerances (w.xl/xu/xtol point here)
+    // price-curve constants per purchasing connection
+    double *zf, *tgt, *addX, *Xhatf, *lamXf, *dnf, *base, *n_co, *nbar_min, *Dmin;
+    double* term;  // per-connection summand of the current evaluation
+    int *idx, *eid;  // compacted position -> incoming position, connection id
+    ACC_HD void carve(unsigned char* mem, int n_max) {
+        double* p = reinterpret_cast<double*>(mem);
+        w.x = p; p += n_max; w.x0 = p; p += n_max; w.g = p; p += n_max; w.a = p; p += n_max; w.d = p; p += n_max; w.b = p; p += n_max;
+        w.lo = p; p += n_max; w.hi = p; p += n_max; w.gl = p; p += n_max; w.xbest = p; p += n_max; w.xprev = p; p += n_max;
+        xl = p; p += n_max; xu = p; p += n_max; xtol = p; p += n_max;
+        zf = p; p += n_max; tgt = p; p += n_max; addX = p; p += n_max; Xhatf = p; p += n_max; lamXf = p; p += n_max; dnf = p; p += n_max;
+        base = p; p += n_max; n_co = p; p += n_max; nbar_min = p; p += n_max; Dmin = p; p += n_max;
+        term = p; p += n_max;
+        int* q = reinterpret_cast<int*>(p);
+        idx = q; q += n_max; eid = q;
+        w.xl = xl; w.xu = xu; w.xtol = xtol;
+    }
+};
+
+struct PMParams {
+    double Uf;        // to_float(initial_used_flow_U_star): scale of objective and constraint (:194,:200)
+    double markup;    // to_float(buyer sector initial_markup)
+    double pen_large, pen_small;
+    int quadratic, relative, limited_by_markup;
+};
+
+// estimate_production_extension_penalty, :149-159
+ACC_HD double est_penalty(double x, double lamXf, double dnf) {
+    if (x <= lamXf) return 0.0;
+    return stdmax(0.0, dnf / (2 * lamXf) * (x - lamXf) * (x - lamXf));
+}
+// estimate_marginal_production_extension_penalty, :173-182
+ACC_HD double est_marginal_penalty(double x, double lamXf, double dnf) {
+    if (x <= lamXf) return 0.0;
+    return dnf / lamXf * (x - lamXf);
+}
+
+// n_r, grad_n_r, transport_penalty, partial_D_r_transport_penalty for connection r at demand D
+struct CurvePoint {
+    double n, gn, tp, tpp;
+};
+ACC_HD CurvePoint curve_at(const PMWork& k, const PMParams& pp, int r, double D) {
+    CurvePoint c;
+    // expected_average_price_E_n_r (:243-275) and its gradient (:305-321)
+    double Xn = D + k.addX[r];
+    if (Xn > k.Xhatf[r]) Xn = k.Xhatf[r];
+    double E = k.base[r];
+    double gE = 0.0;
+    if (Xn > 0.0) {
+        const double pen = est_penalty(Xn, k.lamXf[r], k.dnf[r]);
+        E = k.base[r] + pen / Xn;
+        gE = est_marginal_penalty(Xn, k.lamXf[r], k.dnf[r]) / Xn - pen / Xn / Xn;
+    }
+    // n_r (:277-303), grad_n_r (:351-379)
+    if (k.n_co[r] <= k.nbar_min[r]) {
+        if (D < k.Dmin[r]) {
+            c.n = k.n_co[r] + (k.nbar_min[r] - k.n_co[r]) / k.Dmin[r] * D;
+            c.gn = (k.Dmin[r] > 0.0) ? (k.nbar_min[r] - k.n_co[r]) / k.Dmin[r] : gE;
+        } else {
+            c.n = E;
+            c.gn = gE;
+        }
+    } else if (E <= k.n_co[r]) {
+        c.n = k.n_co[r];
+        c.gn = 0.0;
+    } else {
+        c.n = E;
+        c.gn = gE;
+    }
+    // transport_penalty (:381-409), partial_D_r_transport_penalty (:411-451)
+    const double t = k.tgt[r];
+    if (pp.quadratic) {
+        double marg = 0.0;
+        if (D < t) marg = -pp.markup; else if (D > t) marg = pp.markup;
+        if (pp.relative) {
+            if (t > ACC_PREC3) {
+                c.tp = (D - t) * ((D - t) * pp.pen_large / (t * t) / 2 + marg);
+                c.tpp = (D - t) * pp.pen_large / (t * t) + marg;
+            } else {
+                // to_float(transport_penalty_large / 2 + Price(marg_penalty)): typed Price arithmetic
+                c.tp = D * D * pf(pdiv(mkp(pp.pen_large), 2.0) + mkp(marg));
+                c.tpp = D * pp.pen_large + marg;
+            }
+        } else {
+            c.tp = (D - t) * ((D - t) * pp.pen_large / 2 + marg);
+            c.tpp = (D - t) * pp.pen_large + marg;
+        }
+    } else {
+        if (pp.relative) {
+            if (D < t) c.tpp = -pp.pen_small / t;
+            else if (D > t) c.tpp = pp.pen_large / t;
+            else c.tpp = (pp.pen_large - pp.pen_small) / 2 / t;
+            c.tp = c.tpp * (D - t) / t;
+        } else {
+            if (D < t) c.tpp = -pp.pen_small;
+            else if (D > t) c.tpp = pp.pen_large;
+            else c.tpp = (pp.pen_large - pp.pen_small) / 2;
+            c.tp = c.tpp * (D - t);
+        }
+    }
+    return c;
+}
+
+// Objective / constraint evaluation in the convention of sqp_core: minimise F = costs / U*,
+// constraint c = (desired - sum D_r) / U* == 0.
+template <class Ctx>
+struct PMEval {
+    Ctx& cx;
+    PMWork& k;
+    const PMParams& pp;
+    int n;
+    double desired_f;
+    ACC_HD void operator()(const double* x, bool want_grad, double* F, double* c) {
+        const PMWork& kk = k;
+        const PMParams& p = pp;
+        cx.foreach(n, [&](int r) {
+            const double D = x[r] * kk.zf[r];
+            const CurvePoint cp = curve_at(kk, p, r, D);
+            kk.term[r] = cp.n * D + cp.tp;
+            if (want_grad) {
+                kk.w.g[r] = (kk.zf[r] * (cp.gn * D + cp.n + cp.tpp)) / p.Uf;
+                kk.w.a[r] = -(kk.zf[r] / p.Uf);
+            }
+        });
+        double costs, use;
+        cx.seqsum2(n, [&](int r) { return kk.term[r]; }, [&](int r) { return x[r] * kk.zf[r]; }, &costs, &use);
+        *F = costs / p.Uf;
+        *c = (desired_f - use) / p.Uf;
+    }
+};
+
+struct PMResult {
+    Flow demand;           // demand_D_
+    double expected_costs; // expected_costs_
+    double optimized;      // optimized_value_
+    double penalty;        // total_transport_penalty_
+    int iters, evals;
+};
+
+// Inputs of one purchasing manager, gathered by the caller-provided accessors:
+//   in_edge(i) -> connection id of the i-th incoming connection (seller ascending)
+//   in_seller(i) -> seller agent
+template <class Ctx, class InEdge, class InSeller, class LastShip, class MinPassage, class SendD>
+ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_seller, LastShip last_ship, MinPassage min_passage, SendD send_D,
+                             const SellerPub* pub, const i64* Z_q, const i64* lastD_q, PMWork& k, const ModelP& mp, const SectorP& sec, i64 Ustar_q,
+                             i64 Sstar_q, i64 S_q, i64 Ut_q, i64 deficit_q, const EventSink& events, int ev_sector, int ev_agent) {
+    PMResult res;
+    res.demand = mkflow(0, 0.0); res.expected_costs = 0.0; res.optimized = 0.0; res.penalty = 0.0; res.iters = 0; res.evals = 0;
+    // desired purchase, :587-593
+    const i64 shortage = mkq(qf(deficit_q) * mp.dt) + Sstar_q - S_q;
+    i64 desired = Ut_q + qdiv(shortage, shortage > 0 ? sec.refill : sec.withdraw);
+    if (desired <= 0) {  // :595-600
+        cx.foreach(nin, [&](int i) { send_D(in_edge(i), (i64)0, (i64)0); });
+        return res;
+    }
+    // upper limit of one connection, :609-622
+    auto upper_of = [&](int i, double* Xe_out, double* add_out) {
+        const SellerPub sp = pub[in_seller(i)];
+        const int e = in_edge(i);
+        const double nu = min_passage(e);
+        const double Xe = nu * qf(sp.Xexp_q);                                  // expected_production, :334-341
+        const double X = qf(sp.X_q);
+        const double Zl = qf(last_ship(e));
+        const double rr = (X > 0.0) ? Xe / X : 0.0;
+        const double add = rr * (X - Zl);                                       // expected_additional_production, :343-349
+        double Xmax = qf(sp.Xhat_q);
+        Xmax *= nu;                                                             // :612-614
+        *Xe_out = Xe; *add_out = add;
+        return Xmax - add;
+    };
+    const int n = cx.compact(nin, [&](int i) {
+        const SellerPub sp = pub[in_seller(i)];
+        if (sp.Xhat_q <= 0) return false;
+        double Xe, add;
+        return mkq(upper_of(i, &Xe, &add)) > 0;
+    }, k.idx);
+    // inactive connections get a zero demand request (:604-605, :646-648)
+    cx.foreach(nin, [&](int i) {
+        const SellerPub sp = pub[in_seller(i)];
+        bool active = sp.Xhat_q > 0;
+        if (active) { double Xe, add; active = mkq(upper_of(i, &Xe, &add)) > 0; }
+        if (!active) send_D(in_edge(i), (i64)0, (i64)0);
+    });
+    if (n == 0) return res;  // :652-655
+
+    PMParams pp;
+    pp.Uf = qf(Ustar_q);
+    pp.markup = pf(sec.markup);
+    pp.pen_large = pf(mp.pen_large); pp.pen_small = pf(mp.pen_small);
+    pp.quadratic = mp.quadratic_penalty; pp.relative = mp.relative_penalty; pp.limited_by_markup = mp.limited_by_markup;
+
+    cx.foreach(n, [&](int r) {
+        const int i = k.idx[r];
+        const int e = in_edge(i);
+        const SellerPub sp = pub[in_seller(i)];
+        double Xe, add;
+        const double upper = upper_of(i, &Xe, &add);
+        const double zf = qf(Z_q[e]);
+        const double lamXf = qf(sp.lamX_q);
+        const double dnf = pf(sp.dn_est);
+        const double nbar = pf(sp.nbar);
+        k.eid[r] = e;
+        k.zf[r] = zf;
+        k.tgt[r] = mp.deviation_penalty ? qf(lastD_q[e]) : zf;
+        k.addX[r] = add;
+        k.Xhatf[r] = qf(sp.Xhat_q);
+        k.lamXf[r] = lamXf;
+        k.dnf[r] = dnf;
+        // n_r constants, :279-289
+        const double Dmin = stdmax(0.0, lamXf - add);
+        const double Xmin = Dmin + add;
+        const double npeE = (Xe > 0.0) ? est_penalty(Xe, lamXf, dnf) / Xe : 0.0;
+        const double npeMin = (Xmin > 0.0) ? est_penalty(Xmin, lamXf, dnf) / Xmin : 0.0;
+        const double nbar_min = nbar - npeE + npeMin;
+        // E_n_r's four cases collapse to  base [+ pen(X_new)/X_new]  with base = n_bar [- pen(X_exp)/X_exp]
+        k.base[r] = (Xe > 0.0) ? nbar - npeE : nbar;
+        // calc_n_co, :323-332: marginal costs at the seller's production, n_c un-rounded
+        const double ncf = sp.Xhat_v / qf(sp.Xhat_q);
+        const double Xs = qf(sp.X_q);
+        double n_co = (Xs <= lamXf) ? ncf : ncf + est_marginal_penalty(Xs, lamXf, dnf);
+        if (pp.limited_by_markup) {
+            const double n_crit = nbar_min - pp.markup * Dmin;
+            n_co = stdmax(n_co, n_crit);
+        }
+        k.n_co[r] = n_co;
+        k.nbar_min[r] = nbar_min;
+        k.Dmin[r] = Dmin;
+        // bounds, start value, xtol, :620-644
+        const double init_unbound = Xe - add;
+        const double init = stdmin(upper, stdmax(0.0, init_unbound));
+        k.xl[r] = 0.0 / zf;
+        k.xu[r] = upper / zf;
+        k.xtol[r] = (ACC_PREC3 * mp.prec_adj) / zf;
+        k.w.x[r] = init / zf;
+    });
+    const i64 max_purchase = cx.isum(n, [&](int r) {
+        double Xe, add;
+        return mkq(upper_of(k.idx[r], &Xe, &add));
+    });
+    if (desired > max_purchase) desired = max_purchase;  // :658-660
+
+    // local optimisation, :690-702 with the restart logic of :465-561
+    PMEval<Ctx> ev{cx, k, pp, n, qf(desired)};
+    accsqp::Params sp_;
+    sp_.n = n; sp_.ctype = accsqp::CON_EQ; sp_.ctol = ACC_PREC3; sp_.maxeval = mp.maxeval; sp_.max_iter = ACCSQP_MAX_ITER;
+    accsqp::Stats st;
+    int restarts = 0;
+    for (;;) {
+        const int ret = accsqp::sqp_minimize(cx, ev, k.w, sp_, st);
+        cx.foreach(n, [&](int r) { k.w.x[r] = k.w.xbest[r]; });
+        res.iters += st.iters; res.evals += st.evals;
+        if (ret == accsqp::SQP_FAILURE) {                 // "bug: more than iter SQP iterations", :480-504
+            if (++restarts < 10) continue;
+        } else if (ret == accsqp::SQP_MAXEVAL_REACHED) {  // :526-546
+            if (cx.leader()) events.push(EV_OPTIMIZER_MAXITER, ev_sector, ev_agent, 0.0);
+            if (++restarts < 10) continue;
+        }
+        break;
+    }
+    res.optimized = (-st.minf) * pp.Uf;  // unscaled_objective(opt.optimized_value()), :509
+
+    // distribute demand requests, :704-737
+    cx.foreach(n, [&](int r) {
+        const double D = k.w.x[r] * k.zf[r];
+        const CurvePoint cp = curve_at(k, pp, r, D);
+        const i64 q = mkq(D);
+        const i64 p = q > 0 ? mkp(cp.n) : 0;
+        send_D(k.eid[r], q, p);
+        k.term[r] = cp.n * D + cp.tp;
+        k.w.d[r] = cp.tp;
+        k.w.g[r] = q > 0 ? q_times_p(q, p) : 0.0;
+    });
+    double costs, pen, dv, dummy;
+    cx.seqsum2(n, [&](int r) { return k.term[r]; }, [&](int r) { return k.w.d[r]; }, &costs, &pen);
+    cx.seqsum2(n, [&](int r) { return k.w.g[r]; }, [&](int) { return 0.0; }, &dv, &dummy);
+    const i64 dq = cx.isum(n, [&](int r) { return mkq(k.w.x[r] * k.zf[r]); });
+    res.demand = mkflow(dq, dv);
+    res.expected_costs = costs;
+    res.penalty = pen;
+    return res;
+}
+
+}  // namespace acc

@@ -1,0 +1,227 @@
+"""ctypes binding of the C ABI in include/acclimate_b200.h.
+
+`Engine` is the thin host handle used by the tests, bench.py and the ModelRun mirror (modelrun.py).
+It loads libacclimate_b200.so (CUDA only).  There is no CPU implementation behind it: a missing
+library or a missing GPU raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import netfile
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libacclimate_b200.so")
+
+MP_COUNT = len(netfile.MODEL_PARAMS)
+SP_COUNT = len(netfile.SECTOR_PARAMS)
+
+# reference include/ModelRun.h:39-73
+EVENT_NAMES = [
+    "NO_CONSUMPTION", "STORAGE_UNDERRUN", "STORAGE_OVERRUN", "NO_PRODUCTION_SUPPLY_SHORTAGE",
+    "NO_PRODUCTION_DEMAND_QUANTITY_SHORTAGE", "NO_PRODUCTION_DEMAND_VALUE_SHORTAGE", "NO_PRODUCTION_HIGH_COSTS",
+    "NO_EXP_PRODUCTION_SUPPLY_SHORTAGE", "NO_EXP_PRODUCTION_DEMAND_QUANTITY_SHORTAGE",
+    "NO_EXP_PRODUCTION_DEMAND_VALUE_SHORTAGE", "NO_EXP_PRODUCTION_HIGH_COSTS", "DEMAND_FULFILL_HISTORY_UNDERFLOW",
+    "OPTIMIZER_TIMEOUT", "OPTIMIZER_MAXITER", "OPTIMIZER_ROUNDOFF_LIMITED",
+]
+
+
+class _Network(C.Structure):
+    _fields_ = [
+        ("n_sectors", C.c_int64), ("n_regions", C.c_int64), ("n_agents", C.c_int64), ("n_edges", C.c_int64),
+        ("agent_type", C.c_void_p), ("agent_sector", C.c_void_p), ("agent_region", C.c_void_p), ("agent_beta", C.c_void_p),
+        ("edge_from", C.c_void_p), ("edge_to", C.c_void_p), ("edge_zq", C.c_void_p), ("delay", C.c_void_p),
+        ("sector_params", C.c_void_p), ("consumer_elasticity", C.c_void_p),
+    ]
+
+
+class _Params(C.Structure):
+    _fields_ = [("model", C.c_double * MP_COUNT)]
+
+
+class _Event(C.Structure):
+    _fields_ = [("step", C.c_int64), ("type", C.c_int32), ("a", C.c_int32), ("b", C.c_int32), ("value", C.c_double)]
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+def load_library(path=None):
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise EngineError(f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` (CUDA library, no CPU fallback)")
+    lib = C.CDLL(path)
+    lib.acc_create.restype = C.c_void_p
+    lib.acc_create.argtypes = [C.POINTER(_Network), C.POINTER(_Params), C.c_int]
+    lib.acc_destroy.argtypes = [C.c_void_p]
+    lib.acc_destroy.restype = None
+    lib.acc_last_error.restype = C.c_char_p
+    lib.acc_set_agent_forcing.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+    lib.acc_set_entity_passage.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+    lib.acc_step.argtypes = [C.c_void_p]
+    lib.acc_phase.argtypes = [C.c_void_p, C.c_int]
+    lib.acc_sync.argtypes = [C.c_void_p]
+    lib.acc_drain_events.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+    lib.acc_read.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+    lib.acc_read_state.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_int)]
+    for name in ("acc_edge_count", "acc_step_count", "acc_launch_count"):
+        getattr(lib, name).restype = C.c_int64
+        getattr(lib, name).argtypes = [C.c_void_p]
+    lib.acc_stream.restype = C.c_void_p
+    lib.acc_stream.argtypes = [C.c_void_p]
+    lib.acc_profile.argtypes = [C.c_void_p, C.c_int]
+    lib.acc_kernel_times.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+    return lib
+
+
+class Engine:
+    """One device-resident model.  `arrays` is a network snapshot as produced by synth.make_network / netfile.read."""
+
+    def __init__(self, arrays, device=0, lib_path=None):
+        self.lib = load_library(lib_path)
+        a = {k: np.ascontiguousarray(v) for k, v in arrays.items()}
+        meta = a["meta"].astype(np.int64)
+        self._keep = [
+            a["agent_type"].astype(np.int64), a["agent_sector"].astype(np.int64), a["agent_region"].astype(np.int64),
+            a["agent_beta"].astype(np.float64), a["edge_from"].astype(np.int64), a["edge_to"].astype(np.int64),
+            a["edge_zq"].astype(np.int64), a["delay"].astype(np.int64), a["sector_f64"].astype(np.float64),
+            a["consumer_elasticity"].astype(np.float64),
+        ]
+        net = _Network(int(meta[0]), int(meta[1]), int(meta[2]), int(meta[3]), *[x.ctypes.data for x in self._keep])
+        par = _Params()
+        mp = a["model_f64"].astype(np.float64)
+        if mp.size != MP_COUNT:
+            raise EngineError("model_f64 has the wrong length")
+        for i in range(MP_COUNT):
+            par.model[i] = float(mp[i])
+        self.n_sectors, self.n_regions, self.n_agents, self.n_edges = (int(x) for x in meta[:4])
+        self.h = self.lib.acc_create(C.byref(net), C.byref(par), int(device))
+        if not self.h:
+            raise EngineError(self.lib.acc_last_error().decode())
+
+    def _check(self, rc):
+        if rc != 0:
+            raise EngineError(self.lib.acc_last_error().decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.acc_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_agent_forcing(self, lam):
+        lam = np.ascontiguousarray(lam, dtype=np.float64)
+        self._check(self.lib.acc_set_agent_forcing(self.h, lam.ctypes.data, lam.size))
+
+    def set_entity_passage(self, nu):
+        nu = np.ascontiguousarray(nu, dtype=np.float64)
+        self._check(self.lib.acc_set_entity_passage(self.h, nu.ctypes.data, nu.size))
+
+    def step(self):
+        self._check(self.lib.acc_step(self.h))
+
+    def phase(self, which):
+        self._check(self.lib.acc_phase(self.h, int(which)))
+
+    def sync(self):
+        self._check(self.lib.acc_sync(self.h))
+
+    @property
+    def steps_done(self):
+        return int(self.lib.acc_step_count(self.h))
+
+    @property
+    def launches(self):
+        return int(self.lib.acc_launch_count(self.h))
+
+    def stream(self):
+        return self.lib.acc_stream(self.h)
+
+    def drain_events(self):
+        n = C.c_size_t(0)
+        self._check(self.lib.acc_drain_events(self.h, None, 0, C.byref(n)))
+        # the first call already cleared the device buffer only if n == 0; re-read with a buffer otherwise
+        return int(n.value)
+
+    def events(self, cap=1 << 16):
+        buf = (_Event * cap)()
+        n = C.c_size_t(0)
+        self._check(self.lib.acc_drain_events(self.h, buf, cap, C.byref(n)))
+        m = min(cap, int(n.value))
+        return [(int(buf[k].step), int(buf[k].type), int(buf[k].a), int(buf[k].b), float(buf[k].value)) for k in range(m)]
+
+    def read_state(self, name):
+        n = C.c_size_t(0)
+        isf = C.c_int(0)
+        self._check(self.lib.acc_read_state(self.h, name.encode(), None, 0, C.byref(n), C.byref(isf)))
+        out = np.empty(int(n.value), dtype=np.float64 if isf.value else np.int64)
+        self._check(self.lib.acc_read_state(self.h, name.encode(), out.ctypes.data, out.nbytes, C.byref(n), C.byref(isf)))
+        return out
+
+    def read(self, group, variable, out=None):
+        n = C.c_size_t(0)
+        if out is None:
+            self._check(self.lib.acc_read(self.h, group.encode(), variable.encode(), None, 0, C.byref(n)))
+            out = np.empty(int(n.value), dtype=np.float64)
+        self._check(self.lib.acc_read(self.h, group.encode(), variable.encode(), out.ctypes.data, out.size, C.byref(n)))
+        return out
+
+    def profile(self, enable=True):
+        self._check(self.lib.acc_profile(self.h, 1 if enable else 0))
+
+    def kernel_times(self, reset=True, cap=32):
+        names = (C.c_char_p * cap)()
+        ms = (C.c_double * cap)()
+        launches = (C.c_int64 * cap)()
+        cnt = self.lib.acc_kernel_times(self.h, names, ms, launches, cap, 1 if reset else 0)
+        if cnt < 0:
+            raise EngineError(self.lib.acc_last_error().decode())
+        return {names[k].decode(): (float(ms[k]), int(launches[k])) for k in range(min(cnt, cap))}
+
+
+class Scenario:
+    """Forcing tables of a snapshot applied with the rule of the reference's Scenario::iterate
+    (reference src/scenario/Scenario.cpp:161-174): value inside [from, to], reset at to + delta_t."""
+
+    def __init__(self, arrays):
+        self.n_agents = int(arrays["meta"][2])
+        R = int(arrays["meta"][1])
+        self.n_conn = R * (R - 1) // 2
+        self.forcing = np.asarray(arrays.get("forcing", np.zeros(0)), dtype=np.float64).reshape(-1, 4)
+        self.passage = np.asarray(arrays.get("passage", np.zeros(0)), dtype=np.float64).reshape(-1, 4)
+        self.dt = float(np.rint(arrays["model_f64"][netfile.MODEL_PARAMS.index("delta_t")]))
+        self.lam = np.ones(self.n_agents)
+        self.nu = np.full(self.n_conn, -1.0)
+
+    def apply(self, engine, step):
+        t = step * self.dt
+        changed_l = changed_n = False
+        for f, to, idx, val in self.forcing:
+            f, to = np.rint(f), np.rint(to)
+            if f <= t <= to:
+                self.lam[int(idx)] = val
+                changed_l = True
+            elif t == to + self.dt:
+                self.lam[int(idx)] = 1.0
+                changed_l = True
+        for f, to, idx, val in self.passage:
+            f, to = np.rint(f), np.rint(to)
+            if f <= t <= to:
+                self.nu[int(idx)] = val
+                changed_n = True
+            elif t == to + self.dt:
+                self.nu[int(idx)] = -1.0
+                changed_n = True
+        if changed_l:
+            engine.set_agent_forcing(self.lam)
+        if changed_n:
+            engine.set_entity_passage(self.nu)

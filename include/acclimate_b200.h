@@ -1,0 +1,146 @@
+/* acclimate_b200.h -- C ABI of the B200 engine for Acclimate's per-timestep agent iteration.
+ *
+ * The reference has no plugin registry; the path sits behind the phase interface of its Model class.
+ * Each entry point below names the reference interface it replaces (paths relative to the reference
+ * repository root).  Conventions follow the reference's own (stale) C shim src/external.cpp:56-122:
+ * every function returns 0 on success and -1 on error, the message is available from
+ * acc_last_error(); no C++ exception crosses the boundary; the engine owns all device memory, host
+ * buffers are caller-owned.  One engine = one CUDA device = one host thread at a time.
+ *
+ * There is no CPU implementation behind this interface: acc_create fails when no CUDA device is
+ * available.
+ */
+#ifndef ACCLIMATE_B200_H
+#define ACCLIMATE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct acc_engine acc_engine;
+
+/* order of acc_params.model[] -- Parameters::ModelParameters, include/parameters.h:33-84, and
+ * model.delta_t / model.no_self_supply, src/input/ModelInitializer.cpp:58-62,1015-1079 */
+enum {
+    ACC_MP_TRANSPORT_PENALTY_SMALL = 0,
+    ACC_MP_TRANSPORT_PENALTY_LARGE,
+    ACC_MP_MIN_STORAGE,
+    ACC_MP_CHEAPEST_PRICE_RANGE_WIDTH, /* < 0: "auto" */
+    ACC_MP_OPTIMIZATION_MAXITER,
+    ACC_MP_OPTIMIZATION_PRECISION_ADJUSTMENT,
+    ACC_MP_QUADRATIC_TRANSPORT_PENALTY,
+    ACC_MP_RELATIVE_TRANSPORT_PENALTY,
+    ACC_MP_MAX_DECREASE_RESERVATION_PRICE_LIMITED_BY_MARKUP,
+    ACC_MP_DEVIATION_PENALTY,
+    ACC_MP_CHEAPEST_PRICE_RANGE_PRESERVE_SELLER_PRICE,
+    ACC_MP_NO_SELF_SUPPLY,
+    ACC_MP_UTILITARIAN,
+    ACC_MP_DELTA_T,
+    ACC_MP_COUNT
+};
+
+/* order of each row of acc_network.sector_params -- sectors.<name> keys,
+ * src/input/ModelInitializer.cpp:159-185 */
+enum {
+    ACC_SP_UPPER_STORAGE_LIMIT = 0,
+    ACC_SP_INITIAL_STORAGE_FILL_FACTOR,
+    ACC_SP_TRANSPORT_TYPE, /* 0 aviation, 1 immediate, 2 roadsea */
+    ACC_SP_SUPPLY_ELASTICITY,
+    ACC_SP_PRICE_INCREASE_PRODUCTION_EXTENSION,
+    ACC_SP_ESTIMATED_PRICE_INCREASE_PRODUCTION_EXTENSION,
+    ACC_SP_INITIAL_MARKUP,
+    ACC_SP_TARGET_STORAGE_REFILL_TIME,
+    ACC_SP_TARGET_STORAGE_WITHDRAW_TIME,
+    ACC_SP_COUNT
+};
+
+/* Flat snapshot of what the reference's ModelInitializer builds
+ * (src/input/ModelInitializer.cpp:94-213 agents and connections, :689-700 one transport connection
+ * per region pair, :1081-1085 post_initialize).  All arrays are caller-owned and copied. */
+typedef struct {
+    int64_t n_sectors;            /* including the consumer sector (last) */
+    int64_t n_regions;
+    int64_t n_agents;
+    int64_t n_edges;
+    const int64_t* agent_type;    /* 1 firm, 0 consumer */
+    const int64_t* agent_sector;
+    const int64_t* agent_region;
+    const double* agent_beta;     /* firms.<..>.possible_overcapacity_ratio */
+    const int64_t* edge_from;     /* seller agent; edges must be listed seller-major */
+    const int64_t* edge_to;       /* buying agent */
+    const int64_t* edge_zq;       /* initial flow Z* in 1e-3 quanta */
+    const int64_t* delay;         /* [n_regions * n_regions] transport delay between regions, symmetric */
+    const double* sector_params;  /* [n_sectors * ACC_SP_COUNT] */
+    const double* consumer_elasticity; /* [n_sectors] consumers.<..>.consumption_price_elasticity by supplying sector */
+} acc_network;
+
+typedef struct {
+    double model[ACC_MP_COUNT];
+} acc_params;
+
+/* EventType values are the reference's (include/ModelRun.h:39-55) */
+typedef struct {
+    int64_t step;
+    int32_t type;
+    int32_t a;   /* sector index (storage events) or agent index */
+    int32_t b;   /* agent index or -1 */
+    double value;
+} acc_event;
+
+/* replaces Model::Model + ModelInitializer::initialize + Model::start
+ * (include/model/Model.h:62,72; src/ModelRun.cpp:108-116,163-168) */
+acc_engine* acc_create(const acc_network* net, const acc_params* params, int device);
+/* replaces ~Model */
+void acc_destroy(acc_engine* e);
+
+/* replaces EconomicAgent::set_forcing for all agents at once (src/model/EconomicAgent.cpp:43-47);
+ * lambda has n_agents entries */
+int acc_set_agent_forcing(acc_engine* e, const double* lambda, size_t n);
+/* replaces GeoEntity::set_forcing_nu (src/model/GeoEntity.cpp:30-34); nu has one entry per
+ * region pair (i, j < i) at index i*(i-1)/2 + j; nu < 0 means "no forcing" */
+int acc_set_entity_passage(acc_engine* e, const double* nu, size_t n);
+
+/* one timestep = Model::switch_registers + iterate_consumption_and_production + iterate_expectation
+ * + iterate_purchase + iterate_investment + tick (src/ModelRun.cpp:178-190,226-227) */
+int acc_step(acc_engine* e);
+/* the same, split by phase as ModelRun::run calls them */
+enum { ACC_PHASE_CONSUMPTION_AND_PRODUCTION = 0, ACC_PHASE_EXPECTATION = 1, ACC_PHASE_PURCHASE = 2, ACC_PHASE_TICK = 3 };
+int acc_phase(acc_engine* e, int phase);
+/* block until the device has finished all queued phases */
+int acc_sync(acc_engine* e);
+
+/* replaces ModelRun::event (src/ModelRun.cpp:255-275): copies up to cap pending events and clears them */
+int acc_drain_events(acc_engine* e, acc_event* buf, size_t cap, size_t* n);
+
+/* Observable pull, replaces the observe<>() visitor sweep of ArrayOutput::iterate
+ * (src/output/ArrayOutput.cpp:479-646): gathers one variable of one group ("firms", "consumers",
+ * "sectors", "regions", "storages", "flows"; variable names of the reference, Flow/Stock
+ * observables split into <name>_quantity / <name>_value as ArrayOutput.cpp:58-66 does) into dst
+ * as doubles (to_float), shaped like ArrayOutput::Variable::data.  *n receives the element count. */
+int acc_read(acc_engine* e, const char* group, const char* variable, double* dst, size_t cap, size_t* n);
+
+/* Raw state for parity checks: int64 / f64 arrays named like the oracle's per-step dump
+ * (oracle/ref_harness/harness.cpp dump_step).  is_f64 tells which type was written to dst. */
+int acc_read_state(acc_engine* e, const char* name, void* dst, size_t cap_bytes, size_t* n, int* is_f64);
+
+/* counters */
+int64_t acc_edge_count(const acc_engine* e);
+int64_t acc_step_count(const acc_engine* e);
+/* kernels launched since acc_create */
+int64_t acc_launch_count(const acc_engine* e);
+/* CUDA stream the engine launches on (cudaStream_t as void*) */
+void* acc_stream(acc_engine* e);
+/* per-kernel accumulated device time in ms since the last call with reset != 0 (needs acc_profile(e, 1)):
+ * names[i] are static strings, ms[i] / launches[i] the totals; returns the number of kernels */
+int acc_profile(acc_engine* e, int enable);
+int acc_kernel_times(acc_engine* e, const char** names, double* ms, int64_t* launches, int cap, int reset);
+
+const char* acc_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

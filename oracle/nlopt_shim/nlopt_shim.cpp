@@ -130,6 +130,12 @@ struct CallbackEval {
 
 }  // namespace
 
+// whole-run solver statistics (printed by the harness; serial builds only -- not atomic)
+long long g_stat_calls = 0, g_stat_iters = 0, g_stat_evals = 0, g_stat_qp = 0, g_stat_max_iters = 0;
+extern "C" void nlopt_shim_stats(long long* out) {
+    out[0] = g_stat_calls; out[1] = g_stat_iters; out[2] = g_stat_evals; out[3] = g_stat_qp; out[4] = g_stat_max_iters;
+}
+
 extern "C" nlopt_result nlopt_optimize(nlopt_opt opt, double* x, double* opt_f) {
     if (opt->algorithm != NLOPT_LD_SLSQP) {
         opt->errmsg = "nlopt_shim: only NLOPT_LD_SLSQP is provided";
@@ -157,6 +163,8 @@ extern "C" nlopt_result nlopt_optimize(nlopt_opt opt, double* x, double* opt_f) 
     *opt_f = opt->maximize ? -st.minf : st.minf;
     opt->last_iters = st.iters;
     opt->last_evals = st.evals;
+    g_stat_calls += 1; g_stat_iters += st.iters; g_stat_evals += st.evals; g_stat_qp += st.qp_iters;
+    if (st.iters > g_stat_max_iters) g_stat_max_iters = st.iters;
     if (ret == accsqp::SQP_FAILURE) {
         opt->errmsg = "bug: more than iter SQP iterations";  // NLopt's message for Kraft's mode 9
         return NLOPT_FAILURE;

@@ -40,6 +40,8 @@
 #include "nlopt.h"
 #include "openmp.h"
 
+extern "C" void nlopt_shim_stats(long long* out);
+
 // index of each entry in the "model_f64" array of the network file (acclimate_b200/netfile.py)
 enum ModelParamIdx {
     MP_TRANSPORT_PENALTY_SMALL = 0,
@@ -513,6 +515,11 @@ int main(int argc, char** argv) {
         const auto t1 = std::chrono::high_resolution_clock::now();
         run.run();
         const double init_s = std::chrono::duration<double>(t1 - t0).count();
+        if (std::getenv("ORACLE_SOLVER_STATS") != nullptr) {
+            long long st[5];
+            nlopt_shim_stats(st);
+            std::fprintf(stderr, "solver: calls %lld iters %lld evals %lld qp_iters %lld max_iters %lld\n", st[0], st[1], st[2], st[3], st[4]);
+        }
         std::printf("{\"edges\": %zu, \"steps\": %d, \"threads\": %u, \"init_seconds\": %.6f, \"phase_seconds\": %.6f, \"events\": %zu}\n",
                     acclimate::g_init->edges.size(), cfg.steps, run.thread_count(), init_s, acclimate::g_phase_seconds, g_events.size());
         return 0;
