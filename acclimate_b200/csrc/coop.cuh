@@ -159,7 +159,15 @@ struct WarpCtx : CtxOps<WarpCtx> {
         double a = 0.0, b = 0.0;
         __syncwarp();
         if (lane_ == 0) {
-            for (int i = 0; i < n; ++i) { a += f1(i); b += f2(i); }
+            int i = 0;
+            for (; i + 8 <= n; i += 8) {  // operands first (independent shared-memory loads), then the two ordered chains
+                double t[8], u[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { t[j] = f1(i + j); u[j] = f2(i + j); }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { a += t[j]; b += u[j]; }
+            }
+            for (; i < n; ++i) { a += f1(i); b += f2(i); }
         }
         *s1 = __shfl_sync(0xffffffffu, a, 0);
         *s2 = __shfl_sync(0xffffffffu, b, 0);

@@ -178,10 +178,19 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         cx.foreach(nin, [&](int i) { send_D(in_edge(i), (i64)0, (i64)0); });
         return res;
     }
-    // upper limit of one connection, :609-622
-    auto upper_of = [&](int i, double* Xe_out, double* add_out) {
-        const SellerPub sp = pub[in_seller(i)];
+    PMParams pp;
+    pp.Uf = qf(Ustar_q);
+    pp.markup = pf(sec.markup);
+    pp.pen_large = pf(mp.pen_large); pp.pen_small = pf(mp.pen_small);
+    pp.quadratic = mp.quadratic_penalty; pp.relative = mp.relative_penalty; pp.limited_by_markup = mp.limited_by_markup;
+
+    // One gather pass per connection: bounds (:609-650), price-curve constants (:279-289,:323-332) and start value,
+    // written to slot r.  Returns D_r_max; <= 0 means the connection takes no part in the optimisation.
+    auto fill = [&](int i, int r) -> i64 {
         const int e = in_edge(i);
+        const SellerPub sp = pub[in_seller(i)];
+        k.eid[r] = e;
+        if (sp.Xhat_q <= 0) return 0;                                           // :604-605
         const double nu = min_passage(e);
         const double Xe = nu * qf(sp.Xexp_q);                                  // expected_production, :334-341
         const double X = qf(sp.X_q);
@@ -190,48 +199,19 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         const double add = rr * (X - Zl);                                       // expected_additional_production, :343-349
         double Xmax = qf(sp.Xhat_q);
         Xmax *= nu;                                                             // :612-614
-        *Xe_out = Xe; *add_out = add;
-        return Xmax - add;
-    };
-    const int n = cx.compact(nin, [&](int i) {
-        const SellerPub sp = pub[in_seller(i)];
-        if (sp.Xhat_q <= 0) return false;
-        double Xe, add;
-        return mkq(upper_of(i, &Xe, &add)) > 0;
-    }, k.idx);
-    // inactive connections get a zero demand request (:604-605, :646-648)
-    cx.foreach(nin, [&](int i) {
-        const SellerPub sp = pub[in_seller(i)];
-        bool active = sp.Xhat_q > 0;
-        if (active) { double Xe, add; active = mkq(upper_of(i, &Xe, &add)) > 0; }
-        if (!active) send_D(in_edge(i), (i64)0, (i64)0);
-    });
-    if (n == 0) return res;  // :652-655
-
-    PMParams pp;
-    pp.Uf = qf(Ustar_q);
-    pp.markup = pf(sec.markup);
-    pp.pen_large = pf(mp.pen_large); pp.pen_small = pf(mp.pen_small);
-    pp.quadratic = mp.quadratic_penalty; pp.relative = mp.relative_penalty; pp.limited_by_markup = mp.limited_by_markup;
-
-    cx.foreach(n, [&](int r) {
-        const int i = k.idx[r];
-        const int e = in_edge(i);
-        const SellerPub sp = pub[in_seller(i)];
-        double Xe, add;
-        const double upper = upper_of(i, &Xe, &add);
+        const double upper = Xmax - add;
+        const i64 dmax = mkq(upper);                                            // :622
+        if (dmax <= 0) return 0;                                                // :646-648
         const double zf = qf(Z_q[e]);
         const double lamXf = qf(sp.lamX_q);
         const double dnf = pf(sp.dn_est);
         const double nbar = pf(sp.nbar);
-        k.eid[r] = e;
         k.zf[r] = zf;
         k.tgt[r] = mp.deviation_penalty ? qf(lastD_q[e]) : zf;
         k.addX[r] = add;
         k.Xhatf[r] = qf(sp.Xhat_q);
         k.lamXf[r] = lamXf;
         k.dnf[r] = dnf;
-        // n_r constants, :279-289
         const double Dmin = stdmax(0.0, lamXf - add);
         const double Xmin = Dmin + add;
         const double npeE = (Xe > 0.0) ? est_penalty(Xe, lamXf, dnf) / Xe : 0.0;
@@ -241,27 +221,29 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         k.base[r] = (Xe > 0.0) ? nbar - npeE : nbar;
         // calc_n_co, :323-332: marginal costs at the seller's production, n_c un-rounded
         const double ncf = sp.Xhat_v / qf(sp.Xhat_q);
-        const double Xs = qf(sp.X_q);
-        double n_co = (Xs <= lamXf) ? ncf : ncf + est_marginal_penalty(Xs, lamXf, dnf);
-        if (pp.limited_by_markup) {
-            const double n_crit = nbar_min - pp.markup * Dmin;
-            n_co = stdmax(n_co, n_crit);
-        }
+        double n_co = (X <= lamXf) ? ncf : ncf + est_marginal_penalty(X, lamXf, dnf);
+        if (pp.limited_by_markup) n_co = stdmax(n_co, nbar_min - pp.markup * Dmin);
         k.n_co[r] = n_co;
         k.nbar_min[r] = nbar_min;
         k.Dmin[r] = Dmin;
         // bounds, start value, xtol, :620-644
-        const double init_unbound = Xe - add;
-        const double init = stdmin(upper, stdmax(0.0, init_unbound));
         k.xl[r] = 0.0 / zf;
         k.xu[r] = upper / zf;
         k.xtol[r] = (ACC_PREC3 * mp.prec_adj) / zf;
-        k.w.x[r] = init / zf;
+        k.w.x[r] = stdmin(upper, stdmax(0.0, Xe - add)) / zf;
+        return dmax;
+    };
+    cx.foreach(nin, [&](int i) {
+        const i64 dmax = fill(i, i);
+        k.w.d[i] = (double)dmax;  // exact below 2^53 quanta
+        if (dmax <= 0) send_D(k.eid[i], (i64)0, (i64)0);
     });
-    const i64 max_purchase = cx.isum(n, [&](int r) {
-        double Xe, add;
-        return mkq(upper_of(k.idx[r], &Xe, &add));
-    });
+    const int n = cx.compact(nin, [&](int i) { return k.w.d[i] > 0.0; }, k.idx);
+    if (n == 0) return res;  // :652-655
+    if (n != nin) {  // some connections dropped out: rebuild the slots in compacted order (slot r <= source idx[r])
+        cx.foreach(n, [&](int r) { k.w.d[r] = (double)fill(k.idx[r], r); });
+    }
+    const i64 max_purchase = cx.isum(n, [&](int r) { return (i64)k.w.d[r]; });
     if (desired > max_purchase) desired = max_purchase;  // :658-660
 
     // local optimisation, :690-702 with the restart logic of :465-561
@@ -287,8 +269,11 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
     // distribute demand requests, :704-737
     cx.foreach(n, [&](int r) {
         const double D = k.w.x[r] * k.zf[r];
-        const CurvePoint cp = curve_at(k, pp, r, D);
         const i64 q = mkq(D);
+        // with deviation_penalty the penalty target is last_demand_request_D, which the reference has already
+        // overwritten with the new request when it accumulates the costs (:723 before :729-730)
+        if (mp.deviation_penalty) k.tgt[r] = qf(q);
+        const CurvePoint cp = curve_at(k, pp, r, D);
         const i64 p = q > 0 ? mkp(cp.n) : 0;
         send_D(k.eid[r], q, p);
         k.term[r] = cp.n * D + cp.tp;

@@ -229,6 +229,13 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, Work& w, const Params& p, Stats& st) 
         cx.foreach(n, [&](int i) { w.lo[i] = w.xl[i] - w.x[i]; w.hi[i] = w.xu[i] - w.x[i]; });
         double cres = 0.0;
         const double lambda = qp_solve(cx, n, p.ctype, c, w, st, &cres);
+        // Step test (Kraft's convergence test is on the size of the QP step as well): when the full step is below the
+        // x tolerance in every coordinate, no line search result can move x by a tolerance -- stop here instead of
+        // spending evaluations on a step NLopt's xtol rule would discard at the end of the iteration.
+        {
+            const double large = cx.sum(n, [&](int i) { return (fabs(w.d[i]) < w.xtol[i]) ? 0.0 : 1.0; });
+            if (large == 0.0) { ret = SQP_XTOL_REACHED; break; }
+        }
         // gradient of the Lagrangian at the old point with the new multiplier (Kraft: v)
         cx.foreach(n, [&](int i) { w.gl[i] = w.g[i] - lambda * w.a[i]; w.x0[i] = w.x[i]; });
         const double f0 = F;
@@ -250,9 +257,16 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, Work& w, const Params& p, Stats& st) 
             b_identity = true;
             continue;
         }
-        // Kraft's inexact line search
+        // Kraft's inexact line search (Armijo factor 0.1, quadratic interpolation floored at 0.1, at most 10
+        // backtracks).  Every trial is evaluated WITH gradients (nothing reads the old gradient any more: the
+        // Lagrangian gradient at the old point sits in w.gl), so the accepted trial needs no second evaluation.
+        // Kink detection: the purchasing objective has a |D - Z*| term, and at a kinked optimum no step length
+        // satisfies Armijo.  After two failed trials the secant slopes s(A) = (merit(A) - merit(0)) / A are
+        // extrapolated to A = 0; if that estimate of the directional derivative is not negative the step is rejected
+        // at once (x stays at the old point) instead of being shrunk eight more times to the same end.
         int line = 0;
-        double alpha = 1.0;
+        double alpha = 1.0, A = 1.0, A_prev = 0.0, s_prev = 0.0;
+        bool rejected = false;
         for (;;) {
             ++line;
             h3 = alpha * h3;
@@ -264,7 +278,7 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, Work& w, const Params& p, Stats& st) 
                 if (xi > w.xu[i]) xi = w.xu[i];
                 w.x[i] = xi;
             });
-            ev(w.x, false, &F, &c);
+            ev(w.x, true, &F, &c);
             ++st.evals;
             {   // NLopt: keep the best point seen at every evaluation
                 const double vi = con_violation(p.ctype, c);
@@ -278,20 +292,21 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, Work& w, const Params& p, Stats& st) 
             const double tt = F + mu * con_violation(p.ctype, c);
             const double h1 = tt - t0;
             if (h1 <= h3 / 10.0 || line > 10) break;
+            const double s_now = h1 / A;
+            if (line == 2) {
+                const double s0 = s_now - (s_prev - s_now) * A / (A_prev - A);
+                if (!(s0 < 0.0)) { rejected = true; break; }
+            }
+            s_prev = s_now; A_prev = A;
             const double cand = h3 / (2.0 * (h3 - h1));
             alpha = cand > 0.1 ? cand : 0.1;
+            A *= alpha;
         }
         if (ret != SQP_SUCCESS) break;
-        // completed iteration: gradients at the new point (NLopt re-evaluates f with gradient)
-        ev(w.x, true, &F, &c);
-        ++st.evals;
-        {
-            const double vi = con_violation(p.ctype, c);
-            const bool fc = vi <= p.ctol;
-            if ((F < st.minf && (fc || !feasible)) || (!feasible && vi < infeas)) {
-                feasible = fc; infeas = vi; st.minf = F;
-                cx.foreach(n, [&](int i) { w.xbest[i] = w.x[i]; });
-            }
+        if (rejected) {  // x stays at the old point, so NLopt's xtol rule (no coordinate moved) ends the run here
+            cx.foreach(n, [&](int i) { w.x[i] = w.x0[i]; });
+            ret = SQP_XTOL_REACHED;
+            break;
         }
         // NLopt's xtol test between completed iterations
         const double moved = cx.sum(n, [&](int i) { return (fabs(w.x[i] - w.xprev[i]) < w.xtol[i]) ? 0.0 : 1.0; });

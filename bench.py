@@ -1,0 +1,292 @@
+#!/usr/bin/env python
+"""bench.py -- business-connection updates / second of the per-timestep agent iteration.
+
+A "step" is one full model timestep (consumption & production, expectation, purchase, tick) over every
+BusinessConnection of the network.  Workload at N = 1: BASELINE.json configs[1], the EORA-shaped synthetic MRIO
+(187 regions x 26 sectors, dense, ~24.5 M connections), baseline run.  N > 1: one independent scenario of the ensemble per
+GPU (BASELINE.json configs[4] pattern, no data-path collective), reported as weak scaling.
+
+  python bench.py --gpus N --steps K --warmup W            the CUDA engine through its C ABI
+  python bench.py --impl reference ...                      the reference's own model code (oracle/_ref) on the host cores
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BYTES_PER_UPDATE = 160  # SURVEY.md section 8(d) / BASELINE.md section 2: metric-level algorithmic bytes per connection update
+# per-kernel algorithmic bytes per connection (DESIGN.md "Kernels"): what the launch must read + write at least once
+KERNEL_BYTES_PER_EDGE = {"seller_production": 33.0, "storage_delivery": 37.0, "purchase": 37.0}
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fp:
+            p = json.load(fp)
+        return float(p["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    except Exception:
+        return 7700.0 * 0.85, "fallback: 85% of nominal 7.7 TB/s (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.stop_flag = threading.Event()
+        self.sm, self.reasons, self.sm_max = [], set(), None
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_throttle_reasons.hw_slowdown,clocks_throttle_reasons.hw_thermal_slowdown,clocks_throttle_reasons.sw_thermal_slowdown,clocks_throttle_reasons.sw_power_cap"
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                self.sm.append(float(f[0]))
+                self.sm_max = float(f[1])
+                for n, v in zip(names, f[2:]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            self.stop_flag.wait(0.2)
+
+    def result(self):
+        import statistics
+
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons)}
+
+
+def make_network(args, rank):
+    from acclimate_b200 import synth
+
+    if args.config == "eora":
+        net = synth.make_config("eora")
+        workload = "EORA-shaped synthetic MRIO 187x26 dense, baseline run (BASELINE.json configs[1])"
+    elif args.config == "eora_flood":
+        net = synth.make_config("eora_flood")
+        workload = "EORA-shaped synthetic MRIO 187x26 dense, regional production-loss shock (BASELINE.json configs[2])"
+    else:
+        net = synth.make_config("small")
+        workload = "small synthetic MRIO 10x5 (BASELINE.json configs[0])"
+    if rank > 0:  # ensemble member: its own shocked region (configs[4] pattern)
+        R = int(net["meta"][1])
+        synth.add_shock(net, 1, 10 ** 6, (17 * rank) % R, 0.5 + 0.04 * (rank % 8))
+    return net, workload
+
+
+def run_reference(args):
+    """The reference's own CPU implementation (its model code compiled into oracle/_ref) on the host cores."""
+    import numpy as np
+
+    from acclimate_b200 import netfile, synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    exe = os.path.join(ROOT, "oracle", "_ref", "acclimate_ref_omp")
+    cores = os.cpu_count() or 1
+    # bounded sample: the full 187x26 network needs ~15 GB and ~1.5 s per step per 8 cores of object-graph work; use it when
+    # the box can hold it, else a 60x26 cut of the same generator
+    try:
+        mem_gb = os.sysconf("SC_PAGE_SIZE") * os.sysconf("SC_PHYS_PAGES") / 2 ** 30
+    except Exception:
+        mem_gb = 0
+    if args.config == "eora" and mem_gb >= 48 and not args.reference_small:
+        net = synth.make_config("eora")
+        sample = "full 187x26 network"
+    else:
+        net = synth.make_network(regions=60, sectors=26, seed=20260101 + 2)
+        sample = "60x26 cut of the same generator (per-connection cost measured on %d connections)" % int(net["meta"][3])
+    steps = max(1, min(args.steps, args.ref_steps))
+    warm = 1
+    path = "/tmp/acc_bench_ref.acc"
+    netfile.write(path, net)
+    env = dict(os.environ, OMP_NUM_THREADS=str(cores), OMP_PROC_BIND="spread")
+    edges = int(net["meta"][3])
+
+    def run(n):
+        out = subprocess.run([exe, path, str(n)], capture_output=True, text=True, env=env, check=True).stdout
+        return json.loads(out.strip().splitlines()[-1])
+
+    a = run(warm)
+    b = run(warm + steps)
+    secs = max(b["phase_seconds"] - a["phase_seconds"], 1e-9)
+    value = edges * steps / secs
+    line = {
+        "impl": "reference", "metric": "business-connection updates/sec", "value": value, "unit": "updates/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": warm, "ms_per_step": 1e3 * secs / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64+f64",
+        "data": "synthetic", "config": {"workload": "EORA-shaped synthetic MRIO 187x26 dense, baseline run (BASELINE.json configs[1])", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "updates/s", "cores": cores, "kind": "reference", "sample": sample + ", %d timed steps; optimiser = oracle/nlopt_shim SLSQP restatement (NLopt itself is not available offline)" % steps},
+        "e2e": {"value": value, "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def cpu_baseline_sample(seconds_budget=25.0):
+    """oracle/_ref timed on this box's host cores on a bounded sample (rank 0, N = 1 only)."""
+    from acclimate_b200 import netfile, synth
+
+    exe = os.path.join(ROOT, "oracle", "_ref", "acclimate_ref_omp")
+    if not os.path.exists(exe):
+        return None
+    cores = os.cpu_count() or 1
+    net = synth.make_network(regions=40, sectors=26, seed=20260101 + 2)
+    path = "/tmp/acc_bench_cpu.acc"
+    netfile.write(path, net)
+    env = dict(os.environ, OMP_NUM_THREADS=str(cores), OMP_PROC_BIND="spread")
+    edges = int(net["meta"][3])
+
+    def run(n):
+        out = subprocess.run([exe, path, str(n)], capture_output=True, text=True, env=env, check=True).stdout
+        return json.loads(out.strip().splitlines()[-1])
+
+    a = run(1)
+    b = run(4)
+    secs = max(b["phase_seconds"] - a["phase_seconds"], 1e-9)
+    return {"value": edges * 3 / secs, "unit": "updates/s", "cores": cores, "kind": "reference",
+            "sample": "40x26 cut of the same generator (%d connections), 3 timed steps after 1 warm-up, OpenMP on all host cores; optimiser = oracle/nlopt_shim" % edges}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="eora", choices=["eora", "eora_flood", "small"])
+    ap.add_argument("--ref-steps", type=int, default=3)
+    ap.add_argument("--reference-small", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import numpy as np
+    import torch
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the engine has no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    import __graft_entry__ as g
+
+    g.build_cuda()
+    from acclimate_b200 import engine
+
+    net, workload = make_network(args, rank)
+    E = engine.Engine(net, device=local_rank)
+    sc = engine.Scenario(net)
+    n_edges = E.n_edges
+    stream = torch.cuda.ExternalStream(E.stream(), device=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        E.sync()
+
+    step_no = 0
+    for _ in range(args.warmup):
+        sc.apply(E, step_no)
+        E.step()
+        step_no += 1
+    barrier()
+
+    # ---- device-resident throughput: K steps, CUDA events on the engine's stream ----
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    E.profile(True)
+    E.kernel_times(reset=True)
+    launches0 = E.launches
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        E.step()
+        step_no += 1
+    ev1.record(stream)
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = E.launches - launches0
+    ktimes = E.kernel_times(reset=True)
+    E.profile(False)
+
+    # ---- end to end through the C ABI with host buffers: forcing H2D + step + observable D2H every step ----
+    lam = torch.ones(E.n_agents, dtype=torch.float64).pin_memory()
+    out = np.empty(E.n_agents, dtype=np.float64)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        E.set_agent_forcing(lam.numpy())
+        E.step()
+        E.read("firms", "production_quantity", out)
+        step_no += 1
+    E.sync()
+    e2e_s = time.perf_counter() - t0
+    sampler.stop_flag.set()
+    sampler.join()
+
+    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max, e2e_ms_max = float(t[0]), float(t[1])
+    total_updates = n_edges * args.steps * world
+    value = total_updates / (ms_max * 1e-3)
+    e2e_value = total_updates / (e2e_ms_max * 1e-3)
+
+    if rank == 0:
+        peak, peak_src = load_peaks()
+        dom = max(ktimes.items(), key=lambda kv: kv[1][0]) if ktimes else (None, (0.0, 0))
+        roof = None
+        if dom[0] is not None and dom[1][1] > 0:
+            per_launch_s = dom[1][0] * 1e-3 / dom[1][1]
+            bpe = KERNEL_BYTES_PER_EDGE.get(dom[0], BYTES_PER_UPDATE)
+            achieved = bpe * n_edges / per_launch_s / 1e9
+            roof = {"bound": "hbm", "kernel": dom[0], "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                    "algorithmic_bytes_per_connection": bpe, "avg_launch_ms": per_launch_s * 1e3, "peak_source": peak_src,
+                    "kernel_share_of_step": dom[1][0] / max(sum(v[0] for v in ktimes.values()), 1e-12),
+                    "kernels_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items()},
+                    "whole_step_frac_at_160B_per_update": BYTES_PER_UPDATE * n_edges / (ms_max * 1e-3 / args.steps) / 1e9 / peak}
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                cpu = cpu_baseline_sample()
+            except Exception as ex:  # the oracle binary is test infrastructure; the bench line survives without it
+                cpu = {"error": str(ex)}
+        line = {
+            "metric": "business-connection updates/sec", "value": value, "unit": "updates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64+f64", "data": "synthetic",
+            "config": {"workload": workload, "connections_per_gpu": n_edges, "l2": "inputs larger than L2 (%.1f GB of connection state per GPU)" % (n_edges * 100 / 1e9),
+                       "parallelism": "one ensemble member per GPU, no data-path collective" if world > 1 else "single GPU"},
+            "clocks": sampler.result(),
+            "e2e": {"value": e2e_value, "unit": "updates/s", "h2d_bytes_per_step": int(lam.numel() * 8), "d2h_bytes_per_step": int(out.nbytes),
+                    "call": "acc_set_agent_forcing + acc_step + acc_read(firms/production_quantity) per step, host buffers"},
+            "gpu_launches": launches,
+            "roofline": roof,
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line))
+    E.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

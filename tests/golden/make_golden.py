@@ -1,0 +1,62 @@
+"""Generates the golden fixtures of tests/golden/ by running the REFERENCE's own model code
+(oracle/_ref/acclimate_ref, built from /root/reference by oracle/Makefile) on seeded synthetic networks.
+
+Run here (where /root/reference exists):  python tests/golden/make_golden.py
+Each fixture is an ACCARR1 file holding the network snapshot under "net/<name>" and the reference's per-step state
+under "tNNNNN/<name>"; per-connection arrays are kept for demand requests and shipments only, to keep the files small.
+"""
+import os
+import subprocess
+import sys
+import tempfile
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from acclimate_b200 import netfile, synth  # noqa: E402
+
+ORACLE = os.path.join(ROOT, "oracle", "_ref", "acclimate_ref")
+KEEP_EDGE = ("edge_D_q", "edge_D_p", "edge_ship_q")
+
+
+def cases():
+    a = synth.make_config("small")
+    synth.add_shock(a, 2, 6, 3, 0.5)
+    yield "small_shock12", a, 12
+    a = synth.make_network(regions=8, sectors=4, seed=7, max_delay=6)
+    synth.add_shock(a, 3, 12, 2, 0.05)
+    yield "severe_shock30", a, 30
+    a = synth.make_network(regions=8, sectors=4, seed=8, max_delay=5)
+    synth.add_passage(a, 2, 9, 5, 1, 0.3)
+    synth.add_passage(a, 4, 6, 3, 2, 0.0)
+    yield "passage25", a, 25
+    a = synth.make_network(regions=6, sectors=3, seed=9, const_delay=2)
+    synth.add_shock(a, 2, 5, 1, 0.0)
+    yield "outage25", a, 25
+    a = synth.make_network(regions=6, sectors=4, seed=10, const_delay=1,
+                           model=dict(quadratic_transport_penalty=0, relative_transport_penalty=0, cheapest_price_range_width=0.01, min_storage=0.2,
+                                      deviation_penalty=1, maximal_decrease_reservation_price_limited_by_markup=1))
+    synth.add_shock(a, 1, 8, 0, 0.3)
+    yield "flags20", a, 20
+
+
+def main():
+    for name, net, steps in cases():
+        with tempfile.TemporaryDirectory() as tmp:
+            npath, dpath = os.path.join(tmp, "n.acc"), os.path.join(tmp, "d.acc")
+            netfile.write(npath, net)
+            subprocess.run([ORACLE, npath, str(steps), dpath], check=True, stdout=subprocess.DEVNULL)
+            dump = netfile.read(dpath)
+        out = {"net/" + k: v for k, v in net.items()}
+        out["steps"] = [steps]
+        for k, v in dump.items():
+            base = k.split("/")[-1]
+            if base.startswith("edge_") and base not in KEEP_EDGE:
+                continue
+            out[k] = v
+        path = os.path.join(ROOT, "tests", "golden", name + ".acc")
+        netfile.write(path, out)
+        print(name, os.path.getsize(path) // 1024, "KiB")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,66 @@
+"""Shared checker: run an engine over a golden fixture and compare every dumped array with the reference oracle.
+
+Bar (DESIGN.md "Parity"): int64 fields (quantities, prices) bit-exact, including everything downstream of the optimiser;
+f64 values that the reference folds in a replicable order (storage / firm / purchase values) to 1e-12 relative; region sums
+(folded in lock-arrival order by the reference) to 1e-9 relative.
+"""
+import os
+
+import numpy as np
+
+from acclimate_b200 import engine, netfile
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CASES = ["small_shock12", "severe_shock30", "passage25", "outage25", "flags20"]
+
+EXACT_OR_TIGHT = [
+    "edge_D_q", "edge_D_p", "edge_ship_q", "sto_S_q", "sto_S_v", "sto_I_q", "sto_I_v", "sto_U_q", "sto_U_v", "sto_Ut_q", "sto_Ut_v",
+    "sto_demand_q", "sto_demand_v", "sto_expected_costs", "sto_optimized_value", "sto_transport_penalty", "firm_X_q", "firm_X_v", "firm_Xhat_q",
+    "firm_Xhat_p", "firm_Xexp_q", "firm_Xexp_v", "firm_nbar", "firm_costs_C", "firm_revenue_R", "firm_desired_q", "firm_possible_q",
+    "sector_production_q", "sector_production_v", "region_import_q", "region_export_q", "region_consumption_q", "region_consumption_v",
+]
+LOOSE = ["region_import_v", "region_export_v", "region_gdp_v"]
+# the reference's discarded consumer utility optimisation (Consumer.cpp:270) raises these; the engine does not run it
+IGNORED_EVENT_TYPES = {14}
+
+
+def load_case(name):
+    g = netfile.read(os.path.join(GOLDEN_DIR, name + ".acc"))
+    net = {k[4:]: v for k, v in g.items() if k.startswith("net/")}
+    steps = int(g["steps"][0])
+    return net, g, steps
+
+
+def run_case(name, lib_path=None, device=0):
+    net, gold, steps = load_case(name)
+    E = engine.Engine(net, device=device, lib_path=lib_path)
+    sc = engine.Scenario(net)
+    problems = []
+    for t in range(steps):
+        sc.apply(E, t)
+        E.step()
+        pre = "t%05d/" % t
+        for n in EXACT_OR_TIGHT + LOOSE:
+            if pre + n not in gold:
+                continue
+            got, want = E.read_state(n), gold[pre + n]
+            if got.dtype == np.int64:
+                if not np.array_equal(got, want):
+                    i = int(np.nonzero(got != want)[0][0])
+                    problems.append(f"step {t} {n}: {(got != want).sum()} of {got.size} differ, first at {i}: {got[i]} != {want[i]}")
+            else:
+                tol = 1e-9 if n in LOOSE else 1e-12
+                err = np.abs(got - want) / np.maximum(np.abs(want), 1e-300)
+                err[got == want] = 0.0
+                if err.size and err.max() > tol:
+                    i = int(err.argmax())
+                    problems.append(f"step {t} {n}: rel err {err.max():.3e} at {i}: {got[i]!r} != {want[i]!r}")
+        if len(problems) > 10:
+            break
+    ev = sorted((e[0], e[1], e[2], e[3]) for e in E.events())
+    oe = sorted((int(r[0]), int(r[1]), int(r[2]), int(r[3])) for r in gold["events"].reshape(-1, 4) if int(r[1]) not in IGNORED_EVENT_TYPES)
+    if ev != oe:
+        problems.append(f"events differ: engine {len(ev)} reference {len(oe)}; first engine {ev[:3]} reference {oe[:3]}")
+    launches = E.launches
+    E.close()
+    return problems, launches
