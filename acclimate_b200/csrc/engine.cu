@@ -252,7 +252,7 @@ struct Purchase {  // warp per purchasing manager
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int s, unsigned char* smem) const {
         PMWork k;
-        k.carve(smem, n_max);
+        k.carve(smem, n_max, mp.deviation_penalty != 0);
         const i64 o = in_off[s];
         const int nin = (int)(in_off[s + 1] - o);
         const int* ie = in_edge + o;
@@ -459,7 +459,7 @@ struct acc_engine {
     void phase_pur() {
         Purchase k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, pub.p, n_max,
                    s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
-        timed("purchase", [&] { launch_warp(stream, nSt, pm_workspace_bytes(n_max), k); });
+        timed("purchase", [&] { launch_warp(stream, nSt, pm_workspace_bytes(n_max, mp.deviation_penalty != 0), k); });
     }
     void tick() {
         reg = 1 - reg;  // this step's arrivals become the next step's "other" register (Model::switch_registers)

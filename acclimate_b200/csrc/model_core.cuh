@@ -272,12 +272,14 @@ ACC_HD Flow possible_production(const StorageView& st, const int* list, int n_st
 // per-seller record read by every buyer of that seller (SupplyParameters, SalesManager.h:38-43, plus
 // the seller constants the price curve needs)
 struct SellerPub {
-    i64 Xhat_q; double Xhat_v;   // possible_production_X_hat (price = n_c)
-    i64 X_q;                     // production_X quantity
-    i64 Xexp_q;                  // expected_production_X quantity
-    i64 nbar;                    // offer_price_n_bar
-    i64 lamX_q;                  // X* . lambda, quantised (Firm.h:72)
-    i64 dn_est;                  // seller sector's estimated_price_increase_production_extension
+    i64 Xhat_q;       // possible_production_X_hat quantity
+    double Xhatf;     // ... as float
+    double Xf;        // to_float(production_X quantity)
+    double Xexpf;     // to_float(expected_production_X quantity)
+    double nbarf;     // to_float(offer_price_n_bar)
+    double lamXf;     // forced_initial_production_quantity_lambda_X_star_float (Firm.h:73)
+    double c1, c2;    // est. price increase / (2 lamX) and / lamX: the factors of PurchasingManager.cpp:155-156,179-180
+    double n_co;      // estimate_marginal_production_costs at the seller's production with n_c un-rounded (:323-326)
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -554,8 +556,14 @@ ACC_HD void seller_phase2(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
         fv.Xexp_q[f] = X.q; fv.Xexp_v[f] = X.v;
         fv.nbar[f] = nbar;
         SellerPub pb;
-        pb.Xhat_q = fv.Xhat_q[f]; pb.Xhat_v = fv.Xhat_v[f]; pb.X_q = fv.X_q[f]; pb.Xexp_q = X.q; pb.nbar = nbar;
-        pb.lamX_q = lamX; pb.dn_est = sp.dn_est;
+        const Flow xh = mkflow(fv.Xhat_q[f], fv.Xhat_v[f]);
+        pb.Xhat_q = xh.q; pb.Xhatf = qf(xh.q); pb.Xf = qf(fv.X_q[f]); pb.Xexpf = qf(X.q); pb.nbarf = pf(nbar);
+        pb.lamXf = qf(lamX);
+        const double dnf = pf(sp.dn_est);
+        pb.c1 = dnf / (2 * pb.lamXf);
+        pb.c2 = dnf / pb.lamXf;
+        const double ncf = xh.v / qf(xh.q);  // get_price_float(); only read when Xhat_q > 0
+        pb.n_co = (pb.Xf <= pb.lamXf) ? ncf : ncf + pb.c2 * (pb.Xf - pb.lamXf);
         fv.pub[f] = pb;
     }
     // Firm::iterate_expectation, Firm.cpp:65-73: sum_demand_requests_D was zeroed two lines earlier

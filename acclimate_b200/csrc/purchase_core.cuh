@@ -16,29 +16,39 @@
 
 namespace acc {
 
-// workspace of one purchasing manager: NPM_F64 f64 vectors + 2 int vectors of length n_max
-#define ACC_PM_NVEC_F64 25
+// workspace of one purchasing manager: f64 vectors + 2 int vectors of length n_max
+#define ACC_PM_NVEC_F64 21
 #define ACC_PM_NVEC_I32 2
-ACC_HD size_t pm_workspace_bytes(int n_max) { return (size_t)n_max * (ACC_PM_NVEC_F64 * sizeof(double) + ACC_PM_NVEC_I32 * sizeof(int)); }
+ACC_HD size_t pm_workspace_bytes(int n_max, bool separate_target) {
+    return (size_t)n_max * ((ACC_PM_NVEC_F64 + (separate_target ? 1 : 0)) * sizeof(double) + ACC_PM_NVEC_I32 * sizeof(int));
+}
 
 struct PMWork {
-    accsqp::Work w;
-    double *xl, *xu, *xtol;  // bounds and tolerances (w.xl/xu/xtol point here)
+    accsqp::Work w;          // x, x0, g, a, d, b, gl, xbest
+    double *xu, *xtol;       // upper bounds and tolerances (lower bounds are all zero, :620)
     // price-curve constants per purchasing connection
-    double *zf, *tgt, *addX, *Xhatf, *lamXf, *dnf, *base, *n_co, *nbar_min, *Dmin;
-    double* term;  // per-connection summand of the current evaluation
-    int *idx, *eid;  // compacted position -> incoming position, connection id
-    ACC_HD void carve(unsigned char* mem, int n_max) {
+    double *zf;              // to_float(Z*): scale of the variable (:184-188)
+    double *tgt;             // transport penalty target (Z*, or the last demand request with deviation_penalty)
+    double *addX;            // expected_additional_production (:343-349)
+    double *Xhatf, *lamXf, *c1, *c2;  // seller constants (SellerPub)
+    double *base;            // n_bar [- pen(X_exp)/X_exp]: E_n_r without its X_new term (:255-271)
+    double *n_co, *Dmin;     // reservation price and kink position of the price curve (:283-289)
+    double *slope;           // (n_bar_min - n_co) / D_r_min in the linear regime; NaN marks the cropped regime (n_co > n_bar_min)
+    double *term;            // per-connection summand of the current evaluation
+    int *idx, *eid;          // compacted position -> incoming position, connection id
+    ACC_HD void carve(unsigned char* mem, int n_max, bool separate_target) {
         double* p = reinterpret_cast<double*>(mem);
         w.x = p; p += n_max; w.x0 = p; p += n_max; w.g = p; p += n_max; w.a = p; p += n_max; w.d = p; p += n_max; w.b = p; p += n_max;
-        w.lo = p; p += n_max; w.hi = p; p += n_max; w.gl = p; p += n_max; w.xbest = p; p += n_max; w.xprev = p; p += n_max;
-        xl = p; p += n_max; xu = p; p += n_max; xtol = p; p += n_max;
-        zf = p; p += n_max; tgt = p; p += n_max; addX = p; p += n_max; Xhatf = p; p += n_max; lamXf = p; p += n_max; dnf = p; p += n_max;
-        base = p; p += n_max; n_co = p; p += n_max; nbar_min = p; p += n_max; Dmin = p; p += n_max;
+        w.gl = p; p += n_max; w.xbest = p; p += n_max;
+        xu = p; p += n_max; xtol = p; p += n_max;
+        zf = p; p += n_max; addX = p; p += n_max; Xhatf = p; p += n_max; lamXf = p; p += n_max; c1 = p; p += n_max; c2 = p; p += n_max;
+        base = p; p += n_max; n_co = p; p += n_max; Dmin = p; p += n_max; slope = p; p += n_max;
         term = p; p += n_max;
+        tgt = zf;  // the penalty target is Z* itself unless deviation_penalty is set
+        if (separate_target) { tgt = p; p += n_max; }
         int* q = reinterpret_cast<int*>(p);
         idx = q; q += n_max; eid = q;
-        w.xl = xl; w.xu = xu; w.xtol = xtol;
+        w.xl = nullptr; w.xu = xu; w.xtol = xtol;
     }
 };
 
@@ -49,18 +59,10 @@ struct PMParams {
     int quadratic, relative, limited_by_markup;
 };
 
-// estimate_production_extension_penalty, :149-159
-ACC_HD double est_penalty(double x, double lamXf, double dnf) {
-    if (x <= lamXf) return 0.0;
-    return stdmax(0.0, dnf / (2 * lamXf) * (x - lamXf) * (x - lamXf));
-}
-// estimate_marginal_production_extension_penalty, :173-182
-ACC_HD double est_marginal_penalty(double x, double lamXf, double dnf) {
-    if (x <= lamXf) return 0.0;
-    return dnf / lamXf * (x - lamXf);
-}
-
-// n_r, grad_n_r, transport_penalty, partial_D_r_transport_penalty for connection r at demand D
+// n_r, grad_n_r, transport_penalty, partial_D_r_transport_penalty for connection r at demand D.
+// Same expressions as the reference, with two exact shortcuts: constant sub-expressions (dn/(2 lamX), dn/lamX,
+// the linear-regime slope) are computed once per connection, and 0/X_new terms (no production extension) are not
+// divided out (0.0 / x == 0.0 and base + 0.0 == base bit for bit).
 struct CurvePoint {
     double n, gn, tp, tpp;
 };
@@ -71,21 +73,24 @@ ACC_HD CurvePoint curve_at(const PMWork& k, const PMParams& pp, int r, double D)
     if (Xn > k.Xhatf[r]) Xn = k.Xhatf[r];
     double E = k.base[r];
     double gE = 0.0;
-    if (Xn > 0.0) {
-        const double pen = est_penalty(Xn, k.lamXf[r], k.dnf[r]);
+    const double lam = k.lamXf[r];
+    if (Xn > lam && Xn > 0.0) {  // in production extension (:151,:175)
+        const double dx = Xn - lam;
+        const double pen = stdmax(0.0, k.c1[r] * dx * dx);
         E = k.base[r] + pen / Xn;
-        gE = est_marginal_penalty(Xn, k.lamXf[r], k.dnf[r]) / Xn - pen / Xn / Xn;
+        gE = k.c2[r] * dx / Xn - pen / Xn / Xn;
     }
     // n_r (:277-303), grad_n_r (:351-379)
-    if (k.n_co[r] <= k.nbar_min[r]) {
+    const double sl = k.slope[r];
+    if (sl == sl) {  // n_co <= n_bar_min: linear regime below D_r_min
         if (D < k.Dmin[r]) {
-            c.n = k.n_co[r] + (k.nbar_min[r] - k.n_co[r]) / k.Dmin[r] * D;
-            c.gn = (k.Dmin[r] > 0.0) ? (k.nbar_min[r] - k.n_co[r]) / k.Dmin[r] : gE;
+            c.n = k.n_co[r] + sl * D;
+            c.gn = sl;
         } else {
             c.n = E;
             c.gn = gE;
         }
-    } else if (E <= k.n_co[r]) {
+    } else if (E <= k.n_co[r]) {  // curve cropped from below with n_co
         c.n = k.n_co[r];
         c.gn = 0.0;
     } else {
@@ -99,8 +104,9 @@ ACC_HD CurvePoint curve_at(const PMWork& k, const PMParams& pp, int r, double D)
         if (D < t) marg = -pp.markup; else if (D > t) marg = pp.markup;
         if (pp.relative) {
             if (t > ACC_PREC3) {
-                c.tp = (D - t) * ((D - t) * pp.pen_large / (t * t) / 2 + marg);
-                c.tpp = (D - t) * pp.pen_large / (t * t) + marg;
+                const double qd = (D - t) * pp.pen_large / (t * t);  // shared by both expressions of the reference
+                c.tp = (D - t) * (qd / 2 + marg);
+                c.tpp = qd + marg;
             } else {
                 // to_float(transport_penalty_large / 2 + Price(marg_penalty)): typed Price arithmetic
                 c.tp = D * D * pf(pdiv(mkp(pp.pen_large), 2.0) + mkp(marg));
@@ -127,7 +133,7 @@ ACC_HD CurvePoint curve_at(const PMWork& k, const PMParams& pp, int r, double D)
 }
 
 // Objective / constraint evaluation in the convention of sqp_core: minimise F = costs / U*,
-// constraint c = (desired - sum D_r) / U* == 0.
+// constraint c = (desired - sum D_r) / U* == 0 whose gradient -Z*_r / U* is constant (filled once).
 template <class Ctx>
 struct PMEval {
     Ctx& cx;
@@ -142,10 +148,7 @@ struct PMEval {
             const double D = x[r] * kk.zf[r];
             const CurvePoint cp = curve_at(kk, p, r, D);
             kk.term[r] = cp.n * D + cp.tp;
-            if (want_grad) {
-                kk.w.g[r] = (kk.zf[r] * (cp.gn * D + cp.n + cp.tpp)) / p.Uf;
-                kk.w.a[r] = -(kk.zf[r] / p.Uf);
-            }
+            if (want_grad) kk.w.g[r] = (kk.zf[r] * (cp.gn * D + cp.n + cp.tpp)) / p.Uf;
         });
         double costs, use;
         cx.seqsum2(n, [&](int r) { return kk.term[r]; }, [&](int r) { return x[r] * kk.zf[r]; }, &costs, &use);
@@ -192,45 +195,44 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         k.eid[r] = e;
         if (sp.Xhat_q <= 0) return 0;                                           // :604-605
         const double nu = min_passage(e);
-        const double Xe = nu * qf(sp.Xexp_q);                                  // expected_production, :334-341
-        const double X = qf(sp.X_q);
+        const double Xe = nu * sp.Xexpf;                                        // expected_production, :334-341
+        const double X = sp.Xf;
         const double Zl = qf(last_ship(e));
         const double rr = (X > 0.0) ? Xe / X : 0.0;
         const double add = rr * (X - Zl);                                       // expected_additional_production, :343-349
-        double Xmax = qf(sp.Xhat_q);
+        double Xmax = sp.Xhatf;
         Xmax *= nu;                                                             // :612-614
         const double upper = Xmax - add;
         const i64 dmax = mkq(upper);                                            // :622
         if (dmax <= 0) return 0;                                                // :646-648
         const double zf = qf(Z_q[e]);
-        const double lamXf = qf(sp.lamX_q);
-        const double dnf = pf(sp.dn_est);
-        const double nbar = pf(sp.nbar);
+        const double lamXf = sp.lamXf;
         k.zf[r] = zf;
-        k.tgt[r] = mp.deviation_penalty ? qf(lastD_q[e]) : zf;
+        if (mp.deviation_penalty) k.tgt[r] = qf(lastD_q[e]);
         k.addX[r] = add;
-        k.Xhatf[r] = qf(sp.Xhat_q);
+        k.Xhatf[r] = sp.Xhatf;
         k.lamXf[r] = lamXf;
-        k.dnf[r] = dnf;
+        k.c1[r] = sp.c1;
+        k.c2[r] = sp.c2;
+        // n_r constants, :279-289 (penalty terms only divided out inside the production extension)
         const double Dmin = stdmax(0.0, lamXf - add);
         const double Xmin = Dmin + add;
-        const double npeE = (Xe > 0.0) ? est_penalty(Xe, lamXf, dnf) / Xe : 0.0;
-        const double npeMin = (Xmin > 0.0) ? est_penalty(Xmin, lamXf, dnf) / Xmin : 0.0;
-        const double nbar_min = nbar - npeE + npeMin;
+        double npeE = 0.0, npeMin = 0.0;
+        if (Xe > lamXf && Xe > 0.0) npeE = stdmax(0.0, sp.c1 * (Xe - lamXf) * (Xe - lamXf)) / Xe;
+        if (Xmin > lamXf && Xmin > 0.0) npeMin = stdmax(0.0, sp.c1 * (Xmin - lamXf) * (Xmin - lamXf)) / Xmin;
+        const double nbar_min = sp.nbarf - npeE + npeMin;
         // E_n_r's four cases collapse to  base [+ pen(X_new)/X_new]  with base = n_bar [- pen(X_exp)/X_exp]
-        k.base[r] = (Xe > 0.0) ? nbar - npeE : nbar;
-        // calc_n_co, :323-332: marginal costs at the seller's production, n_c un-rounded
-        const double ncf = sp.Xhat_v / qf(sp.Xhat_q);
-        double n_co = (X <= lamXf) ? ncf : ncf + est_marginal_penalty(X, lamXf, dnf);
+        k.base[r] = (Xe > 0.0) ? sp.nbarf - npeE : sp.nbarf;
+        double n_co = sp.n_co;                                                  // calc_n_co, :323-332
         if (pp.limited_by_markup) n_co = stdmax(n_co, nbar_min - pp.markup * Dmin);
         k.n_co[r] = n_co;
-        k.nbar_min[r] = nbar_min;
         k.Dmin[r] = Dmin;
-        // bounds, start value, xtol, :620-644
-        k.xl[r] = 0.0 / zf;
+        k.slope[r] = (n_co <= nbar_min) ? (nbar_min - n_co) / Dmin : (double)NAN;
+        // bounds, start value, xtol, :620-644; constraint gradient, :209
         k.xu[r] = upper / zf;
         k.xtol[r] = (ACC_PREC3 * mp.prec_adj) / zf;
         k.w.x[r] = stdmin(upper, stdmax(0.0, Xe - add)) / zf;
+        k.w.a[r] = -(zf / pp.Uf);
         return dmax;
     };
     cx.foreach(nin, [&](int i) {
@@ -279,11 +281,12 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         k.term[r] = cp.n * D + cp.tp;
         k.w.d[r] = cp.tp;
         k.w.g[r] = q > 0 ? q_times_p(q, p) : 0.0;
+        k.w.b[r] = (double)q;
     });
     double costs, pen, dv, dummy;
     cx.seqsum2(n, [&](int r) { return k.term[r]; }, [&](int r) { return k.w.d[r]; }, &costs, &pen);
     cx.seqsum2(n, [&](int r) { return k.w.g[r]; }, [&](int) { return 0.0; }, &dv, &dummy);
-    const i64 dq = cx.isum(n, [&](int r) { return mkq(k.w.x[r] * k.zf[r]); });
+    const i64 dq = cx.isum(n, [&](int r) { return (i64)k.w.b[r]; });
     res.demand = mkflow(dq, dv);
     res.expected_costs = costs;
     res.penalty = pen;

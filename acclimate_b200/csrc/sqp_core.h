@@ -60,10 +60,14 @@ struct Params {
 
 struct Work {
     // length-n vectors
-    double *x, *x0, *g, *a, *d, *b, *lo, *hi, *gl, *xbest, *xprev;
+    double *x, *x0, *g, *a, *d, *b, *gl, *xbest;
     const double *xl, *xu, *xtol;
 };
-#define ACCSQP_NVEC 11  // number of length-n work vectors above
+#define ACCSQP_NVEC 8  // number of length-n work vectors above
+// lower bounds may be omitted (null pointer = all zero); step bounds are derived where they are used
+#define ACCSQP_XL(w, i) ((w).xl != nullptr ? (w).xl[i] : 0.0)
+#define ACCSQP_LO(w, i) (ACCSQP_XL(w, i) - (w).x[i])
+#define ACCSQP_HI(w, i) ((w).xu[i] - (w).x[i])
 
 struct Stats {
     int iters;
@@ -86,36 +90,36 @@ SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, Work& w, Stats& st, 
     if (ctype == CON_NONE) {
         cx.foreach(n, [&](int i) {
             const double t = -w.g[i] / w.b[i];
-            w.d[i] = t < w.lo[i] ? w.lo[i] : (t > w.hi[i] ? w.hi[i] : t);
+            w.d[i] = t < ACCSQP_LO(w, i) ? ACCSQP_LO(w, i) : (t > ACCSQP_HI(w, i) ? ACCSQP_HI(w, i) : t);
         });
         *cres = 0.0;
         return 0.0;
     }
     const double target = -c;  // want a^T d = target
     // attainable range of a^T d over the box
-    const double smin = cx.sum(n, [&](int i) { const double p = w.a[i] * w.lo[i], q = w.a[i] * w.hi[i]; return p < q ? p : q; });
-    const double smax = cx.sum(n, [&](int i) { const double p = w.a[i] * w.lo[i], q = w.a[i] * w.hi[i]; return p > q ? p : q; });
+    const double smin = cx.sum(n, [&](int i) { const double p = w.a[i] * ACCSQP_LO(w, i), q = w.a[i] * ACCSQP_HI(w, i); return p < q ? p : q; });
+    const double smax = cx.sum(n, [&](int i) { const double p = w.a[i] * ACCSQP_LO(w, i), q = w.a[i] * ACCSQP_HI(w, i); return p > q ? p : q; });
     int forced = 0;  // -1: push a^T d to its minimum, +1: to its maximum
     if (ctype == CON_EQ && target <= smin) forced = -1;
     else if (target >= smax) forced = 1;
     if (forced != 0) {
         // vertex of the box; multiplier = the extreme ratio that keeps every bound multiplier sign-feasible
         cx.foreach(n, [&](int i) {
-            const double p = w.a[i] * w.lo[i], q = w.a[i] * w.hi[i];
-            w.d[i] = (forced > 0) ? (p >= q ? w.lo[i] : w.hi[i]) : (p <= q ? w.lo[i] : w.hi[i]);
+            const double p = w.a[i] * ACCSQP_LO(w, i), q = w.a[i] * ACCSQP_HI(w, i);
+            w.d[i] = (forced > 0) ? (p >= q ? ACCSQP_LO(w, i) : ACCSQP_HI(w, i)) : (p <= q ? ACCSQP_LO(w, i) : ACCSQP_HI(w, i));
         });
         const double big = 1e300;
         // need  (b d + g)_i - lambda a_i <= 0 where d sits at hi,  >= 0 where it sits at lo
         const double lmin = cx.vmax(n, [&](int i) {
-            if (w.a[i] == 0.0 || w.lo[i] == w.hi[i]) return -big;
-            const bool at_hi = (w.d[i] == w.hi[i]);
+            if (w.a[i] == 0.0 || ACCSQP_LO(w, i) == ACCSQP_HI(w, i)) return -big;
+            const bool at_hi = (w.d[i] == ACCSQP_HI(w, i));
             const double r = (w.b[i] * w.d[i] + w.g[i]) / w.a[i];
             if (at_hi) return (w.a[i] > 0.0) ? r : -big;
             return (w.a[i] < 0.0) ? r : -big;
         });
         const double lmax = cx.vmin(n, [&](int i) {
-            if (w.a[i] == 0.0 || w.lo[i] == w.hi[i]) return big;
-            const bool at_hi = (w.d[i] == w.hi[i]);
+            if (w.a[i] == 0.0 || ACCSQP_LO(w, i) == ACCSQP_HI(w, i)) return big;
+            const bool at_hi = (w.d[i] == ACCSQP_HI(w, i));
             const double r = (w.b[i] * w.d[i] + w.g[i]) / w.a[i];
             if (at_hi) return (w.a[i] < 0.0) ? r : big;
             return (w.a[i] > 0.0) ? r : big;
@@ -143,13 +147,13 @@ SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, Work& w, Stats& st, 
         // psi and its slope at lambda
         const double psi = c + cx.sum(n, [&](int i) {
             const double t = (-w.g[i] + lambda * w.a[i]) / w.b[i];
-            const double di = t < w.lo[i] ? w.lo[i] : (t > w.hi[i] ? w.hi[i] : t);
+            const double di = t < ACCSQP_LO(w, i) ? ACCSQP_LO(w, i) : (t > ACCSQP_HI(w, i) ? ACCSQP_HI(w, i) : t);
             return w.a[i] * di;
         });
         if (it == 0 && ctype == CON_INEQ && psi >= 0.0) { converged = true; break; }  // constraint inactive
         const double slope = cx.sum(n, [&](int i) {
             const double t = (-w.g[i] + lambda * w.a[i]) / w.b[i];
-            return (t > w.lo[i] && t < w.hi[i]) ? w.a[i] * w.a[i] / w.b[i] : 0.0;
+            return (t > ACCSQP_LO(w, i) && t < ACCSQP_HI(w, i)) ? w.a[i] * w.a[i] / w.b[i] : 0.0;
         });
         if (fabs(psi) <= psi_tol) { converged = true; break; }
         if (psi < 0.0) { lamL = lambda; haveL = true; } else { lamR = lambda; haveR = true; }
@@ -176,7 +180,7 @@ SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, Work& w, Stats& st, 
     if (!converged) st.qp_inexact += 1;
     cx.foreach(n, [&](int i) {
         const double t = (-w.g[i] + lambda * w.a[i]) / w.b[i];
-        w.d[i] = t < w.lo[i] ? w.lo[i] : (t > w.hi[i] ? w.hi[i] : t);
+        w.d[i] = t < ACCSQP_LO(w, i) ? ACCSQP_LO(w, i) : (t > ACCSQP_HI(w, i) ? ACCSQP_HI(w, i) : t);
     });
     *cres = c + cx.sum(n, [&](int i) { return w.a[i] * w.d[i]; });
     return lambda;
@@ -203,7 +207,7 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, Work& w, const Params& p, Stats& st) 
     // NLopt clips the start point into the box
     cx.foreach(n, [&](int i) {
         double xi = w.x[i];
-        if (xi < w.xl[i]) xi = w.xl[i];
+        if (xi < ACCSQP_XL(w, i)) xi = ACCSQP_XL(w, i);
         if (xi > w.xu[i]) xi = w.xu[i];
         w.x[i] = xi;
         w.b[i] = 1.0;
@@ -215,7 +219,7 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, Work& w, const Params& p, Stats& st) 
     bool feasible = viol <= p.ctol;
     double infeas = viol;
     st.minf = F;
-    cx.foreach(n, [&](int i) { w.xbest[i] = w.x[i]; w.xprev[i] = w.x[i]; });
+    cx.foreach(n, [&](int i) { w.xbest[i] = w.x[i]; });
 
     bool b_identity = true;
     double mu = 0.0;      // merit penalty parameter
@@ -226,7 +230,6 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, Work& w, const Params& p, Stats& st) 
         ++st.iters;
         if (p.max_iter > 0 && st.iters > p.max_iter) { ret = SQP_FAILURE; break; }
         // bounds on the step
-        cx.foreach(n, [&](int i) { w.lo[i] = w.xl[i] - w.x[i]; w.hi[i] = w.xu[i] - w.x[i]; });
         double cres = 0.0;
         const double lambda = qp_solve(cx, n, p.ctype, c, w, st, &cres);
         // Step test (Kraft's convergence test is on the size of the QP step as well): when the full step is below the
@@ -274,7 +277,7 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, Work& w, const Params& p, Stats& st) 
                 const double si = alpha * w.d[i];
                 w.d[i] = si;
                 double xi = w.x0[i] + si;
-                if (xi < w.xl[i]) xi = w.xl[i];
+                if (xi < ACCSQP_XL(w, i)) xi = ACCSQP_XL(w, i);
                 if (xi > w.xu[i]) xi = w.xu[i];
                 w.x[i] = xi;
             });
@@ -309,8 +312,7 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, Work& w, const Params& p, Stats& st) 
             break;
         }
         // NLopt's xtol test between completed iterations
-        const double moved = cx.sum(n, [&](int i) { return (fabs(w.x[i] - w.xprev[i]) < w.xtol[i]) ? 0.0 : 1.0; });
-        cx.foreach(n, [&](int i) { w.xprev[i] = w.x[i]; });
+        const double moved = cx.sum(n, [&](int i) { return (fabs(w.x[i] - w.x0[i]) < w.xtol[i]) ? 0.0 : 1.0; });
         if (moved == 0.0) { ret = SQP_XTOL_REACHED; break; }
         if (p.maxeval > 0 && st.evals >= p.maxeval) { ret = SQP_MAXEVAL_REACHED; break; }
         // per-coordinate secant update of the diagonal Hessian model

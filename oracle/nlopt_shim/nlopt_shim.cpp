@@ -147,7 +147,7 @@ extern "C" nlopt_result nlopt_optimize(nlopt_opt opt, double* x, double* opt_f) 
     double* q = buf.data();
     accsqp::Work w;
     w.x = q; q += n; w.x0 = q; q += n; w.g = q; q += n; w.a = q; q += n; w.d = q; q += n; w.b = q; q += n;
-    w.lo = q; q += n; w.hi = q; q += n; w.gl = q; q += n; w.xbest = q; q += n; w.xprev = q; q += n;
+    w.gl = q; q += n; w.xbest = q; q += n;
     w.xl = opt->lb.data();
     w.xu = opt->ub.data();
     w.xtol = opt->xtol.data();
