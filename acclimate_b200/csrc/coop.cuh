@@ -75,6 +75,10 @@ struct HostCtx : CtxOps<HostCtx> {
     inline int lane() const { return 0; }
     template <class F>
     inline void foreach(int n, F f) const { for (int i = 0; i < n; ++i) f(i); }
+    // element loop that also names the per-lane slot of the element; contexts without unrolling have one slot
+    enum { SLOTS = 1 };
+    template <class F>
+    inline void foreach_slot(int n, F f) const { for (int i = 0; i < n; ++i) f(i, 0); }
     template <class T, class F>
     inline T reduce(int n, F f) const {
         const int W = G / 32;
@@ -135,21 +139,46 @@ __device__ __forceinline__ T shfl_any(const T& v, int src_lane) {
     return r;
 }
 
-struct WarpCtx : CtxOps<WarpCtx> {
+// One warp per item.  KMAX > 0 promises n <= 32 * KMAX: every element loop is fully unrolled over the KMAX slots of a
+// lane (element i = lane + 32 k), which lets per-lane vectors live in registers (LaneVec below) and gives the
+// scheduler KMAX independent dependency chains per lane.  KMAX == 0 is the general strided loop.
+template <int KMAX>
+struct WarpCtxT : CtxOps<WarpCtxT<KMAX> > {
     int lane_;
-    __device__ WarpCtx() : lane_(threadIdx.x & 31) {}
+    __device__ WarpCtxT() : lane_(threadIdx.x & 31) {}
     __device__ __forceinline__ bool leader() const { return lane_ == 0; }
     __device__ __forceinline__ void sync() const { __syncwarp(); }
     __device__ __forceinline__ int lane() const { return lane_; }
     template <class F>
     __device__ __forceinline__ void foreach(int n, F f) const {
-        for (int i = lane_; i < n; i += 32) f(i);
+        if (KMAX > 0) {
+#pragma unroll
+            for (int k = 0; k < (KMAX > 0 ? KMAX : 1); ++k) { const int i = lane_ + 32 * k; if (i < n) f(i); }
+        } else {
+            for (int i = lane_; i < n; i += 32) f(i);
+        }
+        __syncwarp();
+    }
+    enum { SLOTS = KMAX > 0 ? KMAX : 1 };
+    template <class F>
+    __device__ __forceinline__ void foreach_slot(int n, F f) const {
+        if (KMAX > 0) {
+#pragma unroll
+            for (int k = 0; k < (KMAX > 0 ? KMAX : 1); ++k) { const int i = lane_ + 32 * k; if (i < n) f(i, k); }
+        } else {
+            for (int i = lane_; i < n; i += 32) f(i, 0);
+        }
         __syncwarp();
     }
     template <class T, class F>
     __device__ __forceinline__ T reduce(int n, F f) const {
         T acc_ = T::identity();
-        for (int i = lane_; i < n; i += 32) acc_ = T::combine(acc_, f(i));
+        if (KMAX > 0) {
+#pragma unroll
+            for (int k = 0; k < (KMAX > 0 ? KMAX : 1); ++k) { const int i = lane_ + 32 * k; if (i < n) acc_ = T::combine(acc_, f(i)); }
+        } else {
+            for (int i = lane_; i < n; i += 32) acc_ = T::combine(acc_, f(i));
+        }
 #pragma unroll
         for (int off = 16; off >= 1; off >>= 1) acc_ = T::combine(acc_, shfl_xor_any(acc_, off));
         return acc_;
@@ -175,17 +204,29 @@ struct WarpCtx : CtxOps<WarpCtx> {
     template <class Pred>
     __device__ __forceinline__ int compact(int n, Pred pred, int* out) const {
         int m = 0;
-        for (int base = 0; base < n; base += 32) {
-            const int i = base + lane_;
-            const bool keep = i < n && pred(i);
-            const unsigned mask = __ballot_sync(0xffffffffu, keep);
-            if (keep) out[m + __popc(mask & ((1u << lane_) - 1u))] = i;
-            m += __popc(mask);
+        if (KMAX > 0) {
+#pragma unroll
+            for (int k = 0; k < (KMAX > 0 ? KMAX : 1); ++k) {
+                const int i = lane_ + 32 * k;
+                const bool keep = i < n && pred(i);
+                const unsigned mask = __ballot_sync(0xffffffffu, keep);
+                if (keep) out[m + __popc(mask & ((1u << lane_) - 1u))] = i;
+                m += __popc(mask);
+            }
+        } else {
+            for (int base = 0; base < n; base += 32) {
+                const int i = base + lane_;
+                const bool keep = i < n && pred(i);
+                const unsigned mask = __ballot_sync(0xffffffffu, keep);
+                if (keep) out[m + __popc(mask & ((1u << lane_) - 1u))] = i;
+                m += __popc(mask);
+            }
         }
         __syncwarp();
         return m;
     }
 };
+typedef WarpCtxT<0> WarpCtx;
 
 // A CTA working on one item.  `scratch` is shared memory with room for 33 payloads of the largest
 // reduction type used (ACC_BLOCK_SCRATCH_BYTES).

@@ -69,6 +69,8 @@ static void launch_warp(stream_t, int n, size_t smem, K k) {
     std::vector<unsigned char> sm(smem + 16);
     for (int i = 0; i < n; ++i) { HostCtx cx(32); k(cx, i, sm.data()); }
 }
+template <int KMAX, class K>
+static void launch_warp_k(stream_t s, int n, size_t smem, K k) { launch_warp(s, n, smem, k); }
 #else
 typedef cudaStream_t stream_t;
 #define ACC_CUDA(x)                                                                                   \
@@ -101,10 +103,10 @@ __global__ void __launch_bounds__(256) block_kernel(K k) {
     BlockCtx cx(scratch);
     k(cx, (int)blockIdx.x);
 }
-template <class K>
+template <int KMAX, class K>
 __global__ void __launch_bounds__(32) warp_kernel(K k) {
     extern __shared__ __align__(16) unsigned char dyn_smem[];
-    WarpCtx cx;
+    WarpCtxT<KMAX> cx;
     k(cx, (int)blockIdx.x, dyn_smem);
 }
 template <class K>
@@ -119,17 +121,19 @@ static void launch_block(stream_t s, int n, int threads, K k) {
     block_kernel<K><<<n, threads, 0, s>>>(k);
     ACC_CUDA(cudaGetLastError());
 }
-template <class K>
-static void launch_warp(stream_t s, int n, size_t smem, K k) {
+template <int KMAX, class K>
+static void launch_warp_k(stream_t s, int n, size_t smem, K k) {
     if (n <= 0) return;
     static size_t configured = 0;
     if (smem > configured) {
-        ACC_CUDA(cudaFuncSetAttribute(warp_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ACC_CUDA(cudaFuncSetAttribute(warp_kernel<KMAX, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    warp_kernel<K><<<n, 32, smem, s>>>(k);
+    warp_kernel<KMAX, K><<<n, 32, smem, s>>>(k);
     ACC_CUDA(cudaGetLastError());
 }
+template <class K>
+static void launch_warp(stream_t s, int n, size_t smem, K k) { launch_warp_k<0, K>(s, n, smem, k); }
 #endif
 
 template <class T>
@@ -245,13 +249,23 @@ struct StorageDelivery {  // thread per storage
     }
 };
 
+// solver work vectors: registers of the owning lane under an unrolled warp context, memory otherwise
+template <class Ctx>
+struct WorkFor { typedef PMWorkT<PtrVec> type; };
+#ifndef ACC_HOST_EMU
+template <int KMAX>
+struct WorkFor<WarpCtxT<KMAX> > { typedef PMWorkT<LaneVec<KMAX> > type; };
+template <>
+struct WorkFor<WarpCtxT<0> > { typedef PMWorkT<PtrVec> type; };
+#endif
+
 struct Purchase {  // warp per purchasing manager
     StorageView st; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
     const i64* in_off; const int* in_edge; const int* in_seller; const SellerPub* pub; int n_max;
     i64* dem_q; double* dem_v; double* exp_costs; double* opt_val; double* tpen; int* iters; int* evals;
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int s, unsigned char* smem) const {
-        PMWork k;
+        typename WorkFor<Ctx>::type k;
         k.carve(smem, n_max, mp.deviation_penalty != 0);
         const i64 o = in_off[s];
         const int nin = (int)(in_off[s + 1] - o);
@@ -459,7 +473,17 @@ struct acc_engine {
     void phase_pur() {
         Purchase k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, pub.p, n_max,
                    s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
-        timed("purchase", [&] { launch_warp(stream, nSt, pm_workspace_bytes(n_max, mp.deviation_penalty != 0), k); });
+        const bool dev = mp.deviation_penalty != 0;
+        timed("purchase", [&] {
+            // register-resident solver state when every purchasing manager has at most 192 connections
+#ifdef ACC_HOST_EMU
+            launch_warp(stream, nSt, pm_workspace_bytes(n_max, dev, true), k);
+#else
+            static const int want_regs = std::getenv("ACC_PM_SMEM") == nullptr;  // tuning switch: ACC_PM_SMEM=1 forces the shared-memory variant
+            if (n_max <= 192 && want_regs) launch_warp_k<6>(stream, nSt, pm_workspace_bytes(n_max, dev, false), k);
+            else launch_warp_k<0>(stream, nSt, pm_workspace_bytes(n_max, dev, true), k);
+#endif
+        });
     }
     void tick() {
         reg = 1 - reg;  // this step's arrivals become the next step's "other" register (Model::switch_registers)

@@ -16,17 +16,40 @@
 
 namespace acc {
 
-// workspace of one purchasing manager: f64 vectors + 2 int vectors of length n_max
-#define ACC_PM_NVEC_F64 21
-#define ACC_PM_NVEC_I32 2
-ACC_HD size_t pm_workspace_bytes(int n_max, bool separate_target) {
-    return (size_t)n_max * ((ACC_PM_NVEC_F64 + (separate_target ? 1 : 0)) * sizeof(double) + ACC_PM_NVEC_I32 * sizeof(int));
+// ---- work vectors of the solver: in memory (pointer) or in the registers of the owning lane ----
+struct PtrVec {
+    double* p;
+    ACC_HD double& operator[](int i) const { return p[i]; }
+};
+#if defined(__CUDACC__)
+// element i = lane + 32 k lives in slot k of its lane; only valid under WarpCtxT<K> (unrolled loops make k static)
+template <int K>
+struct LaneVec {
+    double v[K];
+    __device__ __forceinline__ double& operator[](int i) { return v[i >> 5]; }
+    __device__ __forceinline__ const double& operator[](int i) const { return v[i >> 5]; }
+};
+template <int K>
+__device__ __forceinline__ void attach(LaneVec<K>&, double*&, int) {}
+#endif
+ACC_HD void attach(PtrVec& v, double*& p, int n) { v.p = p; p += n; }
+
+// shared-memory vectors of one purchasing manager besides the solver's own: 13 f64 (+1 with deviation_penalty) + 2 int
+#define ACC_PM_NVEC_SOLVER 10
+#define ACC_PM_NVEC_CONST 13
+ACC_HD size_t pm_workspace_bytes(int n_max, bool separate_target, bool solver_in_memory) {
+    const int nvec = ACC_PM_NVEC_CONST + (separate_target ? 1 : 0) + (solver_in_memory ? ACC_PM_NVEC_SOLVER : 0);
+    return (size_t)n_max * (nvec * sizeof(double) + 2 * sizeof(int));
 }
 
-struct PMWork {
-    accsqp::Work w;          // x, x0, g, a, d, b, gl, xbest
-    double *xu, *xtol;       // upper bounds and tolerances (lower bounds are all zero, :620)
-    // price-curve constants per purchasing connection
+template <class Vec>
+struct PMWorkT {
+    struct W {
+        Vec x, x0, g, a, d, b, gl, xbest;  // sqp_core work vectors
+        Vec xu, xtol;                      // upper bounds and tolerances (lower bounds are all zero, :620)
+        ACC_HD double lower(int) const { return 0.0; }
+    } w;
+    // price-curve constants per purchasing connection (shared memory)
     double *zf;              // to_float(Z*): scale of the variable (:184-188)
     double *tgt;             // transport penalty target (Z*, or the last demand request with deviation_penalty)
     double *addX;            // expected_additional_production (:343-349)
@@ -34,23 +57,22 @@ struct PMWork {
     double *base;            // n_bar [- pen(X_exp)/X_exp]: E_n_r without its X_new term (:255-271)
     double *n_co, *Dmin;     // reservation price and kink position of the price curve (:283-289)
     double *slope;           // (n_bar_min - n_co) / D_r_min in the linear regime; NaN marks the cropped regime (n_co > n_bar_min)
-    double *term;            // per-connection summand of the current evaluation
+    double *term, *dval;     // per-connection summands of the current evaluation (cost term, D_r), read by the ordered sums
     int *idx, *eid;          // compacted position -> incoming position, connection id
     ACC_HD void carve(unsigned char* mem, int n_max, bool separate_target) {
         double* p = reinterpret_cast<double*>(mem);
-        w.x = p; p += n_max; w.x0 = p; p += n_max; w.g = p; p += n_max; w.a = p; p += n_max; w.d = p; p += n_max; w.b = p; p += n_max;
-        w.gl = p; p += n_max; w.xbest = p; p += n_max;
-        xu = p; p += n_max; xtol = p; p += n_max;
+        attach(w.x, p, n_max); attach(w.x0, p, n_max); attach(w.g, p, n_max); attach(w.a, p, n_max); attach(w.d, p, n_max);
+        attach(w.b, p, n_max); attach(w.gl, p, n_max); attach(w.xbest, p, n_max); attach(w.xu, p, n_max); attach(w.xtol, p, n_max);
         zf = p; p += n_max; addX = p; p += n_max; Xhatf = p; p += n_max; lamXf = p; p += n_max; c1 = p; p += n_max; c2 = p; p += n_max;
         base = p; p += n_max; n_co = p; p += n_max; Dmin = p; p += n_max; slope = p; p += n_max;
-        term = p; p += n_max;
+        term = p; p += n_max; dval = p; p += n_max;
         tgt = zf;  // the penalty target is Z* itself unless deviation_penalty is set
         if (separate_target) { tgt = p; p += n_max; }
         int* q = reinterpret_cast<int*>(p);
         idx = q; q += n_max; eid = q;
-        w.xl = nullptr; w.xu = xu; w.xtol = xtol;
     }
 };
+typedef PMWorkT<PtrVec> PMWork;
 
 struct PMParams {
     double Uf;        // to_float(initial_used_flow_U_star): scale of objective and constraint (:194,:200)
@@ -66,7 +88,8 @@ struct PMParams {
 struct CurvePoint {
     double n, gn, tp, tpp;
 };
-ACC_HD CurvePoint curve_at(const PMWork& k, const PMParams& pp, int r, double D) {
+template <class PW>
+ACC_HD CurvePoint curve_at(const PW& k, const PMParams& pp, int r, double D) {
     CurvePoint c;
     // expected_average_price_E_n_r (:243-275) and its gradient (:305-321)
     double Xn = D + k.addX[r];
@@ -134,24 +157,31 @@ ACC_HD CurvePoint curve_at(const PMWork& k, const PMParams& pp, int r, double D)
 
 // Objective / constraint evaluation in the convention of sqp_core: minimise F = costs / U*,
 // constraint c = (desired - sum D_r) / U* == 0 whose gradient -Z*_r / U* is constant (filled once).
-template <class Ctx>
+template <class Ctx, class PW>
 struct PMEval {
     Ctx& cx;
-    PMWork& k;
+    PW& k;
     const PMParams& pp;
     int n;
     double desired_f;
-    ACC_HD void operator()(const double* x, bool want_grad, double* F, double* c) {
-        const PMWork& kk = k;
+    template <class X>
+    ACC_HD void operator()(const X& x, bool want_grad, double* F, double* c) {
+        PW& kk = k;
         const PMParams& p = pp;
-        cx.foreach(n, [&](int r) {
+        // results go to per-slot registers first and to shared memory afterwards, so that the independent
+        // per-connection chains of one lane are not ordered by the stores
+        double t_[Ctx::SLOTS], d_[Ctx::SLOTS];
+        cx.foreach_slot(n, [&](int r, int s) {
             const double D = x[r] * kk.zf[r];
             const CurvePoint cp = curve_at(kk, p, r, D);
-            kk.term[r] = cp.n * D + cp.tp;
+            t_[s] = cp.n * D + cp.tp;
+            d_[s] = D;
             if (want_grad) kk.w.g[r] = (kk.zf[r] * (cp.gn * D + cp.n + cp.tpp)) / p.Uf;
+            if (Ctx::SLOTS == 1) { kk.term[r] = t_[0]; kk.dval[r] = d_[0]; }
         });
+        if (Ctx::SLOTS > 1) cx.foreach_slot(n, [&](int r, int s) { kk.term[r] = t_[s]; kk.dval[r] = d_[s]; });
         double costs, use;
-        cx.seqsum2(n, [&](int r) { return kk.term[r]; }, [&](int r) { return x[r] * kk.zf[r]; }, &costs, &use);
+        cx.seqsum2(n, [&](int r) { return kk.term[r]; }, [&](int r) { return kk.dval[r]; }, &costs, &use);
         *F = costs / p.Uf;
         *c = (desired_f - use) / p.Uf;
     }
@@ -168,9 +198,9 @@ struct PMResult {
 // Inputs of one purchasing manager, gathered by the caller-provided accessors:
 //   in_edge(i) -> connection id of the i-th incoming connection (seller ascending)
 //   in_seller(i) -> seller agent
-template <class Ctx, class InEdge, class InSeller, class LastShip, class MinPassage, class SendD>
+template <class Ctx, class PW, class InEdge, class InSeller, class LastShip, class MinPassage, class SendD>
 ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_seller, LastShip last_ship, MinPassage min_passage, SendD send_D,
-                             const SellerPub* pub, const i64* Z_q, const i64* lastD_q, PMWork& k, const ModelP& mp, const SectorP& sec, i64 Ustar_q,
+                             const SellerPub* pub, const i64* Z_q, const i64* lastD_q, PW& k, const ModelP& mp, const SectorP& sec, i64 Ustar_q,
                              i64 Sstar_q, i64 S_q, i64 Ut_q, i64 deficit_q, const EventSink& events, int ev_sector, int ev_agent) {
     PMResult res;
     res.demand = mkflow(0, 0.0); res.expected_costs = 0.0; res.optimized = 0.0; res.penalty = 0.0; res.iters = 0; res.evals = 0;
@@ -229,8 +259,8 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         k.Dmin[r] = Dmin;
         k.slope[r] = (n_co <= nbar_min) ? (nbar_min - n_co) / Dmin : (double)NAN;
         // bounds, start value, xtol, :620-644; constraint gradient, :209
-        k.xu[r] = upper / zf;
-        k.xtol[r] = (ACC_PREC3 * mp.prec_adj) / zf;
+        k.w.xu[r] = upper / zf;
+        k.w.xtol[r] = (ACC_PREC3 * mp.prec_adj) / zf;
         k.w.x[r] = stdmin(upper, stdmax(0.0, Xe - add)) / zf;
         k.w.a[r] = -(zf / pp.Uf);
         return dmax;
@@ -249,7 +279,7 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
     if (desired > max_purchase) desired = max_purchase;  // :658-660
 
     // local optimisation, :690-702 with the restart logic of :465-561
-    PMEval<Ctx> ev{cx, k, pp, n, qf(desired)};
+    PMEval<Ctx, PW> ev{cx, k, pp, n, qf(desired)};
     accsqp::Params sp_;
     sp_.n = n; sp_.ctype = accsqp::CON_EQ; sp_.ctol = ACC_PREC3; sp_.maxeval = mp.maxeval; sp_.max_iter = ACCSQP_MAX_ITER;
     accsqp::Stats st;
@@ -279,13 +309,14 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         const i64 p = q > 0 ? mkp(cp.n) : 0;
         send_D(k.eid[r], q, p);
         k.term[r] = cp.n * D + cp.tp;
-        k.w.d[r] = cp.tp;
+        k.dval[r] = cp.tp;
         k.w.g[r] = q > 0 ? q_times_p(q, p) : 0.0;
         k.w.b[r] = (double)q;
     });
     double costs, pen, dv, dummy;
-    cx.seqsum2(n, [&](int r) { return k.term[r]; }, [&](int r) { return k.w.d[r]; }, &costs, &pen);
-    cx.seqsum2(n, [&](int r) { return k.w.g[r]; }, [&](int) { return 0.0; }, &dv, &dummy);
+    cx.seqsum2(n, [&](int r) { return k.term[r]; }, [&](int r) { return k.dval[r]; }, &costs, &pen);
+    cx.foreach(n, [&](int r) { k.term[r] = k.w.g[r]; });
+    cx.seqsum2(n, [&](int r) { return k.term[r]; }, [&](int) { return 0.0; }, &dv, &dummy);
     const i64 dq = cx.isum(n, [&](int r) { return (i64)k.w.b[r]; });
     res.demand = mkflow(dq, dv);
     res.expected_costs = costs;

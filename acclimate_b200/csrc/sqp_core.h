@@ -62,10 +62,11 @@ struct Work {
     // length-n vectors
     double *x, *x0, *g, *a, *d, *b, *gl, *xbest;
     const double *xl, *xu, *xtol;
+    SQP_HD double lower(int i) const { return xl != nullptr ? xl[i] : 0.0; }
 };
 #define ACCSQP_NVEC 8  // number of length-n work vectors above
 // lower bounds may be omitted (null pointer = all zero); step bounds are derived where they are used
-#define ACCSQP_XL(w, i) ((w).xl != nullptr ? (w).xl[i] : 0.0)
+#define ACCSQP_XL(w, i) ((w).lower(i))
 #define ACCSQP_LO(w, i) (ACCSQP_XL(w, i) - (w).x[i])
 #define ACCSQP_HI(w, i) ((w).xu[i] - (w).x[i])
 
@@ -85,8 +86,8 @@ struct Stats {
 // non-decreasing and piecewise linear, its root is found by Newton steps kept inside a bracket.
 // Returns lambda (gradient condition  B d + g = lambda a + z); *cres = a^T d + c at the solution.
 // ---------------------------------------------------------------------------------------
-template <class Ctx>
-SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, Work& w, Stats& st, double* cres) {
+template <class Ctx, class W>
+SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, double* cres) {
     if (ctype == CON_NONE) {
         cx.foreach(n, [&](int i) {
             const double t = -w.g[i] / w.b[i];
@@ -199,8 +200,10 @@ SQP_HD double con_violation(int ctype, double c) {
     return 0.0;
 }
 
-template <class Ctx, class Eval>
-SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, Work& w, const Params& p, Stats& st) {
+// W is any work-vector set with members x, x0, g, a, d, b, gl, xbest, xu, xtol indexable by [i] and lower(i):
+// plain pointers (struct Work: host shim, emulation, shared-memory kernel) or per-lane register vectors (device).
+template <class Ctx, class Eval, class W>
+SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
     const int n = p.n;
     st.iters = 0; st.evals = 0; st.qp_iters = 0; st.qp_inexact = 0; st.resets = 0; st.minf = 0.0; st.feasible = 0;
 
