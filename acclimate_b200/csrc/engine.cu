@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(256) block_kernel(K k) {
     k(cx, (int)blockIdx.x);
 }
 template <int KMAX, class K>
-__global__ void __launch_bounds__(32) warp_kernel(K k) {
+__global__ void __launch_bounds__(32, KMAX > 0 ? 11 : 1) warp_kernel(K k) {
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     WarpCtxT<KMAX> cx;
     k(cx, (int)blockIdx.x, dyn_smem);
