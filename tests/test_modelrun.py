@@ -12,7 +12,7 @@ def test_phase_split_equals_reference(emu_lib):
     x = series[("firms", "production_quantity")]
     assert x.shape == (steps, int(net["meta"][2]))
     for t in range(steps):
-        want = gold["t%05d/firm_X_q" % t] * 0x1.0624dd2f1a9fdp-10
+        want = gold["t%05d/firm_X_q" % t] * float.fromhex("0x1.0624dd2f1a9fdp-10")
         assert np.array_equal(x[t], want)
     assert len(run.duration_ms) == steps
     run.close()
