@@ -258,6 +258,52 @@ struct BlockCtx : CtxOps<BlockCtx> {
         for (int k = 1; k < W; ++k) total = T::combine(total, slots[k]);
         return total;
     }
+    enum { SLOTS = 1 };
+    template <class F>
+    __device__ __forceinline__ void foreach_slot(int n, F f) const {
+        for (int i = threadIdx.x; i < n; i += blockDim.x) f(i, 0);
+        __syncthreads();
+    }
+    template <class F1, class F2>
+    __device__ __forceinline__ void seqsum2(int n, F1 f1, F2 f2, double* s1, double* s2) const {
+        double* slots = reinterpret_cast<double*>(scratch);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double a = 0.0, b = 0.0;
+            int i = 0;
+            for (; i + 8 <= n; i += 8) {
+                double t[8], u[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { t[j] = f1(i + j); u[j] = f2(i + j); }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { a += t[j]; b += u[j]; }
+            }
+            for (; i < n; ++i) { a += f1(i); b += f2(i); }
+            slots[0] = a; slots[1] = b;
+        }
+        __syncthreads();
+        *s1 = slots[0]; *s2 = slots[1];
+    }
+    template <class Pred>
+    __device__ __forceinline__ int compact(int n, Pred pred, int* out) const {
+        int* counts = reinterpret_cast<int*>(scratch);  // per-warp counts of the current chunk
+        const int w = threadIdx.x >> 5, W = blockDim.x >> 5, lane_ = threadIdx.x & 31;
+        int m = 0;
+        for (int base = 0; base < n; base += blockDim.x) {
+            const int i = base + threadIdx.x;
+            const bool keep = i < n && pred(i);
+            const unsigned mask = __ballot_sync(0xffffffffu, keep);
+            __syncthreads();
+            if (lane_ == 0) counts[w] = __popc(mask);
+            __syncthreads();
+            int before = 0, total = 0;
+            for (int k = 0; k < W; ++k) { if (k < w) before += counts[k]; total += counts[k]; }
+            if (keep) out[m + before + __popc(mask & ((1u << lane_) - 1u))] = i;
+            m += total;
+        }
+        __syncthreads();
+        return m;
+    }
 };
 #endif  // __CUDACC__
 

@@ -71,6 +71,11 @@ static void launch_warp(stream_t, int n, size_t smem, K k) {
 }
 template <int KMAX, class K>
 static void launch_warp_k(stream_t s, int n, size_t smem, K k) { launch_warp(s, n, smem, k); }
+template <class K>
+static void launch_block_smem(stream_t, int n, int threads, size_t smem, K k) {
+    std::vector<unsigned char> sm(smem + 16);
+    for (int i = 0; i < n; ++i) { HostCtx cx(threads); k(cx, i, sm.data()); }
+}
 #else
 typedef cudaStream_t stream_t;
 #define ACC_CUDA(x)                                                                                   \
@@ -103,6 +108,13 @@ __global__ void __launch_bounds__(256) block_kernel(K k) {
     BlockCtx cx(scratch);
     k(cx, (int)blockIdx.x);
 }
+template <class K>
+__global__ void __launch_bounds__(256) block_smem_kernel(K k) {
+    __shared__ __align__(16) unsigned char scratch[ACC_BLOCK_SCRATCH_BYTES];
+    extern __shared__ __align__(16) unsigned char dyn_smem[];
+    BlockCtx cx(scratch);
+    k(cx, (int)blockIdx.x, dyn_smem);
+}
 template <int KMAX, class K>
 __global__ void __launch_bounds__(32, KMAX > 0 ? 11 : 1) warp_kernel(K k) {
     extern __shared__ __align__(16) unsigned char dyn_smem[];
@@ -134,6 +146,17 @@ static void launch_warp_k(stream_t s, int n, size_t smem, K k) {
 }
 template <class K>
 static void launch_warp(stream_t s, int n, size_t smem, K k) { launch_warp_k<0, K>(s, n, smem, k); }
+template <class K>
+static void launch_block_smem(stream_t s, int n, int threads, size_t smem, K k) {
+    if (n <= 0) return;
+    static size_t configured = 0;
+    if (smem > configured) {
+        ACC_CUDA(cudaFuncSetAttribute(block_smem_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    block_smem_kernel<K><<<n, threads, smem, s>>>(k);
+    ACC_CUDA(cudaGetLastError());
+}
 #endif
 
 template <class T>
@@ -474,16 +497,10 @@ struct acc_engine {
         Purchase k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, pub.p, n_max,
                    s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
         const bool dev = mp.deviation_penalty != 0;
-        timed("purchase", [&] {
-            // register-resident solver state when every purchasing manager has at most 192 connections
-#ifdef ACC_HOST_EMU
-            launch_warp(stream, nSt, pm_workspace_bytes(n_max, dev, true), k);
-#else
-            static const int want_regs = std::getenv("ACC_PM_SMEM") == nullptr;  // tuning switch: ACC_PM_SMEM=1 forces the shared-memory variant
-            if (n_max <= 192 && want_regs) launch_warp_k<6>(stream, nSt, pm_workspace_bytes(n_max, dev, false), k);
-            else launch_warp_k<0>(stream, nSt, pm_workspace_bytes(n_max, dev, true), k);
-#endif
-        });
+        // One CTA of ACCSQP_GROUP threads per purchasing manager, all its vectors in shared memory.  The group size is
+        // part of the arithmetic (reduction order), so it is a build constant shared with the oracle's host context.
+        static const int group = std::getenv("ACC_PM_THREADS") ? std::atoi(std::getenv("ACC_PM_THREADS")) : ACCSQP_GROUP;  // timing experiments only
+        timed("purchase", [&] { launch_block_smem(stream, nSt, group, pm_workspace_bytes(n_max, dev, true), k); });
     }
     void tick() {
         reg = 1 - reg;  // this step's arrivals become the next step's "other" register (Model::switch_registers)

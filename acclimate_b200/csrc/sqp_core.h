@@ -35,6 +35,11 @@
 #ifndef ACCSQP_MAX_ITER
 #define ACCSQP_MAX_ITER 200  // SQP iterations per call before "more than iter SQP iterations"
 #endif
+// Size of the thread group that runs one solve on the device.  Its reduction order (coop.cuh) is part of the
+// arithmetic, so the oracle's host context replays exactly this group size.
+#ifndef ACCSQP_GROUP
+#define ACCSQP_GROUP 96
+#endif
 #define ACCSQP_BMIN 1e-12
 #define ACCSQP_BMAX 1e+15
 

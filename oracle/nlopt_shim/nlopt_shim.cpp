@@ -19,6 +19,7 @@
 #include <cstring>
 #include <vector>
 
+#include "../../acclimate_b200/csrc/coop.cuh"
 #include "../../acclimate_b200/csrc/sqp_core.h"
 
 struct nlopt_opt_s {
@@ -156,7 +157,7 @@ extern "C" nlopt_result nlopt_optimize(nlopt_opt opt, double* x, double* opt_f) 
     accsqp::Params p;
     p.n = n; p.ctype = opt->ctype; p.ctol = opt->ctol; p.maxeval = opt->maxeval; p.max_iter = ACCSQP_MAX_ITER;
     accsqp::Stats st;
-    accsqp::HostCtx cx;
+    acc::HostCtx cx(ACCSQP_GROUP);  // replays the device group's reduction order
     CallbackEval ev{opt, &w, std::vector<double>((size_t)n)};
     const int ret = accsqp::sqp_minimize(cx, ev, w, p, st);
     std::memcpy(x, w.xbest, sizeof(double) * n);
