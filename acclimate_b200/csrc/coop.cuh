@@ -75,10 +75,6 @@ struct HostCtx : CtxOps<HostCtx> {
     inline int lane() const { return 0; }
     template <class F>
     inline void foreach(int n, F f) const { for (int i = 0; i < n; ++i) f(i); }
-    // element loop that also names the per-lane slot of the element; contexts without unrolling have one slot
-    enum { SLOTS = 1 };
-    template <class F>
-    inline void foreach_slot(int n, F f) const { for (int i = 0; i < n; ++i) f(i, 0); }
     template <class T, class F>
     inline T reduce(int n, F f) const {
         const int W = G / 32;
@@ -99,12 +95,12 @@ struct HostCtx : CtxOps<HostCtx> {
         }
         return total;
     }
-    // strictly sequential left-to-right folds (the reference's own loop order), two at once
-    template <class F1, class F2>
-    inline void seqsum2(int n, F1 f1, F2 f2, double* s1, double* s2) const {
-        double a = 0.0, b = 0.0;
-        for (int i = 0; i < n; ++i) { a += f1(i); b += f2(i); }
-        *s1 = a; *s2 = b;
+    // K strictly sequential left-to-right folds (the reference's own loop order)
+    template <int K>
+    inline void seqsum(int n, const double* const (&v)[K], double (&out)[K]) const {
+        for (int k = 0; k < K; ++k) out[k] = 0.0;
+        for (int i = 0; i < n; ++i)
+            for (int k = 0; k < K; ++k) out[k] += v[k][i];
     }
     // order-preserving compaction: out[0..m) = ascending i with pred(i); returns m
     template <class Pred>
@@ -139,94 +135,71 @@ __device__ __forceinline__ T shfl_any(const T& v, int src_lane) {
     return r;
 }
 
-// One warp per item.  KMAX > 0 promises n <= 32 * KMAX: every element loop is fully unrolled over the KMAX slots of a
-// lane (element i = lane + 32 k), which lets per-lane vectors live in registers (LaneVec below) and gives the
-// scheduler KMAX independent dependency chains per lane.  KMAX == 0 is the general strided loop.
-template <int KMAX>
-struct WarpCtxT : CtxOps<WarpCtxT<KMAX> > {
+// K strictly sequential left-to-right sums over shared-memory vectors, executed by ONE thread: operands of eight
+// elements are loaded first (independent loads), then folded in element order.
+template <int K>
+__device__ __forceinline__ void seqsum_serial(int n, const double* const (&v)[K], double (&a)[K]) {
+    int i = 0;
+    for (; i + 8 <= n; i += 8) {
+        double t[K][8];
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) t[k][j] = v[k][i + j];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+#pragma unroll
+            for (int k = 0; k < K; ++k) a[k] += t[k][j];
+    }
+    for (; i < n; ++i)
+#pragma unroll
+        for (int k = 0; k < K; ++k) a[k] += v[k][i];
+}
+
+// One warp per item.
+struct WarpCtx : CtxOps<WarpCtx> {
     int lane_;
-    __device__ WarpCtxT() : lane_(threadIdx.x & 31) {}
+    __device__ WarpCtx() : lane_(threadIdx.x & 31) {}
     __device__ __forceinline__ bool leader() const { return lane_ == 0; }
     __device__ __forceinline__ void sync() const { __syncwarp(); }
     __device__ __forceinline__ int lane() const { return lane_; }
     template <class F>
     __device__ __forceinline__ void foreach(int n, F f) const {
-        if (KMAX > 0) {
-#pragma unroll
-            for (int k = 0; k < (KMAX > 0 ? KMAX : 1); ++k) { const int i = lane_ + 32 * k; if (i < n) f(i); }
-        } else {
-            for (int i = lane_; i < n; i += 32) f(i);
-        }
-        __syncwarp();
-    }
-    enum { SLOTS = KMAX > 0 ? KMAX : 1 };
-    template <class F>
-    __device__ __forceinline__ void foreach_slot(int n, F f) const {
-        if (KMAX > 0) {
-#pragma unroll
-            for (int k = 0; k < (KMAX > 0 ? KMAX : 1); ++k) { const int i = lane_ + 32 * k; if (i < n) f(i, k); }
-        } else {
-            for (int i = lane_; i < n; i += 32) f(i, 0);
-        }
+        for (int i = lane_; i < n; i += 32) f(i);
         __syncwarp();
     }
     template <class T, class F>
     __device__ __forceinline__ T reduce(int n, F f) const {
         T acc_ = T::identity();
-        if (KMAX > 0) {
-#pragma unroll
-            for (int k = 0; k < (KMAX > 0 ? KMAX : 1); ++k) { const int i = lane_ + 32 * k; if (i < n) acc_ = T::combine(acc_, f(i)); }
-        } else {
-            for (int i = lane_; i < n; i += 32) acc_ = T::combine(acc_, f(i));
-        }
+        for (int i = lane_; i < n; i += 32) acc_ = T::combine(acc_, f(i));
 #pragma unroll
         for (int off = 16; off >= 1; off >>= 1) acc_ = T::combine(acc_, shfl_xor_any(acc_, off));
         return acc_;
     }
-    template <class F1, class F2>
-    __device__ __forceinline__ void seqsum2(int n, F1 f1, F2 f2, double* s1, double* s2) const {
-        double a = 0.0, b = 0.0;
+    template <int K>
+    __device__ __forceinline__ void seqsum(int n, const double* const (&v)[K], double (&out)[K]) const {
+        double a[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) a[k] = 0.0;
         __syncwarp();
-        if (lane_ == 0) {
-            int i = 0;
-            for (; i + 8 <= n; i += 8) {  // operands first (independent shared-memory loads), then the two ordered chains
-                double t[8], u[8];
+        if (lane_ == 0) seqsum_serial<K>(n, v, a);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) { t[j] = f1(i + j); u[j] = f2(i + j); }
-#pragma unroll
-                for (int j = 0; j < 8; ++j) { a += t[j]; b += u[j]; }
-            }
-            for (; i < n; ++i) { a += f1(i); b += f2(i); }
-        }
-        *s1 = __shfl_sync(0xffffffffu, a, 0);
-        *s2 = __shfl_sync(0xffffffffu, b, 0);
+        for (int k = 0; k < K; ++k) out[k] = __shfl_sync(0xffffffffu, a[k], 0);
     }
     template <class Pred>
     __device__ __forceinline__ int compact(int n, Pred pred, int* out) const {
         int m = 0;
-        if (KMAX > 0) {
-#pragma unroll
-            for (int k = 0; k < (KMAX > 0 ? KMAX : 1); ++k) {
-                const int i = lane_ + 32 * k;
-                const bool keep = i < n && pred(i);
-                const unsigned mask = __ballot_sync(0xffffffffu, keep);
-                if (keep) out[m + __popc(mask & ((1u << lane_) - 1u))] = i;
-                m += __popc(mask);
-            }
-        } else {
-            for (int base = 0; base < n; base += 32) {
-                const int i = base + lane_;
-                const bool keep = i < n && pred(i);
-                const unsigned mask = __ballot_sync(0xffffffffu, keep);
-                if (keep) out[m + __popc(mask & ((1u << lane_) - 1u))] = i;
-                m += __popc(mask);
-            }
+        for (int base = 0; base < n; base += 32) {
+            const int i = base + lane_;
+            const bool keep = i < n && pred(i);
+            const unsigned mask = __ballot_sync(0xffffffffu, keep);
+            if (keep) out[m + __popc(mask & ((1u << lane_) - 1u))] = i;
+            m += __popc(mask);
         }
         __syncwarp();
         return m;
     }
 };
-typedef WarpCtxT<0> WarpCtx;
 
 // A CTA working on one item.  `scratch` is shared memory with room for 33 payloads of the largest
 // reduction type used (ACC_BLOCK_SCRATCH_BYTES).
@@ -258,31 +231,21 @@ struct BlockCtx : CtxOps<BlockCtx> {
         for (int k = 1; k < W; ++k) total = T::combine(total, slots[k]);
         return total;
     }
-    enum { SLOTS = 1 };
-    template <class F>
-    __device__ __forceinline__ void foreach_slot(int n, F f) const {
-        for (int i = threadIdx.x; i < n; i += blockDim.x) f(i, 0);
-        __syncthreads();
-    }
-    template <class F1, class F2>
-    __device__ __forceinline__ void seqsum2(int n, F1 f1, F2 f2, double* s1, double* s2) const {
+    template <int K>
+    __device__ __forceinline__ void seqsum(int n, const double* const (&v)[K], double (&out)[K]) const {
         double* slots = reinterpret_cast<double*>(scratch);
         __syncthreads();
         if (threadIdx.x == 0) {
-            double a = 0.0, b = 0.0;
-            int i = 0;
-            for (; i + 8 <= n; i += 8) {
-                double t[8], u[8];
+            double a[K];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) { t[j] = f1(i + j); u[j] = f2(i + j); }
+            for (int k = 0; k < K; ++k) a[k] = 0.0;
+            seqsum_serial<K>(n, v, a);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) { a += t[j]; b += u[j]; }
-            }
-            for (; i < n; ++i) { a += f1(i); b += f2(i); }
-            slots[0] = a; slots[1] = b;
+            for (int k = 0; k < K; ++k) slots[k] = a[k];
         }
         __syncthreads();
-        *s1 = slots[0]; *s2 = slots[1];
+#pragma unroll
+        for (int k = 0; k < K; ++k) out[k] = slots[k];
     }
     template <class Pred>
     __device__ __forceinline__ int compact(int n, Pred pred, int* out) const {

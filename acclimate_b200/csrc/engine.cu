@@ -69,8 +69,6 @@ static void launch_warp(stream_t, int n, size_t smem, K k) {
     std::vector<unsigned char> sm(smem + 16);
     for (int i = 0; i < n; ++i) { HostCtx cx(32); k(cx, i, sm.data()); }
 }
-template <int KMAX, class K>
-static void launch_warp_k(stream_t s, int n, size_t smem, K k) { launch_warp(s, n, smem, k); }
 template <class K>
 static void launch_block_smem(stream_t, int n, int threads, size_t smem, K k) {
     std::vector<unsigned char> sm(smem + 16);
@@ -115,10 +113,10 @@ __global__ void __launch_bounds__(256) block_smem_kernel(K k) {
     BlockCtx cx(scratch);
     k(cx, (int)blockIdx.x, dyn_smem);
 }
-template <int KMAX, class K>
-__global__ void __launch_bounds__(32, KMAX > 0 ? 11 : 1) warp_kernel(K k) {
+template <class K>
+__global__ void __launch_bounds__(32) warp_kernel(K k) {
     extern __shared__ __align__(16) unsigned char dyn_smem[];
-    WarpCtxT<KMAX> cx;
+    WarpCtx cx;
     k(cx, (int)blockIdx.x, dyn_smem);
 }
 template <class K>
@@ -133,19 +131,17 @@ static void launch_block(stream_t s, int n, int threads, K k) {
     block_kernel<K><<<n, threads, 0, s>>>(k);
     ACC_CUDA(cudaGetLastError());
 }
-template <int KMAX, class K>
-static void launch_warp_k(stream_t s, int n, size_t smem, K k) {
+template <class K>
+static void launch_warp(stream_t s, int n, size_t smem, K k) {
     if (n <= 0) return;
     static size_t configured = 0;
     if (smem > configured) {
-        ACC_CUDA(cudaFuncSetAttribute(warp_kernel<KMAX, K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ACC_CUDA(cudaFuncSetAttribute(warp_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    warp_kernel<KMAX, K><<<n, 32, smem, s>>>(k);
+    warp_kernel<K><<<n, 32, smem, s>>>(k);
     ACC_CUDA(cudaGetLastError());
 }
-template <class K>
-static void launch_warp(stream_t s, int n, size_t smem, K k) { launch_warp_k<0, K>(s, n, smem, k); }
 template <class K>
 static void launch_block_smem(stream_t s, int n, int threads, size_t smem, K k) {
     if (n <= 0) return;
@@ -272,23 +268,13 @@ struct StorageDelivery {  // thread per storage
     }
 };
 
-// solver work vectors: registers of the owning lane under an unrolled warp context, memory otherwise
-template <class Ctx>
-struct WorkFor { typedef PMWorkT<PtrVec> type; };
-#ifndef ACC_HOST_EMU
-template <int KMAX>
-struct WorkFor<WarpCtxT<KMAX> > { typedef PMWorkT<LaneVec<KMAX> > type; };
-template <>
-struct WorkFor<WarpCtxT<0> > { typedef PMWorkT<PtrVec> type; };
-#endif
-
-struct Purchase {  // warp per purchasing manager
+struct Purchase {  // one CTA of ACCSQP_GROUP threads per purchasing manager
     StorageView st; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
     const i64* in_off; const int* in_edge; const int* in_seller; const SellerPub* pub; int n_max;
     i64* dem_q; double* dem_v; double* exp_costs; double* opt_val; double* tpen; int* iters; int* evals;
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int s, unsigned char* smem) const {
-        typename WorkFor<Ctx>::type k;
+        PMWork k;
         k.carve(smem, n_max, mp.deviation_penalty != 0);
         const i64 o = in_off[s];
         const int nin = (int)(in_off[s + 1] - o);

@@ -16,22 +16,11 @@
 
 namespace acc {
 
-// ---- work vectors of the solver: in memory (pointer) or in the registers of the owning lane ----
+// ---- work vectors of the solver (shared memory) ----
 struct PtrVec {
     double* p;
     ACC_HD double& operator[](int i) const { return p[i]; }
 };
-#if defined(__CUDACC__)
-// element i = lane + 32 k lives in slot k of its lane; only valid under WarpCtxT<K> (unrolled loops make k static)
-template <int K>
-struct LaneVec {
-    double v[K];
-    __device__ __forceinline__ double& operator[](int i) { return v[i >> 5]; }
-    __device__ __forceinline__ const double& operator[](int i) const { return v[i >> 5]; }
-};
-template <int K>
-__device__ __forceinline__ void attach(LaneVec<K>&, double*&, int) {}
-#endif
 ACC_HD void attach(PtrVec& v, double*& p, int n) { v.p = p; p += n; }
 
 // shared-memory vectors of one purchasing manager besides the solver's own: 13 f64 (+1 with deviation_penalty) + 2 int
@@ -168,20 +157,17 @@ struct PMEval {
     ACC_HD void operator()(const X& x, bool want_grad, double* F, double* c) {
         PW& kk = k;
         const PMParams& p = pp;
-        // results go to per-slot registers first and to shared memory afterwards, so that the independent
-        // per-connection chains of one lane are not ordered by the stores
-        double t_[Ctx::SLOTS], d_[Ctx::SLOTS];
-        cx.foreach_slot(n, [&](int r, int s) {
+        cx.foreach(n, [&](int r) {
             const double D = x[r] * kk.zf[r];
             const CurvePoint cp = curve_at(kk, p, r, D);
-            t_[s] = cp.n * D + cp.tp;
-            d_[s] = D;
+            kk.term[r] = cp.n * D + cp.tp;
+            kk.dval[r] = D;
             if (want_grad) kk.w.g[r] = (kk.zf[r] * (cp.gn * D + cp.n + cp.tpp)) / p.Uf;
-            if (Ctx::SLOTS == 1) { kk.term[r] = t_[0]; kk.dval[r] = d_[0]; }
         });
-        if (Ctx::SLOTS > 1) cx.foreach_slot(n, [&](int r, int s) { kk.term[r] = t_[s]; kk.dval[r] = d_[s]; });
-        double costs, use;
-        cx.seqsum2(n, [&](int r) { return kk.term[r]; }, [&](int r) { return kk.dval[r]; }, &costs, &use);
+        const double* const v[2] = {kk.term, kk.dval};
+        double s[2];
+        cx.seqsum(n, v, s);
+        const double costs = s[0], use = s[1];
         *F = costs / p.Uf;
         *c = (desired_f - use) / p.Uf;
     }
@@ -313,10 +299,10 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         k.w.g[r] = q > 0 ? q_times_p(q, p) : 0.0;
         k.w.b[r] = (double)q;
     });
-    double costs, pen, dv, dummy;
-    cx.seqsum2(n, [&](int r) { return k.term[r]; }, [&](int r) { return k.dval[r]; }, &costs, &pen);
-    cx.foreach(n, [&](int r) { k.term[r] = k.w.g[r]; });
-    cx.seqsum2(n, [&](int r) { return k.term[r]; }, [&](int) { return 0.0; }, &dv, &dummy);
+    const double* const v[3] = {k.term, k.dval, k.w.g.p};
+    double sums[3];
+    cx.seqsum(n, v, sums);
+    const double costs = sums[0], pen = sums[1], dv = sums[2];
     const i64 dq = cx.isum(n, [&](int r) { return (i64)k.w.b[r]; });
     res.demand = mkflow(dq, dv);
     res.expected_costs = costs;

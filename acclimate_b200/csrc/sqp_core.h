@@ -85,26 +85,49 @@ struct Stats {
     int feasible;
 };
 
+// Reduction payloads (Ctx::reduce<T> folds them in the fixed order documented in coop.cuh).
+struct Sum2 {
+    double a, b;
+    static SQP_HD Sum2 identity() { Sum2 r; r.a = 0.0; r.b = 0.0; return r; }
+    static SQP_HD Sum2 combine(Sum2 x, Sum2 y) { Sum2 r; r.a = x.a + y.a; r.b = x.b + y.b; return r; }
+};
+struct Sum3 {
+    double a, b, c;
+    static SQP_HD Sum3 identity() { Sum3 r; r.a = 0.0; r.b = 0.0; r.c = 0.0; return r; }
+    static SQP_HD Sum3 combine(Sum3 x, Sum3 y) { Sum3 r; r.a = x.a + y.a; r.b = x.b + y.b; r.c = x.c + y.c; return r; }
+};
+struct MinMax {
+    double lo, hi;
+    static SQP_HD MinMax identity() { MinMax r; r.lo = 1e308; r.hi = -1e308; return r; }
+    static SQP_HD MinMax combine(MinMax x, MinMax y) { MinMax r; r.lo = y.lo < x.lo ? y.lo : x.lo; r.hi = y.hi > x.hi ? y.hi : x.hi; return r; }
+};
+
 // ---------------------------------------------------------------------------------------
-// QP sub-problem:  min 1/2 d^T diag(b) d + g^T d   s.t.  a^T d + c (=|>=) 0,  lo <= d <= hi.
-// Solution d_i(lambda) = clamp((-g_i + lambda a_i)/b_i, lo_i, hi_i); psi(lambda) = a^T d + c is
-// non-decreasing and piecewise linear, its root is found by Newton steps kept inside a bracket.
-// Returns lambda (gradient condition  B d + g = lambda a + z); *cres = a^T d + c at the solution.
+// QP sub-problem:  min 1/2 d^T diag(1/h) d + g^T d   s.t.  a^T d + c (=|>=) 0,  lo <= d <= hi,
+// with the INVERSE of the diagonal Hessian model in w.b (h_i = 1/b_i), so the sub-problem needs no division.
+// Solution d_i(lambda) = clamp((-g_i + lambda a_i) h_i, lo_i, hi_i); psi(lambda) = a^T d + c is
+// non-decreasing and piecewise linear, its root is found by Newton steps kept inside a bracket; psi and
+// its slope come out of ONE pass.  Returns lambda (gradient condition  B d + g = lambda a + z).
+// *d_ready tells the caller whether w.d already holds the step (vertex solutions) or is still to be formed
+// from lambda (the caller fuses that pass with its own sums).
 // ---------------------------------------------------------------------------------------
+template <class W>
+SQP_HD double qp_step(const W& w, int i, double lambda) {
+    const double t = (-w.g[i] + lambda * w.a[i]) * w.b[i];
+    return t < ACCSQP_LO(w, i) ? ACCSQP_LO(w, i) : (t > ACCSQP_HI(w, i) ? ACCSQP_HI(w, i) : t);
+}
+
 template <class Ctx, class W>
-SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, double* cres) {
-    if (ctype == CON_NONE) {
-        cx.foreach(n, [&](int i) {
-            const double t = -w.g[i] / w.b[i];
-            w.d[i] = t < ACCSQP_LO(w, i) ? ACCSQP_LO(w, i) : (t > ACCSQP_HI(w, i) ? ACCSQP_HI(w, i) : t);
-        });
-        *cres = 0.0;
-        return 0.0;
-    }
+SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, bool* d_ready) {
+    *d_ready = false;
+    if (ctype == CON_NONE) return 0.0;
     const double target = -c;  // want a^T d = target
     // attainable range of a^T d over the box
-    const double smin = cx.sum(n, [&](int i) { const double p = w.a[i] * ACCSQP_LO(w, i), q = w.a[i] * ACCSQP_HI(w, i); return p < q ? p : q; });
-    const double smax = cx.sum(n, [&](int i) { const double p = w.a[i] * ACCSQP_LO(w, i), q = w.a[i] * ACCSQP_HI(w, i); return p > q ? p : q; });
+    const Sum2 range = cx.template reduce<Sum2>(n, [&](int i) {
+        const double p = w.a[i] * ACCSQP_LO(w, i), q = w.a[i] * ACCSQP_HI(w, i);
+        Sum2 r; r.a = p < q ? p : q; r.b = p > q ? p : q; return r;
+    });
+    const double smin = range.a, smax = range.b;
     int forced = 0;  // -1: push a^T d to its minimum, +1: to its maximum
     if (ctype == CON_EQ && target <= smin) forced = -1;
     else if (target >= smax) forced = 1;
@@ -114,29 +137,25 @@ SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, dou
             const double p = w.a[i] * ACCSQP_LO(w, i), q = w.a[i] * ACCSQP_HI(w, i);
             w.d[i] = (forced > 0) ? (p >= q ? ACCSQP_LO(w, i) : ACCSQP_HI(w, i)) : (p <= q ? ACCSQP_LO(w, i) : ACCSQP_HI(w, i));
         });
+        *d_ready = true;
         const double big = 1e300;
-        // need  (b d + g)_i - lambda a_i <= 0 where d sits at hi,  >= 0 where it sits at lo
-        const double lmin = cx.vmax(n, [&](int i) {
-            if (w.a[i] == 0.0 || ACCSQP_LO(w, i) == ACCSQP_HI(w, i)) return -big;
+        // need  (d/h + g)_i - lambda a_i <= 0 where d sits at hi,  >= 0 where it sits at lo:
+        // lmin = largest lower bound on lambda, lmax = smallest upper bound
+        const MinMax lim = cx.template reduce<MinMax>(n, [&](int i) {
+            MinMax r; r.lo = big; r.hi = -big;
+            if (w.a[i] == 0.0 || ACCSQP_LO(w, i) == ACCSQP_HI(w, i)) return r;
             const bool at_hi = (w.d[i] == ACCSQP_HI(w, i));
-            const double r = (w.b[i] * w.d[i] + w.g[i]) / w.a[i];
-            if (at_hi) return (w.a[i] > 0.0) ? r : -big;
-            return (w.a[i] < 0.0) ? r : -big;
+            const double q = (w.d[i] / w.b[i] + w.g[i]) / w.a[i];
+            if (at_hi == (w.a[i] > 0.0)) r.hi = q; else r.lo = q;
+            return r;
         });
-        const double lmax = cx.vmin(n, [&](int i) {
-            if (w.a[i] == 0.0 || ACCSQP_LO(w, i) == ACCSQP_HI(w, i)) return big;
-            const bool at_hi = (w.d[i] == ACCSQP_HI(w, i));
-            const double r = (w.b[i] * w.d[i] + w.g[i]) / w.a[i];
-            if (at_hi) return (w.a[i] < 0.0) ? r : big;
-            return (w.a[i] > 0.0) ? r : big;
-        });
+        const double lmin = lim.hi, lmax = lim.lo;
         double lambda;
         if (lmin > -big && lmax < big) lambda = (fabs(lmin) < fabs(lmax)) ? lmin : lmax;
         else if (lmin > -big) lambda = lmin;
         else if (lmax < big) lambda = lmax;
         else lambda = 0.0;
         if (ctype == CON_INEQ && lambda < 0.0) lambda = 0.0;
-        *cres = c + cx.sum(n, [&](int i) { return w.a[i] * w.d[i]; });
         return lambda;
     }
 
@@ -151,16 +170,17 @@ SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, dou
     int it = 0;
     for (; it < 200; ++it) {
         // psi and its slope at lambda
-        const double psi = c + cx.sum(n, [&](int i) {
-            const double t = (-w.g[i] + lambda * w.a[i]) / w.b[i];
-            const double di = t < ACCSQP_LO(w, i) ? ACCSQP_LO(w, i) : (t > ACCSQP_HI(w, i) ? ACCSQP_HI(w, i) : t);
-            return w.a[i] * di;
+        const Sum2 ps = cx.template reduce<Sum2>(n, [&](int i) {
+            const double t = (-w.g[i] + lambda * w.a[i]) * w.b[i];
+            const double lo = ACCSQP_LO(w, i), hi = ACCSQP_HI(w, i);
+            Sum2 r;
+            if (t <= lo) { r.a = w.a[i] * lo; r.b = 0.0; }
+            else if (t >= hi) { r.a = w.a[i] * hi; r.b = 0.0; }
+            else { r.a = w.a[i] * t; r.b = w.a[i] * w.a[i] * w.b[i]; }
+            return r;
         });
+        const double psi = c + ps.a, slope = ps.b;
         if (it == 0 && ctype == CON_INEQ && psi >= 0.0) { converged = true; break; }  // constraint inactive
-        const double slope = cx.sum(n, [&](int i) {
-            const double t = (-w.g[i] + lambda * w.a[i]) / w.b[i];
-            return (t > ACCSQP_LO(w, i) && t < ACCSQP_HI(w, i)) ? w.a[i] * w.a[i] / w.b[i] : 0.0;
-        });
         if (fabs(psi) <= psi_tol) { converged = true; break; }
         if (psi < 0.0) { lamL = lambda; haveL = true; } else { lamR = lambda; haveR = true; }
         if (prev_valid && lambda == prev_lambda) { converged = true; break; }
@@ -184,11 +204,6 @@ SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, dou
     }
     st.qp_iters += it;
     if (!converged) st.qp_inexact += 1;
-    cx.foreach(n, [&](int i) {
-        const double t = (-w.g[i] + lambda * w.a[i]) / w.b[i];
-        w.d[i] = t < ACCSQP_LO(w, i) ? ACCSQP_LO(w, i) : (t > ACCSQP_HI(w, i) ? ACCSQP_HI(w, i) : t);
-    });
-    *cres = c + cx.sum(n, [&](int i) { return w.a[i] * w.d[i]; });
     return lambda;
 }
 
@@ -237,20 +252,26 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
     while (ret == SQP_SUCCESS) {
         ++st.iters;
         if (p.max_iter > 0 && st.iters > p.max_iter) { ret = SQP_FAILURE; break; }
-        // bounds on the step
-        double cres = 0.0;
-        const double lambda = qp_solve(cx, n, p.ctype, c, w, st, &cres);
+        bool d_ready = false;
+        const double lambda = qp_solve(cx, n, p.ctype, c, w, st, &d_ready);
+        // One pass forms the step, the Lagrangian gradient at the old point with the new multiplier (Kraft: v), saves
+        // the old point and returns three sums: a.d (linearised constraint), the number of coordinates whose step
+        // reaches the x tolerance, and g.d.
+        const Sum3 sd = cx.template reduce<Sum3>(n, [&](int i) {
+            const double di = d_ready ? w.d[i] : qp_step(w, i, lambda);
+            w.d[i] = di;
+            w.gl[i] = w.g[i] - lambda * w.a[i];
+            w.x0[i] = w.x[i];
+            Sum3 r; r.a = w.a[i] * di; r.b = (fabs(di) < w.xtol[i]) ? 0.0 : 1.0; r.c = w.g[i] * di;
+            return r;
+        });
+        const double cres = (p.ctype == CON_NONE) ? 0.0 : c + sd.a;
         // Step test (Kraft's convergence test is on the size of the QP step as well): when the full step is below the
         // x tolerance in every coordinate, no line search result can move x by a tolerance -- stop here instead of
         // spending evaluations on a step NLopt's xtol rule would discard at the end of the iteration.
-        {
-            const double large = cx.sum(n, [&](int i) { return (fabs(w.d[i]) < w.xtol[i]) ? 0.0 : 1.0; });
-            if (large == 0.0) { ret = SQP_XTOL_REACHED; break; }
-        }
-        // gradient of the Lagrangian at the old point with the new multiplier (Kraft: v)
-        cx.foreach(n, [&](int i) { w.gl[i] = w.g[i] - lambda * w.a[i]; w.x0[i] = w.x[i]; });
+        if (sd.b == 0.0) { ret = SQP_XTOL_REACHED; break; }
         const double f0 = F;
-        const double gs = cx.sum(n, [&](int i) { return w.g[i] * w.d[i]; });
+        const double gs = sd.c;
         const double al = fabs(lambda);
         mu = (al > 0.5 * (mu + al)) ? al : 0.5 * (mu + al);
         const double viol0 = con_violation(p.ctype, c);
@@ -319,59 +340,25 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
             ret = SQP_XTOL_REACHED;
             break;
         }
-        // NLopt's xtol test between completed iterations
-        const double moved = cx.sum(n, [&](int i) { return (fabs(w.x[i] - w.x0[i]) < w.xtol[i]) ? 0.0 : 1.0; });
-        if (moved == 0.0) { ret = SQP_XTOL_REACHED; break; }
-        if (p.maxeval > 0 && st.evals >= p.maxeval) { ret = SQP_MAXEVAL_REACHED; break; }
-        // per-coordinate secant update of the diagonal Hessian model
-        cx.foreach(n, [&](int i) {
+        // NLopt's xtol test between completed iterations, fused with the per-coordinate secant update of the
+        // inverse diagonal Hessian model  h_i = dx_i / dgradL_i
+        const double moved = cx.sum(n, [&](int i) {
             const double si = w.x[i] - w.x0[i];
             if (si != 0.0) {
                 const double ui = (w.g[i] - lambda * w.a[i]) - w.gl[i];
-                const double r = ui / si;
+                const double r = si / ui;
                 if (r > 0.0 && r < 1e300) {
-                    w.b[i] = r < ACCSQP_BMIN ? ACCSQP_BMIN : (r > ACCSQP_BMAX ? ACCSQP_BMAX : r);
+                    w.b[i] = r < 1.0 / ACCSQP_BMAX ? 1.0 / ACCSQP_BMAX : (r > 1.0 / ACCSQP_BMIN ? 1.0 / ACCSQP_BMIN : r);
                 }
             }
+            return (fabs(si) < w.xtol[i]) ? 0.0 : 1.0;
         });
+        if (moved == 0.0) { ret = SQP_XTOL_REACHED; break; }
+        if (p.maxeval > 0 && st.evals >= p.maxeval) { ret = SQP_MAXEVAL_REACHED; break; }
         b_identity = false;
     }
     st.feasible = feasible ? 1 : 0;
     return ret;
 }
-
-// ---------------------------------------------------------------------------------------
-// Host execution context: one logical lane that reproduces the 32-lane reduction order.
-// ---------------------------------------------------------------------------------------
-struct HostCtx {
-    inline int lane() const { return 0; }
-    inline void sync() const {}
-    template <class Fn>
-    inline void foreach(int n, Fn f) const { for (int i = 0; i < n; ++i) f(i); }
-    template <class Fn>
-    inline double sum(int n, Fn f) const {
-        double p[32];
-        for (int l = 0; l < 32; ++l) p[l] = 0.0;
-        for (int i = 0; i < n; ++i) p[i & 31] += f(i);
-        for (int off = 16; off >= 1; off >>= 1) {
-            double q[32];
-            for (int l = 0; l < 32; ++l) q[l] = p[l] + p[l ^ off];
-            for (int l = 0; l < 32; ++l) p[l] = q[l];
-        }
-        return p[0];
-    }
-    template <class Fn>
-    inline double vmax(int n, Fn f) const {
-        double r = -1e308;
-        for (int i = 0; i < n; ++i) { const double val = f(i); if (val > r) r = val; }
-        return r;
-    }
-    template <class Fn>
-    inline double vmin(int n, Fn f) const {
-        double r = 1e308;
-        for (int i = 0; i < n; ++i) { const double val = f(i); if (val < r) r = val; }
-        return r;
-    }
-};
 
 }  // namespace accsqp
