@@ -70,7 +70,8 @@ static void launch_warp(stream_t, int n, size_t smem, K k) {
     for (int i = 0; i < n; ++i) { HostCtx cx(32); k(cx, i, sm.data()); }
 }
 template <class K>
-static void launch_block_smem(stream_t, int n, int threads, size_t smem, K k) {
+static void launch_block_smem(stream_t, int n, size_t smem, K k) {
+    const int threads = K::THREADS;
     std::vector<unsigned char> sm(smem + 16);
     for (int i = 0; i < n; ++i) { HostCtx cx(threads); k(cx, i, sm.data()); }
 }
@@ -107,7 +108,7 @@ __global__ void __launch_bounds__(256) block_kernel(K k) {
     k(cx, (int)blockIdx.x);
 }
 template <class K>
-__global__ void __launch_bounds__(256) block_smem_kernel(K k) {
+__global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) block_smem_kernel(K k) {
     __shared__ __align__(16) unsigned char scratch[ACC_BLOCK_SCRATCH_BYTES];
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     BlockCtx cx(scratch);
@@ -143,7 +144,8 @@ static void launch_warp(stream_t s, int n, size_t smem, K k) {
     ACC_CUDA(cudaGetLastError());
 }
 template <class K>
-static void launch_block_smem(stream_t s, int n, int threads, size_t smem, K k) {
+static void launch_block_smem(stream_t s, int n, size_t smem, K k) {
+    const int threads = K::THREADS;
     if (n <= 0) return;
     static size_t configured = 0;
     if (smem > configured) {
@@ -269,6 +271,7 @@ struct StorageDelivery {  // thread per storage
 };
 
 struct Purchase {  // one CTA of ACCSQP_GROUP threads per purchasing manager
+    enum { THREADS = ACCSQP_GROUP, MIN_BLOCKS = 6 };
     StorageView st; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
     const i64* in_off; const int* in_edge; const int* in_seller; const SellerPub* pub; int n_max;
     i64* dem_q; double* dem_v; double* exp_costs; double* opt_val; double* tpen; int* iters; int* evals;
@@ -485,8 +488,7 @@ struct acc_engine {
         const bool dev = mp.deviation_penalty != 0;
         // One CTA of ACCSQP_GROUP threads per purchasing manager, all its vectors in shared memory.  The group size is
         // part of the arithmetic (reduction order), so it is a build constant shared with the oracle's host context.
-        static const int group = std::getenv("ACC_PM_THREADS") ? std::atoi(std::getenv("ACC_PM_THREADS")) : ACCSQP_GROUP;  // timing experiments only
-        timed("purchase", [&] { launch_block_smem(stream, nSt, group, pm_workspace_bytes(n_max, dev, true), k); });
+        timed("purchase", [&] { launch_block_smem(stream, nSt, pm_workspace_bytes(n_max, dev), k); });
     }
     void tick() {
         reg = 1 - reg;  // this step's arrivals become the next step's "other" register (Model::switch_registers)

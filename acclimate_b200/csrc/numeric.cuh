@@ -41,8 +41,20 @@ ACC_HD i64 iround(double x) {  // types.h:288-294, std::lrint under FE_TONEAREST
 
 ACC_HD double qf(i64 q) { return (double)q * ACC_PREC3; }   // to_float(FlowQuantity), types.h:336-342
 ACC_HD double pf(i64 p) { return (double)p * ACC_PREC6; }   // to_float(Price)
-ACC_HD i64 mkq(double f) { return iround(f / ACC_PREC3); }  // FlowQuantity(f), types.h:316-319,345
-ACC_HD i64 mkp(double f) { return iround(f / ACC_PREC6); }  // Price(f)
+// lrint(f / precision) without the division on the common path.  f * (1/precision rounded) differs from the
+// correctly rounded quotient by less than 2^-50 relative (precision is within 2 ulp of 10^-digits, plus the two
+// roundings), so both round to the same integer unless a half-integer lies within that distance; only then (and for
+// huge or non-finite arguments, where the test fails as well) the division is carried out.  tests/test_numeric.py
+// checks the equivalence exhaustively around the rounding boundaries.
+ACC_HD i64 quantise(double f, double prec, double inv) {
+    const double q1 = f * inv;
+    const double r = rint(q1);
+    const double margin = 0.5 - fabs(q1 - r);
+    if (margin > fabs(q1) * 0x1p-48) return (i64)r;
+    return iround(f / prec);
+}
+ACC_HD i64 mkq(double f) { return quantise(f, ACC_PREC3, 1e3); }  // FlowQuantity(f), types.h:316-319,345
+ACC_HD i64 mkp(double f) { return quantise(f, ACC_PREC6, 1e6); }  // Price(f)
 ACC_HD i64 mkt(double f) { return iround(f / 1.0); }        // Time(f): 0 digits, precision 1
 
 // std::max / std::min with their exact tie and signed-zero behaviour

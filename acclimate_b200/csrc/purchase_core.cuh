@@ -24,25 +24,28 @@ struct PtrVec {
 ACC_HD void attach(PtrVec& v, double*& p, int n) { v.p = p; p += n; }
 
 // shared-memory vectors of one purchasing manager besides the solver's own: 13 f64 (+1 with deviation_penalty) + 2 int
-#define ACC_PM_NVEC_SOLVER 10
-#define ACC_PM_NVEC_CONST 13
-ACC_HD size_t pm_workspace_bytes(int n_max, bool separate_target, bool solver_in_memory) {
-    const int nvec = ACC_PM_NVEC_CONST + (separate_target ? 1 : 0) + (solver_in_memory ? ACC_PM_NVEC_SOLVER : 0);
+// shared-memory vectors of one purchasing manager: 9 of the solver, 11 price-curve vectors (+1 with deviation_penalty), 2 int
+#define ACC_PM_NVEC_SOLVER 9
+#define ACC_PM_NVEC_CONST 11
+ACC_HD size_t pm_workspace_bytes(int n_max, bool separate_target) {
+    const int nvec = ACC_PM_NVEC_CONST + (separate_target ? 1 : 0) + ACC_PM_NVEC_SOLVER;
     return (size_t)n_max * (nvec * sizeof(double) + 2 * sizeof(int));
 }
 
-template <class Vec>
-struct PMWorkT {
+struct PMWork {
     struct W {
-        Vec x, x0, g, a, d, b, gl, xbest;  // sqp_core work vectors
-        Vec xu, xtol;                      // upper bounds and tolerances (lower bounds are all zero, :620)
+        PtrVec x, x0, g, a, d, b, gl, xbest;  // sqp_core work vectors
+        PtrVec xu;                            // upper bounds (lower bounds are all zero, :620)
+        const double* zf;                     // x tolerance = quantum of the demand request over the variable's scale (:640-644)
+        double tol_c;
         ACC_HD double lower(int) const { return 0.0; }
+        ACC_HD double tol(int i) const { return tol_c / zf[i]; }
     } w;
     // price-curve constants per purchasing connection (shared memory)
     double *zf;              // to_float(Z*): scale of the variable (:184-188)
     double *tgt;             // transport penalty target (Z*, or the last demand request with deviation_penalty)
     double *addX;            // expected_additional_production (:343-349)
-    double *Xhatf, *lamXf, *c1, *c2;  // seller constants (SellerPub)
+    double *Xhatf, *lamXf, *c2;  // seller constants (SellerPub); c1 = c2 / 2 exactly
     double *base;            // n_bar [- pen(X_exp)/X_exp]: E_n_r without its X_new term (:255-271)
     double *n_co, *Dmin;     // reservation price and kink position of the price curve (:283-289)
     double *slope;           // (n_bar_min - n_co) / D_r_min in the linear regime; NaN marks the cropped regime (n_co > n_bar_min)
@@ -51,17 +54,17 @@ struct PMWorkT {
     ACC_HD void carve(unsigned char* mem, int n_max, bool separate_target) {
         double* p = reinterpret_cast<double*>(mem);
         attach(w.x, p, n_max); attach(w.x0, p, n_max); attach(w.g, p, n_max); attach(w.a, p, n_max); attach(w.d, p, n_max);
-        attach(w.b, p, n_max); attach(w.gl, p, n_max); attach(w.xbest, p, n_max); attach(w.xu, p, n_max); attach(w.xtol, p, n_max);
-        zf = p; p += n_max; addX = p; p += n_max; Xhatf = p; p += n_max; lamXf = p; p += n_max; c1 = p; p += n_max; c2 = p; p += n_max;
+        attach(w.b, p, n_max); attach(w.gl, p, n_max); attach(w.xbest, p, n_max); attach(w.xu, p, n_max);
+        zf = p; p += n_max; addX = p; p += n_max; Xhatf = p; p += n_max; lamXf = p; p += n_max; c2 = p; p += n_max;
         base = p; p += n_max; n_co = p; p += n_max; Dmin = p; p += n_max; slope = p; p += n_max;
         term = p; p += n_max; dval = p; p += n_max;
+        w.zf = zf;
         tgt = zf;  // the penalty target is Z* itself unless deviation_penalty is set
         if (separate_target) { tgt = p; p += n_max; }
         int* q = reinterpret_cast<int*>(p);
         idx = q; q += n_max; eid = q;
     }
 };
-typedef PMWorkT<PtrVec> PMWork;
 
 struct PMParams {
     double Uf;        // to_float(initial_used_flow_U_star): scale of objective and constraint (:194,:200)
@@ -88,7 +91,7 @@ ACC_HD CurvePoint curve_at(const PW& k, const PMParams& pp, int r, double D) {
     const double lam = k.lamXf[r];
     if (Xn > lam && Xn > 0.0) {  // in production extension (:151,:175)
         const double dx = Xn - lam;
-        const double pen = stdmax(0.0, k.c1[r] * dx * dx);
+        const double pen = stdmax(0.0, 0.5 * k.c2[r] * dx * dx);
         E = k.base[r] + pen / Xn;
         gE = k.c2[r] * dx / Xn - pen / Xn / Xn;
     }
@@ -198,6 +201,7 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         return res;
     }
     PMParams pp;
+    k.w.tol_c = ACC_PREC3 * mp.prec_adj;
     pp.Uf = qf(Ustar_q);
     pp.markup = pf(sec.markup);
     pp.pen_large = pf(mp.pen_large); pp.pen_small = pf(mp.pen_small);
@@ -228,7 +232,6 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         k.addX[r] = add;
         k.Xhatf[r] = sp.Xhatf;
         k.lamXf[r] = lamXf;
-        k.c1[r] = sp.c1;
         k.c2[r] = sp.c2;
         // n_r constants, :279-289 (penalty terms only divided out inside the production extension)
         const double Dmin = stdmax(0.0, lamXf - add);
@@ -246,7 +249,6 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         k.slope[r] = (n_co <= nbar_min) ? (nbar_min - n_co) / Dmin : (double)NAN;
         // bounds, start value, xtol, :620-644; constraint gradient, :209
         k.w.xu[r] = upper / zf;
-        k.w.xtol[r] = (ACC_PREC3 * mp.prec_adj) / zf;
         k.w.x[r] = stdmin(upper, stdmax(0.0, Xe - add)) / zf;
         k.w.a[r] = -(zf / pp.Uf);
         return dmax;

@@ -68,6 +68,7 @@ struct Work {
     double *x, *x0, *g, *a, *d, *b, *gl, *xbest;
     const double *xl, *xu, *xtol;
     SQP_HD double lower(int i) const { return xl != nullptr ? xl[i] : 0.0; }
+    SQP_HD double tol(int i) const { return xtol[i]; }
 };
 #define ACCSQP_NVEC 8  // number of length-n work vectors above
 // lower bounds may be omitted (null pointer = all zero); step bounds are derived where they are used
@@ -220,7 +221,7 @@ SQP_HD double con_violation(int ctype, double c) {
     return 0.0;
 }
 
-// W is any work-vector set with members x, x0, g, a, d, b, gl, xbest, xu, xtol indexable by [i] and lower(i):
+// W is any work-vector set with members x, x0, g, a, d, b, gl, xbest, xu indexable by [i], lower(i) and tol(i) (x tolerance):
 // plain pointers (struct Work: host shim, emulation, shared-memory kernel) or per-lane register vectors (device).
 template <class Ctx, class Eval, class W>
 SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
@@ -262,7 +263,7 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
             w.d[i] = di;
             w.gl[i] = w.g[i] - lambda * w.a[i];
             w.x0[i] = w.x[i];
-            Sum3 r; r.a = w.a[i] * di; r.b = (fabs(di) < w.xtol[i]) ? 0.0 : 1.0; r.c = w.g[i] * di;
+            Sum3 r; r.a = w.a[i] * di; r.b = (fabs(di) < w.tol(i)) ? 0.0 : 1.0; r.c = w.g[i] * di;
             return r;
         });
         const double cres = (p.ctype == CON_NONE) ? 0.0 : c + sd.a;
@@ -351,7 +352,7 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
                     w.b[i] = r < 1.0 / ACCSQP_BMAX ? 1.0 / ACCSQP_BMAX : (r > 1.0 / ACCSQP_BMIN ? 1.0 / ACCSQP_BMIN : r);
                 }
             }
-            return (fabs(si) < w.xtol[i]) ? 0.0 : 1.0;
+            return (fabs(si) < w.tol(i)) ? 0.0 : 1.0;
         });
         if (moved == 0.0) { ret = SQP_XTOL_REACHED; break; }
         if (p.maxeval > 0 && st.evals >= p.maxeval) { ret = SQP_MAXEVAL_REACHED; break; }
