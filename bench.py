@@ -131,6 +131,16 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu --set full capture of this
+    same workload (profiles/r01_traffic.json names the summary it was read from); None when no capture is on file."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            return json.load(f)[kernel]["dram_bytes_per_launch"]
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def cpu_baseline_sample(seconds_budget=25.0):
     """oracle/_ref timed on this box's host cores on a bounded sample (rank 0, N = 1 only)."""
     from acclimate_b200 import netfile, synth
@@ -259,7 +269,8 @@ def main():
             per_launch_s = dom[1][0] * 1e-3 / dom[1][1]
             bpe = KERNEL_BYTES_PER_EDGE.get(dom[0], BYTES_PER_UPDATE)
             achieved = bpe * n_edges / per_launch_s / 1e9
-            roof = {"bound": "hbm", "kernel": dom[0], "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            roof = {"bound": "hbm", "kernel": dom[0], "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": ncu_traffic(dom[0]) if args.config == "eora" else None,
                     "algorithmic_bytes_per_connection": bpe, "avg_launch_ms": per_launch_s * 1e3, "peak_source": peak_src,
                     "kernel_share_of_step": dom[1][0] / max(sum(v[0] for v in ktimes.values()), 1e-12),
                     "kernels_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items()},
