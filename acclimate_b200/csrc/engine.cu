@@ -196,9 +196,10 @@ struct SellerExpectation {  // warp per firm
 
 struct StorageDelivery {  // thread per storage
     StorageView st; FirmView fv; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
-    const i64* ell_off; const int* ell_width; const int* ell_edge;
+    const i64* ell_off; const int* ell_width; const int* ell_edge; const unsigned char* owned;  // owned == nullptr: every agent
     ACC_HD void operator()(int s) const {
         const int a = st.agent[s];
+        if (owned != nullptr && !owned[a]) return;
         const SectorP sp = sectors[st.sector[s]];
         // ---- input use and storage content ----
         const Flow uhat = possible_use(st, s, mp.dt, false);
@@ -273,10 +274,11 @@ struct StorageDelivery {  // thread per storage
 struct Purchase {  // one CTA of ACCSQP_GROUP threads per purchasing manager
     enum { THREADS = ACCSQP_GROUP, MIN_BLOCKS = 6 };
     StorageView st; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
-    const i64* in_off; const int* in_edge; const int* in_seller; const SellerPub* pub; int n_max;
+    const i64* in_off; const int* in_edge; const int* in_seller; const SellerPub* pub; int n_max; const int* pm_ids;  // pm_ids == nullptr: all
     i64* dem_q; double* dem_v; double* exp_costs; double* opt_val; double* tpen; int* iters; int* evals;
     template <class Ctx>
-    ACC_HD void operator()(Ctx& cx, int s, unsigned char* smem) const {
+    ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const {
+        const int s = pm_ids != nullptr ? pm_ids[item] : item;
         PMWork k;
         k.carve(smem, n_max, mp.deviation_penalty != 0);
         const i64 o = in_off[s];
@@ -311,6 +313,50 @@ struct FirmIncomingDemand {  // CTA per firm: sum of the demand requests it hold
         const int e0 = ev.seller_off[f];
         const BookTotals t = book_totals(cx, ev.seller_off[f + 1] - e0, ev.D_q + e0, ev.D_p + e0);
         if (cx.leader()) { out_q[f] = t.sq; out_v[f] = t.sv; }
+    }
+};
+
+// ---- exchange of a region-partitioned run (thread per halo entry / per agent) ----
+ACC_HD i64 f64_bits(double v) { i64 b; memcpy(&b, &v, sizeof b); return b; }
+ACC_HD double bits_f64(i64 b) { double v; memcpy(&v, &b, sizeof v); return v; }
+struct PackFlow {  // shipment of this step: the conveyor slot it was written to
+    EdgeView ev; i64 step; const i64* ids; i64* buf;
+    ACC_HD void operator()(int i) const {
+        const i64 e = ids[i];
+        const i64 at = (i64)((step + ev.tau[e]) % ev.T) * ev.n_edges + e;
+        buf[2 * (i64)i] = ev.conv_q[at]; buf[2 * (i64)i + 1] = f64_bits(ev.conv_v[at]);
+    }
+};
+struct UnpackFlow {
+    EdgeView ev; i64 step; const i64* ids; const i64* buf;
+    ACC_HD void operator()(int i) const {
+        const i64 e = ids[i];
+        const i64 at = (i64)((step + ev.tau[e]) % ev.T) * ev.n_edges + e;
+        ev.conv_q[at] = buf[2 * (i64)i]; ev.conv_v[at] = bits_f64(buf[2 * (i64)i + 1]);
+    }
+};
+struct PackDemand {
+    EdgeView ev; const i64* ids; i64* buf;
+    ACC_HD void operator()(int i) const { const i64 e = ids[i]; buf[2 * (i64)i] = ev.D_q[e]; buf[2 * (i64)i + 1] = ev.D_p[e]; }
+};
+struct UnpackDemand {
+    EdgeView ev; const i64* ids; const i64* buf;
+    ACC_HD void operator()(int i) const { const i64 e = ids[i]; ev.D_q[e] = buf[2 * (i64)i]; ev.D_p[e] = buf[2 * (i64)i + 1]; }
+};
+static_assert(sizeof(SellerPub) == ACC_SELLER_WORDS * sizeof(i64), "seller table row size is part of the C ABI");
+struct PackSellers {  // owned rows as they are, zero elsewhere: an integer SUM over the ranks then copies every row from its owner
+    const SellerPub* pub; const unsigned char* owned; i64* table;
+    ACC_HD void operator()(int a) const {
+        const i64* src = reinterpret_cast<const i64*>(pub + a);
+        for (int k = 0; k < ACC_SELLER_WORDS; ++k) table[(i64)a * ACC_SELLER_WORDS + k] = owned[a] ? src[k] : 0;
+    }
+};
+struct UnpackSellers {
+    SellerPub* pub; const unsigned char* owned; const i64* table;
+    ACC_HD void operator()(int a) const {
+        if (owned[a]) return;
+        i64* dst = reinterpret_cast<i64*>(pub + a);
+        for (int k = 0; k < ACC_SELLER_WORDS; ++k) dst[k] = table[(i64)a * ACC_SELLER_WORDS + k];
     }
 };
 
@@ -371,6 +417,13 @@ struct acc_engine {
     // buyer-side lists
     DBuf<i64> ell_off, in_off;
     DBuf<int> ell_width, ell_edge, in_edge, in_seller;
+    // region partition (empty = the engine owns every agent)
+    bool partitioned = false;
+    int n_pm = 0;  // purchasing managers of owned agents
+    DBuf<unsigned char> owned;
+    DBuf<int> pm_ids;
+    DBuf<i64> halo_send, halo_recv;
+    i64 *x_flow_send = nullptr, *x_flow_recv = nullptr, *x_dem_send = nullptr, *x_dem_recv = nullptr, *x_sellers = nullptr;  // caller-owned
     // events
     DBuf<Event> ev_buf;
     DBuf<int> ev_count;
@@ -464,7 +517,7 @@ struct acc_engine {
 #endif
     }
 
-    void phase_cp() {
+    void stage_sell() {
         {
             FirmPossibleProduction k{firm_view(), storage_view(), mp, firm_ids.p};
             timed("firm_possible_production", [&] { launch_thread(stream, nF, k); });
@@ -473,22 +526,74 @@ struct acc_engine {
             SellerProduction k{firm_view(), edge_view(), mp, sectors.p, sink(), step, firm_ids.p};
             timed("seller_production", [&] { launch_block(stream, nF, 256, k); });
         }
-        {
-            StorageDelivery k{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p};
-            timed("storage_delivery", [&] { launch_thread(stream, nSt, k); });
+        if (halo_send.n) {
+            PackFlow k{edge_view(), step, halo_send.p, x_flow_send};
+            timed("pack_flow", [&] { launch_thread(stream, (int)halo_send.n, k); });
         }
     }
+    void stage_deliver() {
+        if (halo_recv.n) {
+            UnpackFlow k{edge_view(), step, halo_recv.p, x_flow_recv};
+            timed("unpack_flow", [&] { launch_thread(stream, (int)halo_recv.n, k); });
+        }
+        {
+            StorageDelivery k{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p,
+                              partitioned ? owned.p : nullptr};
+            timed("storage_delivery", [&] { launch_thread(stream, nSt, k); });
+        }
+        {
+            SellerExpectation k{firm_view(), edge_view(), storage_view(), mp, sectors.p, sink(), firm_ids.p};
+            timed("seller_expectation", [&] { launch_warp(stream, nF, 0, k); });
+        }
+        if (partitioned && x_sellers != nullptr) {
+            PackSellers k{pub.p, owned.p, x_sellers};
+            timed("pack_sellers", [&] { launch_thread(stream, nA, k); });
+        }
+    }
+    void stage_purchase() {
+        if (partitioned && x_sellers != nullptr) {
+            UnpackSellers k{pub.p, owned.p, x_sellers};
+            timed("unpack_sellers", [&] { launch_thread(stream, nA, k); });
+        }
+        Purchase k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, pub.p, n_max,
+                   partitioned ? pm_ids.p : nullptr, s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
+        const bool dev = mp.deviation_penalty != 0;
+        // One CTA of ACCSQP_GROUP threads per purchasing manager, all its vectors in shared memory.  The group size is
+        // part of the arithmetic (reduction order), so it is a build constant shared with the oracle's host context.
+        timed("purchase", [&] { launch_block_smem(stream, partitioned ? n_pm : nSt, pm_workspace_bytes(n_max, dev), k); });
+        if (halo_recv.n) {
+            PackDemand pk{edge_view(), halo_recv.p, x_dem_send};
+            timed("pack_demand", [&] { launch_thread(stream, (int)halo_recv.n, pk); });
+        }
+    }
+    void stage_close() {
+        if (halo_send.n) {
+            UnpackDemand k{edge_view(), halo_send.p, x_dem_recv};
+            timed("unpack_demand", [&] { launch_thread(stream, (int)halo_send.n, k); });
+        }
+        tick();
+    }
+    void require_single(const char* what) {
+        if (partitioned) fail(std::string(what) + ": this engine is one part of a region-partitioned run; drive it with acc_stage and exchange the halos in between");
+    }
+    // the reference's phases (Model::iterate_*) on an unpartitioned engine
+    void phase_cp() {
+        require_single("acc_phase");
+        FirmPossibleProduction k1{firm_view(), storage_view(), mp, firm_ids.p};
+        timed("firm_possible_production", [&] { launch_thread(stream, nF, k1); });
+        SellerProduction k2{firm_view(), edge_view(), mp, sectors.p, sink(), step, firm_ids.p};
+        timed("seller_production", [&] { launch_block(stream, nF, 256, k2); });
+        StorageDelivery k3{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p, nullptr};
+        timed("storage_delivery", [&] { launch_thread(stream, nSt, k3); });
+    }
     void phase_exp() {
+        require_single("acc_phase");
         SellerExpectation k{firm_view(), edge_view(), storage_view(), mp, sectors.p, sink(), firm_ids.p};
         timed("seller_expectation", [&] { launch_warp(stream, nF, 0, k); });
     }
     void phase_pur() {
-        Purchase k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, pub.p, n_max,
-                   s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
-        const bool dev = mp.deviation_penalty != 0;
-        // One CTA of ACCSQP_GROUP threads per purchasing manager, all its vectors in shared memory.  The group size is
-        // part of the arithmetic (reduction order), so it is a build constant shared with the oracle's host context.
-        timed("purchase", [&] { launch_block_smem(stream, nSt, pm_workspace_bytes(n_max, dev), k); });
+        require_single("acc_phase");
+        stage_purchase();
     }
     void tick() {
         reg = 1 - reg;  // this step's arrivals become the next step's "other" register (Model::switch_registers)
@@ -501,8 +606,9 @@ struct acc_engine {
 // ------------------------------------------------------------------------------------------------
 namespace acc {
 
-static void build(acc_engine& E, const acc_network& net, const acc_params& par) {
+static void build(acc_engine& E, const acc_network& net, const acc_params& par, const uint8_t* agent_owned) {
     stream_t s = E.stream;
+    auto own = [&](i64 a) { return agent_owned == nullptr || agent_owned[a] != 0; };
     const i64 nS = net.n_sectors, nR = net.n_regions, nA = net.n_agents, nE = net.n_edges;
     if (nS <= 0 || nR <= 0 || nA <= 0 || nE <= 0) fail("empty network");
     if (nE >= (i64)0x7fffffff) fail("more than 2^31-1 connections on one device: partition the network");
@@ -639,6 +745,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par) 
     }
     // clean_network must be a no-op for a valid snapshot (ModelInitializer.cpp:215-299)
     for (i64 a = 0; a < nA; ++a) {
+        if (!own(a)) continue;  // agents of other parts are present with only the connections that touch this part
         if (a_type[a] == 1) {
             i64 input = 0;
             for (int k = a_st_off[a]; k < a_st_off[a + 1]; ++k) input += Istar_q[a_st_list[k]];
@@ -652,14 +759,16 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par) 
     std::vector<double> st_a(nSt);
     for (int k = 0; k < nSt; ++k) {
         const int a = st_agent[k];
-        st_a[k] = a_type[a] == 1 ? ratio(Istar_q[k], Xstar_q[a]) : net.consumer_elasticity[st_sector[k]];
+        st_a[k] = !own(a) ? 0.0 : (a_type[a] == 1 ? ratio(Istar_q[k], Xstar_q[a]) : net.consumer_elasticity[st_sector[k]]);
     }
     // SalesManager::initialize, SalesManager.cpp:626-643
     std::vector<i64> markup_eff(nA, 0), var_costs(nA, 0), est_q(nA, 0), X_q(nA, 0);
     std::vector<double> est_v(nA, 0.0), X_v(nA, 0.0);
-    std::vector<int> firm_ids;
+    std::vector<int> firm_ids, all_firms;
     for (i64 a = 0; a < nA; ++a) {
         if (a_type[a] != 1) continue;
+        all_firms.push_back((int)a);
+        if (!own(a)) continue;
         firm_ids.push_back((int)a);
         i64 c0 = 0;
         for (int k = a_st_off[a]; k < a_st_off[a + 1]; ++k) c0 += pmul(mkp(1.0), st_a[a_st_list[k]]);
@@ -768,7 +877,17 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par) 
     dev_sync(s);
 
     E.h_agent_type = a_type; E.h_agent_sector = a_sector; E.h_agent_region = a_region; E.h_st_agent = st_agent; E.h_st_sector = st_sector;
-    E.h_cid2s = cid2s; E.h_firm_ids = firm_ids; E.h_tau = tau;
+    E.h_cid2s = cid2s; E.h_firm_ids = all_firms; E.h_tau = tau;
+    if (agent_owned != nullptr) {
+        E.partitioned = true;
+        std::vector<unsigned char> ow(nA);
+        for (i64 a = 0; a < nA; ++a) ow[a] = own(a) ? 1 : 0;
+        std::vector<int> pm;
+        for (int k = 0; k < nSt; ++k) if (ow[st_agent[k]]) pm.push_back(k);
+        E.n_pm = (int)pm.size();
+        E.owned.upload(ow, s); E.pm_ids.upload(pm, s);
+        dev_sync(s);
+    }
     for (i64 a = 0; a < nA; ++a)
         if (a_type[a] != 1)
             for (int k = a_st_off[a]; k < a_st_off[a + 1]; ++k) E.h_consumer_st.push_back(a_st_list[k]);
@@ -817,6 +936,12 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
         return true;
     }
     // storages (creation order)
+    if (name == "sto_agent" || name == "sto_sector") {  // identity of each storage (creation order): buying agent, input sector
+        const std::vector<int>& h = name == "sto_agent" ? E.h_st_agent : E.h_st_sector;
+        std::vector<i64> dev(h.begin(), h.end());
+        out.i = to_creation_order(E, dev); out.is_f64 = false;
+        return true;
+    }
     if (name == "sto_S_q") return SI(E.s_S_q);
     if (name == "sto_S_v") return SF(E.s_S_v);
     if (name == "sto_I_q") return SI(E.s_Il_q);
@@ -934,7 +1059,9 @@ extern "C" {
 
 const char* acc_last_error(void) { return acc::g_last_error.c_str(); }
 
-acc_engine* acc_create(const acc_network* net, const acc_params* params, int device) {
+acc_engine* acc_create(const acc_network* net, const acc_params* params, int device) { return acc_create_partition(net, params, device, nullptr); }
+
+acc_engine* acc_create_partition(const acc_network* net, const acc_params* params, int device, const uint8_t* agent_owned) {
     acc_engine* E = nullptr;
     try {
         if (net == nullptr || params == nullptr) fail("acc_create: null argument");
@@ -946,7 +1073,7 @@ acc_engine* acc_create(const acc_network* net, const acc_params* params, int dev
         ACC_CUDA(cudaSetDevice(device));
         ACC_CUDA(cudaStreamCreateWithFlags(&E->stream, cudaStreamNonBlocking));
 #endif
-        build(*E, *net, *params);
+        build(*E, *net, *params, agent_owned);
         return E;
     } catch (const acc::EngineError& ex) {
         acc::g_last_error = ex.msg;
@@ -978,6 +1105,7 @@ void acc_destroy(acc_engine* e) {
                          &e->s_evals, &e->e_seller_off, &e->e_entity, &e->ell_width, &e->ell_edge, &e->in_edge, &e->in_seller, &e->ev_count})
         b->free();
     e->e_tau.free(); e->e_dom.free(); e->sectors.free(); e->pub.free(); e->ev_buf.free();
+    e->owned.free(); e->pm_ids.free(); e->halo_send.free(); e->halo_recv.free();
     delete e;
 }
 
@@ -1021,9 +1149,46 @@ int acc_phase(acc_engine* e, int phase) {
     ACC_API_END(-1)
 }
 
+int acc_set_halo(acc_engine* e, const int64_t* send_edges, size_t n_send, const int64_t* recv_edges, size_t n_recv, void* flow_send, void* flow_recv,
+                 void* demand_send, void* demand_recv, void* seller_table) {
+    ACC_API_BEGIN
+    if (e == nullptr) fail("acc_set_halo: null engine");
+    if (!e->partitioned) fail("acc_set_halo: the engine was not created with acc_create_partition");
+    if ((n_send && (send_edges == nullptr || flow_send == nullptr || demand_recv == nullptr)) ||
+        (n_recv && (recv_edges == nullptr || flow_recv == nullptr || demand_send == nullptr)) || seller_table == nullptr)
+        fail("acc_set_halo: null list or exchange buffer");
+    if (n_send >= (size_t)0x7fffffff || n_recv >= (size_t)0x7fffffff) fail("acc_set_halo: halo too large");
+    for (size_t k = 0; k < n_send; ++k) if (send_edges[k] < 0 || send_edges[k] >= e->nE) fail("acc_set_halo: send connection out of range");
+    for (size_t k = 0; k < n_recv; ++k) if (recv_edges[k] < 0 || recv_edges[k] >= e->nE) fail("acc_set_halo: receive connection out of range");
+    e->halo_send.upload(std::vector<i64>(send_edges, send_edges + n_send), e->stream);
+    e->halo_recv.upload(std::vector<i64>(recv_edges, recv_edges + n_recv), e->stream);
+    dev_sync(e->stream);
+    e->x_flow_send = static_cast<i64*>(flow_send); e->x_flow_recv = static_cast<i64*>(flow_recv);
+    e->x_dem_send = static_cast<i64*>(demand_send); e->x_dem_recv = static_cast<i64*>(demand_recv);
+    e->x_sellers = static_cast<i64*>(seller_table);
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_stage(acc_engine* e, int stage) {
+    ACC_API_BEGIN
+    if (e == nullptr) fail("acc_stage: null engine");
+    if (e->partitioned && e->x_sellers == nullptr) fail("acc_stage: call acc_set_halo first");
+    switch (stage) {
+        case ACC_STAGE_SELL: e->stage_sell(); break;
+        case ACC_STAGE_DELIVER: e->stage_deliver(); break;
+        case ACC_STAGE_PURCHASE: e->stage_purchase(); break;
+        case ACC_STAGE_CLOSE: e->stage_close(); break;
+        default: fail("acc_stage: unknown stage");
+    }
+    return 0;
+    ACC_API_END(-1)
+}
+
 int acc_step(acc_engine* e) {
     ACC_API_BEGIN
     if (e == nullptr) fail("acc_step: null engine");
+    e->require_single("acc_step");
     e->phase_cp();
     e->phase_exp();
     e->phase_pur();

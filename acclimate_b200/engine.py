@@ -78,27 +78,33 @@ def load_library(path=None):
     return lib
 
 
+def network_struct(arrays):
+    """acc_network / acc_params views of a snapshot dict; the third value keeps the arrays alive."""
+    a = {k: np.ascontiguousarray(v) for k, v in arrays.items()}
+    meta = a["meta"].astype(np.int64)
+    keep = [
+        a["agent_type"].astype(np.int64), a["agent_sector"].astype(np.int64), a["agent_region"].astype(np.int64),
+        a["agent_beta"].astype(np.float64), a["edge_from"].astype(np.int64), a["edge_to"].astype(np.int64),
+        a["edge_zq"].astype(np.int64), a["delay"].astype(np.int64), a["sector_f64"].astype(np.float64),
+        a["consumer_elasticity"].astype(np.float64),
+    ]
+    net = _Network(int(meta[0]), int(meta[1]), int(meta[2]), int(meta[3]), *[x.ctypes.data for x in keep])
+    par = _Params()
+    mp = a["model_f64"].astype(np.float64)
+    if mp.size != MP_COUNT:
+        raise EngineError("model_f64 has the wrong length")
+    for i in range(MP_COUNT):
+        par.model[i] = float(mp[i])
+    return net, par, keep
+
+
 class Engine:
     """One device-resident model.  `arrays` is a network snapshot as produced by synth.make_network / netfile.read."""
 
     def __init__(self, arrays, device=0, lib_path=None):
         self.lib = load_library(lib_path)
-        a = {k: np.ascontiguousarray(v) for k, v in arrays.items()}
-        meta = a["meta"].astype(np.int64)
-        self._keep = [
-            a["agent_type"].astype(np.int64), a["agent_sector"].astype(np.int64), a["agent_region"].astype(np.int64),
-            a["agent_beta"].astype(np.float64), a["edge_from"].astype(np.int64), a["edge_to"].astype(np.int64),
-            a["edge_zq"].astype(np.int64), a["delay"].astype(np.int64), a["sector_f64"].astype(np.float64),
-            a["consumer_elasticity"].astype(np.float64),
-        ]
-        net = _Network(int(meta[0]), int(meta[1]), int(meta[2]), int(meta[3]), *[x.ctypes.data for x in self._keep])
-        par = _Params()
-        mp = a["model_f64"].astype(np.float64)
-        if mp.size != MP_COUNT:
-            raise EngineError("model_f64 has the wrong length")
-        for i in range(MP_COUNT):
-            par.model[i] = float(mp[i])
-        self.n_sectors, self.n_regions, self.n_agents, self.n_edges = (int(x) for x in meta[:4])
+        net, par, self._keep = network_struct(arrays)
+        self.n_sectors, self.n_regions, self.n_agents, self.n_edges = (int(x) for x in np.asarray(arrays["meta"])[:4])
         self.h = self.lib.acc_create(C.byref(net), C.byref(par), int(device))
         if not self.h:
             raise EngineError(self.lib.acc_last_error().decode())

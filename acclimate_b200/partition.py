@@ -1,0 +1,182 @@
+"""Region-partitioned run: one engine per GPU, agents split by region.
+
+The reference runs its agent loops with OpenMP over shared memory (reference src/model/Model.cpp:59-118).  Across GPUs
+the same loops are split by the REGION of the agent; what the reference passes between agents through pointers
+becomes three exchanges per timestep:
+
+  shipments       seller -> buyer   BusinessConnection::push_flow_Z            (reference src/model/BusinessConnection.cpp:87-94)
+  supply params   seller -> all     SalesManager::communicated_parameters     (reference src/model/SalesManager.cpp:611-624)
+  demand requests buyer  -> seller  BusinessConnection::send_demand_request_D  (reference src/model/BusinessConnection.cpp:127-131)
+
+Every connection datum has one writer and one reader per step, every agent sees its complete connection lists in the
+global order, and reductions keep their fixed order: a P-part run is bit-identical to the single-engine run.
+
+torch.distributed is the plumbing here (NCCL all-to-all / all-reduce on the engine's stream; gloo in the CPU tests);
+the engine itself (csrc/engine.cu) only packs and unpacks the exchange buffers.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import engine as _engine
+
+SELLER_WORDS = 9  # ACC_SELLER_WORDS, include/acclimate_b200.h
+
+
+def assign_regions(arrays, world):
+    """Contiguous blocks of regions per part, balanced by the number of connections that end in the block
+    (the purchasing side is the expensive one).  Returns region -> part."""
+    R = int(arrays["meta"][1])
+    if world > R:
+        raise ValueError("more parts than regions")
+    reg = np.asarray(arrays["agent_region"], dtype=np.int64)
+    load = np.bincount(reg[np.asarray(arrays["edge_to"], dtype=np.int64)], minlength=R).astype(np.float64)
+    load += np.bincount(reg[np.asarray(arrays["edge_from"], dtype=np.int64)], minlength=R) * 0.25
+    cum = np.cumsum(load)
+    owner = np.minimum((cum - load / 2) * world / cum[-1], world - 1).astype(np.int64)
+    # every part needs at least one region: repair empty parts by walking the boundaries
+    for p in range(world):
+        if not np.any(owner == p):
+            owner = np.minimum(np.arange(R) * world // R, world - 1)
+            break
+    return owner
+
+
+class Part:
+    """What one rank needs: its sub-network, ownership mask and halo lists (local connection ids grouped by peer)."""
+
+    def __init__(self, arrays, region_owner, rank):
+        a = arrays
+        world = int(region_owner.max()) + 1
+        agent_part = np.asarray(region_owner, dtype=np.int64)[np.asarray(a["agent_region"], dtype=np.int64)]
+        self.rank, self.world = rank, world
+        self.agent_part = agent_part
+        self.owned = (agent_part == rank).astype(np.uint8)
+        ef = np.asarray(a["edge_from"], dtype=np.int64)
+        et = np.asarray(a["edge_to"], dtype=np.int64)
+        pf, pt = agent_part[ef], agent_part[et]
+        keep = (pf == rank) | (pt == rank)
+        self.edge_gid = np.nonzero(keep)[0]          # local id -> global connection id (order preserved)
+        lf, lt = pf[keep], pt[keep]
+        local = {k: v for k, v in a.items()}
+        local["edge_from"], local["edge_to"] = ef[keep], et[keep]
+        local["edge_zq"] = np.asarray(a["edge_zq"], dtype=np.int64)[keep]
+        meta = np.array(a["meta"], dtype=np.int64).copy()
+        meta[3] = int(keep.sum())
+        local["meta"] = meta
+        self.arrays = local
+        ids = np.arange(meta[3], dtype=np.int64)
+        send, recv, self.send_counts, self.recv_counts = [], [], [], []
+        for p in range(world):
+            s = ids[(lf == rank) & (lt == p)] if p != rank else ids[:0]
+            r = ids[(lt == rank) & (lf == p)] if p != rank else ids[:0]
+            send.append(s); recv.append(r)
+            self.send_counts.append(int(s.size)); self.recv_counts.append(int(r.size))
+        self.send_edges = np.concatenate(send) if send else ids[:0]
+        self.recv_edges = np.concatenate(recv) if recv else ids[:0]
+        # connections whose seller / buyer this part owns (their seller-side / buyer-side state is authoritative here)
+        self.sells = lf == rank
+        self.buys = lt == rank
+
+
+class PartitionedEngine(_engine.Engine):
+    """One part of a region-partitioned model.  Needs an initialised torch.distributed process group with one rank
+    per part (NCCL for the CUDA library; the CPU tests drive the emulation library over gloo)."""
+
+    def __init__(self, arrays, region_owner=None, device=0, lib_path=None, group=None, tensor_device=None):
+        import torch
+        import torch.distributed as dist
+
+        self.torch, self.dist, self.group = torch, dist, group
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        if region_owner is None:
+            region_owner = assign_regions(arrays, world)
+        if int(np.max(region_owner)) + 1 != world:
+            raise _engine.EngineError("region_owner does not name one part per rank")
+        self.part = Part(arrays, np.asarray(region_owner), rank)
+        self.lib = _engine.load_library(lib_path)
+        self._bind()
+        net, par, self._keep = _engine.network_struct(self.part.arrays)
+        meta = self.part.arrays["meta"]
+        self.n_sectors, self.n_regions, self.n_agents, self.n_edges = (int(x) for x in meta[:4])
+        self._owned = np.ascontiguousarray(self.part.owned)
+        self.h = self.lib.acc_create_partition(C.byref(net), C.byref(par), int(device), self._owned.ctypes.data)
+        if not self.h:
+            raise _engine.EngineError(self.lib.acc_last_error().decode())
+        if tensor_device is None:
+            tensor_device = "cuda:%d" % device
+        self.tensor_device = torch.device(tensor_device)
+        p = self.part
+        ns, nr = int(p.send_edges.size), int(p.recv_edges.size)
+        mk = lambda rows, cols: torch.zeros((rows, cols), dtype=torch.int64, device=self.tensor_device)
+        self.flow_send, self.flow_recv = mk(ns, 2), mk(nr, 2)
+        self.demand_send, self.demand_recv = mk(nr, 2), mk(ns, 2)
+        self.seller_table = mk(self.n_agents, SELLER_WORDS)
+        self._send_ids = np.ascontiguousarray(p.send_edges)
+        self._recv_ids = np.ascontiguousarray(p.recv_edges)
+        self._check(self.lib.acc_set_halo(self.h, self._send_ids.ctypes.data, ns, self._recv_ids.ctypes.data, nr, self.flow_send.data_ptr(),
+                                          self.flow_recv.data_ptr(), self.demand_send.data_ptr(), self.demand_recv.data_ptr(),
+                                          self.seller_table.data_ptr()))
+        self._stream = None
+        if self.tensor_device.type == "cuda":
+            self._stream = torch.cuda.ExternalStream(self.stream(), device=self.tensor_device)
+
+    def _bind(self):
+        lib = self.lib
+        lib.acc_create_partition.restype = C.c_void_p
+        lib.acc_create_partition.argtypes = [C.POINTER(_engine._Network), C.POINTER(_engine._Params), C.c_int, C.c_void_p]
+        lib.acc_set_halo.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t] + [C.c_void_p] * 5
+        lib.acc_stage.argtypes = [C.c_void_p, C.c_int]
+
+    def _stage(self, k):
+        self._check(self.lib.acc_stage(self.h, k))
+
+    def _exchange(self, recv, send, recv_counts, send_counts):
+        if self.world == 1:
+            return
+        self.dist.all_to_all_single(recv, send, output_split_sizes=recv_counts, input_split_sizes=send_counts, group=self.group)
+
+    @property
+    def world(self):
+        return self.part.world
+
+    def step(self):
+        """One timestep: four engine stages with the three exchanges between them, all ordered on the engine's stream."""
+        p = self.part
+        if self._stream is not None:
+            with self.torch.cuda.stream(self._stream):
+                self._step(p)
+        else:
+            self._step(p)
+
+    def _step(self, p):
+        self._stage(0)  # possible production, production + distribution, pack shipments
+        self._exchange(self.flow_recv, self.flow_send, p.recv_counts, p.send_counts)
+        self._stage(1)  # unpack shipments, storages + deliveries, expectation, pack supply parameters
+        if self.world > 1:
+            self.dist.all_reduce(self.seller_table, group=self.group)
+        self._stage(2)  # unpack supply parameters, purchase, pack demand requests
+        self._exchange(self.demand_recv, self.demand_send, p.send_counts, p.recv_counts)
+        self._stage(3)  # unpack demand requests, tick
+
+    def halo_bytes_per_step(self):
+        p = self.part
+        return 2 * 16 * (int(p.send_edges.size) + int(p.recv_edges.size)) + 8 * SELLER_WORDS * self.n_agents
+
+    # ---- reads: only what this part owns is meaningful ----
+    def owned_agents(self):
+        return np.nonzero(self.part.owned)[0]
+
+    def read_owned(self, name, storage_agent=None):
+        """Raw state array `name` with, next to it, the mask of entries this part is authoritative for and (for
+        per-connection arrays) the global connection ids.  Per-agent arrays are indexed by global agent id."""
+        x = self.read_state(name)
+        p = self.part
+        if name.startswith("edge_"):
+            mask = p.buys if name.startswith("edge_D") else p.sells
+            return x, mask, p.edge_gid
+        if x.size == self.n_agents:
+            return x, p.owned.astype(bool), None
+        return x, None, None

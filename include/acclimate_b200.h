@@ -96,6 +96,36 @@ acc_engine* acc_create(const acc_network* net, const acc_params* params, int dev
 /* replaces ~Model */
 void acc_destroy(acc_engine* e);
 
+/* ---- region-partitioned run: one engine per device, each owning the agents of a block of regions ----
+ * The reference parallelises the same loops over agents with OpenMP on shared memory (src/model/Model.cpp:59-118);
+ * across devices the agents are split by region and the two per-connection messages of a step cross the wire:
+ * shipments seller -> buyer after SalesManager::distribute (BusinessConnection::push_flow_Z,
+ * src/model/BusinessConnection.cpp:87-94) and demand requests buyer -> seller after iterate_purchase
+ * (BusinessConnection::send_demand_request_D, :127-131), plus the sellers' supply parameters every purchasing manager
+ * reads (SalesManager::communicated_parameters, src/model/SalesManager.cpp:611-624).
+ *
+ * net lists ALL agents (global numbering) but only the connections with an owned seller or an owned buyer, in global
+ * file order; agent_owned[n_agents] marks the agents this engine computes.  The engine never communicates itself: the
+ * caller moves the exchange buffers between the stages (NCCL all-to-all / all-reduce in acclimate_b200/partition.py). */
+acc_engine* acc_create_partition(const acc_network* net, const acc_params* params, int device, const uint8_t* agent_owned);
+/* Halo lists and caller-provided exchange buffers (memory of the engine's device, valid for the engine's life):
+ *   send_edges[n_send]: local ids of connections whose seller is owned and whose buyer is not, grouped by peer
+ *   recv_edges[n_recv]: local ids of connections whose buyer is owned and whose seller is not, grouped by peer
+ *   flow_send [n_send][2], flow_recv [n_recv][2]: shipment (quantity quanta, f64 value bits) as int64 pairs
+ *   demand_send [n_recv][2], demand_recv [n_send][2]: demand request (quantity quanta, price quanta)
+ *   seller_table [n_agents][ACC_SELLER_WORDS] int64: supply parameters, zero outside the owned rows when packed, so
+ *   that an integer SUM all-reduce assembles the full table exactly */
+#define ACC_SELLER_WORDS 9
+int acc_set_halo(acc_engine* e, const int64_t* send_edges, size_t n_send, const int64_t* recv_edges, size_t n_recv, void* flow_send,
+                 void* flow_recv, void* demand_send, void* demand_recv, void* seller_table);
+/* one timestep in four stages; between them the caller exchanges, in order:
+ *   after SELL:     flow_send -> peers' flow_recv            (all-to-all)
+ *   after DELIVER:  seller_table                             (all-reduce SUM over int64)
+ *   after PURCHASE: demand_send -> peers' demand_recv        (all-to-all)
+ * CLOSE applies the received demand requests and ticks.  On an unpartitioned engine the four stages equal acc_step. */
+enum { ACC_STAGE_SELL = 0, ACC_STAGE_DELIVER = 1, ACC_STAGE_PURCHASE = 2, ACC_STAGE_CLOSE = 3 };
+int acc_stage(acc_engine* e, int stage);
+
 /* replaces EconomicAgent::set_forcing for all agents at once (src/model/EconomicAgent.cpp:43-47);
  * lambda has n_agents entries */
 int acc_set_agent_forcing(acc_engine* e, const double* lambda, size_t n);
