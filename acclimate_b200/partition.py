@@ -122,6 +122,7 @@ class PartitionedEngine(_engine.Engine):
         self._stream = None
         if self.tensor_device.type == "cuda":
             self._stream = torch.cuda.ExternalStream(self.stream(), device=self.tensor_device)
+            torch.cuda.synchronize(self.tensor_device)  # the exchange buffers were zeroed on torch's stream, not the engine's
 
     def _bind(self):
         lib = self.lib
@@ -133,10 +134,32 @@ class PartitionedEngine(_engine.Engine):
     def _stage(self, k):
         self._check(self.lib.acc_stage(self.h, k))
 
+    def _staged(self):
+        # gloo moves host memory only: with device tensors (two parts sharing one GPU in the single-GPU test tier) the
+        # exchange is staged through the host.  The NCCL path never takes this branch.
+        return self.tensor_device.type == "cuda" and self.dist.get_backend(self.group) == "gloo"
+
     def _exchange(self, recv, send, recv_counts, send_counts):
         if self.world == 1:
             return
+        if self._staged():
+            self.sync()
+            h_send, h_recv = send.cpu(), self.torch.empty(recv.shape, dtype=recv.dtype)
+            self.dist.all_to_all_single(h_recv, h_send, output_split_sizes=recv_counts, input_split_sizes=send_counts, group=self.group)
+            recv.copy_(h_recv)
+            return
         self.dist.all_to_all_single(recv, send, output_split_sizes=recv_counts, input_split_sizes=send_counts, group=self.group)
+
+    def _gather_sellers(self):
+        if self.world == 1:
+            return
+        if self._staged():
+            self.sync()
+            h = self.seller_table.cpu()
+            self.dist.all_reduce(h, group=self.group)
+            self.seller_table.copy_(h)
+            return
+        self.dist.all_reduce(self.seller_table, group=self.group)
 
     @property
     def world(self):
@@ -155,8 +178,7 @@ class PartitionedEngine(_engine.Engine):
         self._stage(0)  # possible production, production + distribution, pack shipments
         self._exchange(self.flow_recv, self.flow_send, p.recv_counts, p.send_counts)
         self._stage(1)  # unpack shipments, storages + deliveries, expectation, pack supply parameters
-        if self.world > 1:
-            self.dist.all_reduce(self.seller_table, group=self.group)
+        self._gather_sellers()
         self._stage(2)  # unpack supply parameters, purchase, pack demand requests
         self._exchange(self.demand_recv, self.demand_send, p.send_counts, p.recv_counts)
         self._stage(3)  # unpack demand requests, tick

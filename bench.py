@@ -77,7 +77,7 @@ def make_network(args, rank):
     else:
         net = synth.make_config("small")
         workload = "small synthetic MRIO 10x5 (BASELINE.json configs[0])"
-    if rank > 0:  # ensemble member: its own shocked region (configs[4] pattern)
+    if rank > 0 and args.ensemble_shocks and args.mode == "ensemble":  # ensemble member: its own shocked region (configs[4] pattern)
         R = int(net["meta"][1])
         synth.add_shock(net, 1, 10 ** 6, (17 * rank) % R, 0.5 + 0.04 * (rank % 8))
     return net, workload
@@ -176,6 +176,10 @@ def main():
     ap.add_argument("--ref-steps", type=int, default=3)
     ap.add_argument("--reference-small", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--mode", default="ensemble", choices=["ensemble", "partition"],
+                    help="N > 1: one independent member of the same workload per GPU (weak scaling, no collective; default), or ONE network "
+                         "split by region across the GPUs with the shipment / demand halos and the seller table exchanged over NCCL (strong scaling)")
+    ap.add_argument("--ensemble-shocks", action="store_true", help="ensemble members other than the first get their own regional shock")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
@@ -201,9 +205,16 @@ def main():
     from acclimate_b200 import engine
 
     net, workload = make_network(args, rank)
-    E = engine.Engine(net, device=local_rank)
+    partitioned = world > 1 and args.mode == "partition"
+    if partitioned:
+        from acclimate_b200 import partition
+
+        E = partition.PartitionedEngine(net, device=local_rank)
+        n_edges = int(net["meta"][3])  # the whole network; this rank holds E.n_edges of them (owned seller or owned buyer)
+    else:
+        E = engine.Engine(net, device=local_rank)
+        n_edges = E.n_edges
     sc = engine.Scenario(net)
-    n_edges = E.n_edges
     stream = torch.cuda.ExternalStream(E.stream(), device=torch.device("cuda", local_rank))
 
     def barrier():
@@ -257,7 +268,7 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_max, e2e_ms_max = float(t[0]), float(t[1])
-    total_updates = n_edges * args.steps * world
+    total_updates = n_edges * args.steps * (1 if partitioned else world)
     value = total_updates / (ms_max * 1e-3)
     e2e_value = total_updates / (e2e_ms_max * 1e-3)
 
@@ -283,9 +294,10 @@ def main():
                 cpu = {"error": str(ex)}
         line = {
             "metric": "business-connection updates/sec", "value": value, "unit": "updates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64+f64", "data": "synthetic",
-            "config": {"workload": workload, "connections_per_gpu": n_edges, "l2": "inputs larger than L2 (%.1f GB of connection state per GPU)" % (n_edges * 100 / 1e9),
-                       "parallelism": "one ensemble member per GPU, no data-path collective" if world > 1 else "single GPU"},
+            "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "strong" if partitioned else "weak", "vs_baseline": None, "dtype": "int64+f64", "data": "synthetic",
+            "config": {"workload": workload, "connections_per_gpu": E.n_edges, "l2": "inputs larger than L2 (%.1f GB of connection state per GPU)" % (n_edges * 100 / 1e9),
+                       "parallelism": ("one network split by region over %d GPUs; per step 2 all-to-all halos (%d B on this rank) + 1 all-reduce of the seller table" % (world, E.halo_bytes_per_step()))
+                       if partitioned else ("one ensemble member of the workload per GPU, no data-path collective" if world > 1 else "single GPU")},
             "clocks": sampler.result(),
             "e2e": {"value": e2e_value, "unit": "updates/s", "h2d_bytes_per_step": int(lam.numel() * 8), "d2h_bytes_per_step": int(out.nbytes),
                     "call": "acc_set_agent_forcing + acc_step + acc_read(firms/production_quantity) per step, host buffers"},
