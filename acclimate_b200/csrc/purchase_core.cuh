@@ -24,6 +24,34 @@ struct PtrVec {
 ACC_HD void attach(PtrVec& v, double*& p, int n) { v.p = p; p += n; }
 
 // shared-memory vectors of one purchasing manager besides the solver's own: 13 f64 (+1 with deviation_penalty) + 2 int
+struct PMParams {
+    double Uf;        // to_float(initial_used_flow_U_star): scale of objective and constraint (:194,:200)
+    double markup;    // to_float(buyer sector initial_markup)
+    double pen_large, pen_small;
+    int quadratic, relative, limited_by_markup;
+};
+
+// The transport penalty's kink at D_r == target (:388-396 quadratic, :432-450 linear): slopes of the piecewise linear
+// part left and right of the target and the value the reference's gradient contains AT the target, per unit of D_r.
+// Shared with the oracle's harness (oracle/ref_harness), which describes the same kinks to the NLopt shim.
+struct KinkSlopes {
+    double sl, sr, mid;
+};
+ACC_HD KinkSlopes pm_kink_slopes(const PMParams& pp, double target) {
+    KinkSlopes k;
+    if (pp.quadratic) {
+        if (pp.relative && !(target > ACC_PREC3)) { k.sl = 0.0; k.sr = 0.0; k.mid = 0.0; return k; }  // D^2 form: treated as smooth
+        k.sl = -pp.markup; k.sr = pp.markup; k.mid = 0.0;
+    } else if (pp.relative) {
+        k.sl = -pp.pen_small / target; k.sr = pp.pen_large / target; k.mid = (pp.pen_large - pp.pen_small) / 2 / target;
+    } else {
+        k.sl = -pp.pen_small; k.sr = pp.pen_large; k.mid = (pp.pen_large - pp.pen_small) / 2;
+    }
+    return k;
+}
+// in the solver's scaled variables (x = D / Z*, objective / U*): slope * (Z* / U*)
+ACC_HD double pm_scaled_slope(double slope, double z_over_u) { return slope * z_over_u; }
+
 // shared-memory vectors of one purchasing manager: 9 of the solver, 11 price-curve vectors (+1 with deviation_penalty), 2 int
 #define ACC_PM_NVEC_SOLVER 9
 #define ACC_PM_NVEC_CONST 11
@@ -37,9 +65,18 @@ struct PMWork {
         PtrVec x, x0, g, a, d, b, gl, xbest;  // sqp_core work vectors
         PtrVec xu;                            // upper bounds (lower bounds are all zero, :620)
         const double* zf;                     // x tolerance = quantum of the demand request over the variable's scale (:640-644)
+        const double* tgt;                    // kink position in D_r
         double tol_c;
+        PMParams pp;
         ACC_HD double lower(int) const { return 0.0; }
         ACC_HD double tol(int i) const { return tol_c / zf[i]; }
+        // kink of the transport penalty (sqp_core.h "Kinks"); a[i] = -(Z*_i / U*) is the constraint gradient
+        ACC_HD bool kinked() const { return true; }
+        ACC_HD int kside(int i, double xi) const { const double D = xi * zf[i], t = tgt[i]; return D < t ? -1 : (D > t ? 1 : 0); }
+        ACC_HD double kpos(int i) const { return tgt == zf ? 1.0 : tgt[i] / zf[i]; }
+        ACC_HD double ksl(int i) const { return pm_scaled_slope(pm_kink_slopes(pp, tgt[i]).sl, -a[i]); }
+        ACC_HD double ksr(int i) const { return pm_scaled_slope(pm_kink_slopes(pp, tgt[i]).sr, -a[i]); }
+        ACC_HD double kmid(int i) const { return pm_scaled_slope(pm_kink_slopes(pp, tgt[i]).mid, -a[i]); }
     } w;
     // price-curve constants per purchasing connection (shared memory)
     double *zf;              // to_float(Z*): scale of the variable (:184-188)
@@ -61,16 +98,10 @@ struct PMWork {
         w.zf = zf;
         tgt = zf;  // the penalty target is Z* itself unless deviation_penalty is set
         if (separate_target) { tgt = p; p += n_max; }
+        w.tgt = tgt;
         int* q = reinterpret_cast<int*>(p);
         idx = q; q += n_max; eid = q;
     }
-};
-
-struct PMParams {
-    double Uf;        // to_float(initial_used_flow_U_star): scale of objective and constraint (:194,:200)
-    double markup;    // to_float(buyer sector initial_markup)
-    double pen_large, pen_small;
-    int quadratic, relative, limited_by_markup;
 };
 
 // n_r, grad_n_r, transport_penalty, partial_D_r_transport_penalty for connection r at demand D.
@@ -206,6 +237,7 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
     pp.markup = pf(sec.markup);
     pp.pen_large = pf(mp.pen_large); pp.pen_small = pf(mp.pen_small);
     pp.quadratic = mp.quadratic_penalty; pp.relative = mp.relative_penalty; pp.limited_by_markup = mp.limited_by_markup;
+    k.w.pp = pp;
 
     // One gather pass per connection: bounds (:609-650), price-curve constants (:279-289,:323-332) and start value,
     // written to slot r.  Returns D_r_max; <= 0 means the connection takes no part in the optimisation.

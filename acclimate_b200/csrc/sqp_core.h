@@ -16,6 +16,16 @@
 // multiplier, which a warp solves exactly out of shared memory.  The first iteration (identity
 // Hessian) coincides with SLSQP's.
 //
+// Kinks.  The purchasing objective contains, per coordinate, a term that is piecewise linear with ONE kink
+// (markup * |D_r - target_r|, PurchasingManager.cpp:388-396; or the linear transport penalty, :432-450).  A smooth
+// model cannot represent it: at the baseline fixed point every coordinate sits exactly on its kink and line searches
+// along a smooth-model direction fail.  The work set may therefore describe the kink of coordinate i: its position
+// kpos(i), the side kside(i, x) a point lies on, and the slopes ksl(i) <= ksr(i) left and right of it (kmid(i) = what
+// the caller's gradient contains AT the kink).  The solver then works with the SMOOTH part of the gradient
+// (g - sigma_i(x_i)), keeps the kink term exactly inside the QP sub-problem -- whose per-coordinate solution stays
+// closed-form: right branch, left branch, or "stay on the kink" -- and uses the model decrease including the kink term
+// in the merit test.  With no kinks described everything reduces to the smooth algorithm.
+//
 // The file compiles as plain C++ (host, used by oracle/nlopt_shim so that the reference's own
 // CPU run and the device run execute the same arithmetic) and as CUDA device code.  All
 // reductions go through Ctx::sum / Ctx::vmin / Ctx::vmax; Ctx::sum is defined to accumulate
@@ -67,8 +77,16 @@ struct Work {
     // length-n vectors
     double *x, *x0, *g, *a, *d, *b, *gl, *xbest;
     const double *xl, *xu, *xtol;
+    // optional kink descriptors (null = smooth objective), see "Kinks" below
+    const double *kscale = nullptr, *ktarget = nullptr, *ksl_ = nullptr, *ksr_ = nullptr, *kmid_ = nullptr;
     SQP_HD double lower(int i) const { return xl != nullptr ? xl[i] : 0.0; }
     SQP_HD double tol(int i) const { return xtol[i]; }
+    SQP_HD bool kinked() const { return kscale != nullptr; }
+    SQP_HD int kside(int i, double xi) const { const double D = xi * kscale[i]; return D < ktarget[i] ? -1 : (D > ktarget[i] ? 1 : 0); }
+    SQP_HD double kpos(int i) const { return ktarget[i] / kscale[i]; }
+    SQP_HD double ksl(int i) const { return ksl_[i]; }
+    SQP_HD double ksr(int i) const { return ksr_[i]; }
+    SQP_HD double kmid(int i) const { return kmid_[i]; }
 };
 #define ACCSQP_NVEC 8  // number of length-n work vectors above
 // lower bounds may be omitted (null pointer = all zero); step bounds are derived where they are used
@@ -112,15 +130,43 @@ struct MinMax {
 // *d_ready tells the caller whether w.d already holds the step (vertex solutions) or is still to be formed
 // from lambda (the caller fuses that pass with its own sums).
 // ---------------------------------------------------------------------------------------
+// slope of the kink term at xi (what the caller's gradient contains for it) and its value relative to the kink
 template <class W>
-SQP_HD double qp_step(const W& w, int i, double lambda) {
-    const double t = (-w.g[i] + lambda * w.a[i]) * w.b[i];
+SQP_HD double kink_sigma(const W& w, int i, double xi) {
+    const int sd = w.kside(i, xi);
+    return sd < 0 ? w.ksl(i) : (sd > 0 ? w.ksr(i) : w.kmid(i));
+}
+template <class W>
+SQP_HD double kink_phi(const W& w, int i, double xi) {
+    const double u = xi - w.kpos(i);
+    return u < 0.0 ? w.ksl(i) * u : w.ksr(i) * u;
+}
+
+// unclamped minimiser of  d^2 / (2 h) + (g - lambda a) d + kink(x + d)  and whether it lies on a smooth piece
+template <class W>
+SQP_HD double qp_free_step(const W& w, int i, double lambda, bool kinked, bool* smooth) {
+    const double r = -w.g[i] + lambda * w.a[i];
+    *smooth = true;
+    if (!kinked) return r * w.b[i];
+    const double u = w.x[i] - w.kpos(i);
+    const double dr = (r - w.ksr(i)) * w.b[i];
+    if (u + dr > 0.0) return dr;
+    const double dl = (r - w.ksl(i)) * w.b[i];
+    if (u + dl < 0.0) return dl;
+    *smooth = false;
+    return -u;
+}
+template <class W>
+SQP_HD double qp_step(const W& w, int i, double lambda, bool kinked) {
+    bool smooth;
+    const double t = qp_free_step(w, i, lambda, kinked, &smooth);
     return t < ACCSQP_LO(w, i) ? ACCSQP_LO(w, i) : (t > ACCSQP_HI(w, i) ? ACCSQP_HI(w, i) : t);
 }
 
 template <class Ctx, class W>
 SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, bool* d_ready) {
     *d_ready = false;
+    const bool kinked = w.kinked();
     if (ctype == CON_NONE) return 0.0;
     const double target = -c;  // want a^T d = target
     // attainable range of a^T d over the box
@@ -172,12 +218,13 @@ SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, boo
     for (; it < 200; ++it) {
         // psi and its slope at lambda
         const Sum2 ps = cx.template reduce<Sum2>(n, [&](int i) {
-            const double t = (-w.g[i] + lambda * w.a[i]) * w.b[i];
+            bool smooth;
+            const double t = qp_free_step(w, i, lambda, kinked, &smooth);
             const double lo = ACCSQP_LO(w, i), hi = ACCSQP_HI(w, i);
             Sum2 r;
             if (t <= lo) { r.a = w.a[i] * lo; r.b = 0.0; }
             else if (t >= hi) { r.a = w.a[i] * hi; r.b = 0.0; }
-            else { r.a = w.a[i] * t; r.b = w.a[i] * w.a[i] * w.b[i]; }
+            else { r.a = w.a[i] * t; r.b = smooth ? w.a[i] * w.a[i] * w.b[i] : 0.0; }
             return r;
         });
         const double psi = c + ps.a, slope = ps.b;
@@ -236,8 +283,10 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
         w.x[i] = xi;
         w.b[i] = 1.0;
     });
+    const bool kinked = w.kinked();
     double F = 0.0, c = 0.0;
     ev(w.x, true, &F, &c);
+    if (kinked) cx.foreach(n, [&](int i) { w.g[i] -= kink_sigma(w, i, w.x[i]); });  // keep the smooth part only
     st.evals = 1;
     double viol = con_violation(p.ctype, c);
     bool feasible = viol <= p.ctol;
@@ -257,13 +306,14 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
         const double lambda = qp_solve(cx, n, p.ctype, c, w, st, &d_ready);
         // One pass forms the step, the Lagrangian gradient at the old point with the new multiplier (Kraft: v), saves
         // the old point and returns three sums: a.d (linearised constraint), the number of coordinates whose step
-        // reaches the x tolerance, and g.d.
+        // reaches the x tolerance, and the model's first-order change of the objective g.d (+ change of the kink terms).
         const Sum3 sd = cx.template reduce<Sum3>(n, [&](int i) {
-            const double di = d_ready ? w.d[i] : qp_step(w, i, lambda);
+            const double di = d_ready ? w.d[i] : qp_step(w, i, lambda, kinked);
             w.d[i] = di;
             w.gl[i] = w.g[i] - lambda * w.a[i];
             w.x0[i] = w.x[i];
             Sum3 r; r.a = w.a[i] * di; r.b = (fabs(di) < w.tol(i)) ? 0.0 : 1.0; r.c = w.g[i] * di;
+            if (kinked) r.c += kink_phi(w, i, w.x[i] + di) - kink_phi(w, i, w.x[i]);  // model decrease incl. the kink term
             return r;
         });
         const double cres = (p.ctype == CON_NONE) ? 0.0 : c + sd.a;
@@ -293,13 +343,8 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
         // Kraft's inexact line search (Armijo factor 0.1, quadratic interpolation floored at 0.1, at most 10
         // backtracks).  Every trial is evaluated WITH gradients (nothing reads the old gradient any more: the
         // Lagrangian gradient at the old point sits in w.gl), so the accepted trial needs no second evaluation.
-        // Kink detection: the purchasing objective has a |D - Z*| term, and at a kinked optimum no step length
-        // satisfies Armijo.  After two failed trials the secant slopes s(A) = (merit(A) - merit(0)) / A are
-        // extrapolated to A = 0; if that estimate of the directional derivative is not negative the step is rejected
-        // at once (x stays at the old point) instead of being shrunk eight more times to the same end.
         int line = 0;
-        double alpha = 1.0, A = 1.0, A_prev = 0.0, s_prev = 0.0;
-        bool rejected = false;
+        double alpha = 1.0;
         for (;;) {
             ++line;
             h3 = alpha * h3;
@@ -312,6 +357,7 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
                 w.x[i] = xi;
             });
             ev(w.x, true, &F, &c);
+            if (kinked) cx.foreach(n, [&](int i) { w.g[i] -= kink_sigma(w, i, w.x[i]); });
             ++st.evals;
             {   // NLopt: keep the best point seen at every evaluation
                 const double vi = con_violation(p.ctype, c);
@@ -325,22 +371,10 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
             const double tt = F + mu * con_violation(p.ctype, c);
             const double h1 = tt - t0;
             if (h1 <= h3 / 10.0 || line > 10) break;
-            const double s_now = h1 / A;
-            if (line == 2) {
-                const double s0 = s_now - (s_prev - s_now) * A / (A_prev - A);
-                if (!(s0 < 0.0)) { rejected = true; break; }
-            }
-            s_prev = s_now; A_prev = A;
             const double cand = h3 / (2.0 * (h3 - h1));
             alpha = cand > 0.1 ? cand : 0.1;
-            A *= alpha;
         }
         if (ret != SQP_SUCCESS) break;
-        if (rejected) {  // x stays at the old point, so NLopt's xtol rule (no coordinate moved) ends the run here
-            cx.foreach(n, [&](int i) { w.x[i] = w.x0[i]; });
-            ret = SQP_XTOL_REACHED;
-            break;
-        }
         // NLopt's xtol test between completed iterations, fused with the per-coordinate secant update of the
         // inverse diagonal Hessian model  h_i = dx_i / dgradL_i
         const double moved = cx.sum(n, [&](int i) {

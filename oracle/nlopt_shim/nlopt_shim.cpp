@@ -33,6 +33,7 @@ struct nlopt_opt_s {
     int ctype = accsqp::CON_NONE;
     double ctol = 0.0;
     std::vector<double> lb, ub, xtol;
+    std::vector<double> kinks;  // 5 n: scale, target, left slope, right slope, slope at the kink (sqp_core.h "Kinks"); empty = smooth
     int maxeval = 0;
     double maxtime = 0.0;
     const char* errmsg = nullptr;
@@ -92,6 +93,20 @@ nlopt_result nlopt_set_local_optimizer(nlopt_opt opt, const nlopt_opt) {
 }
 nlopt_result nlopt_set_population(nlopt_opt, unsigned) { return NLOPT_SUCCESS; }
 const char* nlopt_get_errmsg(nlopt_opt opt) { return opt->errmsg; }
+/* Not part of NLopt: describes the per-coordinate kink of the objective (sqp_core.h "Kinks").  The device solver
+ * knows the kinks of the purchasing objective from the model; on the oracle side the reference's callbacks cannot tell,
+ * so the harness supplies them through nlopt_shim_kinks below (or a test through this setter). */
+nlopt_result nlopt_shim_set_kinks(nlopt_opt opt, const double* scale, const double* target, const double* sl, const double* sr, const double* mid) {
+    const unsigned n = opt->n;
+    opt->kinks.resize(5 * (size_t)n);
+    std::memcpy(&opt->kinks[0], scale, n * sizeof(double)); std::memcpy(&opt->kinks[n], target, n * sizeof(double));
+    std::memcpy(&opt->kinks[2 * n], sl, n * sizeof(double)); std::memcpy(&opt->kinks[3 * n], sr, n * sizeof(double));
+    std::memcpy(&opt->kinks[4 * n], mid, n * sizeof(double));
+    return NLOPT_SUCCESS;
+}
+/* Optional hook (weak): asked once per nlopt_optimize with the objective's user data; returns 1 after filling the five
+ * arrays when that objective has kinks.  oracle/ref_harness defines it for PurchasingManager objectives. */
+int nlopt_shim_kinks(void* f_data, unsigned n, double* scale, double* target, double* sl, double* sr, double* mid) __attribute__((weak));
 int nlopt_shim_last_iterations(nlopt_opt opt) { return opt->last_iters; }
 int nlopt_shim_last_evals(nlopt_opt opt) { return opt->last_evals; }
 
@@ -153,6 +168,14 @@ extern "C" nlopt_result nlopt_optimize(nlopt_opt opt, double* x, double* opt_f) 
     w.xu = opt->ub.data();
     w.xtol = opt->xtol.data();
     std::memcpy(w.x, x, sizeof(double) * n);
+    std::vector<double> kinks = opt->kinks;
+    if (kinks.empty() && nlopt_shim_kinks != nullptr) {
+        kinks.resize(5 * (size_t)n);
+        if (!nlopt_shim_kinks(opt->f_data, (unsigned)n, &kinks[0], &kinks[n], &kinks[2 * (size_t)n], &kinks[3 * (size_t)n], &kinks[4 * (size_t)n])) kinks.clear();
+    }
+    if (!kinks.empty()) {
+        w.kscale = &kinks[0]; w.ktarget = &kinks[n]; w.ksl_ = &kinks[2 * (size_t)n]; w.ksr_ = &kinks[3 * (size_t)n]; w.kmid_ = &kinks[4 * (size_t)n];
+    }
 
     accsqp::Params p;
     p.n = n; p.ctype = opt->ctype; p.ctol = opt->ctol; p.maxeval = opt->maxeval; p.max_iter = ACCSQP_MAX_ITER;

@@ -40,6 +40,10 @@
 #include "nlopt.h"
 #include "openmp.h"
 
+#include <unordered_set>
+
+#include "../../acclimate_b200/csrc/purchase_core.cuh"  // pm_kink_slopes: the one definition of the transport penalty's kink
+
 extern "C" void nlopt_shim_stats(long long* out);
 
 // index of each entry in the "model_f64" array of the network file (acclimate_b200/netfile.py)
@@ -96,6 +100,7 @@ struct EventRec {
     double value;
 };
 static std::vector<EventRec> g_events;
+static std::unordered_set<const void*> g_purchasing_managers;  // which nlopt user data are PurchasingManagers
 static std::int64_t g_step = 0;
 
 namespace acclimate {
@@ -275,6 +280,7 @@ class ModelInitializer {
             if (static_cast<void*>(firm_from) == static_cast<void*>(to)) firm_from->self_supply_connection(bc);
             edges.push_back(bc);
         }
+        for (auto* st : storages) g_purchasing_managers.insert(st->purchasing_manager.get());
         check_clean();
         // post_initialize, ModelInitializer.cpp:1081-1085
         for (auto& agent : model->economic_agents) agent->initialize();
@@ -299,6 +305,35 @@ class ModelInitializer {
 };
 
 }  // namespace acclimate
+
+// ---- kinks of the purchasing objective for the NLopt shim (nlopt_shim.cpp: nlopt_shim_kinks) ----
+// The reference's callbacks hand NLopt a gradient that jumps at D_r == target (PurchasingManager.cpp:388-396,432-450).
+// The engine's solver is told where (csrc/purchase_core.cuh PMWork::W); this hook tells the shim the same, from the
+// reference's own objects and with the same formula (acc::pm_kink_slopes), so both run identical arithmetic.
+extern "C" int nlopt_shim_kinks(void* f_data, unsigned n, double* scale, double* target, double* sl, double* sr, double* mid) {
+    using namespace acclimate;
+    if (g_purchasing_managers.count(f_data) == 0) return 0;
+    const auto* pm = static_cast<const PurchasingManager*>(f_data);
+    if (pm->purchasing_connections.size() != n) return 0;
+    const auto& P = pm->model()->parameters();
+    acc::PMParams pp;
+    pp.Uf = to_float(pm->storage->initial_used_flow_U_star().get_quantity());
+    pp.markup = to_float(pm->storage->sector->parameters().initial_markup);
+    pp.pen_large = to_float(P.transport_penalty_large);
+    pp.pen_small = to_float(P.transport_penalty_small);
+    pp.quadratic = P.quadratic_transport_penalty; pp.relative = P.relative_transport_penalty;
+    pp.limited_by_markup = P.maximal_decrease_reservation_price_limited_by_markup;
+    for (unsigned r = 0; r < n; ++r) {
+        const BusinessConnection* bc = pm->purchasing_connections[r];
+        const double zf = to_float(bc->initial_flow_Z_star().get_quantity());
+        const double t = P.deviation_penalty ? to_float(bc->last_demand_request_D(pm).get_quantity()) : zf;
+        const acc::KinkSlopes ks = acc::pm_kink_slopes(pp, t);
+        const double z_over_u = zf / pp.Uf;
+        scale[r] = zf; target[r] = t;
+        sl[r] = acc::pm_scaled_slope(ks.sl, z_over_u); sr[r] = acc::pm_scaled_slope(ks.sr, z_over_u); mid[r] = acc::pm_scaled_slope(ks.mid, z_over_u);
+    }
+    return 1;
+}
 
 // ---- ModelRun members (replacement for src/ModelRun.cpp) -------------------------------------------
 namespace acclimate {
