@@ -75,6 +75,9 @@ struct HostCtx : CtxOps<HostCtx> {
     inline int lane() const { return 0; }
     template <class F>
     inline void foreach(int n, F f) const { for (int i = 0; i < n; ++i) f(i); }
+    // code that only the group's leader executes, fenced by group barriers (results travel through the group's memory)
+    template <class F>
+    inline void single(F f) const { f(); }
     template <class T, class F>
     inline T reduce(int n, F f) const {
         const int W = G / 32;
@@ -168,6 +171,12 @@ struct WarpCtx : CtxOps<WarpCtx> {
         for (int i = lane_; i < n; i += 32) f(i);
         __syncwarp();
     }
+    template <class F>
+    __device__ __forceinline__ void single(F f) const {
+        __syncwarp();
+        if (lane_ == 0) f();
+        __syncwarp();
+    }
     template <class T, class F>
     __device__ __forceinline__ T reduce(int n, F f) const {
         T acc_ = T::identity();
@@ -213,6 +222,12 @@ struct BlockCtx : CtxOps<BlockCtx> {
     template <class F>
     __device__ __forceinline__ void foreach(int n, F f) const {
         for (int i = threadIdx.x; i < n; i += blockDim.x) f(i);
+        __syncthreads();
+    }
+    template <class F>
+    __device__ __forceinline__ void single(F f) const {
+        __syncthreads();
+        if (threadIdx.x == 0) f();
         __syncthreads();
     }
     template <class T, class F>

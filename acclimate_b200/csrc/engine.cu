@@ -36,6 +36,7 @@
 
 #include "../../include/acclimate_b200.h"
 #include "purchase_core.cuh"
+#include "consumer_core.cuh"
 
 namespace acc {
 
@@ -208,6 +209,8 @@ struct StorageDelivery {  // thread per storage
             const Flow X = mkflow(fv.X_q[a], fv.X_v[a]);
             used = fcopy(fmul(X, st.a[s]));
             if (X.q > 0) used = set_price(used, flow_price(uhat));
+        } else if (mp.utilitarian) {  // the consumer kernel has set the desired use to the optimised consumption, Consumer.cpp:510-517
+            used = mkflow(st.Ut_q[s], st.Ut_v[s]);
         } else {  // price-elastic consumer, Consumer.cpp:276-302
             i64 rp;
             if (uhat.q > 0) {
@@ -268,6 +271,16 @@ struct StorageDelivery {  // thread per storage
         st.dlv_q[s] = in.q;
         st.imp_q[s] = imp.q; st.imp_v[s] = imp.v;
         st.T_q[s] = tq; st.T_v[s] = tv;
+    }
+};
+
+struct ConsumerUtility {  // one CTA of ACCSQP_GROUP threads per utilitarian consumer
+    enum { THREADS = ACCSQP_GROUP, MIN_BLOCKS = 1 };
+    ConsumerView cv; StorageView st; ModelP mp; EventSink events; int n_max; int* fatal;
+    template <class Ctx>
+    ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const {
+        const bool ok = consumer_one(cx, cv.cons_ids[item], cv, st, mp, events, smem, n_max);
+        if (!ok && cx.leader()) *fatal = 1;
     }
 };
 
@@ -417,6 +430,12 @@ struct acc_engine {
     // buyer-side lists
     DBuf<i64> ell_off, in_off;
     DBuf<int> ell_width, ell_edge, in_edge, in_seller;
+    // utilitarian consumers (nested-CES utility optimisation)
+    int nC = 0, nB = 0, c_n_max = 0;
+    double c_inter_exp = 0.0, c_ctol = 0.0;
+    DBuf<int> cons_ids, c_order_cnt, c_order, c_order_basket, fatal;
+    DBuf<double> c_share, c_eshare, c_prev_v, c_budget, c_bshare, c_ebshare, c_utility, c_intra_exp;
+    DBuf<i64> c_base_q, c_prev_q;
     // region partition (empty = the engine owns every agent)
     bool partitioned = false;
     int n_pm = 0;  // purchasing managers of owned agents
@@ -468,6 +487,15 @@ struct acc_engine {
         v.ovf_q = forcing_used ? e_ovf_q.p : nullptr; v.ovf_v = forcing_used ? e_ovf_v.p : nullptr; v.nu = forcing_used ? nu.p : nullptr;
         return v;
     }
+    ConsumerView consumer_view() {
+        ConsumerView v;
+        v.cons_ids = cons_ids.p; v.st_off = a_st_off.p; v.st_list = a_st_list.p;
+        v.share = c_share.p; v.eshare = c_eshare.p; v.base_q = c_base_q.p; v.prev_q = c_prev_q.p; v.prev_v = c_prev_v.p;
+        v.budget = c_budget.p; v.order_cnt = c_order_cnt.p; v.order = c_order.p; v.order_basket = c_order_basket.p;
+        v.bshare = c_bshare.p; v.ebshare = c_ebshare.p; v.utility = c_utility.p; v.intra_exp = c_intra_exp.p; v.inter_exp = c_inter_exp;
+        v.n_baskets = nB; v.xtol_c = ACC_PREC3 * 1.0; v.ctol = c_ctol; v.maxeval = mp.maxeval;
+        return v;
+    }
     EventSink sink() {
         EventSink s;
         s.buf = ev_buf.p; s.count = ev_count.p; s.cap = ev_cap; s.step = step;
@@ -517,6 +545,11 @@ struct acc_engine {
 #endif
     }
 
+    void consumer_utility() {
+        if (!mp.utilitarian || nC == 0) return;
+        ConsumerUtility k{consumer_view(), storage_view(), mp, sink(), c_n_max, fatal.p};
+        timed("consumer_utility", [&] { launch_block_smem(stream, nC, consumer_workspace_bytes(c_n_max), k); });
+    }
     void stage_sell() {
         {
             FirmPossibleProduction k{firm_view(), storage_view(), mp, firm_ids.p};
@@ -536,6 +569,7 @@ struct acc_engine {
             UnpackFlow k{edge_view(), step, halo_recv.p, x_flow_recv};
             timed("unpack_flow", [&] { launch_thread(stream, (int)halo_recv.n, k); });
         }
+        consumer_utility();
         {
             StorageDelivery k{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p,
                               partitioned ? owned.p : nullptr};
@@ -583,6 +617,7 @@ struct acc_engine {
         timed("firm_possible_production", [&] { launch_thread(stream, nF, k1); });
         SellerProduction k2{firm_view(), edge_view(), mp, sectors.p, sink(), step, firm_ids.p};
         timed("seller_production", [&] { launch_block(stream, nF, 256, k2); });
+        consumer_utility();
         StorageDelivery k3{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p, nullptr};
         timed("storage_delivery", [&] { launch_thread(stream, nSt, k3); });
     }
@@ -630,7 +665,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
     mp.preserve_seller_price = m[ACC_MP_CHEAPEST_PRICE_RANGE_PRESERVE_SELLER_PRICE] != 0.0;
     mp.maxeval = (int)m[ACC_MP_OPTIMIZATION_MAXITER];
     mp.prec_adj = (int)m[ACC_MP_OPTIMIZATION_PRECISION_ADJUSTMENT];
-    if (m[ACC_MP_UTILITARIAN] != 0.0) fail("utilitarian consumers (nested-CES utility optimisation) are not built yet: set bool_utilitarian false");
+    mp.utilitarian = m[ACC_MP_UTILITARIAN] != 0.0;
     const bool no_self_supply = m[ACC_MP_NO_SELF_SUPPLY] != 0.0;
 
     E.h_sectors.resize(nS);
@@ -870,6 +905,75 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
             }
         }
     }
+    if (mp.utilitarian) {
+        // ---- Consumer::Consumer + Consumer::initialize, Consumer.cpp:43-163 (host, once) ----
+        const i64 nB = net.n_baskets;
+        if (nB <= 0 || net.basket_of_sector == nullptr || net.basket_substitution == nullptr) fail("utilitarian consumers need consumer baskets");
+        std::vector<double> intra_exp(nB);
+        for (i64 b = 0; b < nB; ++b) {
+            const double c = net.basket_substitution[b];
+            intra_exp[b] = (c - 1) / c;
+        }
+        const double inter = net.inter_basket_substitution;
+        E.c_inter_exp = (inter - 1) / inter;
+        E.nB = (int)nB;
+        double prec8 = 1.0;
+        for (int k = 0; k < 8; ++k) prec8 = 0.1 * prec8;  // FlowValue::precision, types.h:313-315
+        E.c_ctol = prec8;
+        std::vector<int> cons_ids, order_cnt(nA, 0), order(nSt, -1), order_basket(nSt, -1);
+        std::vector<double> share(nSt, 0.0), eshare(nSt, 0.0), prev_v(nSt, 0.0), budget(nA, 0.0), bshare((size_t)nA * nB, 0.0), ebshare((size_t)nA * nB, 0.0);
+        std::vector<i64> base_q(nSt, 0), prev_q(nSt, 0);
+        int c_n_max = 0;
+        for (i64 a = 0; a < nA; ++a) {
+            if (a_type[a] == 1 || !own(a)) continue;
+            cons_ids.push_back((int)a);
+            const int o = a_st_off[a], n = a_st_off[a + 1] - o;
+            c_n_max = std::max(c_n_max, n);
+            auto sto = [&](int i) { return a_st_list[o + i]; };
+            auto basket_of = [&](int i) { return (int)net.basket_of_sector[st_sector[sto(i)]]; };
+            double B = 0.0;  // consumption_budget
+            for (int i = 0; i < n; ++i) B += Istar_v[sto(i)];
+            budget[a] = B;
+            // visit order of every loop over (basket, sector of the basket, storage of that sector)
+            std::vector<std::pair<int, int> > visit;  // (basket, local index)
+            for (i64 b = 0; b < nB; ++b)
+                for (i64 sec = 0; sec < nS; ++sec) {
+                    if (net.basket_of_sector[sec] != b) continue;
+                    for (int i = 0; i < n; ++i) if (st_sector[sto(i)] == sec) visit.emplace_back((int)b, i);
+                }
+            double* bs = &bshare[(size_t)a * nB];
+            for (auto& v : visit) bs[v.first] += Istar_v[sto(v.second)] / B;
+            for (i64 b = 0; b < nB; ++b)
+                if (bs[b] == 0) fail("a consumer has no consumption in one of its baskets (the reference removes such baskets; not provided)");
+            double Cr = 0.0;  // consumption_in_relevant_baskets
+            for (auto& v : visit) Cr += Istar_v[sto(v.second)];
+            for (auto& v : visit) bs[v.first] = bs[v.first] * (B / Cr);  // once per storage of the basket, as the reference does (:124-131)
+            for (int i = 0; i < n; ++i) {
+                const int k = sto(i);
+                if (basket_of(i) >= 0) {
+                    share[k] = (Istar_v[k] / B) * (B / Cr);
+                    base_q[k] = Istar_q[k]; prev_q[k] = Istar_q[k]; prev_v[k] = Istar_v[k];
+                }
+            }
+            int cnt = 0;
+            for (auto& v : visit) {
+                const int k = sto(v.second);
+                order[o + cnt] = v.second; order_basket[o + cnt] = v.first; ++cnt;
+                share[k] = share[k] / bs[v.first];
+                eshare[k] = std::pow(share[k], 1 / net.basket_substitution[v.first]);
+            }
+            order_cnt[a] = cnt;
+            for (i64 b = 0; b < nB; ++b) ebshare[(size_t)a * nB + b] = std::pow(bs[b], 1 / inter);
+        }
+        E.nC = (int)cons_ids.size();
+        E.c_n_max = (c_n_max + 1) / 2 * 2;
+        E.cons_ids.upload(cons_ids, s); E.c_order_cnt.upload(order_cnt, s); E.c_order.upload(order, s); E.c_order_basket.upload(order_basket, s);
+        E.c_share.upload(share, s); E.c_eshare.upload(eshare, s); E.c_prev_v.upload(prev_v, s); E.c_budget.upload(budget, s);
+        E.c_bshare.upload(bshare, s); E.c_ebshare.upload(ebshare, s); E.c_intra_exp.upload(intra_exp, s);
+        E.c_base_q.upload(base_q, s); E.c_prev_q.upload(prev_q, s);
+        E.c_utility.alloc(nA); E.c_utility.zero(s);
+    }
+    E.fatal.alloc(1); E.fatal.zero(s);
     E.in_off.upload(in_off, s); E.in_edge.upload(in_edge, s); E.in_seller.upload(in_seller, s);
     E.ell_off.upload(ell_off, s); E.ell_width.upload(ell_width, s); E.ell_edge.upload(ell_edge, s);
     E.ev_buf.alloc(E.ev_cap); E.ev_count.alloc(1); E.ev_count.zero(s);
@@ -974,6 +1078,7 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
     }
     // agents
     if (name == "agent_forcing") return F(E.a_lambda);
+    if (name == "consumer_utility" && E.mp.utilitarian) return F(E.c_utility);
     if (name == "firm_X_q") return I(E.f_X_q);
     if (name == "firm_X_v") return F(E.f_X_v);
     if (name == "firm_Xhat_q") return I(E.f_Xhat_q);
@@ -1106,6 +1211,9 @@ void acc_destroy(acc_engine* e) {
         b->free();
     e->e_tau.free(); e->e_dom.free(); e->sectors.free(); e->pub.free(); e->ev_buf.free();
     e->owned.free(); e->pm_ids.free(); e->halo_send.free(); e->halo_recv.free();
+    for (DBuf<int>* b : {&e->cons_ids, &e->c_order_cnt, &e->c_order, &e->c_order_basket, &e->fatal}) b->free();
+    for (DBuf<double>* b : {&e->c_share, &e->c_eshare, &e->c_prev_v, &e->c_budget, &e->c_bshare, &e->c_ebshare, &e->c_utility, &e->c_intra_exp}) b->free();
+    e->c_base_q.free(); e->c_prev_q.free();
     delete e;
 }
 
@@ -1201,6 +1309,12 @@ int acc_sync(acc_engine* e) {
     ACC_API_BEGIN
     if (e == nullptr) fail("acc_sync: null engine");
     dev_sync(e->stream);
+    if (e->mp.utilitarian) {
+        int flag = 0;
+        d2h(&flag, e->fatal.p, sizeof(int), e->stream);
+        // the reference ends the run here: "optimization failed ... (for n consumption goods)", Consumer.cpp:497-502
+        if (flag) fail("utility optimisation of a consumer failed (more than " + std::to_string(ACCSQP_MAX_ITER) + " SQP iterations)");
+    }
     return 0;
     ACC_API_END(-1)
 }

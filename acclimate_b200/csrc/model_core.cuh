@@ -40,6 +40,7 @@ struct ModelP {  // reference include/parameters.h:33-84 (the keys this path rea
     int quadratic_penalty, relative_penalty, limited_by_markup, deviation_penalty, preserve_seller_price;
     int maxeval;             // optimization_maxiter
     int prec_adj;            // optimization_precision_adjustment (int, parameters.h:61)
+    int utilitarian;         // consumers.<..>.bool_utilitarian (ModelInitializer.cpp:136)
 };
 
 struct SectorP {  // reference Sector.h + Parameters::SectorParameters

@@ -35,6 +35,7 @@ class _Network(C.Structure):
         ("agent_type", C.c_void_p), ("agent_sector", C.c_void_p), ("agent_region", C.c_void_p), ("agent_beta", C.c_void_p),
         ("edge_from", C.c_void_p), ("edge_to", C.c_void_p), ("edge_zq", C.c_void_p), ("delay", C.c_void_p),
         ("sector_params", C.c_void_p), ("consumer_elasticity", C.c_void_p),
+        ("n_baskets", C.c_int64), ("basket_of_sector", C.c_void_p), ("basket_substitution", C.c_void_p), ("inter_basket_substitution", C.c_double),
     ]
 
 
@@ -78,6 +79,24 @@ def load_library(path=None):
     return lib
 
 
+def consumer_baskets(arrays):
+    """Consumer baskets of a snapshot: (basket_of_sector, basket_coeff, inter_basket_coeff).  A snapshot without them gets
+    the oracle harness's default: one basket holding every supplying sector, substitution 2.0 inside, 1.5 between."""
+    nS = int(np.asarray(arrays["meta"])[0])
+    if "basket_of_sector" in arrays:
+        bos = np.ascontiguousarray(arrays["basket_of_sector"], dtype=np.int64)
+        bco = np.ascontiguousarray(arrays["basket_coeff"], dtype=np.float64)
+        inter = float(np.asarray(arrays["inter_basket_coeff"]).reshape(-1)[0])
+    else:
+        bos = np.zeros(nS, dtype=np.int64)
+        bos[nS - 1] = -1  # the consumer sector supplies nothing
+        bco = np.array([2.0])
+        inter = 1.5
+    if bos.size != nS:
+        raise EngineError("basket_of_sector needs one entry per sector")
+    return bos, bco, inter
+
+
 def network_struct(arrays):
     """acc_network / acc_params views of a snapshot dict; the third value keeps the arrays alive."""
     a = {k: np.ascontiguousarray(v) for k, v in arrays.items()}
@@ -88,7 +107,10 @@ def network_struct(arrays):
         a["edge_zq"].astype(np.int64), a["delay"].astype(np.int64), a["sector_f64"].astype(np.float64),
         a["consumer_elasticity"].astype(np.float64),
     ]
-    net = _Network(int(meta[0]), int(meta[1]), int(meta[2]), int(meta[3]), *[x.ctypes.data for x in keep])
+    bos, bco, inter = consumer_baskets(a)
+    keep += [bos, bco]
+    net = _Network(int(meta[0]), int(meta[1]), int(meta[2]), int(meta[3]), *[x.ctypes.data for x in keep[:10]], int(bco.size), bos.ctypes.data,
+                   bco.ctypes.data, inter)
     par = _Params()
     mp = a["model_f64"].astype(np.float64)
     if mp.size != MP_COUNT:

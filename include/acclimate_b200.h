@@ -75,6 +75,13 @@ typedef struct {
     const int64_t* delay;         /* [n_regions * n_regions] transport delay between regions, symmetric */
     const double* sector_params;  /* [n_sectors * ACC_SP_COUNT] */
     const double* consumer_elasticity; /* [n_sectors] consumers.<..>.consumption_price_elasticity by supplying sector */
+    /* consumer baskets of the nested-CES utility (consumers.<..>.consumer_baskets / inter_basket_substitution_coefficient,
+     * src/input/ModelInitializer.cpp:118-139); only read when model[ACC_MP_UTILITARIAN] != 0 */
+    int64_t n_baskets;
+    const int64_t* basket_of_sector;   /* [n_sectors] basket of each supplying sector, -1: in no basket; sectors of a
+                                          basket are taken in ascending order */
+    const double* basket_substitution; /* [n_baskets] intra-basket substitution coefficient */
+    double inter_basket_substitution;  /* inter_basket_substitution_coefficient */
 } acc_network;
 
 typedef struct {

@@ -21,6 +21,7 @@
 
 #include "../../acclimate_b200/csrc/coop.cuh"
 #include "../../acclimate_b200/csrc/sqp_core.h"
+#include "../../acclimate_b200/csrc/sqp_dense.h"
 
 struct nlopt_opt_s {
     nlopt_algorithm algorithm;
@@ -144,6 +145,25 @@ struct CallbackEval {
     }
 };
 
+// the same for sqp_dense.h (gradients go to the arrays the solver names)
+struct DenseCallbackEval {
+    nlopt_opt o;
+    void operator()(const double* x, double* g, double* a, double* F, double* c) {
+        const unsigned n = o->n;
+        const double sgn = o->maximize ? -1.0 : 1.0;
+        *F = sgn * o->f(n, x, g, o->f_data);
+        for (unsigned i = 0; i < n; ++i) g[i] = sgn * g[i];
+        if (o->con != nullptr) {
+            const double cs = (o->ctype == accsqp::CON_INEQ) ? -1.0 : 1.0;  // NLopt: fc(x) <= 0
+            *c = cs * o->con(n, x, a, o->con_data);
+            for (unsigned i = 0; i < n; ++i) a[i] = cs * a[i];
+        } else {
+            *c = 0.0;
+            for (unsigned i = 0; i < n; ++i) a[i] = 0.0;
+        }
+    }
+};
+
 }  // namespace
 
 // whole-run solver statistics (printed by the harness; serial builds only -- not atomic)
@@ -180,10 +200,29 @@ extern "C" nlopt_result nlopt_optimize(nlopt_opt opt, double* x, double* opt_f) 
     accsqp::Params p;
     p.n = n; p.ctype = opt->ctype; p.ctol = opt->ctol; p.maxeval = opt->maxeval; p.max_iter = ACCSQP_MAX_ITER;
     accsqp::Stats st;
-    acc::HostCtx cx(ACCSQP_GROUP);  // replays the device group's reduction order
-    CallbackEval ev{opt, &w, std::vector<double>((size_t)n)};
-    const int ret = accsqp::sqp_minimize(cx, ev, w, p, st);
-    std::memcpy(x, w.xbest, sizeof(double) * n);
+    int ret;
+    if (!kinks.empty()) {
+        // separable objective with described kinks (the purchasing managers): diagonal model, sqp_core.h
+        acc::HostCtx cx(ACCSQP_GROUP);  // replays the device group's reduction order
+        CallbackEval ev{opt, &w, std::vector<double>((size_t)n)};
+        ret = accsqp::sqp_minimize(cx, ev, w, p, st);
+        std::memcpy(x, w.xbest, sizeof(double) * n);
+    } else {
+        // anything else (the consumers' nested-CES utility): dense BFGS model, sqp_dense.h
+        std::vector<double> dbuf(accsqp::dense_doubles(n));
+        std::vector<int> ibuf(2 * (size_t)n);
+        accsqp::DenseWork dw;
+        double* r = dbuf.data();
+        dw.n = n;
+        dw.x = r; r += n; dw.x0 = r; r += n; dw.g = r; r += n; dw.a = r; r += n; dw.d = r; r += n; dw.gl = r; r += n; dw.xbest = r; r += n;
+        dw.t1 = r; r += n; dw.t2 = r; r += n; dw.t3 = r; r += n; dw.B = r; r += (size_t)n * n; dw.L = r;
+        dw.state = ibuf.data();
+        dw.xl = opt->lb.data(); dw.xu = opt->ub.data(); dw.xtol = opt->xtol.data();
+        std::memcpy(dw.x, x, sizeof(double) * n);
+        DenseCallbackEval ev{opt};
+        ret = accsqp::sqp_minimize_dense(ev, dw, p, st);
+        std::memcpy(x, dw.xbest, sizeof(double) * n);
+    }
     *opt_f = opt->maximize ? -st.minf : st.minf;
     opt->last_iters = st.iters;
     opt->last_evals = st.evals;

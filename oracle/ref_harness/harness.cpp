@@ -221,11 +221,26 @@ class ModelInitializer {
                 region->economic_agents.add(firm);
                 agents.push_back(firm);
             } else {
+                // consumer_baskets / inter_basket_substitution_coefficient, ModelInitializer.cpp:118-139.  Snapshot keys
+                // basket_of_sector / basket_coeff / inter_basket_coeff; without them: one basket of all supplying sectors
+                // (substitution 2.0 inside, 1.5 between baskets).  Sectors of a basket are listed in ascending order.
                 std::vector<std::pair<std::vector<Sector*>, FloatType>> baskets;
-                std::vector<Sector*> all;
-                for (std::size_t s = 0; s + 1 < n_sectors; ++s) all.push_back(model->sectors[s]);
-                baskets.emplace_back(all, 2.0);
-                auto* consumer = model->economic_agents.add<Consumer>(id_t(name), region, 1.5, baskets, utilitarian);
+                FloatType inter = 1.5;
+                if (cfg.net.count("basket_of_sector") != 0) {
+                    const auto& bos = cfg.I("basket_of_sector");
+                    const auto& bco = cfg.F("basket_coeff");
+                    inter = cfg.F("inter_basket_coeff").at(0);
+                    for (std::size_t b = 0; b < bco.size(); ++b) {
+                        std::vector<Sector*> members;
+                        for (std::size_t s = 0; s < n_sectors; ++s) if (bos.at(s) == std::int64_t(b)) members.push_back(model->sectors[s]);
+                        baskets.emplace_back(members, bco[b]);
+                    }
+                } else {
+                    std::vector<Sector*> all;
+                    for (std::size_t s = 0; s + 1 < n_sectors; ++s) all.push_back(model->sectors[s]);
+                    baskets.emplace_back(all, 2.0);
+                }
+                auto* consumer = model->economic_agents.add<Consumer>(id_t(name), region, inter, baskets, utilitarian);
                 region->economic_agents.add(consumer);
                 agents.push_back(consumer);
             }
@@ -454,6 +469,8 @@ static void dump_step(accio::Writer& out, Model* model, std::int64_t t, bool wit
     const auto& A = g_init->agents;
     auto firm = [&](std::size_t k) -> const Firm* { return A[k]->is_firm() ? A[k]->as_firm() : nullptr; };
     put_f("agent_forcing", A.size(), [&](std::size_t k) { return A[k]->forcing(); });
+    if (g_cfg->F("model_f64")[MP_UTILITARIAN] != 0.0)
+        put_f("consumer_utility", A.size(), [&](std::size_t k) { return A[k]->is_consumer() ? A[k]->as_consumer()->utility : 0.0; });
     put_i("firm_X_q", A.size(), [&](std::size_t k) { return firm(k) ? qi(firm(k)->production_X().get_quantity()) : 0; });
     put_f("firm_X_v", A.size(), [&](std::size_t k) { return firm(k) ? to_float(firm(k)->production_X().get_value()) : 0.0; });
     put_i("firm_Xhat_q", A.size(), [&](std::size_t k) { return firm(k) ? qi(firm(k)->sales_manager->communicated_parameters().possible_production_X_hat.get_quantity()) : 0; });

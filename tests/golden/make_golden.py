@@ -10,6 +10,8 @@ import subprocess
 import sys
 import tempfile
 
+import numpy as np
+
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from acclimate_b200 import netfile, synth  # noqa: E402
@@ -37,6 +39,18 @@ def cases():
                                       deviation_penalty=1, maximal_decrease_reservation_price_limited_by_markup=1))
     synth.add_shock(a, 1, 8, 0, 0.3)
     yield "flags20", a, 20
+    # utilitarian consumers (the reference's default, ModelInitializer.cpp:136): nested-CES utility optimisation, one basket
+    a = synth.make_network(regions=8, sectors=4, seed=11, max_delay=4, model=dict(utilitarian=1))
+    synth.add_shock(a, 2, 9, 3, 0.3)
+    yield "utilitarian20", a, 20
+    # three baskets with different substitution coefficients, one sector outside every basket, severe shock + blocked passage
+    a = synth.make_network(regions=6, sectors=7, seed=12, max_delay=3, model=dict(utilitarian=1))
+    a["basket_of_sector"] = np.array([0, 0, 1, 2, 2, -1, 1, -1])
+    a["basket_coeff"] = np.array([2.0, 0.7, 4.0])
+    a["inter_basket_coeff"] = np.array([1.3])
+    synth.add_shock(a, 1, 7, 2, 0.1)
+    synth.add_passage(a, 3, 8, 4, 1, 0.2)
+    yield "baskets20", a, 20
 
 
 def main():

@@ -11,13 +11,13 @@ import numpy as np
 from acclimate_b200 import engine, netfile
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-CASES = ["small_shock12", "severe_shock30", "passage25", "outage25", "flags20"]
+CASES = ["small_shock12", "severe_shock30", "passage25", "outage25", "flags20", "utilitarian20", "baskets20"]
 
 EXACT_OR_TIGHT = [
     "edge_D_q", "edge_D_p", "edge_ship_q", "sto_S_q", "sto_S_v", "sto_I_q", "sto_I_v", "sto_U_q", "sto_U_v", "sto_Ut_q", "sto_Ut_v",
     "sto_demand_q", "sto_demand_v", "sto_expected_costs", "sto_optimized_value", "sto_transport_penalty", "firm_X_q", "firm_X_v", "firm_Xhat_q",
     "firm_Xhat_p", "firm_Xexp_q", "firm_Xexp_v", "firm_nbar", "firm_costs_C", "firm_revenue_R", "firm_desired_q", "firm_possible_q",
-    "sector_production_q", "sector_production_v", "region_import_q", "region_export_q", "region_consumption_q", "region_consumption_v",
+    "consumer_utility", "sector_production_q", "sector_production_v", "region_import_q", "region_export_q", "region_consumption_q", "region_consumption_v",
 ]
 LOOSE = ["region_import_v", "region_export_v", "region_gdp_v"]
 # the reference's discarded consumer utility optimisation (Consumer.cpp:270) raises these; the engine does not run it
@@ -67,7 +67,7 @@ def run_case(name, lib_path=None, device=0):
 
 
 # ---- region-partitioned run: every rank checks what it owns against the same golden dump ----
-PER_AGENT = [n for n in EXACT_OR_TIGHT if n.startswith("firm_")]
+PER_AGENT = [n for n in EXACT_OR_TIGHT if n.startswith("firm_")] + ["consumer_utility"]
 PER_STORAGE = [n for n in EXACT_OR_TIGHT if n.startswith("sto_")]
 PER_EDGE = ["edge_D_q", "edge_D_p", "edge_ship_q"]
 PER_REGION = ["region_import_q", "region_export_q", "region_consumption_q", "region_consumption_v", "region_import_v", "region_export_v", "region_gdp_v"]
