@@ -29,7 +29,7 @@ DEFAULT_MODEL = dict(
     deviation_penalty=0,
     cheapest_price_range_preserve_seller_price=0,
     no_self_supply=1,
-    utilitarian=0,
+    utilitarian=1,  # consumers.<..>.bool_utilitarian defaults to true (reference ModelInitializer.cpp:136)
     delta_t=1.0,
 )
 DEFAULT_SECTOR = dict(

@@ -24,14 +24,14 @@ def cases():
     a = synth.make_config("small")
     synth.add_shock(a, 2, 6, 3, 0.5)
     yield "small_shock12", a, 12
-    a = synth.make_network(regions=8, sectors=4, seed=7, max_delay=6)
+    a = synth.make_network(regions=8, sectors=4, seed=7, max_delay=6, model=dict(utilitarian=0))  # price-elastic consumers
     synth.add_shock(a, 3, 12, 2, 0.05)
     yield "severe_shock30", a, 30
     a = synth.make_network(regions=8, sectors=4, seed=8, max_delay=5)
     synth.add_passage(a, 2, 9, 5, 1, 0.3)
     synth.add_passage(a, 4, 6, 3, 2, 0.0)
     yield "passage25", a, 25
-    a = synth.make_network(regions=6, sectors=3, seed=9, const_delay=2)
+    a = synth.make_network(regions=6, sectors=3, seed=9, const_delay=2, model=dict(utilitarian=0))
     synth.add_shock(a, 2, 5, 1, 0.0)
     yield "outage25", a, 25
     a = synth.make_network(regions=6, sectors=4, seed=10, const_delay=1,
