@@ -64,7 +64,7 @@ static void dev_sync(stream_t) {}
 template <class K>
 static void launch_thread(stream_t, int n, K k) { for (int i = 0; i < n; ++i) k(i); }
 template <class K>
-static void launch_block(stream_t, int n, int threads, K k) { for (int i = 0; i < n; ++i) { HostCtx cx(threads); k(cx, i); } }
+static void launch_block(stream_t, int n, K k) { for (int i = 0; i < n; ++i) { HostCtx cx(K::THREADS); k(cx, i); } }
 template <class K>
 static void launch_warp(stream_t, int n, size_t smem, K k) {
     std::vector<unsigned char> sm(smem + 16);
@@ -103,13 +103,13 @@ __global__ void __launch_bounds__(128) thread_kernel(int n, K k) {
     if (i < n) k(i);
 }
 template <class K>
-__global__ void __launch_bounds__(256) block_kernel(K k) {
+__global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) block_kernel(K k) {
     __shared__ __align__(16) unsigned char scratch[ACC_BLOCK_SCRATCH_BYTES];
     BlockCtx cx(scratch);
     k(cx, (int)blockIdx.x);
 }
 template <class K>
-__global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) block_smem_kernel(K k) {
+__global__ void __maxnreg__(K::MAXREG) block_smem_kernel(K k) {
     __shared__ __align__(16) unsigned char scratch[ACC_BLOCK_SCRATCH_BYTES];
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     BlockCtx cx(scratch);
@@ -128,9 +128,9 @@ static void launch_thread(stream_t s, int n, K k) {
     ACC_CUDA(cudaGetLastError());
 }
 template <class K>
-static void launch_block(stream_t s, int n, int threads, K k) {
+static void launch_block(stream_t s, int n, K k) {
     if (n <= 0) return;
-    block_kernel<K><<<n, threads, 0, s>>>(k);
+    block_kernel<K><<<n, K::THREADS, 0, s>>>(k);
     ACC_CUDA(cudaGetLastError());
 }
 template <class K>
@@ -184,6 +184,11 @@ struct FirmPossibleProduction {  // thread per firm
 };
 
 struct SellerProduction {  // CTA per firm
+#ifndef ACC_SELLER_THREADS
+#define ACC_SELLER_THREADS 256
+#define ACC_SELLER_MIN_BLOCKS 4
+#endif
+    enum { THREADS = ACC_SELLER_THREADS, MIN_BLOCKS = ACC_SELLER_MIN_BLOCKS };
     FirmView fv; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step; const int* firm_ids;
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int k) const { seller_phase1(cx, firm_ids[k], fv, ev, mp, sectors, events, step); }
@@ -275,7 +280,7 @@ struct StorageDelivery {  // thread per storage
 };
 
 struct ConsumerUtility {  // one CTA of ACCSQP_GROUP threads per utilitarian consumer
-    enum { THREADS = ACCSQP_GROUP, MIN_BLOCKS = 1 };
+    enum { THREADS = ACCSQP_GROUP, MAXREG = 255 };
     ConsumerView cv; StorageView st; ModelP mp; EventSink events; int n_max; int* fatal;
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const {
@@ -285,7 +290,7 @@ struct ConsumerUtility {  // one CTA of ACCSQP_GROUP threads per utilitarian con
 };
 
 struct Purchase {  // one CTA of ACCSQP_GROUP threads per purchasing manager
-    enum { THREADS = ACCSQP_GROUP, MIN_BLOCKS = 6 };
+    enum { THREADS = ACCSQP_GROUP, MAXREG = 112 };  // 6 CTAs of 3 warps per SM: 65536 / (18 * 32) = 113
     StorageView st; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
     const i64* in_off; const int* in_edge; const int* in_seller; const SellerPub* pub; int n_max; const int* pm_ids;  // pm_ids == nullptr: all
     i64* dem_q; double* dem_v; double* exp_costs; double* opt_val; double* tpen; int* iters; int* evals;
@@ -319,6 +324,7 @@ struct Purchase {  // one CTA of ACCSQP_GROUP threads per purchasing manager
 };
 
 struct FirmIncomingDemand {  // CTA per firm: sum of the demand requests it holds (output surface only)
+    enum { THREADS = 256, MIN_BLOCKS = 1 };
     EdgeView ev; const int* firm_ids; i64* out_q; double* out_v;
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int k) const {
@@ -392,6 +398,10 @@ using namespace acc;
 struct acc_engine {
     int device = 0;
     stream_t stream = nullptr;
+    stream_t side = nullptr;  // consumers' utility optimisation, concurrent with the sellers' pass
+#ifndef ACC_HOST_EMU
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+#endif
     i64 step = 0;
     i64 launches = 0;
     bool profile = false;
@@ -452,6 +462,9 @@ struct acc_engine {
 #ifndef ACC_HOST_EMU
         for (auto& c : clocks)
             for (auto& pr : c.pending) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+        if (ev_fork) cudaEventDestroy(ev_fork);
+        if (ev_join) cudaEventDestroy(ev_join);
+        if (side) cudaStreamDestroy(side);
         if (stream) cudaStreamDestroy(stream);
 #endif
     }
@@ -510,7 +523,9 @@ struct acc_engine {
         return (int)clocks.size() - 1;
     }
     template <class Fn>
-    void timed(const char* name, Fn fn) {
+    void timed(const char* name, Fn fn) { timed_on(stream, name, fn); }
+    template <class Fn>
+    void timed_on(stream_t on, const char* name, Fn fn) {
         ++launches;
 #ifndef ACC_HOST_EMU
         if (profile) {
@@ -518,15 +533,15 @@ struct acc_engine {
             cudaEvent_t a, b;
             ACC_CUDA(cudaEventCreate(&a));
             ACC_CUDA(cudaEventCreate(&b));
-            ACC_CUDA(cudaEventRecord(a, stream));
+            ACC_CUDA(cudaEventRecord(a, on));
             fn();
-            ACC_CUDA(cudaEventRecord(b, stream));
+            ACC_CUDA(cudaEventRecord(b, on));
             clocks[id].pending.push_back(std::make_pair(a, b));
             clocks[id].launches += 1;
             return;
         }
 #endif
-        (void)name;
+        (void)name; (void)on;
         fn();
     }
     void collect_clocks() {
@@ -545,19 +560,34 @@ struct acc_engine {
 #endif
     }
 
-    void consumer_utility() {
+    // The consumers' utility optimisation reads storages and writes their desired use only, so it runs on a side
+    // stream next to the sellers' production / distribution pass; the storage pass waits for both.
+    void consumer_fork() {
         if (!mp.utilitarian || nC == 0) return;
         ConsumerUtility k{consumer_view(), storage_view(), mp, sink(), c_n_max, fatal.p};
-        timed("consumer_utility", [&] { launch_block_smem(stream, nC, consumer_workspace_bytes(c_n_max), k); });
+#ifndef ACC_HOST_EMU
+        ACC_CUDA(cudaEventRecord(ev_fork, stream));
+        ACC_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+#endif
+        timed_on(side, "consumer_utility", [&] { launch_block_smem(side, nC, consumer_workspace_bytes(c_n_max), k); });
+#ifndef ACC_HOST_EMU
+        ACC_CUDA(cudaEventRecord(ev_join, side));
+#endif
+    }
+    void consumer_join() {
+#ifndef ACC_HOST_EMU
+        if (mp.utilitarian && nC != 0) ACC_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
+#endif
     }
     void stage_sell() {
+        consumer_fork();
         {
             FirmPossibleProduction k{firm_view(), storage_view(), mp, firm_ids.p};
             timed("firm_possible_production", [&] { launch_thread(stream, nF, k); });
         }
         {
             SellerProduction k{firm_view(), edge_view(), mp, sectors.p, sink(), step, firm_ids.p};
-            timed("seller_production", [&] { launch_block(stream, nF, 256, k); });
+            timed("seller_production", [&] { launch_block(stream, nF, k); });
         }
         if (halo_send.n) {
             PackFlow k{edge_view(), step, halo_send.p, x_flow_send};
@@ -569,7 +599,7 @@ struct acc_engine {
             UnpackFlow k{edge_view(), step, halo_recv.p, x_flow_recv};
             timed("unpack_flow", [&] { launch_thread(stream, (int)halo_recv.n, k); });
         }
-        consumer_utility();
+        consumer_join();
         {
             StorageDelivery k{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p,
                               partitioned ? owned.p : nullptr};
@@ -613,11 +643,12 @@ struct acc_engine {
     // the reference's phases (Model::iterate_*) on an unpartitioned engine
     void phase_cp() {
         require_single("acc_phase");
+        consumer_fork();
         FirmPossibleProduction k1{firm_view(), storage_view(), mp, firm_ids.p};
         timed("firm_possible_production", [&] { launch_thread(stream, nF, k1); });
         SellerProduction k2{firm_view(), edge_view(), mp, sectors.p, sink(), step, firm_ids.p};
-        timed("seller_production", [&] { launch_block(stream, nF, 256, k2); });
-        consumer_utility();
+        timed("seller_production", [&] { launch_block(stream, nF, k2); });
+        consumer_join();
         StorageDelivery k3{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p, nullptr};
         timed("storage_delivery", [&] { launch_thread(stream, nSt, k3); });
     }
@@ -1104,7 +1135,7 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
         DBuf<i64> q; DBuf<double> v;
         q.alloc(E.nA); v.alloc(E.nA); q.zero(s); v.zero(s);
         FirmIncomingDemand k{E.edge_view(), E.firm_ids.p, q.p, v.p};
-        E.timed("firm_incoming_demand", [&] { launch_block(s, E.nF, 256, k); });
+        E.timed("firm_incoming_demand", [&] { launch_block(s, E.nF, k); });
         if (name == "firm_incoming_demand_q") I(q); else F(v);
         q.free(); v.free();
         return true;
@@ -1177,6 +1208,9 @@ acc_engine* acc_create_partition(const acc_network* net, const acc_params* param
         if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) fail("acc_create: no CUDA device available (this library has no CPU path)");
         ACC_CUDA(cudaSetDevice(device));
         ACC_CUDA(cudaStreamCreateWithFlags(&E->stream, cudaStreamNonBlocking));
+        ACC_CUDA(cudaStreamCreateWithFlags(&E->side, cudaStreamNonBlocking));
+        ACC_CUDA(cudaEventCreateWithFlags(&E->ev_fork, cudaEventDisableTiming));
+        ACC_CUDA(cudaEventCreateWithFlags(&E->ev_join, cudaEventDisableTiming));
 #endif
         build(*E, *net, *params, agent_owned);
         return E;

@@ -52,7 +52,7 @@ class EngineError(RuntimeError):
 
 
 def load_library(path=None):
-    path = path or LIB_PATH
+    path = path or os.environ.get("ACCLIMATE_B200_LIB") or LIB_PATH  # the override serves kernel-variant experiments
     if not os.path.exists(path):
         raise EngineError(f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` (CUDA library, no CPU fallback)")
     lib = C.CDLL(path)
