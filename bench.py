@@ -279,7 +279,12 @@ def main():
         if dom[0] is not None and dom[1][1] > 0:
             per_launch_s = dom[1][0] * 1e-3 / dom[1][1]
             bpe = KERNEL_BYTES_PER_EDGE.get(dom[0], BYTES_PER_UPDATE)
-            achieved = bpe * n_edges / per_launch_s / 1e9
+            # connections one launch of that kernel processes on this rank (a part computes the buyer side of the connections it
+            # buys and the seller side of those it sells)
+            units = n_edges
+            if partitioned:
+                units = int(E.part.sells.sum()) if dom[0] == "seller_production" else int(E.part.buys.sum())
+            achieved = bpe * units / per_launch_s / 1e9
             roof = {"bound": "hbm", "kernel": dom[0], "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": ncu_traffic(dom[0]) if args.config == "eora" else None,
                     "algorithmic_bytes_per_connection": bpe, "avg_launch_ms": per_launch_s * 1e3, "peak_source": peak_src,
