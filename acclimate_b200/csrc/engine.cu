@@ -241,36 +241,59 @@ struct StorageDelivery {  // thread per storage
         Flow imp = mkflow(0, 0.0);
         i64 tq = st.T_q[s];
         double tv = st.T_v[s];
-        for (int k = 0; k < width; ++k) {
-            const int e = ell_edge[base + (i64)k * 32 + lane];
-            if (e < 0) continue;
-            const Flow front = mkflow(ev.conv_q[now + e], ev.conv_v[now + e]);
-            const int tau = ev.tau[e];
-            Flow ship = front;
-            if (tau != 0) {
-                const i64 pl = (i64)((step + tau) % T) * ev.n_edges;
-                ship = mkflow(ev.conv_q[pl + e], ev.conv_v[pl + e]);
+        // The fold below is strictly sequential (the reference's delivery order: sellers ascending), so the loads of
+        // eight connections are issued together first: one thread keeps 8 x 5 independent requests in flight instead
+        // of walking a chain of dependent ones.
+        enum { U = 8 };
+        for (int k0 = 0; k0 < width; k0 += U) {
+            int e_[U], tau_[U];
+            Flow front_[U], ship_[U];
+            unsigned char dom_[U];
+#pragma unroll
+            for (int j = 0; j < U; ++j) e_[j] = (k0 + j < width) ? ell_edge[base + (i64)(k0 + j) * 32 + lane] : -1;
+#pragma unroll
+            for (int j = 0; j < U; ++j) {
+                const int e = e_[j] < 0 ? 0 : e_[j];
+                tau_[j] = ev.tau[e];
+                dom_[j] = ev.domestic[e];
+                front_[j] = mkflow(ev.conv_q[now + e], ev.conv_v[now + e]);
             }
-            Flow out;
-            if (ev.ovf_q == nullptr) {
-                out = fcopy(front);  // overflow == 0, no passage forcing ever set
-            } else {
-                const int ent = ev.entity[e];
-                const double nu = ent >= 0 ? ev.nu[ent] : -1.0;
-                const Flow total = fadd(mkflow(ev.ovf_q[e], ev.ovf_v[e]), front);
-                if (nu < 0) {
-                    out = fcopy(total);
-                } else {
-                    const Flow cap = flow_qp(qmul_l(nu, ev.Z_q[e]), flow_price(front));
-                    out = fcopy(cap.q < total.q ? cap : total);  // std::min by quantity
+#pragma unroll
+            for (int j = 0; j < U; ++j) {
+                const int e = e_[j] < 0 ? 0 : e_[j];
+                ship_[j] = front_[j];
+                if (tau_[j] != 0) {
+                    const i64 pl = (i64)((step + tau_[j]) % T) * ev.n_edges;
+                    ship_[j] = mkflow(ev.conv_q[pl + e], ev.conv_v[pl + e]);
                 }
-                const Flow ovf = fcopy(fsub(total, out));
-                ev.ovf_q[e] = ovf.q; ev.ovf_v[e] = ovf.v;
             }
-            in = fadd(in, out);
-            if (!ev.domestic[e]) imp = fadd(imp, out);
-            tq += ship.q - out.q;
-            tv += ship.v - out.v;
+#pragma unroll
+            for (int j = 0; j < U; ++j) {
+                const int e = e_[j];
+                if (e < 0) continue;
+                const Flow front = front_[j];
+                const Flow ship = ship_[j];
+                Flow out;
+                if (ev.ovf_q == nullptr) {
+                    out = fcopy(front);  // overflow == 0, no passage forcing ever set
+                } else {
+                    const int ent = ev.entity[e];
+                    const double nu = ent >= 0 ? ev.nu[ent] : -1.0;
+                    const Flow total = fadd(mkflow(ev.ovf_q[e], ev.ovf_v[e]), front);
+                    if (nu < 0) {
+                        out = fcopy(total);
+                    } else {
+                        const Flow cap = flow_qp(qmul_l(nu, ev.Z_q[e]), flow_price(front));
+                        out = fcopy(cap.q < total.q ? cap : total);  // std::min by quantity
+                    }
+                    const Flow ovf = fcopy(fsub(total, out));
+                    ev.ovf_q[e] = ovf.q; ev.ovf_v[e] = ovf.v;
+                }
+                in = fadd(in, out);
+                if (!dom_[j]) imp = fadd(imp, out);
+                tq += ship.q - out.q;
+                tv += ship.v - out.v;
+            }
         }
         st.In_q[s] = in.q; st.In_v[s] = in.v;
         st.dlv_q[s] = in.q;
