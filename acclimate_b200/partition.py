@@ -44,29 +44,45 @@ def assign_regions(arrays, world):
     return owner
 
 
-class Part:
-    """What one rank needs: its sub-network, ownership mask and halo lists (local connection ids grouped by peer)."""
+def assign_regions_uniform(n_regions, world):
+    """Equal contiguous blocks of regions (what assign_regions gives for a dense network of equally sized regions)."""
+    return np.minimum(np.arange(n_regions) * world // n_regions, world - 1)
 
-    def __init__(self, arrays, region_owner, rank):
+
+class Part:
+    """What one rank needs: its sub-network, ownership mask and halo lists (local connection ids grouped by peer).
+    `local=True`: `arrays` already holds only this part's connections (synth.make_network(part=...))."""
+
+    def __init__(self, arrays, region_owner, rank, local=False):
         a = arrays
-        world = int(region_owner.max()) + 1
-        agent_part = np.asarray(region_owner, dtype=np.int64)[np.asarray(a["agent_region"], dtype=np.int64)]
+        world = int(np.max(region_owner)) + 1
+        agent_part = np.asarray(region_owner, dtype=np.int8)[np.asarray(a["agent_region"], dtype=np.int64)]
         self.rank, self.world = rank, world
         self.agent_part = agent_part
         self.owned = (agent_part == rank).astype(np.uint8)
         ef = np.asarray(a["edge_from"], dtype=np.int64)
         et = np.asarray(a["edge_to"], dtype=np.int64)
         pf, pt = agent_part[ef], agent_part[et]
-        keep = (pf == rank) | (pt == rank)
-        self.edge_gid = np.nonzero(keep)[0]          # local id -> global connection id (order preserved)
-        lf, lt = pf[keep], pt[keep]
-        local = {k: v for k, v in a.items()}
-        local["edge_from"], local["edge_to"] = ef[keep], et[keep]
-        local["edge_zq"] = np.asarray(a["edge_zq"], dtype=np.int64)[keep]
-        meta = np.array(a["meta"], dtype=np.int64).copy()
-        meta[3] = int(keep.sum())
-        local["meta"] = meta
-        self.arrays = local
+        if local:
+            if not np.all((pf == rank) | (pt == rank)):
+                raise ValueError("a local snapshot may only hold connections of this part")
+            self.edge_gid = None
+            self.global_edges = int(np.asarray(a["global_edges"]).reshape(-1)[0])
+            lf, lt = pf, pt
+            self.arrays = a
+            meta = np.asarray(a["meta"], dtype=np.int64)
+        else:
+            keep = (pf == rank) | (pt == rank)
+            self.edge_gid = np.nonzero(keep)[0]          # local id -> global connection id (order preserved)
+            self.global_edges = int(ef.size)
+            lf, lt = pf[keep], pt[keep]
+            local_arrays = {k: v for k, v in a.items()}
+            local_arrays["edge_from"], local_arrays["edge_to"] = ef[keep], et[keep]
+            local_arrays["edge_zq"] = np.asarray(a["edge_zq"], dtype=np.int64)[keep]
+            meta = np.array(a["meta"], dtype=np.int64).copy()
+            meta[3] = int(keep.sum())
+            local_arrays["meta"] = meta
+            self.arrays = local_arrays
         ids = np.arange(meta[3], dtype=np.int64)
         send, recv, self.send_counts, self.recv_counts = [], [], [], []
         for p in range(world):
@@ -85,7 +101,7 @@ class PartitionedEngine(_engine.Engine):
     """One part of a region-partitioned model.  Needs an initialised torch.distributed process group with one rank
     per part (NCCL for the CUDA library; the CPU tests drive the emulation library over gloo)."""
 
-    def __init__(self, arrays, region_owner=None, device=0, lib_path=None, group=None, tensor_device=None):
+    def __init__(self, arrays, region_owner=None, device=0, lib_path=None, group=None, tensor_device=None, local=False):
         import torch
         import torch.distributed as dist
 
@@ -95,7 +111,7 @@ class PartitionedEngine(_engine.Engine):
             region_owner = assign_regions(arrays, world)
         if int(np.max(region_owner)) + 1 != world:
             raise _engine.EngineError("region_owner does not name one part per rank")
-        self.part = Part(arrays, np.asarray(region_owner), rank)
+        self.part = Part(arrays, np.asarray(region_owner), rank, local=local)
         self.lib = _engine.load_library(lib_path)
         self._bind()
         net, par, self._keep = _engine.network_struct(self.part.arrays)

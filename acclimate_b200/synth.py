@@ -12,6 +12,8 @@ makes the file order the CSR-by-seller order.
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 
 from . import netfile
@@ -55,8 +57,12 @@ def _haversine_km(lon1, lat1, lon2, lat2):
     return 2 * r * np.arcsin(np.sqrt(np.clip(a, 0, 1)))
 
 
-def make_network(regions, sectors, seed, const_delay=None, world_output=None, beta=1.15, model=None, sector=None, max_delay=30):
-    """Returns an OrderedDict of arrays (see netfile.py) for a dense `regions` x `sectors` network."""
+def make_network(regions, sectors, seed, const_delay=None, world_output=None, beta=1.15, model=None, sector=None, max_delay=30, part=None):
+    """Returns an OrderedDict of arrays (see netfile.py) for a dense `regions` x `sectors` network.
+
+    part = (region_owner, rank) emits only the connections a part of a region-partitioned run holds (seller or buyer in
+    a region of `rank`), in the global order, plus "global_edges" = the size of the whole network: a part of a network
+    that is too large for one host buffer can be generated without ever materialising the rest (partition.Part.from_local)."""
     rng = np.random.Generator(np.random.PCG64(seed))
     R, S = int(regions), int(sectors)
     A = rng.dirichlet(np.full(S, 0.3), size=S).T  # A[s_from, s_to], columns sum to 1
@@ -111,6 +117,13 @@ def make_network(regions, sectors, seed, const_delay=None, world_output=None, be
     # pass 2: emit seller-major edges
     blocks_from, blocks_to, blocks_z = [], [], []
     buyers_all = (np.arange(R)[:, None] * n_per + to_sector[None, :]).reshape(-1)
+    global_edges = 0
+    out_q = np.zeros(n_agents)
+    in_q2 = np.zeros(n_agents)
+    owned_buyer = None
+    if part is not None:
+        owner, rank = np.asarray(part[0]), int(part[1])
+        owned_buyer = np.repeat(owner == rank, n_per)
     for rf in range(R):
         z = block(rf)
         z[:, :, S] *= lift[rf][:, None]
@@ -118,6 +131,11 @@ def make_network(regions, sectors, seed, const_delay=None, world_output=None, be
         for sf in range(S):
             seller = rf * n_per + sf
             keep = buyers_all != seller
+            global_edges += int(keep.sum())
+            out_q[seller] = zq[sf][keep].sum()
+            in_q2 += np.where(keep, zq[sf], 0)
+            if owned_buyer is not None and owner[rf] != rank:
+                keep = keep & owned_buyer
             blocks_from.append(np.full(int(keep.sum()), seller, dtype=np.int64))
             blocks_to.append(buyers_all[keep])
             blocks_z.append(zq[sf][keep])
@@ -151,10 +169,8 @@ def make_network(regions, sectors, seed, const_delay=None, world_output=None, be
     np.fill_diagonal(delay, 0)
 
     # invariants the reference's clean_network checks (ModelInitializer.cpp:230-236)
-    out_q = np.bincount(edge_from, weights=edge_zq.astype(np.float64), minlength=n_agents)
-    in_q = np.bincount(edge_to, weights=edge_zq.astype(np.float64), minlength=n_agents)
     firms = agent_type == 1
-    if not np.all(out_q[firms] - in_q[firms] > 0):
+    if not np.all(out_q[firms] - in_q2[firms] > 0):
         raise ValueError("generated network has a firm without positive value added")
 
     from collections import OrderedDict
@@ -174,6 +190,8 @@ def make_network(regions, sectors, seed, const_delay=None, world_output=None, be
     arrays["consumer_elasticity"] = np.full(S + 1, -0.5)
     arrays["forcing"] = np.zeros(0)
     arrays["passage"] = np.zeros(0)
+    if part is not None:
+        arrays["global_edges"] = np.array([global_edges], dtype=np.int64)
     return arrays
 
 
@@ -204,9 +222,11 @@ CONFIGS = {
 }
 
 
-def make_config(name):
-    cfg = CONFIGS[name]
-    arrays = make_network(**cfg)
+def make_config(name, part=None):
+    cfg = dict(CONFIGS[name])
+    if name == "x4" and os.environ.get("ACC_X4_REGIONS"):  # dry runs of the partitioned generator path at a small size
+        cfg["regions"] = int(os.environ["ACC_X4_REGIONS"])
+    arrays = make_network(part=part, **cfg)
     if name == "eora_flood":
         add_shock(arrays, 10, 24, 17, 0.5)
     return arrays

@@ -65,9 +65,16 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons)}
 
 
-def make_network(args, rank):
+def make_network(args, rank, part=None):
     from acclimate_b200 import synth
 
+    if args.config == "x4":
+        # 748 x 26: ~393 M connections, too large for one GPU; every rank generates only its own part
+        if part is None:
+            raise SystemExit("bench.py: --config x4 needs --mode partition on 2 or more GPUs")
+        net = synth.make_config("x4", part=part)
+        workload = "synthetic MRIO 748x26 dense, 4x the regions of the EORA shape, baseline run (BASELINE.json configs[3])"
+        return net, workload
     if args.config == "eora":
         net = synth.make_config("eora")
         workload = "EORA-shaped synthetic MRIO 187x26 dense, baseline run (BASELINE.json configs[1])"
@@ -172,7 +179,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--config", default="eora", choices=["eora", "eora_flood", "small"])
+    ap.add_argument("--config", default="eora", choices=["eora", "eora_flood", "small", "x4"])
     ap.add_argument("--ref-steps", type=int, default=3)
     ap.add_argument("--reference-small", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -204,14 +211,22 @@ def main():
     g.build_cuda()
     from acclimate_b200 import engine
 
-    net, workload = make_network(args, rank)
     partitioned = world > 1 and args.mode == "partition"
-    if partitioned:
+    if partitioned and args.config == "x4":
+        from acclimate_b200 import partition, synth
+
+        owner = partition.assign_regions_uniform(int(os.environ.get("ACC_X4_REGIONS", synth.CONFIGS["x4"]["regions"])), world)
+        net, workload = make_network(args, rank, part=(owner, rank))
+        E = partition.PartitionedEngine(net, region_owner=owner, device=local_rank, local=True)
+        n_edges = E.part.global_edges
+    elif partitioned:
         from acclimate_b200 import partition
 
+        net, workload = make_network(args, rank)
         E = partition.PartitionedEngine(net, device=local_rank)
         n_edges = int(net["meta"][3])  # the whole network; this rank holds E.n_edges of them (owned seller or owned buyer)
     else:
+        net, workload = make_network(args, rank)
         E = engine.Engine(net, device=local_rank)
         n_edges = E.n_edges
     sc = engine.Scenario(net)
