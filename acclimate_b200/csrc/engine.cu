@@ -71,8 +71,7 @@ static void launch_warp(stream_t, int n, size_t smem, K k) {
     for (int i = 0; i < n; ++i) { HostCtx cx(32); k(cx, i, sm.data()); }
 }
 template <class K>
-static void launch_block_smem(stream_t, int n, size_t smem, K k) {
-    const int threads = K::THREADS;
+static void launch_block_smem(stream_t, int n, int threads, size_t smem, K k) {
     std::vector<unsigned char> sm(smem + 16);
     for (int i = 0; i < n; ++i) { HostCtx cx(threads); k(cx, i, sm.data()); }
 }
@@ -145,8 +144,7 @@ static void launch_warp(stream_t s, int n, size_t smem, K k) {
     ACC_CUDA(cudaGetLastError());
 }
 template <class K>
-static void launch_block_smem(stream_t s, int n, size_t smem, K k) {
-    const int threads = K::THREADS;
+static void launch_block_smem(stream_t s, int n, int threads, size_t smem, K k) {
     if (n <= 0) return;
     static size_t configured = 0;
     if (smem > configured) {
@@ -303,7 +301,7 @@ struct StorageDelivery {  // thread per storage
 };
 
 struct ConsumerUtility {  // one CTA of ACCSQP_GROUP threads per utilitarian consumer
-    enum { THREADS = ACCSQP_GROUP, MAXREG = 255 };
+    enum { MAXREG = 255 };
     ConsumerView cv; StorageView st; ModelP mp; EventSink events; int n_max; int* fatal;
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const {
@@ -313,7 +311,7 @@ struct ConsumerUtility {  // one CTA of ACCSQP_GROUP threads per utilitarian con
 };
 
 struct Purchase {  // one CTA of ACCSQP_GROUP threads per purchasing manager
-    enum { THREADS = ACCSQP_GROUP, MAXREG = 112 };  // 6 CTAs of 3 warps per SM: 65536 / (18 * 32) = 113
+    enum { MAXREG = 112 };  // 6 CTAs of 3 warps per SM at the base group size: 65536 / (18 * 32) = 113; 512 threads still fit
     StorageView st; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
     const i64* in_off; const int* in_edge; const int* in_seller; const SellerPub* pub; int n_max; const int* pm_ids;  // pm_ids == nullptr: all
     i64* dem_q; double* dem_v; double* exp_costs; double* opt_val; double* tpen; int* iters; int* evals;
@@ -432,6 +430,7 @@ struct acc_engine {
 
     // sizes
     int nA = 0, nS = 0, nR = 0, nSt = 0, nF = 0, n_max = 0, T = 1;
+    int pm_group = ACCSQP_GROUP;  // threads per purchasing manager
     i64 nE = 0;
     ModelP mp;
     std::vector<SectorP> h_sectors;
@@ -592,7 +591,7 @@ struct acc_engine {
         ACC_CUDA(cudaEventRecord(ev_fork, stream));
         ACC_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
 #endif
-        timed_on(side, "consumer_utility", [&] { launch_block_smem(side, nC, consumer_workspace_bytes(c_n_max), k); });
+        timed_on(side, "consumer_utility", [&] { launch_block_smem(side, nC, ACCSQP_GROUP, consumer_workspace_bytes(c_n_max), k); });
 #ifndef ACC_HOST_EMU
         ACC_CUDA(cudaEventRecord(ev_join, side));
 #endif
@@ -645,9 +644,10 @@ struct acc_engine {
         Purchase k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, pub.p, n_max,
                    partitioned ? pm_ids.p : nullptr, s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
         const bool dev = mp.deviation_penalty != 0;
-        // One CTA of ACCSQP_GROUP threads per purchasing manager, all its vectors in shared memory.  The group size is
-        // part of the arithmetic (reduction order), so it is a build constant shared with the oracle's host context.
-        timed("purchase", [&] { launch_block_smem(stream, partitioned ? n_pm : nSt, pm_workspace_bytes(n_max, dev), k); });
+        // One CTA of pm_group threads per purchasing manager, all its vectors in shared memory.  The group size is part
+        // of the arithmetic (reduction order): ACCSQP_GROUP, or accsqp_group_for(largest manager) -- the same rule the
+        // oracle's host context follows.
+        timed("purchase", [&] { launch_block_smem(stream, partitioned ? n_pm : nSt, pm_group, pm_workspace_bytes(n_max, dev), k); });
         if (halo_recv.n) {
             PackDemand pk{edge_view(), halo_recv.p, x_dem_send};
             timed("pack_demand", [&] { launch_thread(stream, (int)halo_recv.n, pk); });
@@ -888,6 +888,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
     int n_max = 0;
     for (int k = 0; k < nSt; ++k) n_max = std::max<i64>(n_max, in_off[k + 1] - in_off[k]);
     E.n_max = (n_max + 7) / 8 * 8;
+    E.pm_group = accsqp_group_for(n_max);
     const int n_slices = (nSt + 31) / 32;
     std::vector<i64> ell_off(n_slices + 1, 0);
     std::vector<int> ell_width(n_slices, 0);
@@ -1457,6 +1458,16 @@ int acc_read(acc_engine* e, const char* group, const char* variable, double* dst
     ACC_API_END(-1)
 }
 
+int acc_solver_group(const acc_engine* e) { return e ? e->pm_group : -1; }
+int acc_set_solver_group(acc_engine* e, int group) {
+    ACC_API_BEGIN
+    if (e == nullptr) fail("acc_set_solver_group: null engine");
+    if (group < 32 || group > 512 || group % 32 != 0) fail("acc_set_solver_group: the group must be a multiple of 32 in 32..512");
+    if (e->step != 0) fail("acc_set_solver_group: only before the first step");
+    e->pm_group = group;
+    return 0;
+    ACC_API_END(-1)
+}
 int64_t acc_edge_count(const acc_engine* e) { return e ? e->nE : -1; }
 int64_t acc_step_count(const acc_engine* e) { return e ? e->step : -1; }
 int64_t acc_launch_count(const acc_engine* e) { return e ? e->launches : -1; }

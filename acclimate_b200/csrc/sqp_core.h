@@ -50,6 +50,17 @@
 #ifndef ACCSQP_GROUP
 #define ACCSQP_GROUP 96
 #endif
+// Purchasing managers with more connections than two per thread of the base group get a larger group, chosen from the
+// LARGEST manager of the network (one launch shape for all; the oracle's harness applies the same rule):
+// two connections per thread, a multiple of the warp size, at most 512 threads.
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline int accsqp_group_for(int n_max) {
+    if (n_max <= 2 * ACCSQP_GROUP) return ACCSQP_GROUP;
+    const int g = ((n_max + 1) / 2 + 31) / 32 * 32;
+    return g > 512 ? 512 : g;
+}
 #define ACCSQP_BMIN 1e-12
 #define ACCSQP_BMAX 1e+15
 

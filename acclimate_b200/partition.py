@@ -112,7 +112,7 @@ class PartitionedEngine(_engine.Engine):
         if int(np.max(region_owner)) + 1 != world:
             raise _engine.EngineError("region_owner does not name one part per rank")
         self.part = Part(arrays, np.asarray(region_owner), rank, local=local)
-        self.lib = _engine.load_library(lib_path)
+        self.lib = lib = _engine.load_library(lib_path)
         self._bind()
         net, par, self._keep = _engine.network_struct(self.part.arrays)
         meta = self.part.arrays["meta"]
@@ -135,6 +135,15 @@ class PartitionedEngine(_engine.Engine):
         self._check(self.lib.acc_set_halo(self.h, self._send_ids.ctypes.data, ns, self._recv_ids.ctypes.data, nr, self.flow_send.data_ptr(),
                                           self.flow_recv.data_ptr(), self.demand_send.data_ptr(), self.demand_recv.data_ptr(),
                                           self.seller_table.data_ptr()))
+        # one solver group size for all parts: the reduction order is part of the arithmetic
+        lib.acc_solver_group.argtypes = [C.c_void_p]
+        lib.acc_set_solver_group.argtypes = [C.c_void_p, C.c_int]
+        grp = torch.tensor([self.lib.acc_solver_group(self.h)], dtype=torch.int64)
+        if world > 1:
+            g_dev = grp.to(self.tensor_device) if dist.get_backend(group) == "nccl" else grp
+            dist.all_reduce(g_dev, op=dist.ReduceOp.MAX, group=group)
+            grp = g_dev.cpu()
+        self._check(self.lib.acc_set_solver_group(self.h, int(grp[0])))
         self._stream = None
         if self.tensor_device.type == "cuda":
             self._stream = torch.cuda.ExternalStream(self.stream(), device=self.tensor_device)

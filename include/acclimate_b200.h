@@ -133,6 +133,13 @@ int acc_set_halo(acc_engine* e, const int64_t* send_edges, size_t n_send, const 
 enum { ACC_STAGE_SELL = 0, ACC_STAGE_DELIVER = 1, ACC_STAGE_PURCHASE = 2, ACC_STAGE_CLOSE = 3 };
 int acc_stage(acc_engine* e, int stage);
 
+/* Threads that solve one purchasing manager's optimisation.  The order of the solver's reductions -- part of its
+ * floating-point arithmetic -- follows from it, so all parts of a partitioned run must agree: each part derives the
+ * value from its own largest manager, the caller takes the maximum over the parts and sets it everywhere before the
+ * first step (acclimate_b200/partition.py does). */
+int acc_solver_group(const acc_engine* e);
+int acc_set_solver_group(acc_engine* e, int group);
+
 /* replaces EconomicAgent::set_forcing for all agents at once (src/model/EconomicAgent.cpp:43-47);
  * lambda has n_agents entries */
 int acc_set_agent_forcing(acc_engine* e, const double* lambda, size_t n);

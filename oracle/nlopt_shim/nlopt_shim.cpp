@@ -166,6 +166,10 @@ struct DenseCallbackEval {
 
 }  // namespace
 
+// thread-group size whose reduction order the diagonal solver replays (accsqp_group_for of the network's largest manager)
+static int g_group = ACCSQP_GROUP;
+extern "C" void nlopt_shim_set_group(int group) { g_group = group; }
+
 // whole-run solver statistics (printed by the harness; serial builds only -- not atomic)
 long long g_stat_calls = 0, g_stat_iters = 0, g_stat_evals = 0, g_stat_qp = 0, g_stat_max_iters = 0;
 extern "C" void nlopt_shim_stats(long long* out) {
@@ -203,7 +207,7 @@ extern "C" nlopt_result nlopt_optimize(nlopt_opt opt, double* x, double* opt_f) 
     int ret;
     if (!kinks.empty()) {
         // separable objective with described kinks (the purchasing managers): diagonal model, sqp_core.h
-        acc::HostCtx cx(ACCSQP_GROUP);  // replays the device group's reduction order
+        acc::HostCtx cx(g_group);  // replays the device group's reduction order
         CallbackEval ev{opt, &w, std::vector<double>((size_t)n)};
         ret = accsqp::sqp_minimize(cx, ev, w, p, st);
         std::memcpy(x, w.xbest, sizeof(double) * n);

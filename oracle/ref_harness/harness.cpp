@@ -100,6 +100,7 @@ struct EventRec {
     double value;
 };
 static std::vector<EventRec> g_events;
+extern "C" void nlopt_shim_set_group(int group);
 static std::unordered_set<const void*> g_purchasing_managers;  // which nlopt user data are PurchasingManagers
 static std::int64_t g_step = 0;
 
@@ -295,7 +296,12 @@ class ModelInitializer {
             if (static_cast<void*>(firm_from) == static_cast<void*>(to)) firm_from->self_supply_connection(bc);
             edges.push_back(bc);
         }
-        for (auto* st : storages) g_purchasing_managers.insert(st->purchasing_manager.get());
+        std::size_t n_max = 0;
+        for (auto* st : storages) {
+            g_purchasing_managers.insert(st->purchasing_manager.get());
+            n_max = std::max(n_max, st->purchasing_manager->business_connections.size());
+        }
+        nlopt_shim_set_group(accsqp_group_for(int(n_max)));  // the engine's rule for its solver group (csrc/sqp_core.h)
         check_clean();
         // post_initialize, ModelInitializer.cpp:1081-1085
         for (auto& agent : model->economic_agents) agent->initialize();

@@ -51,6 +51,11 @@ def cases():
     synth.add_shock(a, 1, 7, 2, 0.1)
     synth.add_passage(a, 3, 8, 4, 1, 0.2)
     yield "baskets20", a, 20
+    # 200 regions x 1 sector: every purchasing manager has 199 connections, more than two per thread of the base solver
+    # group, so engine and oracle switch to the larger group (accsqp_group_for); per-connection arrays are left out
+    a = synth.make_network(regions=200, sectors=1, seed=13, max_delay=3)
+    synth.add_shock(a, 1, 4, 7, 0.4)
+    yield "wide8", a, 8
 
 
 def main():
@@ -64,7 +69,7 @@ def main():
         out["steps"] = [steps]
         for k, v in dump.items():
             base = k.split("/")[-1]
-            if base.startswith("edge_") and base not in KEEP_EDGE:
+            if base.startswith("edge_") and (base not in KEEP_EDGE or name == "wide8"):
                 continue
             out[k] = v
         path = os.path.join(ROOT, "tests", "golden", name + ".acc")
