@@ -272,21 +272,38 @@ struct StorageDelivery {  // thread per storage
                 const Flow front = front_[j];
                 const Flow ship = ship_[j];
                 Flow out;
-                if (ev.ovf_q == nullptr) {
-                    out = fcopy(front);  // overflow == 0, no passage forcing ever set
+                const int rt = ev.ovf_q == nullptr ? -1 : ev.route[e];
+                if (rt < 0) {
+                    out = fcopy(front);  // no passage forcing was ever set (overflow == 0), or no geo entity on the way
                 } else {
-                    const int ent = ev.entity[e];
-                    const double nu = ent >= 0 ? ev.nu[ent] : -1.0;
-                    const Flow total = fadd(mkflow(ev.ovf_q[e], ev.ovf_v[e]), front);
-                    if (nu < 0) {
-                        out = fcopy(total);
-                    } else {
-                        const Flow cap = flow_qp(qmul_l(nu, ev.Z_q[e]), flow_price(front));
-                        out = fcopy(cap.q < total.q ? cap : total);  // std::min by quantity
+                    // the chain of links, TransportChainLink.cpp:65-97: at this step hop h releases the shipment that
+                    // still has rem_h steps to go, i.e. the conveyor slot (step + rem_h) mod T; what it lets pass goes
+                    // back into that slot for the next hop (zero-delay hops follow at once), the last hop delivers
+                    int rem = tau_[j];
+                    const int h0 = ev.route_off[rt], h1 = ev.route_off[rt + 1];
+                    out = mkflow(0, 0.0);
+                    for (int h = h0; h < h1; ++h) {
+                        const int ent = ev.route_ent[h];
+                        rem -= ev.ent_delay[ent];
+                        const i64 slot = (i64)((step + rem) % T) * ev.n_edges + e;
+                        const i64 oslot = (i64)(h - h0) * ev.n_edges + e;
+                        const Flow fr = mkflow(ev.conv_q[slot], ev.conv_v[slot]);
+                        const double nu = ev.nu[ent];
+                        const Flow total = fadd(mkflow(ev.ovf_q[oslot], ev.ovf_v[oslot]), fr);
+                        Flow o;
+                        if (nu < 0) {
+                            o = fcopy(total);
+                        } else {
+                            const Flow cap = flow_qp(qmul_l(nu, ev.Z_q[e]), flow_price(fr));
+                            o = fcopy(cap.q < total.q ? cap : total);  // std::min by quantity
+                        }
+                        const Flow ovf = fcopy(fsub(total, o));
+                        ev.ovf_q[oslot] = ovf.q; ev.ovf_v[oslot] = ovf.v;
+                        if (h + 1 < h1) { ev.conv_q[slot] = o.q; ev.conv_v[slot] = o.v; }
+                        else out = o;
                     }
-                    const Flow ovf = fcopy(fsub(total, out));
-                    ev.ovf_q[e] = ovf.q; ev.ovf_v[e] = ovf.v;
                 }
+                if (ev.ship_q != nullptr) ev.ship_q[e] = ship.q;
                 in = fadd(in, out);
                 if (!dom_[j]) imp = fadd(imp, out);
                 tq += ship.q - out.q;
@@ -329,10 +346,15 @@ struct Purchase {  // one CTA of ACCSQP_GROUP threads per purchasing manager
         const i64 deficit = st.defc[s] - st.dlv_q[s] - st.T_q[s];
         const PMResult r = purchase_one(
             cx, nin, [&](int i) { return ie[i]; }, [&](int i) { return is[i]; },
-            [&](int e) { return E.conv_q[(i64)((stp + E.tau[e]) % E.T) * E.n_edges + e]; },
-            [&](int e) {  // BusinessConnection::get_minimum_passage, BusinessConnection.cpp:69-83 (single hop)
+            [&](int e) { return E.ship_q != nullptr ? E.ship_q[e] : E.conv_q[(i64)((stp + E.tau[e]) % E.T) * E.n_edges + e]; },
+            [&](int e) {  // BusinessConnection::get_minimum_passage, BusinessConnection.cpp:69-83
                 double m = 1.0;
-                if (E.nu != nullptr && E.entity[e] >= 0) { const double nu = E.nu[E.entity[e]]; if (nu >= 0.0 && nu < m) m = nu; }
+                if (E.nu != nullptr && E.route[e] >= 0) {
+                    for (int h = E.route_off[E.route[e]]; h < E.route_off[E.route[e] + 1]; ++h) {
+                        const double nu = E.nu[E.route_ent[h]];
+                        if (nu >= 0.0 && nu < m) m = nu;
+                    }
+                }
                 return m;
             },
             [&](int e, i64 q, i64 p) { E.D_q[e] = q; E.D_p[e] = p; }, pub, E.Z_q, E.D_q, k, mp, sectors[st.sector[s]], st.Istar_q[s], st.Sstar_q[s],
@@ -454,7 +476,11 @@ struct acc_engine {
     DBuf<int> s_agent, s_sector, s_iters, s_evals;
     int reg = 0;  // which of I0/I1 is the "other" register (arrived during the previous step)
     // connections
-    DBuf<int> e_seller_off, e_entity;
+    DBuf<int> e_seller_off, e_route, route_off, route_ent;
+    DBuf<unsigned char> ent_delay;
+    DBuf<i64> e_ship_q;
+    int nEnt = 0, h_max = 1;
+    bool hops_rewrite_shipment = false;  // some route starts with a zero-delay entity
     DBuf<i64> e_D_q, e_D_p, e_Z_q, conv_q, e_ovf_q;
     DBuf<double> conv_v, e_ovf_v, nu;
     DBuf<unsigned char> e_tau, e_dom;
@@ -517,9 +543,10 @@ struct acc_engine {
     }
     EdgeView edge_view() {
         EdgeView v;
-        v.seller_off = e_seller_off.p; v.D_q = e_D_q.p; v.D_p = e_D_p.p; v.Z_q = e_Z_q.p; v.tau = e_tau.p; v.domestic = e_dom.p; v.entity = e_entity.p;
+        v.seller_off = e_seller_off.p; v.D_q = e_D_q.p; v.D_p = e_D_p.p; v.Z_q = e_Z_q.p; v.tau = e_tau.p; v.domestic = e_dom.p; v.route = e_route.p; v.route_off = route_off.p; v.route_ent = route_ent.p; v.ent_delay = ent_delay.p;
         v.conv_q = conv_q.p; v.conv_v = conv_v.p; v.n_edges = nE; v.T = T;
         v.ovf_q = forcing_used ? e_ovf_q.p : nullptr; v.ovf_v = forcing_used ? e_ovf_v.p : nullptr; v.nu = forcing_used ? nu.p : nullptr;
+        v.ship_q = e_ship_q.n ? e_ship_q.p : nullptr;
         return v;
     }
     ConsumerView consumer_view() {
@@ -792,22 +819,60 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
     }
 
     // ---- per-connection constants, transport (BusinessConnection.cpp:38-65, ModelInitializer.cpp:689-700) ----
+    // Routes: the geo entities between two regions per kind of transport (k = 0 aviation, 1 road/sea), at index
+    // (k R + from) R + to.  A snapshot without routes has one connection entity per unordered region pair
+    // (create_simple_transport_connection, ModelInitializer.cpp:689-700), numbered i (i - 1) / 2 + j for j < i.
+    std::vector<unsigned char> ent_delay;
+    std::vector<int> route_off((size_t)2 * nR * nR + 1, 0), route_ent;
+    if (net.n_entities > 0) {
+        if (net.entity_delay == nullptr || net.route_off == nullptr || net.route_entity == nullptr) fail("routes: null table");
+        ent_delay.resize(net.n_entities);
+        for (i64 k = 0; k < net.n_entities; ++k) {
+            if (net.entity_delay[k] < 0 || net.entity_delay[k] > 254) fail("geo entity delay out of range (0..254 steps)");
+            ent_delay[k] = (unsigned char)net.entity_delay[k];
+        }
+        const i64 n_routes = 2 * nR * nR;
+        route_ent.assign(net.route_entity, net.route_entity + net.route_off[n_routes]);
+        for (i64 r = 0; r <= n_routes; ++r) route_off[r] = (int)net.route_off[r];
+        for (int x : route_ent) if (x < 0 || x >= net.n_entities) fail("route names an unknown geo entity");
+    } else {
+        ent_delay.resize((size_t)nR * (nR - 1) / 2 + 1, 0);
+        for (i64 k = 0; k < 2; ++k)
+            for (i64 i = 0; i < nR; ++i)
+                for (i64 j = 0; j < nR; ++j) {
+                    if (i != j) {
+                        const i64 hi = i > j ? i : j, lo = i > j ? j : i;
+                        const i64 d = net.delay[hi * nR + lo];
+                        if (d < 0 || d > 254) fail("transport delay out of range (0..254 steps)");
+                        ent_delay[hi * (hi - 1) / 2 + lo] = (unsigned char)d;
+                        route_ent.push_back((int)(hi * (hi - 1) / 2 + lo));
+                    }
+                    route_off[(k * nR + i) * nR + j + 1] = (int)route_ent.size();
+                }
+    }
+    E.nEnt = net.n_entities > 0 ? (int)net.n_entities : (int)(nR * (nR - 1) / 2);
     std::vector<unsigned char> tau(nE), dom(nE);
-    std::vector<int> entity(nE);
+    std::vector<int> route(nE);
     std::vector<i64> Zq(net.edge_zq, net.edge_zq + nE);
     int Tmax = 0;
+    E.h_max = 1;
     for (i64 e = 0; e < nE; ++e) {
         const int f = (int)net.edge_from[e], t = (int)net.edge_to[e];
         const int rf = a_region[f], rt = a_region[t];
         dom[e] = rf == rt;
-        if (E.h_sectors[a_sector[f]].transport_type == 1 || rf == rt) {
-            tau[e] = 0; entity[e] = -1;
+        const int kind = E.h_sectors[a_sector[f]].transport_type;
+        if (kind == 1 || rf == rt) {  // immediate transport or domestic: one link without geo entity, BusinessConnection.cpp:49-50
+            tau[e] = 0; route[e] = -1;
         } else {
-            const int hi = rf > rt ? rf : rt, lo = rf > rt ? rt : rf;
-            const i64 d = net.delay[(i64)hi * nR + lo];
-            if (d < 0 || d > 254) fail("transport delay out of range (0..254 steps)");
-            tau[e] = (unsigned char)d;
-            entity[e] = hi * (hi - 1) / 2 + lo;
+            const i64 r = ((i64)(kind == 0 ? 0 : 1) * nR + rf) * nR + rt;
+            const int h0 = route_off[r], h1 = route_off[r + 1];
+            if (h1 <= h0) fail("no route between two regions that trade");
+            int d = 0;
+            for (int h = h0; h < h1; ++h) d += ent_delay[route_ent[h]];
+            if (d > 254) fail("transport delay out of range (0..254 steps)");
+            tau[e] = (unsigned char)d; route[e] = (int)r;
+            if (h1 - h0 > E.h_max) E.h_max = h1 - h0;
+            if (ent_delay[route_ent[h0]] == 0 && d > 0) E.hops_rewrite_shipment = true;
         }
         if (tau[e] > Tmax) Tmax = tau[e];
     }
@@ -933,7 +998,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
     h2d(E.s_dem_v.p, Istar_v.data(), nSt * sizeof(double), s);
     h2d(E.s_exp_costs.p, Istar_v.data(), nSt * sizeof(double), s);
 
-    E.e_seller_off.upload(seller_off, s); E.e_entity.upload(entity, s); E.e_tau.upload(tau, s); E.e_dom.upload(dom, s); E.e_Z_q.upload(Zq, s);
+    E.e_seller_off.upload(seller_off, s); E.e_route.upload(route, s); E.route_off.upload(route_off, s); E.route_ent.upload(route_ent, s); E.ent_delay.upload(ent_delay, s); E.e_tau.upload(tau, s); E.e_dom.upload(dom, s); E.e_Z_q.upload(Zq, s);
     {   // last_demand_request_D = Z* at price 1 (BusinessConnection.cpp:42)
         std::vector<i64> p1(nE, mkp(1.0));
         E.e_D_q.upload(Zq, s); E.e_D_p.upload(p1, s);
@@ -1032,7 +1097,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
     E.in_off.upload(in_off, s); E.in_edge.upload(in_edge, s); E.in_seller.upload(in_seller, s);
     E.ell_off.upload(ell_off, s); E.ell_width.upload(ell_width, s); E.ell_edge.upload(ell_edge, s);
     E.ev_buf.alloc(E.ev_cap); E.ev_count.alloc(1); E.ev_count.zero(s);
-    E.nu.alloc((size_t)nR * (nR - 1) / 2 + 1);
+    E.nu.alloc((size_t)E.nEnt + 1);
     dev_sync(s);
 
     E.h_agent_type = a_type; E.h_agent_sector = a_sector; E.h_agent_region = a_region; E.h_st_agent = st_agent; E.h_st_sector = st_sector;
@@ -1086,6 +1151,8 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
             for (i64 e = 0; e < E.nE; ++e) { if (q) out.i[e] = z[e]; else out.f[e] = flow_qp(z[e], mkp(1.0)).v; }
             return true;
         }
+        if (q && E.e_ship_q.n) { out.i = E.e_ship_q.download(s); return true; }  // kept apart: hops may rewrite the conveyor slot
+        if (!q && E.e_ship_q.n) return false;  // the value of a rewritten shipment is not kept
         std::vector<i64> hq = q ? E.conv_q.download(s) : std::vector<i64>();
         std::vector<double> hv = q ? std::vector<double>() : E.conv_v.download(s);
         for (i64 e = 0; e < E.nE; ++e) {
@@ -1265,9 +1332,10 @@ void acc_destroy(acc_engine* e) {
                             &e->e_ovf_v, &e->nu})
         b->free();
     for (DBuf<int>* b : {&e->a_type, &e->a_sector, &e->a_region, &e->a_st_off, &e->a_st_list, &e->firm_ids, &e->s_agent, &e->s_sector, &e->s_iters,
-                         &e->s_evals, &e->e_seller_off, &e->e_entity, &e->ell_width, &e->ell_edge, &e->in_edge, &e->in_seller, &e->ev_count})
+                         &e->s_evals, &e->e_seller_off, &e->e_route, &e->route_off, &e->route_ent, &e->ell_width, &e->ell_edge, &e->in_edge, &e->in_seller, &e->ev_count})
         b->free();
     e->e_tau.free(); e->e_dom.free(); e->sectors.free(); e->pub.free(); e->ev_buf.free();
+    e->ent_delay.free(); e->e_ship_q.free();
     e->owned.free(); e->pm_ids.free(); e->halo_send.free(); e->halo_recv.free();
     for (DBuf<int>* b : {&e->cons_ids, &e->c_order_cnt, &e->c_order, &e->c_order_basket, &e->fatal}) b->free();
     for (DBuf<double>* b : {&e->c_share, &e->c_eshare, &e->c_prev_v, &e->c_budget, &e->c_bshare, &e->c_ebshare, &e->c_utility, &e->c_intra_exp}) b->free();
@@ -1287,13 +1355,14 @@ int acc_set_agent_forcing(acc_engine* e, const double* lambda, size_t n) {
 int acc_set_entity_passage(acc_engine* e, const double* nu, size_t n) {
     ACC_API_BEGIN
     if (e == nullptr || nu == nullptr) fail("acc_set_entity_passage: null argument");
-    if (n != (size_t)e->nR * (e->nR - 1) / 2) fail("acc_set_entity_passage: expected one entry per region pair");
+    if (n != (size_t)e->nEnt) fail("acc_set_entity_passage: expected one entry per geo entity (per region pair for a snapshot without routes)");
     if (!e->forcing_used) {
         bool any = false;
         for (size_t k = 0; k < n; ++k) any = any || nu[k] >= 0.0;
         if (!any) return 0;  // nothing forced yet: overflow stays identically zero
-        e->e_ovf_q.alloc((size_t)e->nE); e->e_ovf_v.alloc((size_t)e->nE);
+        e->e_ovf_q.alloc((size_t)e->nE * e->h_max); e->e_ovf_v.alloc((size_t)e->nE * e->h_max);
         e->e_ovf_q.zero(e->stream); e->e_ovf_v.zero(e->stream);
+        if (e->hops_rewrite_shipment) { e->e_ship_q.alloc((size_t)e->nE); e->e_ship_q.zero(e->stream); }
         e->forcing_used = true;
     }
     h2d(e->nu.p, nu, n * sizeof(double), e->stream);

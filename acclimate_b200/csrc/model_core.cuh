@@ -310,13 +310,16 @@ struct EdgeView {
     const int* seller_off;          // [n_agents + 1]
     i64* D_q; i64* D_p;             // last_demand_request_D (quantity, price)
     const i64* Z_q;                 // initial_flow_Z_star
-    const unsigned char* tau;       // transport delay of the (single) hop
+    const unsigned char* tau;       // transport delay: sum over the hops of the connection's route
     const unsigned char* domestic;  // buyer in the seller's region
-    const int* entity;              // geo entity of the hop (-1: none)
+    const int* route;               // route of the connection (-1: immediate / domestic, no geo entity)
+    const int* route_off; const int* route_ent;  // route -> its geo entities in travel order (TransportChainLink chain)
+    const unsigned char* ent_delay; // delay of each geo entity
     i64* conv_q; double* conv_v;    // conveyor planes [T][n_edges]: plane (t + tau) mod T receives the shipment of step t
     i64 n_edges; int T;
-    i64* ovf_q; double* ovf_v;      // per-connection overflow (null until passage forcing is used)
+    i64* ovf_q; double* ovf_v;      // overflow per (hop, connection): [hop][n_edges] (null until passage forcing is used)
     const double* nu;               // passage per geo entity (null until used; < 0: none)
+    i64* ship_q;                    // last shipment (only kept apart when hops may rewrite its conveyor slot, else null)
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -429,6 +432,7 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
         cx.foreach(n, [&](int i) {
             const int pl = (plane_now + tau[i]) % T;
             ev.conv_q[(i64)pl * ev.n_edges + e0 + i] = 0;
+            if (ev.ship_q != nullptr) ev.ship_q[e0 + i] = 0;
             ev.conv_v[(i64)pl * ev.n_edges + e0 + i] = 0.0;
         });
     } else {
@@ -476,6 +480,7 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
             }
             const int pl = (plane_now + tau[i]) % T;
             ev.conv_q[(i64)pl * ev.n_edges + e0 + i] = z.q;           // BusinessConnection::push_flow_Z -> first transport link
+            if (ev.ship_q != nullptr) ev.ship_q[e0 + i] = z.q;        // last_shipment_Z, kept apart when hops rewrite the slot
             ev.conv_v[(i64)pl * ev.n_edges + e0 + i] = z.v;
             if (!dom[i]) { r.eq = z.q; r.ev = z.v; }                  // Region::add_export_Z, BusinessConnection.cpp:91-93
             return r;

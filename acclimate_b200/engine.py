@@ -36,6 +36,7 @@ class _Network(C.Structure):
         ("edge_from", C.c_void_p), ("edge_to", C.c_void_p), ("edge_zq", C.c_void_p), ("delay", C.c_void_p),
         ("sector_params", C.c_void_p), ("consumer_elasticity", C.c_void_p),
         ("n_baskets", C.c_int64), ("basket_of_sector", C.c_void_p), ("basket_substitution", C.c_void_p), ("inter_basket_substitution", C.c_double),
+        ("n_entities", C.c_int64), ("entity_delay", C.c_void_p), ("route_off", C.c_void_p), ("route_entity", C.c_void_p),
     ]
 
 
@@ -109,8 +110,15 @@ def network_struct(arrays):
     ]
     bos, bco, inter = consumer_baskets(a)
     keep += [bos, bco]
+    routes = [0, None, None, None]
+    if "entity_delay" in a:
+        rt = [a[k].astype(np.int64) for k in ("entity_delay", "route_off", "route_entity")]
+        if rt[1].size != 2 * int(meta[1]) ** 2 + 1:
+            raise EngineError("route_off needs 2 * n_regions^2 + 1 entries")
+        keep += rt
+        routes = [int(rt[0].size)] + [x.ctypes.data for x in rt]
     net = _Network(int(meta[0]), int(meta[1]), int(meta[2]), int(meta[3]), *[x.ctypes.data for x in keep[:10]], int(bco.size), bos.ctypes.data,
-                   bco.ctypes.data, inter)
+                   bco.ctypes.data, inter, *routes)
     par = _Params()
     mp = a["model_f64"].astype(np.float64)
     if mp.size != MP_COUNT:
@@ -223,7 +231,7 @@ class Scenario:
     def __init__(self, arrays):
         self.n_agents = int(arrays["meta"][2])
         R = int(arrays["meta"][1])
-        self.n_conn = R * (R - 1) // 2
+        self.n_conn = int(np.asarray(arrays["entity_delay"]).size) if "entity_delay" in arrays else R * (R - 1) // 2
         self.forcing = np.asarray(arrays.get("forcing", np.zeros(0)), dtype=np.float64).reshape(-1, 4)
         self.passage = np.asarray(arrays.get("passage", np.zeros(0)), dtype=np.float64).reshape(-1, 4)
         self.dt = float(np.rint(arrays["model_f64"][netfile.MODEL_PARAMS.index("delta_t")]))

@@ -195,6 +195,58 @@ def make_network(regions, sectors, seed, const_delay=None, world_output=None, be
     return arrays
 
 
+def add_routes(arrays, seed, hubs=3):
+    """Multi-hop transport routes (the reference's "network" transport, ModelInitializer.cpp:339-607): every region
+    reaches a sea hub over an access connection, hubs are zero-delay locations joined by sea lanes; road/sea sectors
+    ship region -> access -> hub [-> lane -> hub] -> access -> region, aviation sectors over one direct connection per
+    region pair.  Adds entity_delay / route_off / route_entity (see oracle/ref_harness and include/acclimate_b200.h);
+    passage forcing (add_entity_passage) then addresses these entities."""
+    rng = np.random.Generator(np.random.PCG64([seed, 77]))
+    R = int(arrays["meta"][1])
+    hubs = max(1, min(int(hubs), R))
+    hub_of = rng.integers(0, hubs, size=R)
+    delays = []
+    access = []
+    for r in range(R):
+        access.append(len(delays)); delays.append(int(rng.integers(0, 3)))
+    hub_loc = []
+    for h in range(hubs):
+        hub_loc.append(len(delays)); delays.append(0)
+    lane = {}
+    for a in range(hubs):
+        for b in range(a):
+            lane[(a, b)] = lane[(b, a)] = len(delays); delays.append(int(rng.integers(1, 4)))
+    direct = {}
+    for i in range(R):
+        for j in range(i):
+            direct[(i, j)] = direct[(j, i)] = len(delays); delays.append(1)
+    off, ent = [0], []
+    for k in range(2):
+        for i in range(R):
+            for j in range(R):
+                if i != j:
+                    if k == 0:
+                        ent += [direct[(i, j)]]
+                    else:
+                        hi, hj = int(hub_of[i]), int(hub_of[j])
+                        path = [access[i], hub_loc[hi]]
+                        if hi != hj:
+                            path += [lane[(hi, hj)], hub_loc[hj]]
+                        path += [access[j]]
+                        ent += path
+                off.append(len(ent))
+    arrays["entity_delay"] = np.array(delays, dtype=np.int64)
+    arrays["route_off"] = np.array(off, dtype=np.int64)
+    arrays["route_entity"] = np.array(ent, dtype=np.int64)
+    return dict(access=access, hub_loc=hub_loc, lane=lane, direct=direct, hub_of=hub_of)
+
+
+def add_entity_passage(arrays, t_from, t_to, entity, nu):
+    """Passage forcing of one geo entity of a routed network (index into entity_delay)."""
+    rec = np.array([t_from, t_to, int(entity), nu], dtype=np.float64)
+    arrays["passage"] = np.concatenate([np.asarray(arrays.get("passage", np.zeros(0)), dtype=np.float64).reshape(-1), rec])
+
+
 def add_shock(arrays, t_from, t_to, region, remaining_capacity):
     """Production-loss shock on every firm of `region` (reference Scenario.cpp:45-56: forcing = capacity / beta)."""
     at, ar, ab = arrays["agent_type"], arrays["agent_region"], arrays["agent_beta"]

@@ -82,6 +82,14 @@ typedef struct {
                                           basket are taken in ascending order */
     const double* basket_substitution; /* [n_baskets] intra-basket substitution coefficient */
     double inter_basket_substitution;  /* inter_basket_substitution_coefficient */
+    /* multi-hop transport routes (the "network" transport, src/input/ModelInitializer.cpp:339-607): the geo entities
+     * (connections, ports, sea areas) a shipment passes between two regions, each a TransportChainLink with its own
+     * delay and passage forcing (src/model/TransportChainLink.cpp:40-97).  n_entities == 0: one connection per region
+     * pair with the delays of `delay` above */
+    int64_t n_entities;
+    const int64_t* entity_delay;       /* [n_entities] steps */
+    const int64_t* route_off;          /* [2 * n_regions * n_regions + 1]: route (k * n_regions + from) * n_regions + to, k = 0 aviation, 1 road/sea */
+    const int64_t* route_entity;       /* entities of each route in travel order */
 } acc_network;
 
 typedef struct {
@@ -143,8 +151,8 @@ int acc_set_solver_group(acc_engine* e, int group);
 /* replaces EconomicAgent::set_forcing for all agents at once (src/model/EconomicAgent.cpp:43-47);
  * lambda has n_agents entries */
 int acc_set_agent_forcing(acc_engine* e, const double* lambda, size_t n);
-/* replaces GeoEntity::set_forcing_nu (src/model/GeoEntity.cpp:30-34); nu has one entry per
- * region pair (i, j < i) at index i*(i-1)/2 + j; nu < 0 means "no forcing" */
+/* replaces GeoEntity::set_forcing_nu (src/model/GeoEntity.cpp:30-34); nu has one entry per geo entity -- for a
+ * snapshot without routes one per region pair (i, j < i) at index i*(i-1)/2 + j; nu < 0 means "no forcing" */
 int acc_set_entity_passage(acc_engine* e, const double* nu, size_t n);
 
 /* one timestep = Model::switch_registers + iterate_consumption_and_production + iterate_expectation

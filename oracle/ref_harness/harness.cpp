@@ -248,6 +248,30 @@ class ModelInitializer {
         }
         // transport: one simple connection per unordered region pair (create_simple_transport_connection,
         // ModelInitializer.cpp:689-700; loop order of build_transport_network "const", :985-992)
+        if (cfg.net.count("entity_delay") != 0) {
+            // multi-hop routes ("network" transport, ModelInitializer.cpp:575-607): snapshot keys entity_delay[n_entities],
+            // route_off[2 R R + 1] / route_entity[]: the geo entities a shipment passes between two regions, for
+            // aviation (k = 0) and road/sea (k = 1) sectors, at index (k R + from) R + to.  Every entity is created as a
+            // GeoConnection: a transport chain link only reads its delay and forcing (TransportChainLink.cpp:40-63).
+            const auto& ed = cfg.I("entity_delay");
+            const auto& ro = cfg.I("route_off");
+            const auto& re = cfg.I("route_entity");
+            for (std::size_t k = 0; k < ed.size(); ++k) {
+                connections.push_back(std::make_shared<GeoConnection>(model, TransportDelay(ed[k]), GeoConnection::type_t::UNSPECIFIED, model->regions[0],
+                                                                      model->regions[n_regions > 1 ? 1 : 0]));
+            }
+            const Sector::transport_type_t kinds[2] = {Sector::transport_type_t::AVIATION, Sector::transport_type_t::ROADSEA};
+            for (std::size_t k = 0; k < 2; ++k)
+                for (std::size_t i = 0; i < n_regions; ++i)
+                    for (std::size_t j = 0; j < n_regions; ++j) {
+                        if (i == j) continue;
+                        const std::size_t r = (k * n_regions + i) * n_regions + j;
+                        GeoRoute route;
+                        for (std::int64_t q = ro.at(r); q < ro.at(r + 1); ++q) route.path.add(connections.at(std::size_t(re.at(std::size_t(q)))).get());
+                        if (route.path.size() == 0) throw std::runtime_error("empty route in the snapshot");
+                        model->regions[i]->routes.emplace(std::make_pair(IndexType(model->regions[j]->id.index()), kinds[k]), route);
+                    }
+        } else {
         const auto& delay = cfg.I("delay");
         for (std::size_t i = 0; i < n_regions; ++i) {
             for (std::size_t j = 0; j < i; ++j) {
@@ -266,6 +290,7 @@ class ModelInitializer {
                 conn_a.push_back(i);
                 conn_b.push_back(j);
             }
+        }
         }
         // connections: initialize_connection, ModelInitializer.cpp:187-213
         const auto& ef = cfg.I("edge_from");

@@ -51,6 +51,15 @@ def cases():
     synth.add_shock(a, 1, 7, 2, 0.1)
     synth.add_passage(a, 3, 8, 4, 1, 0.2)
     yield "baskets20", a, 20
+    # multi-hop routes ("network" transport): access connections, zero-delay hub locations, sea lanes; passage forcing
+    # on a zero-delay hub, a blocked lane and a throttled access connection
+    a = synth.make_network(regions=7, sectors=4, seed=21, max_delay=3)
+    info = synth.add_routes(a, seed=21, hubs=3)
+    synth.add_shock(a, 2, 8, 3, 0.3)
+    synth.add_entity_passage(a, 3, 9, info["hub_loc"][0], 0.4)
+    synth.add_entity_passage(a, 5, 7, list(info["lane"].values())[0], 0.0)
+    synth.add_entity_passage(a, 4, 10, info["access"][2], 0.6)
+    yield "routes25", a, 25
     # 200 regions x 1 sector: every purchasing manager has 199 connections, more than two per thread of the base solver
     # group, so engine and oracle switch to the larger group (accsqp_group_for); per-connection arrays are left out
     a = synth.make_network(regions=200, sectors=1, seed=13, max_delay=3)

@@ -48,7 +48,7 @@ def _run(world, case, lib, owner=None):
     return sorted(results)
 
 
-@pytest.mark.parametrize("case,world", [("severe_shock30", 2), ("passage25", 2), ("flags20", 3), ("baskets20", 2)])
+@pytest.mark.parametrize("case,world", [("severe_shock30", 2), ("passage25", 2), ("flags20", 3), ("baskets20", 2), ("routes25", 2)])
 def test_parts_equal_reference(case, world, emu_lib):
     results = _run(world, case, emu_lib)
     problems = [m for _, p, _ in results for m in p]
