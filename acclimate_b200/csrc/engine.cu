@@ -198,6 +198,7 @@ struct SellerExpectation {  // warp per firm
     ACC_HD void operator()(Ctx& cx, int k, unsigned char*) const { seller_phase2(cx, firm_ids[k], fv, ev, st, mp, sectors, events); }
 };
 
+template <bool FORCED>  // FORCED: passage forcing has been used, the chain of hops with its overflows is walked
 struct StorageDelivery {  // thread per storage
     StorageView st; FirmView fv; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
     const i64* ell_off; const int* ell_width; const int* ell_edge; const unsigned char* owned;  // owned == nullptr: every agent
@@ -272,7 +273,7 @@ struct StorageDelivery {  // thread per storage
                 const Flow front = front_[j];
                 const Flow ship = ship_[j];
                 Flow out;
-                const int rt = ev.ovf_q == nullptr ? -1 : ev.route[e];
+                const int rt = FORCED ? ev.route[e] : -1;
                 if (rt < 0) {
                     out = fcopy(front);  // no passage forcing was ever set (overflow == 0), or no geo entity on the way
                 } else {
@@ -303,7 +304,7 @@ struct StorageDelivery {  // thread per storage
                         else out = o;
                     }
                 }
-                if (ev.ship_q != nullptr) ev.ship_q[e] = ship.q;
+                if (FORCED && ev.ship_q != nullptr) ev.ship_q[e] = ship.q;
                 in = fadd(in, out);
                 if (!dom_[j]) imp = fadd(imp, out);
                 tq += ship.q - out.q;
@@ -611,6 +612,15 @@ struct acc_engine {
 
     // The consumers' utility optimisation reads storages and writes their desired use only, so it runs on a side
     // stream next to the sellers' production / distribution pass; the storage pass waits for both.
+    void launch_delivery(const unsigned char* own) {
+        if (forcing_used) {
+            StorageDelivery<true> k{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p, own};
+            timed("storage_delivery", [&] { launch_thread(stream, nSt, k); });
+        } else {
+            StorageDelivery<false> k{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p, own};
+            timed("storage_delivery", [&] { launch_thread(stream, nSt, k); });
+        }
+    }
     void consumer_fork() {
         if (!mp.utilitarian || nC == 0) return;
         ConsumerUtility k{consumer_view(), storage_view(), mp, sink(), c_n_max, fatal.p};
@@ -650,9 +660,7 @@ struct acc_engine {
         }
         consumer_join();
         {
-            StorageDelivery k{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p,
-                              partitioned ? owned.p : nullptr};
-            timed("storage_delivery", [&] { launch_thread(stream, nSt, k); });
+            launch_delivery(partitioned ? owned.p : nullptr);
         }
         {
             SellerExpectation k{firm_view(), edge_view(), storage_view(), mp, sectors.p, sink(), firm_ids.p};
@@ -699,8 +707,7 @@ struct acc_engine {
         SellerProduction k2{firm_view(), edge_view(), mp, sectors.p, sink(), step, firm_ids.p};
         timed("seller_production", [&] { launch_block(stream, nF, k2); });
         consumer_join();
-        StorageDelivery k3{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p, nullptr};
-        timed("storage_delivery", [&] { launch_thread(stream, nSt, k3); });
+        launch_delivery(nullptr);
     }
     void phase_exp() {
         require_single("acc_phase");
@@ -747,6 +754,8 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
     mp.maxeval = (int)m[ACC_MP_OPTIMIZATION_MAXITER];
     mp.prec_adj = (int)m[ACC_MP_OPTIMIZATION_PRECISION_ADJUSTMENT];
     mp.utilitarian = m[ACC_MP_UTILITARIAN] != 0.0;
+    mp.naive_expectations = m[ACC_MP_NAIVE_EXPECTATIONS] != 0.0;
+    mp.always_extend = m[ACC_MP_ALWAYS_EXTEND_EXPECTED_DEMAND_CURVE] != 0.0;
     const bool no_self_supply = m[ACC_MP_NO_SELF_SUPPLY] != 0.0;
 
     E.h_sectors.resize(nS);

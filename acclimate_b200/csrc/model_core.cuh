@@ -41,6 +41,7 @@ struct ModelP {  // reference include/parameters.h:33-84 (the keys this path rea
     int maxeval;             // optimization_maxiter
     int prec_adj;            // optimization_precision_adjustment (int, parameters.h:61)
     int utilitarian;         // consumers.<..>.bool_utilitarian (ModelInitializer.cpp:136)
+    int naive_expectations, always_extend;  // naive_expectations, always_extend_expected_demand_curve (ModelInitializer.cpp:1024-1025)
 };
 
 struct SectorP {  // reference Sector.h + Parameters::SectorParameters
@@ -536,6 +537,42 @@ ACC_HD void seller_phase2(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
     } else {
         const ScanResult sc = seller_scan(cx, n, ev.D_q + e0, ev.D_p + e0, tot, est.q, lamX, sp.dn, n_c);
         X = fcopy(sc.cum);                                            // :498
+        if (sc.all_served && !mp.naive_expectations && (mp.always_extend || X.q < lamX)) {
+            // Expectations: extend the demand curve beyond the sum of the demand requests with the sector's supply
+            // elasticity and produce up to where marginal costs meet marginal revenue (:505-545, :704-779)
+            const i64 nmin = sc.p_prev;                               // price of the cheapest served connection
+            const i64 sumD = tot.sq;                                  // sum_demand_requests_D_
+            const double eps = sp.eps;
+            auto goal = [&](i64 xq) {                                 // goal_fkt_marginal_costs_minus_marginal_revenue, :737-744
+                return marginal_costs(xq, lamX, sp.dn, offer_min) - pmul(nmin, pow(ratio(sumD, xq), eps));
+            };
+            auto add_rev = [&](i64 xq) {                              // calc_additional_revenue_expectation, :704-716
+                const i64 t = qmul(xq, pow(ratio(sumD, xq), eps)) - sumD;
+                return (pf(nmin) * qf(t)) / (1.0 - eps);
+            };
+            if (goal(X.q) < 0) {
+                const i64 lam_beta_X = qmul(Xstar.q, fv.beta[f] * lambda);  // forced_maximal_production_quantity_lambda_beta_X_star
+                const i64 max_add = (est.q < lam_beta_X ? est.q : lam_beta_X) - X.q;
+                Flow add;
+                if (goal(X.q + max_add) < 0) {
+                    add = mkflow(max_add, add_rev(X.q + max_add));
+                } else {                                              // search_root_bisec_expectation, :754-779
+                    i64 left = 0, right = max_add;
+                    const i64 prec = 1;                               // Price(Price::precision): one quantum
+                    for (;;) {
+                        const i64 middle = qdiv(left + right, 2.0);
+                        auto mag = [&](i64 d) { const i64 g = goal(X.q + d); return g < 0 ? -g : g; };
+                        if (left + 1 >= right) { const i64 d = mag(left) < mag(right) ? left : right; add = mkflow(d, add_rev(X.q + d)); break; }
+                        if (mag(middle) < prec) { add = mkflow(middle, add_rev(X.q + middle)); break; }
+                        if (mag(left) < prec) { add = mkflow(left, add_rev(X.q + left)); break; }
+                        if (mag(right) < prec) { add = mkflow(right, add_rev(X.q + right)); break; }
+                        const bool sm = goal(X.q + middle) >= 0, sr = goal(X.q + right) >= 0;  // same_sgn: (t >= 0) == (t >= 0)
+                        if (sm != sr) left = middle; else right = middle;
+                    }
+                }
+                X = fcopy(fadd(X, fcopy(add)));
+            }
+        }
         if (!sc.all_served) {                                         // :554-599
             Flow extra = mkflow(0, 0.0);
             if (marginal_costs(X.q, lamX, sp.dn, n_c) - sc.p_stop < 0) {

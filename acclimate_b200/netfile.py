@@ -29,6 +29,8 @@ MODEL_PARAMS = [
     "no_self_supply",
     "utilitarian",
     "delta_t",
+    "naive_expectations",
+    "always_extend_expected_demand_curve",
 ]
 # order of each row of "sector_f64" (reference ModelInitializer.cpp:159-185)
 SECTOR_PARAMS = [

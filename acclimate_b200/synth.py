@@ -33,6 +33,8 @@ DEFAULT_MODEL = dict(
     no_self_supply=1,
     utilitarian=1,  # consumers.<..>.bool_utilitarian defaults to true (reference ModelInitializer.cpp:136)
     delta_t=1.0,
+    naive_expectations=1,
+    always_extend_expected_demand_curve=0,
 )
 DEFAULT_SECTOR = dict(
     upper_storage_limit=3.0,

@@ -39,6 +39,8 @@ enum {
     ACC_MP_NO_SELF_SUPPLY,
     ACC_MP_UTILITARIAN,
     ACC_MP_DELTA_T,
+    ACC_MP_NAIVE_EXPECTATIONS,
+    ACC_MP_ALWAYS_EXTEND_EXPECTED_DEMAND_CURVE,
     ACC_MP_COUNT
 };
 

@@ -62,6 +62,8 @@ enum ModelParamIdx {
     MP_NO_SELF_SUPPLY,
     MP_UTILITARIAN,
     MP_DELTA_T,
+    MP_NAIVE_EXPECTATIONS,
+    MP_ALWAYS_EXTEND_EXPECTED_DEMAND_CURVE,
     MP_COUNT
 };
 // per-sector parameters in "sector_f64" (row-major, SP_COUNT per sector)
@@ -149,8 +151,8 @@ class ModelInitializer {
         P.optimization_timeout = 3600;
         P.quadratic_transport_penalty = mp[MP_QUADRATIC_TRANSPORT_PENALTY] != 0.0;
         P.maximal_decrease_reservation_price_limited_by_markup = mp[MP_MAX_DECREASE_RESERVATION_PRICE_LIMITED_BY_MARKUP] != 0.0;
-        P.always_extend_expected_demand_curve = false;
-        P.naive_expectations = true;
+        P.always_extend_expected_demand_curve = mp.size() > MP_ALWAYS_EXTEND_EXPECTED_DEMAND_CURVE && mp[MP_ALWAYS_EXTEND_EXPECTED_DEMAND_CURVE] != 0.0;
+        P.naive_expectations = !(mp.size() > MP_NAIVE_EXPECTATIONS) || mp[MP_NAIVE_EXPECTATIONS] != 0.0;
         P.deviation_penalty = mp[MP_DEVIATION_PENALTY] != 0.0;
         P.min_storage = mp[MP_MIN_STORAGE];
         P.cheapest_price_range_preserve_seller_price = mp[MP_CHEAPEST_PRICE_RANGE_PRESERVE_SELLER_PRICE] != 0.0;

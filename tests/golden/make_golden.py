@@ -60,6 +60,15 @@ def cases():
     synth.add_entity_passage(a, 5, 7, list(info["lane"].values())[0], 0.0)
     synth.add_entity_passage(a, 4, 10, info["access"][2], 0.6)
     yield "routes25", a, 25
+    # naive_expectations = false: sellers extend their expected demand curve with the supply elasticity and look for
+    # the production where marginal costs meet marginal revenue (bisection); second half: always_extend as well
+    a = synth.make_network(regions=6, sectors=4, seed=14, max_delay=3, model=dict(naive_expectations=0),
+                           sector=dict(supply_elasticity=0.4))
+    synth.add_shock(a, 2, 10, 1, 0.2)
+    yield "expectations20", a, 20
+    a = synth.make_network(regions=5, sectors=3, seed=15, const_delay=2, model=dict(naive_expectations=0, always_extend_expected_demand_curve=1))
+    synth.add_shock(a, 3, 8, 0, 0.5)
+    yield "extend15", a, 15
     # 200 regions x 1 sector: every purchasing manager has 199 connections, more than two per thread of the base solver
     # group, so engine and oracle switch to the larger group (accsqp_group_for); per-connection arrays are left out
     a = synth.make_network(regions=200, sectors=1, seed=13, max_delay=3)

@@ -11,7 +11,7 @@ import numpy as np
 from acclimate_b200 import engine, netfile
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-CASES = ["small_shock12", "severe_shock30", "passage25", "outage25", "flags20", "utilitarian20", "baskets20", "wide8", "routes25"]
+CASES = ["small_shock12", "severe_shock30", "passage25", "outage25", "flags20", "utilitarian20", "baskets20", "wide8", "routes25", "expectations20", "extend15"]
 
 EXACT_OR_TIGHT = [
     "edge_D_q", "edge_D_p", "edge_ship_q", "sto_S_q", "sto_S_v", "sto_I_q", "sto_I_v", "sto_U_q", "sto_U_v", "sto_Ut_q", "sto_Ut_v",
