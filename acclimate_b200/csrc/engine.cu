@@ -66,6 +66,8 @@ static void launch_thread(stream_t, int n, K k) { for (int i = 0; i < n; ++i) k(
 template <class K>
 static void launch_block(stream_t, int n, K k) { for (int i = 0; i < n; ++i) { HostCtx cx(K::THREADS); k(cx, i); } }
 template <class K>
+static void launch_seller(stream_t, int n, int, K k) { for (int i = 0; i < n; ++i) { HostCtx cx(K::THREADS); k(cx, i, SellerBook{nullptr, nullptr, nullptr, nullptr}); } }
+template <class K>
 static void launch_warp(stream_t, int n, size_t smem, K k) {
     std::vector<unsigned char> sm(smem + 16);
     for (int i = 0; i < n; ++i) { HostCtx cx(32); k(cx, i, sm.data()); }
@@ -107,6 +109,20 @@ __global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) block_kernel(K k) {
     BlockCtx cx(scratch);
     k(cx, (int)blockIdx.x);
 }
+// One CTA per seller; `cap` > 0: the seller's demand book is staged in dynamic shared memory first (csrc/stage.cuh),
+// books larger than `cap` connections are read in place.
+template <class K>
+__global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) seller_kernel(K k, int cap) {
+    __shared__ __align__(16) unsigned char scratch[ACC_BLOCK_SCRATCH_BYTES];
+    __shared__ __align__(8) unsigned long long bar;
+    extern __shared__ __align__(16) unsigned char dyn_smem[];
+    BlockCtx cx(scratch);
+    SellerBook book{nullptr, nullptr, nullptr, nullptr};
+    int e0, n;
+    k.range((int)blockIdx.x, &e0, &n);
+    if (n > 0 && n <= cap) book = stage_seller_book(dyn_smem, cap, &bar, k.ev.D_q, k.ev.D_p, k.ev.tau, k.ev.domestic, e0, n);
+    k(cx, (int)blockIdx.x, book);
+}
 template <class K>
 __global__ void __maxnreg__(K::MAXREG) block_smem_kernel(K k) {
     __shared__ __align__(16) unsigned char scratch[ACC_BLOCK_SCRATCH_BYTES];
@@ -130,6 +146,18 @@ template <class K>
 static void launch_block(stream_t s, int n, K k) {
     if (n <= 0) return;
     block_kernel<K><<<n, K::THREADS, 0, s>>>(k);
+    ACC_CUDA(cudaGetLastError());
+}
+template <class K>
+static void launch_seller(stream_t s, int n, int cap, K k) {
+    if (n <= 0) return;
+    const size_t smem = cap > 0 ? seller_book_bytes(cap) : 0;
+    static size_t configured = 0;
+    if (smem > configured) {
+        ACC_CUDA(cudaFuncSetAttribute(seller_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    seller_kernel<K><<<n, K::THREADS, smem, s>>>(k, cap);
     ACC_CUDA(cudaGetLastError());
 }
 template <class K>
@@ -184,12 +212,20 @@ struct FirmPossibleProduction {  // thread per firm
 struct SellerProduction {  // CTA per firm
 #ifndef ACC_SELLER_THREADS
 #define ACC_SELLER_THREADS 256
-#define ACC_SELLER_MIN_BLOCKS 4
+#define ACC_SELLER_MIN_BLOCKS 2
+#endif
+#ifndef ACC_SELLER_BOOK_BUDGET
+#define ACC_SELLER_BOOK_BUDGET (108 * 1024)  // bytes of dynamic shared memory per CTA: two CTAs per SM
 #endif
     enum { THREADS = ACC_SELLER_THREADS, MIN_BLOCKS = ACC_SELLER_MIN_BLOCKS };
     FirmView fv; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step; const int* firm_ids;
+    ACC_HD void range(int k, int* e0, int* n) const {  // the seller's connections (none for a consumer)
+        const int f = firm_ids[k];
+        *e0 = ev.seller_off[f];
+        *n = fv.type[f] == 1 ? ev.seller_off[f + 1] - *e0 : 0;
+    }
     template <class Ctx>
-    ACC_HD void operator()(Ctx& cx, int k) const { seller_phase1(cx, firm_ids[k], fv, ev, mp, sectors, events, step); }
+    ACC_HD void operator()(Ctx& cx, int k, const SellerBook& book) const { seller_phase1(cx, firm_ids[k], fv, ev, mp, sectors, events, step, book); }
 };
 
 struct SellerExpectation {  // warp per firm
@@ -454,6 +490,7 @@ struct acc_engine {
     // sizes
     int nA = 0, nS = 0, nR = 0, nSt = 0, nF = 0, n_max = 0, T = 1;
     int pm_group = ACCSQP_GROUP;  // threads per purchasing manager
+    int book_cap = 0;             // largest seller's number of connections when its demand book fits the shared-memory budget, else 0
     i64 nE = 0;
     ModelP mp;
     std::vector<SectorP> h_sectors;
@@ -646,7 +683,7 @@ struct acc_engine {
         }
         {
             SellerProduction k{firm_view(), edge_view(), mp, sectors.p, sink(), step, firm_ids.p};
-            timed("seller_production", [&] { launch_block(stream, nF, k); });
+            timed("seller_production", [&] { launch_seller(stream, nF, book_cap, k); });
         }
         if (halo_send.n) {
             PackFlow k{edge_view(), step, halo_send.p, x_flow_send};
@@ -705,7 +742,7 @@ struct acc_engine {
         FirmPossibleProduction k1{firm_view(), storage_view(), mp, firm_ids.p};
         timed("firm_possible_production", [&] { launch_thread(stream, nF, k1); });
         SellerProduction k2{firm_view(), edge_view(), mp, sectors.p, sink(), step, firm_ids.p};
-        timed("seller_production", [&] { launch_block(stream, nF, k2); });
+        timed("seller_production", [&] { launch_seller(stream, nF, book_cap, k2); });
         consumer_join();
         launch_delivery(nullptr);
     }
@@ -805,6 +842,11 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
         e_cid[e] = it->second;
     }
     for (i64 a = 0; a < nA; ++a) seller_off[a + 1] += seller_off[a];
+    {   // the sellers' demand books are staged in shared memory when two CTAs with the largest book fit one SM
+        int out_max = 0;
+        for (i64 a = 0; a < nA; ++a) out_max = std::max(out_max, seller_off[a + 1] - seller_off[a]);
+        E.book_cap = seller_book_bytes(out_max) <= ACC_SELLER_BOOK_BUDGET ? out_max : 0;
+    }
     const int nSt = (int)c_agent.size();
     E.nSt = nSt;
     // internal order: sector-major, buyer-minor

@@ -9,6 +9,7 @@
 #pragma once
 
 #include "coop.cuh"
+#include "stage.cuh"
 
 namespace acc {
 
@@ -349,12 +350,14 @@ ACC_HD i64 half_width(const ModelP& mp, i64 dn, double beta) {
 }
 
 template <class Ctx>
-ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev, const ModelP& mp, const SectorP* sectors, const EventSink& events, i64 step) {
+ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev, const ModelP& mp, const SectorP* sectors, const EventSink& events, i64 step,
+                          const SellerBook& book) {
     const int e0 = fv.type[f] == 1 ? ev.seller_off[f] : 0;
     const int n = fv.type[f] == 1 ? ev.seller_off[f + 1] - e0 : 0;
     if (n == 0) return;
-    const i64* Dq = ev.D_q + e0;
-    const i64* Dp = ev.D_p + e0;
+    // the demand book: staged in shared memory by the caller (csrc/stage.cuh) or read in place
+    const i64* Dq = book.q != nullptr ? book.q : ev.D_q + e0;
+    const i64* Dp = book.q != nullptr ? book.p : ev.D_p + e0;
     const SectorP sp = sectors[fv.sector[f]];
     const double lambda = fv.lambda[f];
     const Flow Xstar = mkflow(fv.Xstar_q[f], fv.Xstar_v[f]);
@@ -425,8 +428,8 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
     // ---- distribute, :140-251 ----
     const int T = ev.T;
     const int plane_now = (int)(step % T);
-    const unsigned char* tau = ev.tau + e0;
-    const unsigned char* dom = ev.domestic + e0;
+    const unsigned char* tau = book.q != nullptr ? book.tau : ev.tau + e0;
+    const unsigned char* dom = book.q != nullptr ? book.dom : ev.domestic + e0;
     double R = 0.0;
     i64 exq = 0; double exv = 0.0;
     if (X.q <= 0) {
