@@ -99,17 +99,21 @@ struct HostCtx : CtxOps<HostCtx> {
         return total;
     }
     // K strictly sequential left-to-right folds (the reference's own loop order)
-    template <int K>
-    inline void seqsum(int n, const double* const (&v)[K], double (&out)[K]) const {
+    // elem(i, t) fills the K summands of element i
+    template <int K, class Elem>
+    inline void seqsum(int n, Elem elem, double (&out)[K]) const {
         for (int k = 0; k < K; ++k) out[k] = 0.0;
-        for (int i = 0; i < n; ++i)
-            for (int k = 0; k < K; ++k) out[k] += v[k][i];
+        for (int i = 0; i < n; ++i) {
+            double t[K];
+            elem(i, t);
+            for (int k = 0; k < K; ++k) out[k] += t[k];
+        }
     }
-    // order-preserving compaction: out[0..m) = ascending i with pred(i); returns m
-    template <class Pred>
-    inline int compact(int n, Pred pred, int* out) const {
+    // order-preserving compaction: put(m, i) for ascending i with pred(i), m = 0, 1, ...; returns the count
+    template <class Pred, class Put>
+    inline int compact(int n, Pred pred, Put put) const {
         int m = 0;
-        for (int i = 0; i < n; ++i) if (pred(i)) out[m++] = i;
+        for (int i = 0; i < n; ++i) if (pred(i)) put(m++, i);
         return m;
     }
 };
@@ -138,25 +142,26 @@ __device__ __forceinline__ T shfl_any(const T& v, int src_lane) {
     return r;
 }
 
-// K strictly sequential left-to-right sums over shared-memory vectors, executed by ONE thread: operands of eight
-// elements are loaded first (independent loads), then folded in element order.
-template <int K>
-__device__ __forceinline__ void seqsum_serial(int n, const double* const (&v)[K], double (&a)[K]) {
+// K strictly sequential left-to-right sums, executed by ONE thread: the summands of eight elements are fetched
+// first (independent loads; elem(i, t) fills the K summands of element i), then folded in element order.
+template <int K, class Elem>
+__device__ __forceinline__ void seqsum_serial(int n, Elem elem, double (&a)[K]) {
     int i = 0;
     for (; i + 8 <= n; i += 8) {
-        double t[K][8];
+        double t[8][K];
 #pragma unroll
-        for (int k = 0; k < K; ++k)
-#pragma unroll
-            for (int j = 0; j < 8; ++j) t[k][j] = v[k][i + j];
+        for (int j = 0; j < 8; ++j) elem(i + j, t[j]);
 #pragma unroll
         for (int j = 0; j < 8; ++j)
 #pragma unroll
-            for (int k = 0; k < K; ++k) a[k] += t[k][j];
+            for (int k = 0; k < K; ++k) a[k] += t[j][k];
     }
-    for (; i < n; ++i)
+    for (; i < n; ++i) {
+        double t[K];
+        elem(i, t);
 #pragma unroll
-        for (int k = 0; k < K; ++k) a[k] += v[k][i];
+        for (int k = 0; k < K; ++k) a[k] += t[k];
+    }
 }
 
 // One warp per item.
@@ -185,24 +190,24 @@ struct WarpCtx : CtxOps<WarpCtx> {
         for (int off = 16; off >= 1; off >>= 1) acc_ = T::combine(acc_, shfl_xor_any(acc_, off));
         return acc_;
     }
-    template <int K>
-    __device__ __forceinline__ void seqsum(int n, const double* const (&v)[K], double (&out)[K]) const {
+    template <int K, class Elem>
+    __device__ __forceinline__ void seqsum(int n, Elem elem, double (&out)[K]) const {
         double a[K];
 #pragma unroll
         for (int k = 0; k < K; ++k) a[k] = 0.0;
         __syncwarp();
-        if (lane_ == 0) seqsum_serial<K>(n, v, a);
+        if (lane_ == 0) seqsum_serial<K>(n, elem, a);
 #pragma unroll
         for (int k = 0; k < K; ++k) out[k] = __shfl_sync(0xffffffffu, a[k], 0);
     }
-    template <class Pred>
-    __device__ __forceinline__ int compact(int n, Pred pred, int* out) const {
+    template <class Pred, class Put>
+    __device__ __forceinline__ int compact(int n, Pred pred, Put put) const {
         int m = 0;
         for (int base = 0; base < n; base += 32) {
             const int i = base + lane_;
             const bool keep = i < n && pred(i);
             const unsigned mask = __ballot_sync(0xffffffffu, keep);
-            if (keep) out[m + __popc(mask & ((1u << lane_) - 1u))] = i;
+            if (keep) put(m + __popc(mask & ((1u << lane_) - 1u)), i);
             m += __popc(mask);
         }
         __syncwarp();
@@ -210,18 +215,22 @@ struct WarpCtx : CtxOps<WarpCtx> {
     }
 };
 
-// A CTA working on one item.  `scratch` is shared memory with room for 33 payloads of the largest
-// reduction type used (ACC_BLOCK_SCRATCH_BYTES).
+// A CTA working on one item.  `scratch` is shared memory with room for one payload of the largest reduction type
+// per warp (+1), see ACC_BLOCK_SCRATCH_BYTES.  G > 0 fixes the CTA size at compile time (strides and the fold over
+// the warps unroll); G == 0 reads blockDim.x.
 #define ACC_BLOCK_SCRATCH_BYTES (33 * 64)
-struct BlockCtx : CtxOps<BlockCtx> {
+#define ACC_BLOCK_SCRATCH_BYTES_FOR(G) ((((G) + 31) / 32 + 1) * 64)
+template <int G>
+struct BlockCtxT : CtxOps<BlockCtxT<G>> {
     unsigned char* scratch;
-    __device__ explicit BlockCtx(unsigned char* s) : scratch(s) {}
+    __device__ explicit BlockCtxT(unsigned char* s) : scratch(s) {}
+    __device__ __forceinline__ int size() const { return G > 0 ? G : (int)blockDim.x; }
     __device__ __forceinline__ bool leader() const { return threadIdx.x == 0; }
     __device__ __forceinline__ void sync() const { __syncthreads(); }
     __device__ __forceinline__ int lane() const { return threadIdx.x; }
     template <class F>
     __device__ __forceinline__ void foreach(int n, F f) const {
-        for (int i = threadIdx.x; i < n; i += blockDim.x) f(i);
+        for (int i = threadIdx.x; i < n; i += size()) f(i);
         __syncthreads();
     }
     template <class F>
@@ -234,27 +243,32 @@ struct BlockCtx : CtxOps<BlockCtx> {
     __device__ __forceinline__ T reduce(int n, F f) const {
         static_assert(sizeof(T) <= 64, "reduction payload too large for the block scratch");
         T acc_ = T::identity();
-        for (int i = threadIdx.x; i < n; i += blockDim.x) acc_ = T::combine(acc_, f(i));
+        for (int i = threadIdx.x; i < n; i += size()) acc_ = T::combine(acc_, f(i));
 #pragma unroll
         for (int off = 16; off >= 1; off >>= 1) acc_ = T::combine(acc_, shfl_xor_any(acc_, off));
         T* slots = reinterpret_cast<T*>(scratch);
-        const int w = threadIdx.x >> 5, W = blockDim.x >> 5;
+        const int w = threadIdx.x >> 5, W = size() >> 5;
         __syncthreads();  // scratch may still be read by a previous reduction
         if ((threadIdx.x & 31) == 0) slots[w] = acc_;
         __syncthreads();
         T total = slots[0];
-        for (int k = 1; k < W; ++k) total = T::combine(total, slots[k]);
+        if (G > 0) {
+#pragma unroll
+            for (int k = 1; k < (G > 0 ? G / 32 : 1); ++k) total = T::combine(total, slots[k]);
+        } else {
+            for (int k = 1; k < W; ++k) total = T::combine(total, slots[k]);
+        }
         return total;
     }
-    template <int K>
-    __device__ __forceinline__ void seqsum(int n, const double* const (&v)[K], double (&out)[K]) const {
+    template <int K, class Elem>
+    __device__ __forceinline__ void seqsum(int n, Elem elem, double (&out)[K]) const {
         double* slots = reinterpret_cast<double*>(scratch);
         __syncthreads();
         if (threadIdx.x == 0) {
             double a[K];
 #pragma unroll
             for (int k = 0; k < K; ++k) a[k] = 0.0;
-            seqsum_serial<K>(n, v, a);
+            seqsum_serial<K>(n, elem, a);
 #pragma unroll
             for (int k = 0; k < K; ++k) slots[k] = a[k];
         }
@@ -262,12 +276,12 @@ struct BlockCtx : CtxOps<BlockCtx> {
 #pragma unroll
         for (int k = 0; k < K; ++k) out[k] = slots[k];
     }
-    template <class Pred>
-    __device__ __forceinline__ int compact(int n, Pred pred, int* out) const {
+    template <class Pred, class Put>
+    __device__ __forceinline__ int compact(int n, Pred pred, Put put) const {
         int* counts = reinterpret_cast<int*>(scratch);  // per-warp counts of the current chunk
-        const int w = threadIdx.x >> 5, W = blockDim.x >> 5, lane_ = threadIdx.x & 31;
+        const int w = threadIdx.x >> 5, W = size() >> 5, lane_ = threadIdx.x & 31;
         int m = 0;
-        for (int base = 0; base < n; base += blockDim.x) {
+        for (int base = 0; base < n; base += size()) {
             const int i = base + threadIdx.x;
             const bool keep = i < n && pred(i);
             const unsigned mask = __ballot_sync(0xffffffffu, keep);
@@ -275,14 +289,20 @@ struct BlockCtx : CtxOps<BlockCtx> {
             if (lane_ == 0) counts[w] = __popc(mask);
             __syncthreads();
             int before = 0, total = 0;
-            for (int k = 0; k < W; ++k) { if (k < w) before += counts[k]; total += counts[k]; }
-            if (keep) out[m + before + __popc(mask & ((1u << lane_) - 1u))] = i;
+            if (G > 0) {
+#pragma unroll
+                for (int k = 0; k < (G > 0 ? G / 32 : 1); ++k) { if (k < w) before += counts[k]; total += counts[k]; }
+            } else {
+                for (int k = 0; k < W; ++k) { if (k < w) before += counts[k]; total += counts[k]; }
+            }
+            if (keep) put(m + before + __popc(mask & ((1u << lane_) - 1u)), i);
             m += total;
         }
         __syncthreads();
         return m;
     }
 };
+typedef BlockCtxT<0> BlockCtx;
 #endif  // __CUDACC__
 
 }  // namespace acc

@@ -38,6 +38,10 @@
 #include "purchase_core.cuh"
 #include "consumer_core.cuh"
 
+#ifndef ACC_PM_MAXREG_FIXED
+#define ACC_PM_MAXREG_FIXED 80  // registers per thread of the purchase kernel at the base group size (see struct Purchase)
+#endif
+
 namespace acc {
 
 // ------------------------------------------------------------------------------------------------
@@ -72,7 +76,7 @@ static void launch_warp(stream_t, int n, size_t smem, K k) {
     std::vector<unsigned char> sm(smem + 16);
     for (int i = 0; i < n; ++i) { HostCtx cx(32); k(cx, i, sm.data()); }
 }
-template <class K>
+template <int G, class K>
 static void launch_block_smem(stream_t, int n, int threads, size_t smem, K k) {
     std::vector<unsigned char> sm(smem + 16);
     for (int i = 0; i < n; ++i) { HostCtx cx(threads); k(cx, i, sm.data()); }
@@ -123,11 +127,12 @@ __global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) seller_kernel(K k, 
     if (n > 0 && n <= cap) book = stage_seller_book(dyn_smem, cap, &bar, k.ev.D_q, k.ev.D_p, k.ev.tau, k.ev.domestic, e0, n);
     k(cx, (int)blockIdx.x, book);
 }
-template <class K>
-__global__ void __maxnreg__(K::MAXREG) block_smem_kernel(K k) {
-    __shared__ __align__(16) unsigned char scratch[ACC_BLOCK_SCRATCH_BYTES];
+// G > 0: the CTA size is a compile-time constant (K::MAXREG_FIXED registers); G == 0: any CTA size (K::MAXREG)
+template <class K, int G>
+__global__ void __maxnreg__(G > 0 ? K::MAXREG_FIXED : K::MAXREG) block_smem_kernel(K k) {
+    __shared__ __align__(16) unsigned char scratch[G > 0 ? ACC_BLOCK_SCRATCH_BYTES_FOR(G) : ACC_BLOCK_SCRATCH_BYTES];
     extern __shared__ __align__(16) unsigned char dyn_smem[];
-    BlockCtx cx(scratch);
+    BlockCtxT<G> cx(scratch);
     k(cx, (int)blockIdx.x, dyn_smem);
 }
 template <class K>
@@ -171,15 +176,17 @@ static void launch_warp(stream_t s, int n, size_t smem, K k) {
     warp_kernel<K><<<n, 32, smem, s>>>(k);
     ACC_CUDA(cudaGetLastError());
 }
-template <class K>
+template <int G, class K>
 static void launch_block_smem(stream_t s, int n, int threads, size_t smem, K k) {
     if (n <= 0) return;
+    if (G > 0 && threads != G) fail("launch_block_smem: CTA size does not match the compiled group size");
     static size_t configured = 0;
     if (smem > configured) {
-        ACC_CUDA(cudaFuncSetAttribute(block_smem_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ACC_CUDA(cudaFuncSetAttribute(block_smem_kernel<K, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ACC_CUDA(cudaFuncSetAttribute(block_smem_kernel<K, G>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         configured = smem;
     }
-    block_smem_kernel<K><<<n, threads, smem, s>>>(k);
+    block_smem_kernel<K, G><<<n, threads, smem, s>>>(k);
     ACC_CUDA(cudaGetLastError());
 }
 #endif
@@ -355,7 +362,7 @@ struct StorageDelivery {  // thread per storage
 };
 
 struct ConsumerUtility {  // one CTA of ACCSQP_GROUP threads per utilitarian consumer
-    enum { MAXREG = 255 };
+    enum { MAXREG = 255, MAXREG_FIXED = 255 };
     ConsumerView cv; StorageView st; ModelP mp; EventSink events; int n_max; int* fatal;
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const {
@@ -364,16 +371,21 @@ struct ConsumerUtility {  // one CTA of ACCSQP_GROUP threads per utilitarian con
     }
 };
 
-struct Purchase {  // one CTA of ACCSQP_GROUP threads per purchasing manager
-    enum { MAXREG = 112 };  // 6 CTAs of 3 warps per SM at the base group size: 65536 / (18 * 32) = 113; 512 threads still fit
+// One CTA of pm_group threads per purchasing manager.  SEP: deviation_penalty (separate penalty target); STD: the
+// reference's default transport penalty (quadratic, relative) folded at compile time.
+template <bool SEP, bool STD>
+struct Purchase {
+    // any group size: 512 threads still fit; base group (96 threads, compile-time): 8 CTAs of 3 warps per SM,
+    // 6 warps per scheduler: 16384 / (6 * 32) = 85
+    enum { MAXREG = 112, MAXREG_FIXED = ACC_PM_MAXREG_FIXED };
     StorageView st; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
     const i64* in_off; const int* in_edge; const int* in_seller; const SellerPub* pub; int n_max; const int* pm_ids;  // pm_ids == nullptr: all
     i64* dem_q; double* dem_v; double* exp_costs; double* opt_val; double* tpen; int* iters; int* evals;
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const {
         const int s = pm_ids != nullptr ? pm_ids[item] : item;
-        PMWork k;
-        k.carve(smem, n_max, mp.deviation_penalty != 0);
+        PMWorkT<SEP, STD> k;
+        k.carve(smem, n_max);
         const i64 o = in_off[s];
         const int nin = (int)(in_off[s + 1] - o);
         const int* ie = in_edge + o;
@@ -381,7 +393,7 @@ struct Purchase {  // one CTA of ACCSQP_GROUP threads per purchasing manager
         const EdgeView& E = ev;
         const i64 stp = step;
         const i64 deficit = st.defc[s] - st.dlv_q[s] - st.T_q[s];
-        const PMResult r = purchase_one(
+        const PMResult r = purchase_one<SEP, STD>(
             cx, nin, [&](int i) { return ie[i]; }, [&](int i) { return is[i]; },
             [&](int e) { return E.ship_q != nullptr ? E.ship_q[e] : E.conv_q[(i64)((stp + E.tau[e]) % E.T) * E.n_edges + e]; },
             [&](int e) {  // BusinessConnection::get_minimum_passage, BusinessConnection.cpp:69-83
@@ -665,7 +677,7 @@ struct acc_engine {
         ACC_CUDA(cudaEventRecord(ev_fork, stream));
         ACC_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
 #endif
-        timed_on(side, "consumer_utility", [&] { launch_block_smem(side, nC, ACCSQP_GROUP, consumer_workspace_bytes(c_n_max), k); });
+        timed_on(side, "consumer_utility", [&] { launch_block_smem<0>(side, nC, ACCSQP_GROUP, consumer_workspace_bytes(c_n_max), k); });
 #ifndef ACC_HOST_EMU
         ACC_CUDA(cudaEventRecord(ev_join, side));
 #endif
@@ -708,18 +720,30 @@ struct acc_engine {
             timed("pack_sellers", [&] { launch_thread(stream, nA, k); });
         }
     }
+    template <bool SEP, bool STD, int G>
+    void launch_purchase() {
+        Purchase<SEP, STD> k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, pub.p, n_max,
+                             partitioned ? pm_ids.p : nullptr, s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
+        timed("purchase", [&] { launch_block_smem<G>(stream, partitioned ? n_pm : nSt, pm_group, pm_workspace_bytes(n_max, SEP), k); });
+    }
     void stage_purchase() {
         if (partitioned && x_sellers != nullptr) {
             UnpackSellers k{pub.p, owned.p, x_sellers};
             timed("unpack_sellers", [&] { launch_thread(stream, nA, k); });
         }
-        Purchase k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, pub.p, n_max,
-                   partitioned ? pm_ids.p : nullptr, s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
-        const bool dev = mp.deviation_penalty != 0;
         // One CTA of pm_group threads per purchasing manager, all its vectors in shared memory.  The group size is part
         // of the arithmetic (reduction order): ACCSQP_GROUP, or accsqp_group_for(largest manager) -- the same rule the
         // oracle's host context follows.
-        timed("purchase", [&] { launch_block_smem(stream, partitioned ? n_pm : nSt, pm_group, pm_workspace_bytes(n_max, dev), k); });
+        const bool dev = mp.deviation_penalty != 0;
+        const bool std_pen = mp.quadratic_penalty != 0 && mp.relative_penalty != 0 && !dev;
+        if (std_pen) {
+            if (pm_group == ACCSQP_GROUP) launch_purchase<false, true, ACCSQP_GROUP>();
+            else launch_purchase<false, true, 0>();
+        } else if (dev) {
+            launch_purchase<true, false, 0>();
+        } else {
+            launch_purchase<false, false, 0>();
+        }
         if (halo_recv.n) {
             PackDemand pk{edge_view(), halo_recv.p, x_dem_send};
             timed("pack_demand", [&] { launch_thread(stream, (int)halo_recv.n, pk); });

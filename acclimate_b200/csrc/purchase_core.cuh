@@ -1,5 +1,5 @@
 // purchase_core.cuh -- PurchasingManager::iterate_purchase for ONE purchasing manager, executed by
-// one warp with the connection data staged in shared memory.
+// one thread group (a small CTA) with the connection data staged in shared memory.
 //
 // Follows reference src/model/PurchasingManager.cpp:
 //   :563-660  desired purchase, per-connection bounds / start value / xtol, filtering
@@ -16,14 +16,7 @@
 
 namespace acc {
 
-// ---- work vectors of the solver (shared memory) ----
-struct PtrVec {
-    double* p;
-    ACC_HD double& operator[](int i) const { return p[i]; }
-};
-ACC_HD void attach(PtrVec& v, double*& p, int n) { v.p = p; p += n; }
-
-// shared-memory vectors of one purchasing manager besides the solver's own: 13 f64 (+1 with deviation_penalty) + 2 int
+// ---- transport penalty parameters of one purchasing manager ----
 struct PMParams {
     double Uf;        // to_float(initial_used_flow_U_star): scale of objective and constraint (:194,:200)
     double markup;    // to_float(buyer sector initial_markup)
@@ -34,15 +27,18 @@ struct PMParams {
 // The transport penalty's kink at D_r == target (:388-396 quadratic, :432-450 linear): slopes of the piecewise linear
 // part left and right of the target and the value the reference's gradient contains AT the target, per unit of D_r.
 // Shared with the oracle's harness (oracle/ref_harness), which describes the same kinks to the NLopt shim.
+// STD = the reference's default penalty (quadratic, relative) known at compile time.
 struct KinkSlopes {
     double sl, sr, mid;
 };
+template <bool STD = false>
 ACC_HD KinkSlopes pm_kink_slopes(const PMParams& pp, double target) {
     KinkSlopes k;
-    if (pp.quadratic) {
-        if (pp.relative && !(target > ACC_PREC3)) { k.sl = 0.0; k.sr = 0.0; k.mid = 0.0; return k; }  // D^2 form: treated as smooth
+    const bool quadratic = STD || pp.quadratic, relative = STD || pp.relative;
+    if (quadratic) {
+        if (relative && !(target > ACC_PREC3)) { k.sl = 0.0; k.sr = 0.0; k.mid = 0.0; return k; }  // D^2 form: treated as smooth
         k.sl = -pp.markup; k.sr = pp.markup; k.mid = 0.0;
-    } else if (pp.relative) {
+    } else if (relative) {
         k.sl = -pp.pen_small / target; k.sr = pp.pen_large / target; k.mid = (pp.pen_large - pp.pen_small) / 2 / target;
     } else {
         k.sl = -pp.pen_small; k.sr = pp.pen_large; k.mid = (pp.pen_large - pp.pen_small) / 2;
@@ -52,20 +48,32 @@ ACC_HD KinkSlopes pm_kink_slopes(const PMParams& pp, double target) {
 // in the solver's scaled variables (x = D / Z*, objective / U*): slope * (Z* / U*)
 ACC_HD double pm_scaled_slope(double slope, double z_over_u) { return slope * z_over_u; }
 
-// shared-memory vectors of one purchasing manager: 9 of the solver, 11 price-curve vectors (+1 with deviation_penalty), 2 int
-#define ACC_PM_NVEC_SOLVER 9
-#define ACC_PM_NVEC_CONST 11
+// ---- work vectors of one purchasing manager (shared memory) ----
+// Slot-major: the V f64 values of connection slot r are contiguous, so one index computation per slot serves every
+// vector (the vector is a compile-time offset) and one base register serves them all.  With an even V one f64 of
+// padding follows every eight slots, which keeps the 16 eight-byte accesses of a half-warp on different banks.
+// V = 18: 9 of the solver (x, x0, g, a, d, b, gl, xbest, xu) + 9 price-curve values; 19 with deviation_penalty (the
+// penalty target is then the last demand request instead of Z*).  Connection ids are a separate int vector.
+template <int V>
+ACC_HD int pm_slot_off(int i) { return (V % 2 == 0) ? i * V + (i >> 3) : i * V; }
 ACC_HD size_t pm_workspace_bytes(int n_max, bool separate_target) {
-    const int nvec = ACC_PM_NVEC_CONST + (separate_target ? 1 : 0) + ACC_PM_NVEC_SOLVER;
-    return (size_t)n_max * (nvec * sizeof(double) + 2 * sizeof(int));
+    const size_t doubles = separate_target ? (size_t)n_max * 19 : (size_t)n_max * 18 + (size_t)(n_max >> 3) + 1;
+    return doubles * sizeof(double) + (size_t)n_max * sizeof(int);
 }
 
-struct PMWork {
+template <bool SEP, bool STD>
+struct PMWorkT {
+    enum { V = SEP ? 19 : 18, TGT = SEP ? 18 : 9 };
+    template <int K>
+    struct Col {
+        double* base;
+        ACC_HD double& operator[](int i) const { return base[pm_slot_off<V>(i) + K]; }
+    };
     struct W {
-        PtrVec x, x0, g, a, d, b, gl, xbest;  // sqp_core work vectors
-        PtrVec xu;                            // upper bounds (lower bounds are all zero, :620)
-        const double* zf;                     // x tolerance = quantum of the demand request over the variable's scale (:640-644)
-        const double* tgt;                    // kink position in D_r
+        Col<0> x; Col<1> x0; Col<2> g; Col<3> a; Col<4> d; Col<5> b; Col<6> gl; Col<7> xbest;  // sqp_core work vectors
+        Col<8> xu;                            // upper bounds (lower bounds are all zero, :620)
+        Col<9> zf;                            // x tolerance = quantum of the demand request over the variable's scale (:640-644)
+        Col<TGT> tgt;                         // kink position in D_r
         double tol_c;
         PMParams pp;
         ACC_HD double lower(int) const { return 0.0; }
@@ -73,34 +81,31 @@ struct PMWork {
         // kink of the transport penalty (sqp_core.h "Kinks"); a[i] = -(Z*_i / U*) is the constraint gradient
         ACC_HD bool kinked() const { return true; }
         ACC_HD int kside(int i, double xi) const { const double D = xi * zf[i], t = tgt[i]; return D < t ? -1 : (D > t ? 1 : 0); }
-        ACC_HD double kpos(int i) const { return tgt == zf ? 1.0 : tgt[i] / zf[i]; }
-        ACC_HD double ksl(int i) const { return pm_scaled_slope(pm_kink_slopes(pp, tgt[i]).sl, -a[i]); }
-        ACC_HD double ksr(int i) const { return pm_scaled_slope(pm_kink_slopes(pp, tgt[i]).sr, -a[i]); }
-        ACC_HD double kmid(int i) const { return pm_scaled_slope(pm_kink_slopes(pp, tgt[i]).mid, -a[i]); }
+        ACC_HD double kpos(int i) const { return SEP ? tgt[i] / zf[i] : 1.0; }
+        ACC_HD double ksl(int i) const { return pm_scaled_slope(pm_kink_slopes<STD>(pp, tgt[i]).sl, -a[i]); }
+        ACC_HD double ksr(int i) const { return pm_scaled_slope(pm_kink_slopes<STD>(pp, tgt[i]).sr, -a[i]); }
+        ACC_HD double kmid(int i) const { return pm_scaled_slope(pm_kink_slopes<STD>(pp, tgt[i]).mid, -a[i]); }
     } w;
-    // price-curve constants per purchasing connection (shared memory)
-    double *zf;              // to_float(Z*): scale of the variable (:184-188)
-    double *tgt;             // transport penalty target (Z*, or the last demand request with deviation_penalty)
-    double *addX;            // expected_additional_production (:343-349)
-    double *Xhatf, *lamXf, *c2;  // seller constants (SellerPub); c1 = c2 / 2 exactly
-    double *base;            // n_bar [- pen(X_exp)/X_exp]: E_n_r without its X_new term (:255-271)
-    double *n_co, *Dmin;     // reservation price and kink position of the price curve (:283-289)
-    double *slope;           // (n_bar_min - n_co) / D_r_min in the linear regime; NaN marks the cropped regime (n_co > n_bar_min)
-    double *term, *dval;     // per-connection summands of the current evaluation (cost term, D_r), read by the ordered sums
-    int *idx, *eid;          // compacted position -> incoming position, connection id
-    ACC_HD void carve(unsigned char* mem, int n_max, bool separate_target) {
+    // price-curve constants per purchasing connection
+    Col<9> zf;               // to_float(Z*): scale of the variable (:184-188)
+    Col<TGT> tgt;            // transport penalty target (Z*, or the last demand request with deviation_penalty)
+    Col<10> addX;            // expected_additional_production (:343-349)
+    Col<11> Xhatf;           // seller constants (SellerPub); c1 = c2 / 2 exactly
+    Col<12> lamXf;
+    Col<13> c2;
+    Col<14> base;            // n_bar [- pen(X_exp)/X_exp]: E_n_r without its X_new term (:255-271)
+    Col<15> n_co;            // reservation price (:283-289); the kink position of the price curve D_r_min is max(0, lamX - addX)
+    Col<16> slope;           // (n_bar_min - n_co) / D_r_min in the linear regime; NaN marks the cropped regime (n_co > n_bar_min)
+    Col<17> term;            // per-connection cost term of the current evaluation, read by the ordered sum
+    int* eid;                // connection id of slot r
+    ACC_HD int& idx(int r) const { return *reinterpret_cast<int*>(&term[r]); }  // compacted position -> incoming position (set-up only)
+    ACC_HD void carve(unsigned char* mem, int n_max) {
         double* p = reinterpret_cast<double*>(mem);
-        attach(w.x, p, n_max); attach(w.x0, p, n_max); attach(w.g, p, n_max); attach(w.a, p, n_max); attach(w.d, p, n_max);
-        attach(w.b, p, n_max); attach(w.gl, p, n_max); attach(w.xbest, p, n_max); attach(w.xu, p, n_max);
-        zf = p; p += n_max; addX = p; p += n_max; Xhatf = p; p += n_max; lamXf = p; p += n_max; c2 = p; p += n_max;
-        base = p; p += n_max; n_co = p; p += n_max; Dmin = p; p += n_max; slope = p; p += n_max;
-        term = p; p += n_max; dval = p; p += n_max;
-        w.zf = zf;
-        tgt = zf;  // the penalty target is Z* itself unless deviation_penalty is set
-        if (separate_target) { tgt = p; p += n_max; }
-        w.tgt = tgt;
-        int* q = reinterpret_cast<int*>(p);
-        idx = q; q += n_max; eid = q;
+        w.x.base = p; w.x0.base = p; w.g.base = p; w.a.base = p; w.d.base = p; w.b.base = p; w.gl.base = p; w.xbest.base = p;
+        w.xu.base = p; w.zf.base = p; w.tgt.base = p;
+        zf.base = p; tgt.base = p; addX.base = p; Xhatf.base = p; lamXf.base = p; c2.base = p; base.base = p; n_co.base = p;
+        slope.base = p; term.base = p;
+        eid = reinterpret_cast<int*>(mem + pm_workspace_bytes(n_max, SEP) - (size_t)n_max * sizeof(int));
     }
 };
 
@@ -111,8 +116,9 @@ struct PMWork {
 struct CurvePoint {
     double n, gn, tp, tpp;
 };
-template <class PW>
+template <bool STD, class PW>
 ACC_HD CurvePoint curve_at(const PW& k, const PMParams& pp, int r, double D) {
+    const bool quadratic = STD || pp.quadratic, relative = STD || pp.relative;
     CurvePoint c;
     // expected_average_price_E_n_r (:243-275) and its gradient (:305-321)
     double Xn = D + k.addX[r];
@@ -129,7 +135,7 @@ ACC_HD CurvePoint curve_at(const PW& k, const PMParams& pp, int r, double D) {
     // n_r (:277-303), grad_n_r (:351-379)
     const double sl = k.slope[r];
     if (sl == sl) {  // n_co <= n_bar_min: linear regime below D_r_min
-        if (D < k.Dmin[r]) {
+        if (D < stdmax(0.0, lam - k.addX[r])) {  // D_r_min, :283
             c.n = k.n_co[r] + sl * D;
             c.gn = sl;
         } else {
@@ -145,10 +151,10 @@ ACC_HD CurvePoint curve_at(const PW& k, const PMParams& pp, int r, double D) {
     }
     // transport_penalty (:381-409), partial_D_r_transport_penalty (:411-451)
     const double t = k.tgt[r];
-    if (pp.quadratic) {
+    if (quadratic) {
         double marg = 0.0;
         if (D < t) marg = -pp.markup; else if (D > t) marg = pp.markup;
-        if (pp.relative) {
+        if (relative) {
             if (t > ACC_PREC3) {
                 const double qd = (D - t) * pp.pen_large / (t * t);  // shared by both expressions of the reference
                 c.tp = (D - t) * (qd / 2 + marg);
@@ -163,7 +169,7 @@ ACC_HD CurvePoint curve_at(const PW& k, const PMParams& pp, int r, double D) {
             c.tpp = (D - t) * pp.pen_large + marg;
         }
     } else {
-        if (pp.relative) {
+        if (relative) {
             if (D < t) c.tpp = -pp.pen_small / t;
             else if (D > t) c.tpp = pp.pen_large / t;
             else c.tpp = (pp.pen_large - pp.pen_small) / 2 / t;
@@ -180,7 +186,7 @@ ACC_HD CurvePoint curve_at(const PW& k, const PMParams& pp, int r, double D) {
 
 // Objective / constraint evaluation in the convention of sqp_core: minimise F = costs / U*,
 // constraint c = (desired - sum D_r) / U* == 0 whose gradient -Z*_r / U* is constant (filled once).
-template <class Ctx, class PW>
+template <bool STD, class Ctx, class PW>
 struct PMEval {
     Ctx& cx;
     PW& k;
@@ -193,14 +199,12 @@ struct PMEval {
         const PMParams& p = pp;
         cx.foreach(n, [&](int r) {
             const double D = x[r] * kk.zf[r];
-            const CurvePoint cp = curve_at(kk, p, r, D);
+            const CurvePoint cp = curve_at<STD>(kk, p, r, D);
             kk.term[r] = cp.n * D + cp.tp;
-            kk.dval[r] = D;
             if (want_grad) kk.w.g[r] = (kk.zf[r] * (cp.gn * D + cp.n + cp.tpp)) / p.Uf;
         });
-        const double* const v[2] = {kk.term, kk.dval};
         double s[2];
-        cx.seqsum(n, v, s);
+        cx.template seqsum<2>(n, [&](int r, double* t) { t[0] = kk.term[r]; t[1] = x[r] * kk.zf[r]; }, s);  // costs, sum of D_r
         const double costs = s[0], use = s[1];
         *F = costs / p.Uf;
         *c = (desired_f - use) / p.Uf;
@@ -218,7 +222,7 @@ struct PMResult {
 // Inputs of one purchasing manager, gathered by the caller-provided accessors:
 //   in_edge(i) -> connection id of the i-th incoming connection (seller ascending)
 //   in_seller(i) -> seller agent
-template <class Ctx, class PW, class InEdge, class InSeller, class LastShip, class MinPassage, class SendD>
+template <bool SEP, bool STD, class Ctx, class PW, class InEdge, class InSeller, class LastShip, class MinPassage, class SendD>
 ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_seller, LastShip last_ship, MinPassage min_passage, SendD send_D,
                              const SellerPub* pub, const i64* Z_q, const i64* lastD_q, PW& k, const ModelP& mp, const SectorP& sec, i64 Ustar_q,
                              i64 Sstar_q, i64 S_q, i64 Ut_q, i64 deficit_q, const EventSink& events, int ev_sector, int ev_agent) {
@@ -260,7 +264,7 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         const double zf = qf(Z_q[e]);
         const double lamXf = sp.lamXf;
         k.zf[r] = zf;
-        if (mp.deviation_penalty) k.tgt[r] = qf(lastD_q[e]);
+        if (SEP) k.tgt[r] = qf(lastD_q[e]);
         k.addX[r] = add;
         k.Xhatf[r] = sp.Xhatf;
         k.lamXf[r] = lamXf;
@@ -277,7 +281,6 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         double n_co = sp.n_co;                                                  // calc_n_co, :323-332
         if (pp.limited_by_markup) n_co = stdmax(n_co, nbar_min - pp.markup * Dmin);
         k.n_co[r] = n_co;
-        k.Dmin[r] = Dmin;
         k.slope[r] = (n_co <= nbar_min) ? (nbar_min - n_co) / Dmin : (double)NAN;
         // bounds, start value, xtol, :620-644; constraint gradient, :209
         k.w.xu[r] = upper / zf;
@@ -290,16 +293,16 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         k.w.d[i] = (double)dmax;  // exact below 2^53 quanta
         if (dmax <= 0) send_D(k.eid[i], (i64)0, (i64)0);
     });
-    const int n = cx.compact(nin, [&](int i) { return k.w.d[i] > 0.0; }, k.idx);
+    const int n = cx.compact(nin, [&](int i) { return k.w.d[i] > 0.0; }, [&](int m, int i) { k.idx(m) = i; });
     if (n == 0) return res;  // :652-655
     if (n != nin) {  // some connections dropped out: rebuild the slots in compacted order (slot r <= source idx[r])
-        cx.foreach(n, [&](int r) { k.w.d[r] = (double)fill(k.idx[r], r); });
+        cx.foreach(n, [&](int r) { k.w.d[r] = (double)fill(k.idx(r), r); });
     }
     const i64 max_purchase = cx.isum(n, [&](int r) { return (i64)k.w.d[r]; });
     if (desired > max_purchase) desired = max_purchase;  // :658-660
 
     // local optimisation, :690-702 with the restart logic of :465-561
-    PMEval<Ctx, PW> ev{cx, k, pp, n, qf(desired)};
+    PMEval<STD, Ctx, PW> ev{cx, k, pp, n, qf(desired)};
     accsqp::Params sp_;
     sp_.n = n; sp_.ctype = accsqp::CON_EQ; sp_.ctol = ACC_PREC3; sp_.maxeval = mp.maxeval; sp_.max_iter = ACCSQP_MAX_ITER;
     accsqp::Stats st;
@@ -324,18 +327,17 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         const i64 q = mkq(D);
         // with deviation_penalty the penalty target is last_demand_request_D, which the reference has already
         // overwritten with the new request when it accumulates the costs (:723 before :729-730)
-        if (mp.deviation_penalty) k.tgt[r] = qf(q);
-        const CurvePoint cp = curve_at(k, pp, r, D);
+        if (SEP) k.tgt[r] = qf(q);
+        const CurvePoint cp = curve_at<STD>(k, pp, r, D);
         const i64 p = q > 0 ? mkp(cp.n) : 0;
         send_D(k.eid[r], q, p);
         k.term[r] = cp.n * D + cp.tp;
-        k.dval[r] = cp.tp;
+        k.w.x0[r] = cp.tp;
         k.w.g[r] = q > 0 ? q_times_p(q, p) : 0.0;
         k.w.b[r] = (double)q;
     });
-    const double* const v[3] = {k.term, k.dval, k.w.g.p};
     double sums[3];
-    cx.seqsum(n, v, sums);
+    cx.template seqsum<3>(n, [&](int r, double* t) { t[0] = k.term[r]; t[1] = k.w.x0[r]; t[2] = k.w.g[r]; }, sums);
     const double costs = sums[0], pen = sums[1], dv = sums[2];
     const i64 dq = cx.isum(n, [&](int r) { return (i64)k.w.b[r]; });
     res.demand = mkflow(dq, dv);
