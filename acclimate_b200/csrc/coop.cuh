@@ -99,15 +99,17 @@ struct HostCtx : CtxOps<HostCtx> {
         return total;
     }
     // K strictly sequential left-to-right folds (the reference's own loop order)
-    // elem(i, t) fills the K summands of element i
+    // reduce over f(i, pre(i)); on the device pre() of a thread's next element is issued before f() of the current one
+    template <class T, class Pre, class F>
+    inline T reduce_staged(int n, Pre pre, F f) const {
+        return reduce<T>(n, [&](int i) { return f(i, pre(i)); });
+    }
+    // K strictly sequential left-to-right sums (the reference's own loop order); elem(i, k) = k-th summand of element i
     template <int K, class Elem>
     inline void seqsum(int n, Elem elem, double (&out)[K]) const {
         for (int k = 0; k < K; ++k) out[k] = 0.0;
-        for (int i = 0; i < n; ++i) {
-            double t[K];
-            elem(i, t);
-            for (int k = 0; k < K; ++k) out[k] += t[k];
-        }
+        for (int i = 0; i < n; ++i)
+            for (int k = 0; k < K; ++k) out[k] += elem(i, k);
     }
     // order-preserving compaction: put(m, i) for ascending i with pred(i), m = 0, 1, ...; returns the count
     template <class Pred, class Put>
@@ -142,26 +144,31 @@ __device__ __forceinline__ T shfl_any(const T& v, int src_lane) {
     return r;
 }
 
-// K strictly sequential left-to-right sums, executed by ONE thread: the summands of eight elements are fetched
-// first (independent loads; elem(i, t) fills the K summands of element i), then folded in element order.
-template <int K, class Elem>
-__device__ __forceinline__ void seqsum_serial(int n, Elem elem, double (&a)[K]) {
-    int i = 0;
-    for (; i + 8 <= n; i += 8) {
-        double t[8][K];
+// One strictly sequential left-to-right sum per lane: lane k < K folds the k-th summand elem(i, k) over i = 0..n-1.
+// The K chains run side by side in the lanes of one warp (one instruction stream); each chain is bound by the latency
+// of its dependent additions, so the summands of eight elements are fetched first (independent loads).
+template <class Elem>
+__device__ __forceinline__ double seqsum_lane(int n, Elem elem, int k) {
+    double a = 0.0;
+    const int nb = n >> 3;
+    if (nb > 0) {
+        double t[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) elem(i + j, t[j]);
+        for (int j = 0; j < 8; ++j) t[j] = elem(j, k);
+        for (int b = 0; b < nb; ++b) {
+            // the next batch is fetched (the last one once more: no branch) while the additions of this one run
+            const int nxt = (b + 1 < nb ? b + 1 : b) << 3;
+            double u[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
+            for (int j = 0; j < 8; ++j) u[j] = elem(nxt + j, k);
 #pragma unroll
-            for (int k = 0; k < K; ++k) a[k] += t[j][k];
+            for (int j = 0; j < 8; ++j) a += t[j];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) t[j] = u[j];
+        }
     }
-    for (; i < n; ++i) {
-        double t[K];
-        elem(i, t);
-#pragma unroll
-        for (int k = 0; k < K; ++k) a[k] += t[k];
-    }
+    for (int i = nb << 3; i < n; ++i) a += elem(i, k);
+    return a;
 }
 
 // One warp per item.
@@ -190,15 +197,17 @@ struct WarpCtx : CtxOps<WarpCtx> {
         for (int off = 16; off >= 1; off >>= 1) acc_ = T::combine(acc_, shfl_xor_any(acc_, off));
         return acc_;
     }
+    template <class T, class Pre, class F>
+    __device__ __forceinline__ T reduce_staged(int n, Pre pre, F f) const {
+        return reduce<T>(n, [&](int i) { return f(i, pre(i)); });
+    }
     template <int K, class Elem>
     __device__ __forceinline__ void seqsum(int n, Elem elem, double (&out)[K]) const {
-        double a[K];
-#pragma unroll
-        for (int k = 0; k < K; ++k) a[k] = 0.0;
+        double a = 0.0;
         __syncwarp();
-        if (lane_ == 0) seqsum_serial<K>(n, elem, a);
+        if (lane_ < K) a = seqsum_lane(n, elem, lane_);
 #pragma unroll
-        for (int k = 0; k < K; ++k) out[k] = __shfl_sync(0xffffffffu, a[k], 0);
+        for (int k = 0; k < K; ++k) out[k] = __shfl_sync(0xffffffffu, a, k);
     }
     template <class Pred, class Put>
     __device__ __forceinline__ int compact(int n, Pred pred, Put put) const {
@@ -241,9 +250,28 @@ struct BlockCtxT : CtxOps<BlockCtxT<G>> {
     }
     template <class T, class F>
     __device__ __forceinline__ T reduce(int n, F f) const {
-        static_assert(sizeof(T) <= 64, "reduction payload too large for the block scratch");
         T acc_ = T::identity();
         for (int i = threadIdx.x; i < n; i += size()) acc_ = T::combine(acc_, f(i));
+        return fold_group(acc_);
+    }
+    // Same fold order as reduce(); the gather pre() of a thread's two next elements is issued (clamped index, no
+    // branch) before either element is worked on, so their dependent loads overlap.
+    template <class T, class Pre, class F>
+    __device__ __forceinline__ T reduce_staged(int n, Pre pre, F f) const {
+        T acc_ = T::identity();
+        const int g = size();
+        for (int i = threadIdx.x; i < n; i += 2 * g) {
+            const int i1 = i + g;
+            const auto p0 = pre(i);
+            const auto p1 = pre(i1 < n ? i1 : n - 1);
+            acc_ = T::combine(acc_, f(i, p0));
+            if (i1 < n) acc_ = T::combine(acc_, f(i1, p1));
+        }
+        return fold_group(acc_);
+    }
+    template <class T>
+    __device__ __forceinline__ T fold_group(T acc_) const {
+        static_assert(sizeof(T) <= 64, "reduction payload too large for the block scratch");
 #pragma unroll
         for (int off = 16; off >= 1; off >>= 1) acc_ = T::combine(acc_, shfl_xor_any(acc_, off));
         T* slots = reinterpret_cast<T*>(scratch);
@@ -264,14 +292,7 @@ struct BlockCtxT : CtxOps<BlockCtxT<G>> {
     __device__ __forceinline__ void seqsum(int n, Elem elem, double (&out)[K]) const {
         double* slots = reinterpret_cast<double*>(scratch);
         __syncthreads();
-        if (threadIdx.x == 0) {
-            double a[K];
-#pragma unroll
-            for (int k = 0; k < K; ++k) a[k] = 0.0;
-            seqsum_serial<K>(n, elem, a);
-#pragma unroll
-            for (int k = 0; k < K; ++k) slots[k] = a[k];
-        }
+        if (threadIdx.x < K) slots[threadIdx.x] = seqsum_lane(n, elem, (int)threadIdx.x);
         __syncthreads();
 #pragma unroll
         for (int k = 0; k < K; ++k) out[k] = slots[k];

@@ -394,8 +394,17 @@ struct Purchase {
         const i64 stp = step;
         const i64 deficit = st.defc[s] - st.dlv_q[s] - st.T_q[s];
         const PMResult r = purchase_one<SEP, STD>(
-            cx, nin, [&](int i) { return ie[i]; }, [&](int i) { return is[i]; },
-            [&](int e) { return E.ship_q != nullptr ? E.ship_q[e] : E.conv_q[(i64)((stp + E.tau[e]) % E.T) * E.n_edges + e]; },
+            cx, nin, [&](int i) { return ie[i]; },
+            [&](int i) {
+                PMGather g;
+                g.e = ie[i]; g.seller = is[i];
+                const int e = g.e;
+                const i64* conv = E.conv_q + (i64)((stp + E.tau[e]) % E.T) * E.n_edges;
+                g.last_q = (E.ship_q != nullptr ? E.ship_q : conv)[e];  // a select, not a branch: loads of two gathers overlap
+                g.Z_q = E.Z_q[e];
+                g.lastD_q = SEP ? E.D_q[e] : 0;
+                return g;
+            },
             [&](int e) {  // BusinessConnection::get_minimum_passage, BusinessConnection.cpp:69-83
                 double m = 1.0;
                 if (E.nu != nullptr && E.route[e] >= 0) {
@@ -406,7 +415,7 @@ struct Purchase {
                 }
                 return m;
             },
-            [&](int e, i64 q, i64 p) { E.D_q[e] = q; E.D_p[e] = p; }, pub, E.Z_q, E.D_q, k, mp, sectors[st.sector[s]], st.Istar_q[s], st.Sstar_q[s],
+            [&](int e, i64 q, i64 p) { E.D_q[e] = q; E.D_p[e] = p; }, pub, k, mp, sectors[st.sector[s]], st.Istar_q[s], st.Sstar_q[s],
             st.S_q[s], st.Ut_q[s], deficit, events, st.sector[s], st.agent[s]);
         if (cx.leader()) {
             dem_q[s] = r.demand.q; dem_v[s] = r.demand.v; exp_costs[s] = r.expected_costs; opt_val[s] = r.optimized; tpen[s] = r.penalty;

@@ -63,7 +63,7 @@ ACC_HD size_t pm_workspace_bytes(int n_max, bool separate_target) {
 
 template <bool SEP, bool STD>
 struct PMWorkT {
-    enum { V = SEP ? 19 : 18, TGT = SEP ? 18 : 9 };
+    enum { V = SEP ? 19 : 18, TGT = SEP ? 18 : 9, COL_X = 0, COL_X0 = 1, COL_G = 2, COL_ZF = 9, COL_TERM = 17 };
     template <int K>
     struct Col {
         double* base;
@@ -98,6 +98,7 @@ struct PMWorkT {
     Col<16> slope;           // (n_bar_min - n_co) / D_r_min in the linear regime; NaN marks the cropped regime (n_co > n_bar_min)
     Col<17> term;            // per-connection cost term of the current evaluation, read by the ordered sum
     int* eid;                // connection id of slot r
+    ACC_HD double& at(int r, int col) const { return term.base[pm_slot_off<V>(r) + col]; }  // vector chosen at run time
     ACC_HD int& idx(int r) const { return *reinterpret_cast<int*>(&term[r]); }  // compacted position -> incoming position (set-up only)
     ACC_HD void carve(unsigned char* mem, int n_max) {
         double* p = reinterpret_cast<double*>(mem);
@@ -186,6 +187,7 @@ ACC_HD CurvePoint curve_at(const PW& k, const PMParams& pp, int r, double D) {
 
 // Objective / constraint evaluation in the convention of sqp_core: minimise F = costs / U*,
 // constraint c = (desired - sum D_r) / U* == 0 whose gradient -Z*_r / U* is constant (filled once).
+// The objective is separable, so it is handed to the solver coordinate by coordinate (accsqp::EvalTraits).
 template <bool STD, class Ctx, class PW>
 struct PMEval {
     Ctx& cx;
@@ -193,22 +195,37 @@ struct PMEval {
     const PMParams& pp;
     int n;
     double desired_f;
-    template <class X>
-    ACC_HD void operator()(const X& x, bool want_grad, double* F, double* c) {
-        PW& kk = k;
-        const PMParams& p = pp;
-        cx.foreach(n, [&](int r) {
-            const double D = x[r] * kk.zf[r];
-            const CurvePoint cp = curve_at<STD>(kk, p, r, D);
-            kk.term[r] = cp.n * D + cp.tp;
-            if (want_grad) kk.w.g[r] = (kk.zf[r] * (cp.gn * D + cp.n + cp.tpp)) / p.Uf;
-        });
-        double s[2];
-        cx.template seqsum<2>(n, [&](int r, double* t) { t[0] = kk.term[r]; t[1] = x[r] * kk.zf[r]; }, s);  // costs, sum of D_r
-        const double costs = s[0], use = s[1];
-        *F = costs / p.Uf;
-        *c = (desired_f - use) / p.Uf;
+    // connection r at x_r = xi: its cost term (kept for the ordered sum) and the gradient entry
+    ACC_HD void coord(int r, double xi) const {
+        const double D = xi * k.zf[r];
+        const CurvePoint cp = curve_at<STD>(k, pp, r, D);
+        k.term[r] = cp.n * D + cp.tp;
+        k.w.g[r] = (k.zf[r] * (cp.gn * D + cp.n + cp.tpp)) / pp.Uf;
     }
+    // costs and purchase summed strictly left to right, like the reference's loops (:203-217, :221-240)
+    template <class X>
+    ACC_HD void finish(const X& x, double* F, double* c) const {
+        const PW& kk = k;
+        double s[2];
+        // summand 0: the cost term; summand 1: D_r = x_r Z*_r (x is the solver's x vector)
+        cx.template seqsum<2>(n, [&](int r, int j) {
+            const double a = kk.at(r, j == 0 ? PW::COL_TERM : PW::COL_X), b = kk.at(r, PW::COL_ZF);
+            return j == 0 ? a : a * b;
+        }, s);
+        *F = s[0] / pp.Uf;
+        *c = (desired_f - s[1]) / pp.Uf;
+    }
+    template <class X>
+    ACC_HD void operator()(const X& x, bool, double* F, double* c) const {
+        cx.foreach(n, [&](int r) { coord(r, x[r]); });
+        finish(x, F, c);
+    }
+};
+
+struct CountSum {
+    i64 n, s;
+    static ACC_HD CountSum identity() { CountSum r; r.n = 0; r.s = 0; return r; }
+    static ACC_HD CountSum combine(CountSum a, CountSum b) { CountSum r; r.n = a.n + b.n; r.s = a.s + b.s; return r; }
 };
 
 struct PMResult {
@@ -219,12 +236,21 @@ struct PMResult {
     int iters, evals;
 };
 
+// What the set-up pass reads per incoming connection through index chains (connection id -> delay -> conveyor slot).
+// The caller's `gather(i)` resolves it; the group contexts call it for two connections of a thread before either is
+// worked on (reduce_staged), so the dependent loads of both are in flight together.
+struct PMGather {
+    int e, seller;   // connection id, seller agent of the i-th incoming connection (seller ascending)
+    i64 last_q;      // last shipment on the connection (:346)
+    i64 Z_q;         // initial flow Z*
+    i64 lastD_q;     // last demand request (read with deviation_penalty only)
+};
+
 // Inputs of one purchasing manager, gathered by the caller-provided accessors:
-//   in_edge(i) -> connection id of the i-th incoming connection (seller ascending)
-//   in_seller(i) -> seller agent
-template <bool SEP, bool STD, class Ctx, class PW, class InEdge, class InSeller, class LastShip, class MinPassage, class SendD>
-ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_seller, LastShip last_ship, MinPassage min_passage, SendD send_D,
-                             const SellerPub* pub, const i64* Z_q, const i64* lastD_q, PW& k, const ModelP& mp, const SectorP& sec, i64 Ustar_q,
+//   in_edge(i) -> connection id of the i-th incoming connection;  gather(i) -> PMGather of it
+template <bool SEP, bool STD, class Ctx, class PW, class InEdge, class Gather, class MinPassage, class SendD>
+ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, Gather gather, MinPassage min_passage, SendD send_D,
+                             const SellerPub* pub, PW& k, const ModelP& mp, const SectorP& sec, i64 Ustar_q,
                              i64 Sstar_q, i64 S_q, i64 Ut_q, i64 deficit_q, const EventSink& events, int ev_sector, int ev_agent) {
     PMResult res;
     res.demand = mkflow(0, 0.0); res.expected_costs = 0.0; res.optimized = 0.0; res.penalty = 0.0; res.iters = 0; res.evals = 0;
@@ -245,15 +271,15 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
 
     // One gather pass per connection: bounds (:609-650), price-curve constants (:279-289,:323-332) and start value,
     // written to slot r.  Returns D_r_max; <= 0 means the connection takes no part in the optimisation.
-    auto fill = [&](int i, int r) -> i64 {
-        const int e = in_edge(i);
-        const SellerPub sp = pub[in_seller(i)];
+    auto fill = [&](const PMGather& in, int r) -> i64 {
+        const int e = in.e;
+        const SellerPub sp = pub[in.seller];
         k.eid[r] = e;
         if (sp.Xhat_q <= 0) return 0;                                           // :604-605
         const double nu = min_passage(e);
         const double Xe = nu * sp.Xexpf;                                        // expected_production, :334-341
         const double X = sp.Xf;
-        const double Zl = qf(last_ship(e));
+        const double Zl = qf(in.last_q);
         const double rr = (X > 0.0) ? Xe / X : 0.0;
         const double add = rr * (X - Zl);                                       // expected_additional_production, :343-349
         double Xmax = sp.Xhatf;
@@ -261,10 +287,10 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         const double upper = Xmax - add;
         const i64 dmax = mkq(upper);                                            // :622
         if (dmax <= 0) return 0;                                                // :646-648
-        const double zf = qf(Z_q[e]);
+        const double zf = qf(in.Z_q);
         const double lamXf = sp.lamXf;
         k.zf[r] = zf;
-        if (SEP) k.tgt[r] = qf(lastD_q[e]);
+        if (SEP) k.tgt[r] = qf(in.lastD_q);
         k.addX[r] = add;
         k.Xhatf[r] = sp.Xhatf;
         k.lamXf[r] = lamXf;
@@ -288,17 +314,22 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         k.w.a[r] = -(zf / pp.Uf);
         return dmax;
     };
-    cx.foreach(nin, [&](int i) {
-        const i64 dmax = fill(i, i);
+    // the same pass counts the connections that take part and sums their D_r_max (integers: any order)
+    const CountSum part = cx.template reduce_staged<CountSum>(nin, gather, [&](int i, const PMGather& in) {
+        const i64 dmax = fill(in, i);
         k.w.d[i] = (double)dmax;  // exact below 2^53 quanta
+        CountSum r; r.n = 0; r.s = 0;
         if (dmax <= 0) send_D(k.eid[i], (i64)0, (i64)0);
+        else { r.n = 1; r.s = dmax; }
+        return r;
     });
-    const int n = cx.compact(nin, [&](int i) { return k.w.d[i] > 0.0; }, [&](int m, int i) { k.idx(m) = i; });
+    const int n = (int)part.n;
     if (n == 0) return res;  // :652-655
     if (n != nin) {  // some connections dropped out: rebuild the slots in compacted order (slot r <= source idx[r])
-        cx.foreach(n, [&](int r) { k.w.d[r] = (double)fill(k.idx(r), r); });
+        cx.compact(nin, [&](int i) { return k.w.d[i] > 0.0; }, [&](int m, int i) { k.idx(m) = i; });
+        cx.foreach(n, [&](int r) { fill(gather(k.idx(r)), r); });
     }
-    const i64 max_purchase = cx.isum(n, [&](int r) { return (i64)k.w.d[r]; });
+    const i64 max_purchase = part.s;
     if (desired > max_purchase) desired = max_purchase;  // :658-660
 
     // local optimisation, :690-702 with the restart logic of :465-561
@@ -309,21 +340,22 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
     int restarts = 0;
     for (;;) {
         const int ret = accsqp::sqp_minimize(cx, ev, k.w, sp_, st);
-        cx.foreach(n, [&](int r) { k.w.x[r] = k.w.xbest[r]; });
         res.iters += st.iters; res.evals += st.evals;
+        bool again = false;
         if (ret == accsqp::SQP_FAILURE) {                 // "bug: more than iter SQP iterations", :480-504
-            if (++restarts < 10) continue;
+            again = ++restarts < 10;
         } else if (ret == accsqp::SQP_MAXEVAL_REACHED) {  // :526-546
             if (cx.leader()) events.push(EV_OPTIMIZER_MAXITER, ev_sector, ev_agent, 0.0);
-            if (++restarts < 10) continue;
+            again = ++restarts < 10;
         }
-        break;
+        if (!again) break;
+        cx.foreach(n, [&](int r) { k.w.x[r] = k.w.xbest[r]; });  // restart from the best point (the result is read from xbest below)
     }
     res.optimized = (-st.minf) * pp.Uf;  // unscaled_objective(opt.optimized_value()), :509
 
     // distribute demand requests, :704-737
-    cx.foreach(n, [&](int r) {
-        const double D = k.w.x[r] * k.zf[r];
+    const i64 dq = cx.isum(n, [&](int r) {
+        const double D = k.w.xbest[r] * k.zf[r];
         const i64 q = mkq(D);
         // with deviation_penalty the penalty target is last_demand_request_D, which the reference has already
         // overwritten with the new request when it accumulates the costs (:723 before :729-730)
@@ -334,12 +366,11 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
         k.term[r] = cp.n * D + cp.tp;
         k.w.x0[r] = cp.tp;
         k.w.g[r] = q > 0 ? q_times_p(q, p) : 0.0;
-        k.w.b[r] = (double)q;
+        return q;
     });
     double sums[3];
-    cx.template seqsum<3>(n, [&](int r, double* t) { t[0] = k.term[r]; t[1] = k.w.x0[r]; t[2] = k.w.g[r]; }, sums);
+    cx.template seqsum<3>(n, [&](int r, int j) { return k.at(r, j == 0 ? PW::COL_TERM : (j == 1 ? PW::COL_X0 : PW::COL_G)); }, sums);
     const double costs = sums[0], pen = sums[1], dv = sums[2];
-    const i64 dq = cx.isum(n, [&](int r) { return (i64)k.w.b[r]; });
     res.demand = mkflow(dq, dv);
     res.expected_costs = costs;
     res.penalty = pen;
@@ -347,3 +378,10 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, InSeller in_selle
 }
 
 }  // namespace acc
+
+namespace accsqp {
+template <bool STD, class Ctx, class PW>
+struct EvalTraits<acc::PMEval<STD, Ctx, PW>> {
+    enum { PER_COORD = 1 };
+};
+}  // namespace accsqp

@@ -174,17 +174,23 @@ SQP_HD double qp_step(const W& w, int i, double lambda, bool kinked) {
     return t < ACCSQP_LO(w, i) ? ACCSQP_LO(w, i) : (t > ACCSQP_HI(w, i) ? ACCSQP_HI(w, i) : t);
 }
 
+// contribution of coordinate i to the attainable range [sum of minima, sum of maxima] of a^T d over the box
+template <class W>
+SQP_HD Sum2 qp_range_term(const W& w, int i) {
+    const double p = w.a[i] * ACCSQP_LO(w, i), q = w.a[i] * ACCSQP_HI(w, i);
+    Sum2 r; r.a = p < q ? p : q; r.b = p > q ? p : q; return r;
+}
+
+// `known_range`: the attainable range of a^T d at the current x when the caller has it already (the evaluation pass
+// of a per-coordinate objective computes it on the way, see sqp_eval_pass), else null.
 template <class Ctx, class W>
-SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, bool* d_ready) {
+SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, bool* d_ready, const Sum2* known_range) {
     *d_ready = false;
     const bool kinked = w.kinked();
     if (ctype == CON_NONE) return 0.0;
     const double target = -c;  // want a^T d = target
     // attainable range of a^T d over the box
-    const Sum2 range = cx.template reduce<Sum2>(n, [&](int i) {
-        const double p = w.a[i] * ACCSQP_LO(w, i), q = w.a[i] * ACCSQP_HI(w, i);
-        Sum2 r; r.a = p < q ? p : q; r.b = p > q ? p : q; return r;
-    });
+    const Sum2 range = known_range != nullptr ? *known_range : cx.template reduce<Sum2>(n, [&](int i) { return qp_range_term(w, i); });
     const double smin = range.a, smax = range.b;
     int forced = 0;  // -1: push a^T d to its minimum, +1: to its maximum
     if (ctype == CON_EQ && target <= smin) forced = -1;
@@ -273,6 +279,40 @@ SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, boo
 // and w.a (constraint gradient).  On return w.xbest holds the best point found (NLopt's rule:
 // best feasible objective, else least infeasible) and st.minf its objective.
 // ---------------------------------------------------------------------------------------
+// An objective may declare itself separable: EvalTraits<Eval>::PER_COORD = 1 promises
+//   ev.coord(i, xi)      evaluates coordinate i at xi (stores its summand, fills w.g[i]; touches nothing else), and
+//   ev.finish(x, F, c)   completes the evaluation (the ordered sums over all coordinates).
+// The solver then moves x, evaluates, strips the kink slope and gathers the QP's range in ONE pass over the coordinates
+// instead of four.  Every coordinate sees the same operations in the same order as in the generic sequence, so the
+// results are bit-identical (the oracle's NLopt shim runs the generic sequence: its objective is the reference's
+// callback, a black box).
+template <class Eval>
+struct EvalTraits {
+    enum { PER_COORD = 0 };
+};
+
+// x_i <- newx(i) for every coordinate, objective / constraint / gradient there, smooth part of the gradient in w.g.
+// Returns true when *range holds the attainable range of a^T d at the new x.
+template <class Ctx, class Eval, class W, class NewX>
+SQP_HD bool sqp_eval_pass(Ctx& cx, Eval& ev, W& w, int n, bool kinked, NewX newx, double* F, double* c, Sum2* range) {
+    if constexpr (EvalTraits<Eval>::PER_COORD != 0) {
+        *range = cx.template reduce<Sum2>(n, [&](int i) {
+            const double xi = newx(i);
+            w.x[i] = xi;
+            ev.coord(i, xi);
+            if (kinked) w.g[i] -= kink_sigma(w, i, xi);
+            return qp_range_term(w, i);
+        });
+        ev.finish(w.x, F, c);
+        return true;
+    } else {
+        cx.foreach(n, [&](int i) { w.x[i] = newx(i); });
+        ev(w.x, true, F, c);
+        if (kinked) cx.foreach(n, [&](int i) { w.g[i] -= kink_sigma(w, i, w.x[i]); });  // keep the smooth part only
+        return false;
+    }
+}
+
 SQP_HD double con_violation(int ctype, double c) {
     if (ctype == CON_EQ) return fabs(c);
     if (ctype == CON_INEQ) return c < 0.0 ? -c : 0.0;
@@ -286,24 +326,23 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
     const int n = p.n;
     st.iters = 0; st.evals = 0; st.qp_iters = 0; st.qp_inexact = 0; st.resets = 0; st.minf = 0.0; st.feasible = 0;
 
-    // NLopt clips the start point into the box
-    cx.foreach(n, [&](int i) {
+    const bool kinked = w.kinked();
+    double F = 0.0, c = 0.0;
+    Sum2 range;
+    // NLopt clips the start point into the box; the first point is the best one so far
+    bool have_range = sqp_eval_pass(cx, ev, w, n, kinked, [&](int i) {
         double xi = w.x[i];
         if (xi < ACCSQP_XL(w, i)) xi = ACCSQP_XL(w, i);
         if (xi > w.xu[i]) xi = w.xu[i];
-        w.x[i] = xi;
         w.b[i] = 1.0;
-    });
-    const bool kinked = w.kinked();
-    double F = 0.0, c = 0.0;
-    ev(w.x, true, &F, &c);
-    if (kinked) cx.foreach(n, [&](int i) { w.g[i] -= kink_sigma(w, i, w.x[i]); });  // keep the smooth part only
+        w.xbest[i] = xi;
+        return xi;
+    }, &F, &c, &range);
     st.evals = 1;
     double viol = con_violation(p.ctype, c);
     bool feasible = viol <= p.ctol;
     double infeas = viol;
     st.minf = F;
-    cx.foreach(n, [&](int i) { w.xbest[i] = w.x[i]; });
 
     bool b_identity = true;
     double mu = 0.0;      // merit penalty parameter
@@ -314,7 +353,7 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
         ++st.iters;
         if (p.max_iter > 0 && st.iters > p.max_iter) { ret = SQP_FAILURE; break; }
         bool d_ready = false;
-        const double lambda = qp_solve(cx, n, p.ctype, c, w, st, &d_ready);
+        const double lambda = qp_solve(cx, n, p.ctype, c, w, st, &d_ready, have_range ? &range : nullptr);
         // One pass forms the step, the Lagrangian gradient at the old point with the new multiplier (Kraft: v), saves
         // the old point and returns three sums: a.d (linearised constraint), the number of coordinates whose step
         // reaches the x tolerance, and the model's first-order change of the objective g.d (+ change of the kink terms).
@@ -359,16 +398,14 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
         for (;;) {
             ++line;
             h3 = alpha * h3;
-            cx.foreach(n, [&](int i) {
+            have_range = sqp_eval_pass(cx, ev, w, n, kinked, [&](int i) {
                 const double si = alpha * w.d[i];
                 w.d[i] = si;
                 double xi = w.x0[i] + si;
                 if (xi < ACCSQP_XL(w, i)) xi = ACCSQP_XL(w, i);
                 if (xi > w.xu[i]) xi = w.xu[i];
-                w.x[i] = xi;
-            });
-            ev(w.x, true, &F, &c);
-            if (kinked) cx.foreach(n, [&](int i) { w.g[i] -= kink_sigma(w, i, w.x[i]); });
+                return xi;
+            }, &F, &c, &range);
             ++st.evals;
             {   // NLopt: keep the best point seen at every evaluation
                 const double vi = con_violation(p.ctype, c);
