@@ -39,7 +39,7 @@
 #include "consumer_core.cuh"
 
 #ifndef ACC_PM_MAXREG_FIXED
-#define ACC_PM_MAXREG_FIXED 80  // registers per thread of the purchase kernel at the base group size (see struct Purchase)
+#define ACC_PM_MAXREG_FIXED 96  // registers per thread of the purchase kernel at the base group size (see struct Purchase)
 #endif
 
 namespace acc {
@@ -375,11 +375,14 @@ struct ConsumerUtility {  // one CTA of ACCSQP_GROUP threads per utilitarian con
 // reference's default transport penalty (quadratic, relative) folded at compile time.
 template <bool SEP, bool STD>
 struct Purchase {
-    // any group size: 512 threads still fit; base group (96 threads, compile-time): 8 CTAs of 3 warps per SM,
-    // 6 warps per scheduler: 16384 / (6 * 32) = 85
+    // any group size: 512 threads still fit; base group (96 threads, compile-time): 96 registers = 6 CTAs of 3 warps per
+    // SM (5 warps on a scheduler: 16384 / (5 * 32) = 102).  80 registers would admit the 7 CTAs the shared memory allows
+    // but spill: measured 3.22 ms against 3.10 ms on the EORA shape
     enum { MAXREG = 112, MAXREG_FIXED = ACC_PM_MAXREG_FIXED };
     StorageView st; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
-    const i64* in_off; const int* in_edge; const int* in_seller; const SellerPub* pub; int n_max; const int* pm_ids;  // pm_ids == nullptr: all
+    // incoming connections per storage (seller ascending): connection id, seller | delay << 24, Z* (copies in this order:
+    // one coalesced read instead of a gather through the connection id)
+    const i64* in_off; const int* in_edge; const int* in_seller; const i64* in_Z; const SellerPub* pub; int n_max; const int* pm_ids;  // pm_ids == nullptr: all
     i64* dem_q; double* dem_v; double* exp_costs; double* opt_val; double* tpen; int* iters; int* evals;
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const {
@@ -390,19 +393,26 @@ struct Purchase {
         const int nin = (int)(in_off[s + 1] - o);
         const int* ie = in_edge + o;
         const int* is = in_seller + o;
+        const i64* iz = in_Z + o;
         const EdgeView& E = ev;
-        const i64 stp = step;
+        const int T = E.T, plane0 = (int)(step % T);
+        const SellerPub* const pubs = pub;
         const i64 deficit = st.defc[s] - st.dlv_q[s] - st.T_q[s];
         const PMResult r = purchase_one<SEP, STD>(
             cx, nin, [&](int i) { return ie[i]; },
             [&](int i) {
                 PMGather g;
-                g.e = ie[i]; g.seller = is[i];
+                g.e = ie[i];
+                const unsigned st_ = (unsigned)is[i];
+                g.seller = (int)(st_ & 0xffffffu);
                 const int e = g.e;
-                const i64* conv = E.conv_q + (i64)((stp + E.tau[e]) % E.T) * E.n_edges;
+                int plane = plane0 + (int)(st_ >> 24);  // the conveyor plane of the last shipment: (step + delay) mod T
+                if (plane >= T) plane -= T;
+                const i64* conv = E.conv_q + (i64)plane * E.n_edges;
                 g.last_q = (E.ship_q != nullptr ? E.ship_q : conv)[e];  // a select, not a branch: loads of two gathers overlap
-                g.Z_q = E.Z_q[e];
+                g.Z_q = iz[i];
                 g.lastD_q = SEP ? E.D_q[e] : 0;
+                g.sp = pubs[g.seller];
                 return g;
             },
             [&](int e) {  // BusinessConnection::get_minimum_passage, BusinessConnection.cpp:69-83
@@ -415,7 +425,7 @@ struct Purchase {
                 }
                 return m;
             },
-            [&](int e, i64 q, i64 p) { E.D_q[e] = q; E.D_p[e] = p; }, pub, k, mp, sectors[st.sector[s]], st.Istar_q[s], st.Sstar_q[s],
+            [&](int e, i64 q, i64 p) { E.D_q[e] = q; E.D_p[e] = p; }, k, mp, sectors[st.sector[s]], st.Istar_q[s], st.Sstar_q[s],
             st.S_q[s], st.Ut_q[s], deficit, events, st.sector[s], st.agent[s]);
         if (cx.leader()) {
             dem_q[s] = r.demand.q; dem_v[s] = r.demand.v; exp_costs[s] = r.expected_costs; opt_val[s] = r.optimized; tpen[s] = r.penalty;
@@ -547,6 +557,7 @@ struct acc_engine {
     // buyer-side lists
     DBuf<i64> ell_off, in_off;
     DBuf<int> ell_width, ell_edge, in_edge, in_seller;
+    DBuf<i64> in_Z;
     // utilitarian consumers (nested-CES utility optimisation)
     int nC = 0, nB = 0, c_n_max = 0;
     double c_inter_exp = 0.0, c_ctol = 0.0;
@@ -731,7 +742,7 @@ struct acc_engine {
     }
     template <bool SEP, bool STD, int G>
     void launch_purchase() {
-        Purchase<SEP, STD> k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, pub.p, n_max,
+        Purchase<SEP, STD> k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, in_Z.p, pub.p, n_max,
                              partitioned ? pm_ids.p : nullptr, s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
         timed("purchase", [&] { launch_block_smem<G>(stream, partitioned ? n_pm : nSt, pm_group, pm_workspace_bytes(n_max, SEP), k); });
     }
@@ -1024,13 +1035,16 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
     // ---- buyer-side lists ----
     std::vector<i64> in_off(nSt + 1, 0);
     for (int k = 0; k < nSt; ++k) in_off[k + 1] = in_off[k] + in_cnt[k + 1];
-    std::vector<int> in_edge(nE), in_seller(nE);
+    std::vector<int> in_edge(nE), in_seller(nE);  // in_seller: seller agent | delay << 24
+    std::vector<i64> in_Z(nE);
+    if (nA >= (1 << 24)) fail("more than 2^24 agents");
     {
         std::vector<i64> fill(in_off.begin(), in_off.end() - 1);
         for (i64 e = 0; e < nE; ++e) {  // file order == seller ascending
             const int st = cid2s[e_cid[e]];
             in_edge[fill[st]] = (int)e;
-            in_seller[fill[st]] = (int)net.edge_from[e];
+            in_seller[fill[st]] = (int)((unsigned)net.edge_from[e] | ((unsigned)tau[e] << 24));
+            in_Z[fill[st]] = Zq[e];
             ++fill[st];
         }
     }
@@ -1178,7 +1192,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
         E.c_utility.alloc(nA); E.c_utility.zero(s);
     }
     E.fatal.alloc(1); E.fatal.zero(s);
-    E.in_off.upload(in_off, s); E.in_edge.upload(in_edge, s); E.in_seller.upload(in_seller, s);
+    E.in_off.upload(in_off, s); E.in_edge.upload(in_edge, s); E.in_seller.upload(in_seller, s); E.in_Z.upload(in_Z, s);
     E.ell_off.upload(ell_off, s); E.ell_width.upload(ell_width, s); E.ell_edge.upload(ell_edge, s);
     E.ev_buf.alloc(E.ev_cap); E.ev_count.alloc(1); E.ev_count.zero(s);
     E.nu.alloc((size_t)E.nEnt + 1);
@@ -1408,7 +1422,7 @@ void acc_destroy(acc_engine* e) {
     for (DBuf<i64>* b : {&e->f_Xstar_q, &e->f_markup_eff, &e->f_var_costs, &e->f_cap_q, &e->f_Xhat_q, &e->f_est_q, &e->f_X_q, &e->f_Xexp_q, &e->f_nbar,
                          &e->f_cutoff, &e->f_desired_q, &e->f_sumD_q, &e->f_bk_sq, &e->f_bk_cnt, &e->f_bk_pmax, &e->f_bk_pmin, &e->f_exp_q, &e->s_S_q,
                          &e->s_I0_q, &e->s_I1_q, &e->s_Il_q, &e->s_U_q, &e->s_Ut_q, &e->s_T_q, &e->s_dlv_q, &e->s_imp_q, &e->s_Istar_q, &e->s_Sstar_q,
-                         &e->s_defc, &e->s_dem_q, &e->e_D_q, &e->e_D_p, &e->e_Z_q, &e->conv_q, &e->e_ovf_q, &e->ell_off, &e->in_off})
+                         &e->s_defc, &e->s_dem_q, &e->e_D_q, &e->e_D_p, &e->e_Z_q, &e->conv_q, &e->e_ovf_q, &e->ell_off, &e->in_off, &e->in_Z})
         b->free();
     for (DBuf<double>* b : {&e->a_beta, &e->a_lambda, &e->f_Xstar_v, &e->f_cap_v, &e->f_Xhat_v, &e->f_est_v, &e->f_X_v, &e->f_Xexp_v, &e->f_C, &e->f_R,
                             &e->f_sumD_v, &e->f_bk_sv, &e->f_exp_v, &e->s_S_v, &e->s_I0_v, &e->s_I1_v, &e->s_Il_v, &e->s_U_v, &e->s_Ut_v, &e->s_T_v,

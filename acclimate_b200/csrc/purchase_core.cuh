@@ -52,18 +52,19 @@ ACC_HD double pm_scaled_slope(double slope, double z_over_u) { return slope * z_
 // Slot-major: the V f64 values of connection slot r are contiguous, so one index computation per slot serves every
 // vector (the vector is a compile-time offset) and one base register serves them all.  With an even V one f64 of
 // padding follows every eight slots, which keeps the 16 eight-byte accesses of a half-warp on different banks.
-// V = 18: 9 of the solver (x, x0, g, a, d, b, gl, xbest, xu) + 9 price-curve values; 19 with deviation_penalty (the
-// penalty target is then the last demand request instead of Z*).  Connection ids are a separate int vector.
+// V = 19: 9 of the solver (x, x0, g, a, d, b, gl, xbest, xu) + 8 price-curve values + the two summands of the ordered
+// sums; 20 with deviation_penalty (the penalty target is then the last demand request instead of Z*).  Connection ids
+// are a separate int vector.
 template <int V>
 ACC_HD int pm_slot_off(int i) { return (V % 2 == 0) ? i * V + (i >> 3) : i * V; }
 ACC_HD size_t pm_workspace_bytes(int n_max, bool separate_target) {
-    const size_t doubles = separate_target ? (size_t)n_max * 19 : (size_t)n_max * 18 + (size_t)(n_max >> 3) + 1;
+    const size_t doubles = separate_target ? (size_t)n_max * 20 + (size_t)(n_max >> 3) + 1 : (size_t)n_max * 19;
     return doubles * sizeof(double) + (size_t)n_max * sizeof(int);
 }
 
 template <bool SEP, bool STD>
 struct PMWorkT {
-    enum { V = SEP ? 19 : 18, TGT = SEP ? 18 : 9, COL_X = 0, COL_X0 = 1, COL_G = 2, COL_ZF = 9, COL_TERM = 17 };
+    enum { V = SEP ? 20 : 19, TGT = SEP ? 19 : 9, COL_X0 = 1, COL_G = 2, COL_TERM = 17, COL_DVAL = 18 };
     template <int K>
     struct Col {
         double* base;
@@ -96,7 +97,8 @@ struct PMWorkT {
     Col<14> base;            // n_bar [- pen(X_exp)/X_exp]: E_n_r without its X_new term (:255-271)
     Col<15> n_co;            // reservation price (:283-289); the kink position of the price curve D_r_min is max(0, lamX - addX)
     Col<16> slope;           // (n_bar_min - n_co) / D_r_min in the linear regime; NaN marks the cropped regime (n_co > n_bar_min)
-    Col<17> term;            // per-connection cost term of the current evaluation, read by the ordered sum
+    Col<17> term;            // per-connection summands of the current evaluation (cost term, D_r), read by the ordered sums
+    Col<18> dval;
     int* eid;                // connection id of slot r
     ACC_HD double& at(int r, int col) const { return term.base[pm_slot_off<V>(r) + col]; }  // vector chosen at run time
     ACC_HD int& idx(int r) const { return *reinterpret_cast<int*>(&term[r]); }  // compacted position -> incoming position (set-up only)
@@ -105,7 +107,7 @@ struct PMWorkT {
         w.x.base = p; w.x0.base = p; w.g.base = p; w.a.base = p; w.d.base = p; w.b.base = p; w.gl.base = p; w.xbest.base = p;
         w.xu.base = p; w.zf.base = p; w.tgt.base = p;
         zf.base = p; tgt.base = p; addX.base = p; Xhatf.base = p; lamXf.base = p; c2.base = p; base.base = p; n_co.base = p;
-        slope.base = p; term.base = p;
+        slope.base = p; term.base = p; dval.base = p;
         eid = reinterpret_cast<int*>(mem + pm_workspace_bytes(n_max, SEP) - (size_t)n_max * sizeof(int));
     }
 };
@@ -200,6 +202,7 @@ struct PMEval {
         const double D = xi * k.zf[r];
         const CurvePoint cp = curve_at<STD>(k, pp, r, D);
         k.term[r] = cp.n * D + cp.tp;
+        k.dval[r] = D;
         k.w.g[r] = (k.zf[r] * (cp.gn * D + cp.n + cp.tpp)) / pp.Uf;
     }
     // costs and purchase summed strictly left to right, like the reference's loops (:203-217, :221-240)
@@ -207,11 +210,7 @@ struct PMEval {
     ACC_HD void finish(const X& x, double* F, double* c) const {
         const PW& kk = k;
         double s[2];
-        // summand 0: the cost term; summand 1: D_r = x_r Z*_r (x is the solver's x vector)
-        cx.template seqsum<2>(n, [&](int r, int j) {
-            const double a = kk.at(r, j == 0 ? PW::COL_TERM : PW::COL_X), b = kk.at(r, PW::COL_ZF);
-            return j == 0 ? a : a * b;
-        }, s);
+        cx.template seqsum<2>(n, [&](int r, int j) { return kk.at(r, PW::COL_TERM + j); }, s);  // costs, sum of D_r
         *F = s[0] / pp.Uf;
         *c = (desired_f - s[1]) / pp.Uf;
     }
@@ -244,13 +243,13 @@ struct PMGather {
     i64 last_q;      // last shipment on the connection (:346)
     i64 Z_q;         // initial flow Z*
     i64 lastD_q;     // last demand request (read with deviation_penalty only)
+    SellerPub sp;    // the seller's published supply parameters (SalesManager.h:38-43)
 };
 
 // Inputs of one purchasing manager, gathered by the caller-provided accessors:
 //   in_edge(i) -> connection id of the i-th incoming connection;  gather(i) -> PMGather of it
 template <bool SEP, bool STD, class Ctx, class PW, class InEdge, class Gather, class MinPassage, class SendD>
-ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, Gather gather, MinPassage min_passage, SendD send_D,
-                             const SellerPub* pub, PW& k, const ModelP& mp, const SectorP& sec, i64 Ustar_q,
+ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, Gather gather, MinPassage min_passage, SendD send_D, PW& k, const ModelP& mp, const SectorP& sec, i64 Ustar_q,
                              i64 Sstar_q, i64 S_q, i64 Ut_q, i64 deficit_q, const EventSink& events, int ev_sector, int ev_agent) {
     PMResult res;
     res.demand = mkflow(0, 0.0); res.expected_costs = 0.0; res.optimized = 0.0; res.penalty = 0.0; res.iters = 0; res.evals = 0;
@@ -273,7 +272,7 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, Gather gather, Mi
     // written to slot r.  Returns D_r_max; <= 0 means the connection takes no part in the optimisation.
     auto fill = [&](const PMGather& in, int r) -> i64 {
         const int e = in.e;
-        const SellerPub sp = pub[in.seller];
+        const SellerPub& sp = in.sp;
         k.eid[r] = e;
         if (sp.Xhat_q <= 0) return 0;                                           // :604-605
         const double nu = min_passage(e);
