@@ -81,6 +81,8 @@ static void launch_block_smem(stream_t, int n, int threads, size_t smem, K k) {
     std::vector<unsigned char> sm(smem + 16);
     for (int i = 0; i < n; ++i) { HostCtx cx(threads); k(cx, i, sm.data()); }
 }
+template <class K>
+static void launch_warps(stream_t s, int n, size_t smem_per_warp, K k) { launch_warp(s, n, smem_per_warp, k); }
 #else
 typedef cudaStream_t stream_t;
 #define ACC_CUDA(x)                                                                                   \
@@ -140,6 +142,29 @@ __global__ void __launch_bounds__(32) warp_kernel(K k) {
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     WarpCtx cx;
     k(cx, (int)blockIdx.x, dyn_smem);
+}
+// K::WARPS items per CTA, one warp each, every warp with its own slice of the dynamic shared memory
+template <class K>
+__global__ void __launch_bounds__(K::WARPS * 32) warps_kernel(K k, int n, unsigned smem_per_warp) {
+    extern __shared__ __align__(16) unsigned char dyn_smem[];
+    const int w = threadIdx.x >> 5;
+    const int item = (int)blockIdx.x * K::WARPS + w;
+    if (item >= n) return;  // whole warps leave; the contexts of the others only use warp-level synchronisation
+    WarpCtx cx;
+    k(cx, item, dyn_smem + (size_t)w * smem_per_warp);
+}
+template <class K>
+static void launch_warps(stream_t s, int n, size_t smem_per_warp, K k) {
+    if (n <= 0) return;
+    smem_per_warp = (smem_per_warp + 15) / 16 * 16;
+    const size_t smem = smem_per_warp * K::WARPS;
+    static size_t configured = 0;
+    if (smem > configured) {
+        ACC_CUDA(cudaFuncSetAttribute(warps_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    warps_kernel<K><<<(n + K::WARPS - 1) / K::WARPS, K::WARPS * 32, smem, s>>>(k, n, (unsigned)smem_per_warp);
+    ACC_CUDA(cudaGetLastError());
 }
 template <class K>
 static void launch_thread(stream_t s, int n, K k) {
@@ -278,7 +303,8 @@ struct StorageDelivery {  // thread per storage
         const i64 base = ell_off[slice];
         const int width = ell_width[slice];
         const int T = ev.T;
-        const i64 now = (i64)(step % T) * ev.n_edges;
+        const int plane_now = (int)(step % T);
+        const i64 now = (i64)plane_now * ev.n_edges;
         Flow in = mkflow(0, 0.0);
         Flow imp = mkflow(0, 0.0);
         i64 tq = st.T_q[s];
@@ -305,7 +331,9 @@ struct StorageDelivery {  // thread per storage
                 const int e = e_[j] < 0 ? 0 : e_[j];
                 ship_[j] = front_[j];
                 if (tau_[j] != 0) {
-                    const i64 pl = (i64)((step + tau_[j]) % T) * ev.n_edges;
+                    int pj = plane_now + tau_[j];  // (step + delay) mod T without the division: delay < T
+                    if (pj >= T) pj -= T;
+                    const i64 pl = (i64)pj * ev.n_edges;
                     ship_[j] = mkflow(ev.conv_q[pl + e], ev.conv_v[pl + e]);
                 }
             }
@@ -329,7 +357,9 @@ struct StorageDelivery {  // thread per storage
                     for (int h = h0; h < h1; ++h) {
                         const int ent = ev.route_ent[h];
                         rem -= ev.ent_delay[ent];
-                        const i64 slot = (i64)((step + rem) % T) * ev.n_edges + e;
+                        int ps = plane_now + rem;
+                        if (ps >= T) ps -= T;
+                        const i64 slot = (i64)ps * ev.n_edges + e;
                         const i64 oslot = (i64)(h - h0) * ev.n_edges + e;
                         const Flow fr = mkflow(ev.conv_q[slot], ev.conv_v[slot]);
                         const double nu = ev.nu[ent];
@@ -361,8 +391,11 @@ struct StorageDelivery {  // thread per storage
     }
 };
 
-struct ConsumerUtility {  // one CTA of ACCSQP_GROUP threads per utilitarian consumer
-    enum { MAXREG = 255, MAXREG_FIXED = 255 };
+// One warp per utilitarian consumer, eight consumers per CTA: the solve is sequential code run by the warp's leader, so
+// the kernel needs residency, not width -- packed like this it takes two dozen SMs instead of one CTA slot on every SM
+// next to seller_production, which runs at the same time.
+struct ConsumerUtility {
+    enum { WARPS = 8 };
     ConsumerView cv; StorageView st; ModelP mp; EventSink events; int n_max; int* fatal;
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const {
@@ -449,19 +482,24 @@ struct FirmIncomingDemand {  // CTA per firm: sum of the demand requests it hold
 // ---- exchange of a region-partitioned run (thread per halo entry / per agent) ----
 ACC_HD i64 f64_bits(double v) { i64 b; memcpy(&b, &v, sizeof b); return b; }
 ACC_HD double bits_f64(i64 b) { double v; memcpy(&v, &b, sizeof v); return v; }
+ACC_HD i64 conveyor_slot(const EdgeView& ev, int plane_now, i64 e) {  // slot of plane (step + delay) mod T, plane_now = step mod T
+    int pl = plane_now + ev.tau[e];
+    if (pl >= ev.T) pl -= ev.T;
+    return (i64)pl * ev.n_edges + e;
+}
 struct PackFlow {  // shipment of this step: the conveyor slot it was written to
-    EdgeView ev; i64 step; const i64* ids; i64* buf;
+    EdgeView ev; int plane_now; const i64* ids; i64* buf;
     ACC_HD void operator()(int i) const {
         const i64 e = ids[i];
-        const i64 at = (i64)((step + ev.tau[e]) % ev.T) * ev.n_edges + e;
+        const i64 at = conveyor_slot(ev, plane_now, e);
         buf[2 * (i64)i] = ev.conv_q[at]; buf[2 * (i64)i + 1] = f64_bits(ev.conv_v[at]);
     }
 };
 struct UnpackFlow {
-    EdgeView ev; i64 step; const i64* ids; const i64* buf;
+    EdgeView ev; int plane_now; const i64* ids; const i64* buf;
     ACC_HD void operator()(int i) const {
         const i64 e = ids[i];
-        const i64 at = (i64)((step + ev.tau[e]) % ev.T) * ev.n_edges + e;
+        const i64 at = conveyor_slot(ev, plane_now, e);
         ev.conv_q[at] = buf[2 * (i64)i]; ev.conv_v[at] = bits_f64(buf[2 * (i64)i + 1]);
     }
 };
@@ -697,7 +735,7 @@ struct acc_engine {
         ACC_CUDA(cudaEventRecord(ev_fork, stream));
         ACC_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
 #endif
-        timed_on(side, "consumer_utility", [&] { launch_block_smem<0>(side, nC, ACCSQP_GROUP, consumer_workspace_bytes(c_n_max), k); });
+        timed_on(side, "consumer_utility", [&] { launch_warps(side, nC, consumer_workspace_bytes(c_n_max), k); });
 #ifndef ACC_HOST_EMU
         ACC_CUDA(cudaEventRecord(ev_join, side));
 #endif
@@ -718,13 +756,13 @@ struct acc_engine {
             timed("seller_production", [&] { launch_seller(stream, nF, book_cap, k); });
         }
         if (halo_send.n) {
-            PackFlow k{edge_view(), step, halo_send.p, x_flow_send};
+            PackFlow k{edge_view(), (int)(step % T), halo_send.p, x_flow_send};
             timed("pack_flow", [&] { launch_thread(stream, (int)halo_send.n, k); });
         }
     }
     void stage_deliver() {
         if (halo_recv.n) {
-            UnpackFlow k{edge_view(), step, halo_recv.p, x_flow_recv};
+            UnpackFlow k{edge_view(), (int)(step % T), halo_recv.p, x_flow_recv};
             timed("unpack_flow", [&] { launch_thread(stream, (int)halo_recv.n, k); });
         }
         consumer_join();

@@ -434,7 +434,8 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
     i64 exq = 0; double exv = 0.0;
     if (X.q <= 0) {
         cx.foreach(n, [&](int i) {
-            const int pl = (plane_now + tau[i]) % T;
+            int pl = plane_now + tau[i];  // (step + delay) mod T without the division: delay < T
+            if (pl >= T) pl -= T;
             ev.conv_q[(i64)pl * ev.n_edges + e0 + i] = 0;
             if (ev.ship_q != nullptr) ev.ship_q[e0 + i] = 0;
             ev.conv_v[(i64)pl * ev.n_edges + e0 + i] = 0.0;
@@ -482,7 +483,8 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
                     }
                 }
             }
-            const int pl = (plane_now + tau[i]) % T;
+            int pl = plane_now + tau[i];  // (step + delay) mod T without the division: delay < T
+            if (pl >= T) pl -= T;
             ev.conv_q[(i64)pl * ev.n_edges + e0 + i] = z.q;           // BusinessConnection::push_flow_Z -> first transport link
             if (ev.ship_q != nullptr) ev.ship_q[e0 + i] = z.q;        // last_shipment_Z, kept apart when hops rewrite the slot
             ev.conv_v[(i64)pl * ev.n_edges + e0 + i] = z.v;

@@ -223,7 +223,9 @@ SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, boo
         return lambda;
     }
 
-    const double psi_tol = 4e-16 * (fabs(c) + (fabs(smin) > fabs(smax) ? fabs(smin) : fabs(smax)));
+    // |psi| below the rounding noise of the n-term sums it is made of (c itself is such a sum) counts as zero:
+    // n * 2^-52 relative to the magnitudes involved.  A tighter test only makes Newton chase that noise.
+    const double psi_tol = 2.3e-16 * (n < 2 ? 2 : n) * (fabs(c) + (fabs(smin) > fabs(smax) ? fabs(smin) : fabs(smax)));
     double lambda = 0.0;
     double lamL = 0.0, lamR = 0.0;
     bool haveL = false, haveR = false;
