@@ -38,6 +38,10 @@
 #include "purchase_core.cuh"
 #include "consumer_core.cuh"
 
+#ifndef ACC_PM_MAXREG_ANY
+#define ACC_PM_MAXREG_ANY 80  // ... at any other group size: two CTAs of 384 threads (748 connections per manager) per SM; measured on a
+                              // 748x3 network: 1.81 ms with 112 registers (one CTA per SM), 1.30 ms with 80
+#endif
 #ifndef ACC_PM_MAXREG_FIXED
 #define ACC_PM_MAXREG_FIXED 96  // registers per thread of the purchase kernel at the base group size (see struct Purchase)
 #endif
@@ -406,12 +410,12 @@ struct ConsumerUtility {
 
 // One CTA of pm_group threads per purchasing manager.  SEP: deviation_penalty (separate penalty target); STD: the
 // reference's default transport penalty (quadratic, relative) folded at compile time.
-template <bool SEP, bool STD>
+template <bool SEP, bool STD, bool DVAL>
 struct Purchase {
     // any group size: 512 threads still fit; base group (96 threads, compile-time): 96 registers = 6 CTAs of 3 warps per
     // SM (5 warps on a scheduler: 16384 / (5 * 32) = 102).  80 registers would admit the 7 CTAs the shared memory allows
     // but spill: measured 3.22 ms against 3.10 ms on the EORA shape
-    enum { MAXREG = 112, MAXREG_FIXED = ACC_PM_MAXREG_FIXED };
+    enum { MAXREG = ACC_PM_MAXREG_ANY, MAXREG_FIXED = ACC_PM_MAXREG_FIXED };
     StorageView st; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
     // incoming connections per storage (seller ascending): connection id, seller | delay << 24, Z* (copies in this order:
     // one coalesced read instead of a gather through the connection id)
@@ -420,7 +424,7 @@ struct Purchase {
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const {
         const int s = pm_ids != nullptr ? pm_ids[item] : item;
-        PMWorkT<SEP, STD> k;
+        PMWorkT<SEP, STD, DVAL> k;
         k.carve(smem, n_max);
         const i64 o = in_off[s];
         const int nin = (int)(in_off[s + 1] - o);
@@ -780,9 +784,10 @@ struct acc_engine {
     }
     template <bool SEP, bool STD, int G>
     void launch_purchase() {
-        Purchase<SEP, STD> k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, in_Z.p, pub.p, n_max,
+        constexpr bool DVAL = G > 0;  // the base group keeps the D_r summands; the large groups trade them for a second CTA per SM
+        Purchase<SEP, STD, DVAL> k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, in_Z.p, pub.p, n_max,
                              partitioned ? pm_ids.p : nullptr, s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
-        timed("purchase", [&] { launch_block_smem<G>(stream, partitioned ? n_pm : nSt, pm_group, pm_workspace_bytes(n_max, SEP), k); });
+        timed("purchase", [&] { launch_block_smem<G>(stream, partitioned ? n_pm : nSt, pm_group, pm_workspace_bytes(n_max, SEP, DVAL), k); });
     }
     void stage_purchase() {
         if (partitioned && x_sellers != nullptr) {

@@ -55,16 +55,20 @@ ACC_HD double pm_scaled_slope(double slope, double z_over_u) { return slope * z_
 // V = 19: 9 of the solver (x, x0, g, a, d, b, gl, xbest, xu) + 8 price-curve values + the two summands of the ordered
 // sums; 20 with deviation_penalty (the penalty target is then the last demand request instead of Z*).  Connection ids
 // are a separate int vector.
+// DVAL = false drops the D_r summand (the ordered sum then recomputes x_r Z*_r on the way): one vector less, which is
+// what lets two CTAs of the large solver groups (748 connections: 111 KB instead of 117 KB) share an SM.
 template <int V>
 ACC_HD int pm_slot_off(int i) { return (V % 2 == 0) ? i * V + (i >> 3) : i * V; }
-ACC_HD size_t pm_workspace_bytes(int n_max, bool separate_target) {
-    const size_t doubles = separate_target ? (size_t)n_max * 20 + (size_t)(n_max >> 3) + 1 : (size_t)n_max * 19;
+ACC_HD size_t pm_workspace_bytes(int n_max, bool separate_target, bool dval) {
+    const int v = 18 + (separate_target ? 1 : 0) + (dval ? 1 : 0);
+    const size_t doubles = (size_t)n_max * v + (v % 2 == 0 ? (size_t)(n_max >> 3) + 1 : 0);
     return doubles * sizeof(double) + (size_t)n_max * sizeof(int);
 }
 
-template <bool SEP, bool STD>
+template <bool SEP, bool STD, bool DVAL>
 struct PMWorkT {
-    enum { V = SEP ? 20 : 19, TGT = SEP ? 19 : 9, COL_X0 = 1, COL_G = 2, COL_TERM = 17, COL_DVAL = 18 };
+    enum { V = 18 + (SEP ? 1 : 0) + (DVAL ? 1 : 0), TGT = SEP ? V - 1 : 9, COL_X = 0, COL_X0 = 1, COL_G = 2, COL_ZF = 9, COL_TERM = 17, COL_DVAL = 18,
+           HAS_DVAL = DVAL ? 1 : 0 };
     template <int K>
     struct Col {
         double* base;
@@ -98,7 +102,7 @@ struct PMWorkT {
     Col<15> n_co;            // reservation price (:283-289); the kink position of the price curve D_r_min is max(0, lamX - addX)
     Col<16> slope;           // (n_bar_min - n_co) / D_r_min in the linear regime; NaN marks the cropped regime (n_co > n_bar_min)
     Col<17> term;            // per-connection summands of the current evaluation (cost term, D_r), read by the ordered sums
-    Col<18> dval;
+    Col<18> dval;            // (only with DVAL)
     int* eid;                // connection id of slot r
     ACC_HD double& at(int r, int col) const { return term.base[pm_slot_off<V>(r) + col]; }  // vector chosen at run time
     ACC_HD int& idx(int r) const { return *reinterpret_cast<int*>(&term[r]); }  // compacted position -> incoming position (set-up only)
@@ -108,7 +112,7 @@ struct PMWorkT {
         w.xu.base = p; w.zf.base = p; w.tgt.base = p;
         zf.base = p; tgt.base = p; addX.base = p; Xhatf.base = p; lamXf.base = p; c2.base = p; base.base = p; n_co.base = p;
         slope.base = p; term.base = p; dval.base = p;
-        eid = reinterpret_cast<int*>(mem + pm_workspace_bytes(n_max, SEP) - (size_t)n_max * sizeof(int));
+        eid = reinterpret_cast<int*>(mem + pm_workspace_bytes(n_max, SEP, DVAL) - (size_t)n_max * sizeof(int));
     }
 };
 
@@ -202,7 +206,7 @@ struct PMEval {
         const double D = xi * k.zf[r];
         const CurvePoint cp = curve_at<STD>(k, pp, r, D);
         k.term[r] = cp.n * D + cp.tp;
-        k.dval[r] = D;
+        if (PW::HAS_DVAL) k.dval[r] = D;
         k.w.g[r] = (k.zf[r] * (cp.gn * D + cp.n + cp.tpp)) / pp.Uf;
     }
     // costs and purchase summed strictly left to right, like the reference's loops (:203-217, :221-240)
@@ -210,7 +214,15 @@ struct PMEval {
     ACC_HD void finish(const X& x, double* F, double* c) const {
         const PW& kk = k;
         double s[2];
-        cx.template seqsum<2>(n, [&](int r, int j) { return kk.at(r, PW::COL_TERM + j); }, s);  // costs, sum of D_r
+        // summand 0: the cost term; summand 1: D_r = x_r Z*_r (x is the solver's x vector), stored or recomputed
+        if (PW::HAS_DVAL) {
+            cx.template seqsum<2>(n, [&](int r, int j) { return kk.at(r, PW::COL_TERM + j); }, s);
+        } else {
+            cx.template seqsum<2>(n, [&](int r, int j) {
+                const double a = kk.at(r, j == 0 ? PW::COL_TERM : PW::COL_X), b = kk.at(r, PW::COL_ZF);
+                return j == 0 ? a : a * b;
+            }, s);
+        }
         *F = s[0] / pp.Uf;
         *c = (desired_f - s[1]) / pp.Uf;
     }

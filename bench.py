@@ -78,6 +78,11 @@ def make_network(args, rank, part=None):
     if args.config == "eora":
         net = synth.make_config("eora")
         workload = "EORA-shaped synthetic MRIO 187x26 dense, baseline run (BASELINE.json configs[1])"
+    elif args.config == "wide":
+        # probe of the purchasing managers of the 4x network on ONE GPU: 748 regions (so 748 connections per manager, the
+        # solver group of configs[3]) but only 3 sectors, ~6.7 M connections
+        net = synth.make_network(regions=748, sectors=3, seed=20260101 + 4)
+        workload = "probe: synthetic MRIO 748x3 dense (purchasing managers shaped like those of BASELINE.json configs[3])"
     elif args.config == "eora_flood":
         net = synth.make_config("eora_flood")
         workload = "EORA-shaped synthetic MRIO 187x26 dense, regional production-loss shock (BASELINE.json configs[2])"
@@ -179,7 +184,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--config", default="eora", choices=["eora", "eora_flood", "small", "x4"])
+    ap.add_argument("--config", default="eora", choices=["eora", "eora_flood", "small", "x4", "wide"])
     ap.add_argument("--ref-steps", type=int, default=3)
     ap.add_argument("--reference-small", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
