@@ -398,8 +398,11 @@ struct StorageDelivery {  // thread per storage
 // One warp per utilitarian consumer, eight consumers per CTA: the solve is sequential code run by the warp's leader, so
 // the kernel needs residency, not width -- packed like this it takes two dozen SMs instead of one CTA slot on every SM
 // next to seller_production, which runs at the same time.
+#ifndef ACC_CONSUMER_WARPS
+#define ACC_CONSUMER_WARPS 8
+#endif
 struct ConsumerUtility {
-    enum { WARPS = 8 };
+    enum { WARPS = ACC_CONSUMER_WARPS };
     ConsumerView cv; StorageView st; ModelP mp; EventSink events; int n_max; int* fatal;
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const {
