@@ -62,7 +62,7 @@ struct ConsumerWork {
         w.n = n;
         w.x = p; p += n_max; w.x0 = p; p += n_max; w.g = p; p += n_max; w.a = p; p += n_max; w.d = p; p += n_max;
         w.gl = p; p += n_max; w.xbest = p; p += n_max; w.t1 = p; p += n_max; w.t2 = p; p += n_max; w.t3 = p; p += n_max;
-        w.B = p; p += (size_t)n_max * n_max; w.L = p; p += (size_t)n_max * n_max;
+        w.B = p; p += (size_t)n_max * n_max; w.L = p; p += (size_t)n_max * n_max; w.scal = p; p += 4;
         xl = p; p += n_max; xu = p; p += n_max; xtol = p; p += n_max;
         price = p; p += n_max; basef = p; p += n_max; share = p; p += n_max; eshare = p; p += n_max;
         chain = p; p += n_max + 4;
@@ -80,50 +80,67 @@ struct ConsumerEval {
     const ConsumerView& cv;
     int agent, n, n_in;
     double budget;
-    ACC_HD void operator()(const double* x, double* g, double* ga, double* F, double* c) {
+    // Group convention of sqp_dense.h: the pow() of every good is taken side by side (the expensive part), the sums
+    // over goods and baskets stay strictly sequential in one thread, in the reference's order.
+    template <class Par>
+    ACC_HD void operator()(Par& par, const double* x, double* g, double* ga, double* scal) {
         ConsumerWork& kk = k;
         const ConsumerView& v = cv;
         const int a = agent, nn = n, nin = n_in;
         const double B = budget;
+        double* const powsum = kk.w.t1;  // per ordered good: pow(c, e_b) * exp-share, the summand of its basket (t1 is free during an evaluation)
         // ---- autodiff_nested_CES_utility_function, :170-187 ----
-        for (int i = 0; i < nn; ++i) kk.chain[i] = 0.0;
-        double U = 0.0;
-        int q = 0;
-        while (q < nin) {
-            const int b = kk.bsk[q];
-            const double eb = v.intra_exp[b];
-            const int q0 = q;
-            double ub = 0.0;
-            for (; q < nin && kk.bsk[q] == b; ++q) {
-                const int i = kk.ord[q];
-                const double cq = x[i] * kk.share[i];
-                ub += pow(cq, eb) * kk.eshare[i];
-                kk.chain[i] = (kk.share[i] * (eb * pow(cq, eb - 1))) * kk.eshare[i];
+        par.foreach(nn, [&](int i) { kk.chain[i] = 0.0; });
+        par.foreach(nin, [&](int q) {
+            const int i = kk.ord[q];
+            const double eb = v.intra_exp[kk.bsk[q]];
+            const double cq = x[i] * kk.share[i];
+            powsum[q] = pow(cq, eb) * kk.eshare[i];
+            kk.chain[i] = (kk.share[i] * (eb * pow(cq, eb - 1))) * kk.eshare[i];
+        });
+        par.single([&] {
+            double U = 0.0;
+            int q = 0;
+            while (q < nin) {
+                const int b = kk.bsk[q];
+                const double eb = v.intra_exp[b];
+                const int q0 = q;
+                double ub = 0.0;
+                for (; q < nin && kk.bsk[q] == b; ++q) ub += powsum[q];
+                const double inv = 1 / eb;
+                const double bs = v.bshare[a * v.n_baskets + b], ebs = v.ebshare[a * v.n_baskets + b];
+                const double ub2 = pow(ub, inv) * bs;
+                const double term = pow(ub2, v.inter_exp) * ebs;
+                const double f1 = inv * pow(ub, inv - 1);
+                const double f2 = v.inter_exp * pow(ub2, v.inter_exp - 1);
+                for (int r = q0; r < q; ++r) { const int i = kk.ord[r]; kk.chain[i] = (((kk.chain[i] * f1) * bs) * f2) * ebs; }
+                U += term;
             }
-            const double inv = 1 / eb;
-            const double bs = v.bshare[a * v.n_baskets + b], ebs = v.ebshare[a * v.n_baskets + b];
-            const double ub2 = pow(ub, inv) * bs;
-            const double term = pow(ub2, v.inter_exp) * ebs;
-            const double f1 = inv * pow(ub, inv - 1);
-            const double f2 = v.inter_exp * pow(ub2, v.inter_exp - 1);
-            for (int r = q0; r < q; ++r) { const int i = kk.ord[r]; kk.chain[i] = (((kk.chain[i] * f1) * bs) * f2) * ebs; }
-            U += term;
-        }
-        const double invE = 1 / v.inter_exp;
-        const double util = pow(U, invE);
-        *F = -1.0 * util;
-        const double f3 = invE * pow(U, invE - 1);
-        for (int i = 0; i < nn; ++i) g[i] = -1.0 * (kk.chain[i] * f3);
-        // ---- equality_constraint == inequality_constraint, :204-226 (not_spent_budget is 0 here, :521) ----
-        double scaled_budget = B / B;
-        for (int i = 0; i < nn; ++i) {
-            const double price = x[i] * (kk.price[i] * ACC_PREC6);
-            const double term = (x[i] * kk.basef[i]) * price / B;
-            scaled_budget -= term;
-            ga[i] = 1.0 * term;
-        }
-        *c = 1.0 * (-scaled_budget);
+            const double invE = 1 / v.inter_exp;
+            const double util = pow(U, invE);
+            scal[0] = -1.0 * util;
+            const double f3 = invE * pow(U, invE - 1);
+            for (int i = 0; i < nn; ++i) g[i] = -1.0 * (kk.chain[i] * f3);
+            // ---- equality_constraint == inequality_constraint, :204-226 (not_spent_budget is 0 here, :521) ----
+            double scaled_budget = B / B;
+            for (int i = 0; i < nn; ++i) {
+                const double price = x[i] * (kk.price[i] * ACC_PREC6);
+                const double term = (x[i] * kk.basef[i]) * price / B;
+                scaled_budget -= term;
+                ga[i] = 1.0 * term;
+            }
+            scal[1] = 1.0 * (-scaled_budget);
+        });
     }
+};
+
+// the group of a context as sqp_dense.h's executor
+template <class Ctx>
+struct CtxPar {
+    Ctx& cx;
+    // barrier first: the threads may still be reading (redundant scalar loops) what this loop overwrites
+    template <class F> ACC_HD void foreach(int m, F f) const { cx.sync(); cx.foreach(m, f); }
+    template <class F> ACC_HD void single(F f) const { cx.single(f); }
 };
 
 // returns false when the optimiser failed outright (the reference throws, Consumer.cpp:497-502)
@@ -165,20 +182,18 @@ ACC_HD bool consumer_one(Ctx& cx, int a, const ConsumerView& cv, const StorageVi
         k.ord[i] = i < n_in ? cv.order[s0 + i] : -1;
         k.bsk[i] = i < n_in ? cv.order_basket[s0 + i] : -1;
     });
-    int* result = k.w.state + n;  // the leader's verdict for the group (read after the barrier; the solver's scratch is free then)
-    cx.single([&] {
-        ConsumerEval ev{k, cv, a, n, n_in, B};
-        accsqp::Params sp;
-        sp.n = n; sp.ctype = accsqp::CON_EQ; sp.ctol = cv.ctol; sp.maxeval = cv.maxeval; sp.max_iter = ACCSQP_MAX_ITER;
-        accsqp::Stats stt;
-        const int ret = accsqp::sqp_minimize_dense(ev, k.w, sp, stt);
-        // consumption_optimize, :455-503
+    // the whole group runs the solver (same control flow on every thread, loops shared out: sqp_dense.h)
+    ConsumerEval ev{k, cv, a, n, n_in, B};
+    accsqp::Params sp;
+    sp.n = n; sp.ctype = accsqp::CON_EQ; sp.ctol = cv.ctol; sp.maxeval = cv.maxeval; sp.max_iter = ACCSQP_MAX_ITER;
+    accsqp::Stats stt;
+    CtxPar<Ctx> par{cx};
+    const int ret = accsqp::sqp_minimize_dense(par, ev, k.w, sp, stt);
+    if (cx.leader()) {  // consumption_optimize, :455-503
         if (ret == accsqp::SQP_ROUNDOFF_LIMITED) events.push(EV_OPTIMIZER_ROUNDOFF_LIMITED, a, -1, (double)NAN);
         else if (ret == accsqp::SQP_MAXEVAL_REACHED) events.push(EV_OPTIMIZER_MAXITER, a, -1, (double)NAN);
         cv.utility[a] = -stt.minf;
-        *result = ret;
-    });
-    const int ret = *result;
+    }
     // consume_optimisation_result, :510-523: desired use = use = previous consumption = optimised consumption
     cx.foreach(n, [&](int i) {
         const int s = cv.st_list[s0 + i];

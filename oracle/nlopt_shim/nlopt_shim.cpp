@@ -148,7 +148,10 @@ struct CallbackEval {
 // the same for sqp_dense.h (gradients go to the arrays the solver names)
 struct DenseCallbackEval {
     nlopt_opt o;
-    void operator()(const double* x, double* g, double* a, double* F, double* c) {
+    // sqp_dense.h's group convention with the serial executor: F -> scal[0], c -> scal[1]
+    void operator()(accsqp::SerialPar&, const double* x, double* g, double* a, double* scal) {
+        double* F = &scal[0];
+        double* c = &scal[1];
         const unsigned n = o->n;
         const double sgn = o->maximize ? -1.0 : 1.0;
         *F = sgn * o->f(n, x, g, o->f_data);
@@ -219,12 +222,13 @@ extern "C" nlopt_result nlopt_optimize(nlopt_opt opt, double* x, double* opt_f) 
         double* r = dbuf.data();
         dw.n = n;
         dw.x = r; r += n; dw.x0 = r; r += n; dw.g = r; r += n; dw.a = r; r += n; dw.d = r; r += n; dw.gl = r; r += n; dw.xbest = r; r += n;
-        dw.t1 = r; r += n; dw.t2 = r; r += n; dw.t3 = r; r += n; dw.B = r; r += (size_t)n * n; dw.L = r;
+        dw.t1 = r; r += n; dw.t2 = r; r += n; dw.t3 = r; r += n; dw.B = r; r += (size_t)n * n; dw.L = r; r += (size_t)n * n; dw.scal = r;
         dw.state = ibuf.data();
         dw.xl = opt->lb.data(); dw.xu = opt->ub.data(); dw.xtol = opt->xtol.data();
         std::memcpy(dw.x, x, sizeof(double) * n);
         DenseCallbackEval ev{opt};
-        ret = accsqp::sqp_minimize_dense(ev, dw, p, st);
+        accsqp::SerialPar par;
+        ret = accsqp::sqp_minimize_dense(par, ev, dw, p, st);
         std::memcpy(x, dw.xbest, sizeof(double) * n);
     }
     *opt_f = opt->maximize ? -st.minf : st.minf;
