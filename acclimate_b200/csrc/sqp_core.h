@@ -183,8 +183,10 @@ SQP_HD Sum2 qp_range_term(const W& w, int i) {
 
 // `known_range`: the attainable range of a^T d at the current x when the caller has it already (the evaluation pass
 // of a per-coordinate objective computes it on the way, see sqp_eval_pass), else null.
+// `lambda_start`: where the root-find begins -- the multiplier of the previous SQP iteration (psi is piecewise linear and
+// Newton's steps exact between breakpoints, so starting next to the root saves passes; 0 for the first iteration).
 template <class Ctx, class W>
-SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, bool* d_ready, const Sum2* known_range) {
+SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, bool* d_ready, const Sum2* known_range, double lambda_start) {
     *d_ready = false;
     const bool kinked = w.kinked();
     if (ctype == CON_NONE) return 0.0;
@@ -226,7 +228,7 @@ SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, boo
     // |psi| below the rounding noise of the n-term sums it is made of (c itself is such a sum) counts as zero:
     // n * 2^-52 relative to the magnitudes involved.  A tighter test only makes Newton chase that noise.
     const double psi_tol = 2.3e-16 * (n < 2 ? 2 : n) * (fabs(c) + (fabs(smin) > fabs(smax) ? fabs(smin) : fabs(smax)));
-    double lambda = 0.0;
+    double lambda = (ctype == CON_EQ) ? lambda_start : 0.0;  // the inequality form tests psi(0) first (constraint inactive)
     double lamL = 0.0, lamR = 0.0;
     bool haveL = false, haveR = false;
     double step = 1.0;
@@ -347,6 +349,7 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
     st.minf = F;
 
     bool b_identity = true;
+    double lambda_prev = 0.0;
     double mu = 0.0;      // merit penalty parameter
     int ireset = 0;
     int ret = SQP_SUCCESS;
@@ -355,7 +358,8 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
         ++st.iters;
         if (p.max_iter > 0 && st.iters > p.max_iter) { ret = SQP_FAILURE; break; }
         bool d_ready = false;
-        const double lambda = qp_solve(cx, n, p.ctype, c, w, st, &d_ready, have_range ? &range : nullptr);
+        const double lambda = qp_solve(cx, n, p.ctype, c, w, st, &d_ready, have_range ? &range : nullptr, lambda_prev);
+        lambda_prev = lambda;
         // One pass forms the step, the Lagrangian gradient at the old point with the new multiplier (Kraft: v), saves
         // the old point and returns three sums: a.d (linearised constraint), the number of coordinates whose step
         // reaches the x tolerance, and the model's first-order change of the objective g.d (+ change of the kink terms).
