@@ -621,6 +621,30 @@ struct acc_engine {
     DBuf<int> ev_count;
     int ev_cap = 1 << 16;
 
+    // every array that changes from step to step, in the fixed order of the checkpoint blob (acc_save_state / acc_load_state)
+    template <class V>
+    void visit_state(V& v) {
+        v(a_lambda); v(nu);
+        v(f_cap_q); v(f_Xhat_q); v(f_est_q); v(f_X_q); v(f_Xexp_q); v(f_nbar); v(f_cutoff); v(f_desired_q); v(f_sumD_q); v(f_bk_sq); v(f_bk_cnt);
+        v(f_bk_pmax); v(f_bk_pmin); v(f_exp_q);
+        v(f_cap_v); v(f_Xhat_v); v(f_est_v); v(f_X_v); v(f_Xexp_v); v(f_C); v(f_R); v(f_sumD_v); v(f_bk_sv); v(f_exp_v);
+        v(pub);
+        v(s_S_q); v(s_I0_q); v(s_I1_q); v(s_Il_q); v(s_U_q); v(s_Ut_q); v(s_T_q); v(s_dlv_q); v(s_imp_q); v(s_dem_q);
+        v(s_S_v); v(s_I0_v); v(s_I1_v); v(s_Il_v); v(s_U_v); v(s_Ut_v); v(s_T_v); v(s_imp_v); v(s_dem_v); v(s_exp_costs); v(s_opt_val); v(s_tpen);
+        v(s_iters); v(s_evals);
+        v(e_D_q); v(e_D_p); v(conv_q); v(conv_v);
+        v(e_ovf_q); v(e_ovf_v); v(e_ship_q);  // empty until passage forcing is used
+        v(c_prev_q); v(c_prev_v); v(c_utility);
+        v(ev_count); v(ev_buf);
+    }
+    void ensure_forcing_state() {  // overflow per (hop, connection) exists from the first non-negative passage on
+        if (forcing_used) return;
+        e_ovf_q.alloc((size_t)nE * h_max); e_ovf_v.alloc((size_t)nE * h_max);
+        e_ovf_q.zero(stream); e_ovf_v.zero(stream);
+        if (hops_rewrite_shipment) { e_ship_q.alloc((size_t)nE); e_ship_q.zero(stream); }
+        forcing_used = true;
+    }
+
     ~acc_engine() {
 #ifndef ACC_HOST_EMU
         for (auto& c : clocks)
@@ -1426,6 +1450,26 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
         return failval;                                          \
     }
 
+// ---- state checkpoint: blob header and the visitors over acc_engine::visit_state ----
+namespace {
+struct StateHeader {
+    char magic[8];
+    int64_t n_agents, n_storages, n_edges, planes, step, reg, forcing_used, payload_bytes;
+};
+struct SizeVisitor {
+    size_t bytes = 0;
+    template <class T> void operator()(acc::DBuf<T>& b) { bytes += b.n * sizeof(T); }
+};
+struct SaveVisitor {
+    unsigned char* dst; acc::stream_t s;
+    template <class T> void operator()(acc::DBuf<T>& b) { if (b.n) { acc::d2h(dst, b.p, b.n * sizeof(T), s); dst += b.n * sizeof(T); } }
+};
+struct LoadVisitor {
+    const unsigned char* src; acc::stream_t s;
+    template <class T> void operator()(acc::DBuf<T>& b) { if (b.n) { acc::h2d(b.p, src, b.n * sizeof(T), s); src += b.n * sizeof(T); } }
+};
+}  // namespace
+
 extern "C" {
 
 const char* acc_last_error(void) { return acc::g_last_error.c_str(); }
@@ -1504,10 +1548,7 @@ int acc_set_entity_passage(acc_engine* e, const double* nu, size_t n) {
         bool any = false;
         for (size_t k = 0; k < n; ++k) any = any || nu[k] >= 0.0;
         if (!any) return 0;  // nothing forced yet: overflow stays identically zero
-        e->e_ovf_q.alloc((size_t)e->nE * e->h_max); e->e_ovf_v.alloc((size_t)e->nE * e->h_max);
-        e->e_ovf_q.zero(e->stream); e->e_ovf_v.zero(e->stream);
-        if (e->hops_rewrite_shipment) { e->e_ship_q.alloc((size_t)e->nE); e->e_ship_q.zero(e->stream); }
-        e->forcing_used = true;
+        e->ensure_forcing_state();
     }
     h2d(e->nu.p, nu, n * sizeof(double), e->stream);
     return 0;
@@ -1685,6 +1726,62 @@ int64_t acc_edge_count(const acc_engine* e) { return e ? e->nE : -1; }
 int64_t acc_step_count(const acc_engine* e) { return e ? e->step : -1; }
 int64_t acc_launch_count(const acc_engine* e) { return e ? e->launches : -1; }
 void* acc_stream(acc_engine* e) { return e ? (void*)e->stream : nullptr; }
+
+// ---- state checkpoint ----
+
+int acc_state_bytes(acc_engine* e, size_t* bytes) {
+    ACC_API_BEGIN
+    if (e == nullptr || bytes == nullptr) fail("acc_state_bytes: null argument");
+    SizeVisitor v;
+    e->visit_state(v);
+    *bytes = sizeof(StateHeader) + v.bytes;
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_save_state(acc_engine* e, void* dst, size_t cap, size_t* written) {
+    ACC_API_BEGIN
+    if (e == nullptr || dst == nullptr) fail("acc_save_state: null argument");
+    SizeVisitor sz;
+    e->visit_state(sz);
+    const size_t total = sizeof(StateHeader) + sz.bytes;
+    if (cap < total) fail("acc_save_state: buffer too small (see acc_state_bytes)");
+    acc::dev_sync(e->stream);
+    StateHeader h;
+    std::memcpy(h.magic, "ACCSTAT1", 8);
+    h.n_agents = e->nA; h.n_storages = e->nSt; h.n_edges = e->nE; h.planes = e->T; h.step = e->step; h.reg = e->reg;
+    h.forcing_used = e->forcing_used ? 1 : 0; h.payload_bytes = (int64_t)sz.bytes;
+    std::memcpy(dst, &h, sizeof h);
+    SaveVisitor v{static_cast<unsigned char*>(dst) + sizeof h, e->stream};
+    e->visit_state(v);
+    acc::dev_sync(e->stream);
+    if (written) *written = total;
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_load_state(acc_engine* e, const void* src, size_t bytes) {
+    ACC_API_BEGIN
+    if (e == nullptr || src == nullptr) fail("acc_load_state: null argument");
+    if (bytes < sizeof(StateHeader)) fail("acc_load_state: not a state blob");
+    StateHeader h;
+    std::memcpy(&h, src, sizeof h);
+    if (std::memcmp(h.magic, "ACCSTAT1", 8) != 0) fail("acc_load_state: not a state blob");
+    if (h.n_agents != e->nA || h.n_storages != e->nSt || h.n_edges != e->nE || h.planes != e->T)
+        fail("acc_load_state: the blob belongs to a different network snapshot");
+    if (h.forcing_used != 0) e->ensure_forcing_state();
+    else if (e->forcing_used) fail("acc_load_state: this engine has used passage forcing, the blob's run had not; load into a fresh engine");
+    SizeVisitor sz;
+    e->visit_state(sz);
+    if ((int64_t)sz.bytes != h.payload_bytes || bytes < sizeof h + sz.bytes) fail("acc_load_state: blob size does not match this engine");
+    acc::dev_sync(e->stream);
+    LoadVisitor v{static_cast<const unsigned char*>(src) + sizeof h, e->stream};
+    e->visit_state(v);
+    acc::dev_sync(e->stream);
+    e->step = h.step; e->reg = (int)h.reg;
+    return 0;
+    ACC_API_END(-1)
+}
 
 int acc_profile(acc_engine* e, int enable) {
     if (e == nullptr) return -1;

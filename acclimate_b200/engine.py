@@ -77,6 +77,9 @@ def load_library(path=None):
     lib.acc_stream.argtypes = [C.c_void_p]
     lib.acc_profile.argtypes = [C.c_void_p, C.c_int]
     lib.acc_kernel_times.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+    lib.acc_state_bytes.argtypes = [C.c_void_p, C.POINTER(C.c_size_t)]
+    lib.acc_save_state.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+    lib.acc_load_state.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
     return lib
 
 
@@ -194,6 +197,19 @@ class Engine:
         self._check(self.lib.acc_drain_events(self.h, buf, cap, C.byref(n)))
         m = min(cap, int(n.value))
         return [(int(buf[k].step), int(buf[k].type), int(buf[k].a), int(buf[k].b), float(buf[k].value)) for k in range(m)]
+
+    def save_state(self):
+        """Checkpoint: everything that changes from step to step as one blob (numpy uint8 array); see acc_save_state."""
+        n = C.c_size_t(0)
+        self._check(self.lib.acc_state_bytes(self.h, C.byref(n)))
+        blob = np.empty(int(n.value), dtype=np.uint8)
+        self._check(self.lib.acc_save_state(self.h, blob.ctypes.data, blob.nbytes, C.byref(n)))
+        return blob[: int(n.value)]
+
+    def load_state(self, blob):
+        """Restart from a blob of save_state(), taken from an engine created from the same snapshot."""
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        self._check(self.lib.acc_load_state(self.h, blob.ctypes.data, blob.nbytes))
 
     def read_state(self, name):
         n = C.c_size_t(0)

@@ -192,6 +192,17 @@ void* acc_stream(acc_engine* e);
 int acc_profile(acc_engine* e, int enable);
 int acc_kernel_times(acc_engine* e, const char** names, double* ms, int64_t* launches, int cap, int reset);
 
+/* ---- state checkpoint ----
+ * Replaces the reference's process-level DMTCP checkpoint (reference src/checkpointing.cpp:40-68, the request handled in
+ * the time loop at src/ModelRun.cpp:208-223): everything that changes from step to step -- storages, firms, demand
+ * requests, the conveyor planes, overflows, forcing, the consumers' previous consumption, pending events, the step
+ * counter -- as one flat little-endian blob in a caller-owned HOST buffer.  The topology is not part of it: a blob loads
+ * into an engine created from the same snapshot (sizes are checked).  acc_state_bytes tells the size the blob has NOW
+ * (it grows once when passage forcing is first used). */
+int acc_state_bytes(acc_engine* e, size_t* bytes);
+int acc_save_state(acc_engine* e, void* dst, size_t cap, size_t* written);
+int acc_load_state(acc_engine* e, const void* src, size_t bytes);
+
 const char* acc_last_error(void);
 
 #ifdef __cplusplus
