@@ -15,8 +15,9 @@
 //     for the warp-per-purchasing-manager pass.
 //
 // Kernels of one step (reference phase they implement):
-//   firm_possible_production   CapacityManager::get_possible_production_X_hat            (phase 1)
-//   seller_production          SalesManager::calc_production_X + distribute              (phase 1)
+//   seller_production          CapacityManager::get_possible_production_X_hat (one warp, while the demand book is staged),
+//                              SalesManager::calc_production_X + distribute              (phase 1)
+//   consumer_utility           Consumer::iterate_consumption_and_production, side stream (phase 1)
 //   storage_delivery           Firm/Consumer input use, Storage::calc_content_S, TransportChainLink::push_flow_Z
 //                              arrivals, Storage::push_flow_Z accumulation               (phase 1)
 //   seller_expectation         SalesManager::iterate_expectation, Firm::iterate_expectation (phase 2)
@@ -74,7 +75,13 @@ static void launch_thread(stream_t, int n, K k) { for (int i = 0; i < n; ++i) k(
 template <class K>
 static void launch_block(stream_t, int n, K k) { for (int i = 0; i < n; ++i) { HostCtx cx(K::THREADS); k(cx, i); } }
 template <class K>
-static void launch_seller(stream_t, int n, int, K k) { for (int i = 0; i < n; ++i) { HostCtx cx(K::THREADS); k(cx, i, SellerBook{nullptr, nullptr, nullptr, nullptr}); } }
+static void launch_seller(stream_t, int n, int, K k) {
+    for (int i = 0; i < n; ++i) {
+        HostCtx warp(32), cx(K::THREADS);
+        k.prepare(warp, i);
+        k(cx, i, SellerBook{nullptr, nullptr, nullptr, nullptr});
+    }
+}
 template <class K>
 static void launch_warp(stream_t, int n, size_t smem, K k) {
     std::vector<unsigned char> sm(smem + 16);
@@ -130,7 +137,17 @@ __global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) seller_kernel(K k, 
     SellerBook book{nullptr, nullptr, nullptr, nullptr};
     int e0, n;
     k.range((int)blockIdx.x, &e0, &n);
-    if (n > 0 && n <= cap) book = stage_seller_book(dyn_smem, cap, &bar, k.ev.D_q, k.ev.D_p, k.ev.tau, k.ev.domestic, e0, n);
+    // k.prepare: the seller's possible production (one input storage per lane of the second warp), computed while the
+    // copy engine brings in the book
+    const auto prepare = [&] {
+        if ((threadIdx.x >> 5) == 1) { WarpCtx warp; k.prepare(warp, (int)blockIdx.x); }
+    };
+    if (n > 0 && n <= cap) {
+        book = stage_seller_book(dyn_smem, cap, &bar, k.ev.D_q, k.ev.D_p, k.ev.tau, k.ev.domestic, e0, n, prepare);
+    } else {
+        prepare();
+        __syncthreads();
+    }
     k(cx, (int)blockIdx.x, book);
 }
 // G > 0: the CTA size is a compile-time constant (K::MAXREG_FIXED registers); G == 0: any CTA size (K::MAXREG)
@@ -234,17 +251,6 @@ struct DBuf {  // device array with its element count
 // ------------------------------------------------------------------------------------------------
 // kernels (functors over the routines of model_core.cuh / purchase_core.cuh)
 // ------------------------------------------------------------------------------------------------
-struct FirmPossibleProduction {  // thread per firm
-    FirmView fv; StorageView st; ModelP mp; const int* firm_ids;
-    ACC_HD void operator()(int k) const {
-        const int f = firm_ids[k];
-        const int s0 = fv.st_off[f];
-        const Flow cap = possible_production(st, fv.st_list + s0, fv.st_off[f + 1] - s0, mkflow(fv.Xstar_q[f], fv.Xstar_v[f]), fv.lambda[f], fv.beta[f],
-                                             fv.var_costs[f], mp.dt, false);
-        fv.cap_q[f] = cap.q; fv.cap_v[f] = cap.v;
-    }
-};
-
 struct SellerProduction {  // CTA per firm
 #ifndef ACC_SELLER_THREADS
 #define ACC_SELLER_THREADS 256
@@ -254,7 +260,16 @@ struct SellerProduction {  // CTA per firm
 #define ACC_SELLER_BOOK_BUDGET (108 * 1024)  // bytes of dynamic shared memory per CTA: two CTAs per SM
 #endif
     enum { THREADS = ACC_SELLER_THREADS, MIN_BLOCKS = ACC_SELLER_MIN_BLOCKS };
-    FirmView fv; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step; const int* firm_ids;
+    FirmView fv; EdgeView ev; StorageView st; ModelP mp; const SectorP* sectors; EventSink events; i64 step; const int* firm_ids;
+    // CapacityManager::get_possible_production_X_hat (CapacityManager.cpp:72-102) by one warp, before the sales manager's pass
+    template <class Ctx>
+    ACC_HD void prepare(Ctx& warp, int k) const {
+        const int f = firm_ids[k];
+        const int s0 = fv.st_off[f];
+        const Flow cap = possible_production(warp, st, fv.st_list + s0, fv.st_off[f + 1] - s0, mkflow(fv.Xstar_q[f], fv.Xstar_v[f]), fv.lambda[f],
+                                             fv.beta[f], fv.var_costs[f], mp.dt, false);
+        if (warp.leader()) { fv.cap_q[f] = cap.q; fv.cap_v[f] = cap.v; }
+    }
     ACC_HD void range(int k, int* e0, int* n) const {  // the seller's connections (none for a consumer)
         const int f = firm_ids[k];
         *e0 = ev.seller_off[f];
@@ -779,11 +794,7 @@ struct acc_engine {
     void stage_sell() {
         consumer_fork();
         {
-            FirmPossibleProduction k{firm_view(), storage_view(), mp, firm_ids.p};
-            timed("firm_possible_production", [&] { launch_thread(stream, nF, k); });
-        }
-        {
-            SellerProduction k{firm_view(), edge_view(), mp, sectors.p, sink(), step, firm_ids.p};
+            SellerProduction k{firm_view(), edge_view(), storage_view(), mp, sectors.p, sink(), step, firm_ids.p};
             timed("seller_production", [&] { launch_seller(stream, nF, book_cap, k); });
         }
         if (halo_send.n) {
@@ -853,9 +864,7 @@ struct acc_engine {
     void phase_cp() {
         require_single("acc_phase");
         consumer_fork();
-        FirmPossibleProduction k1{firm_view(), storage_view(), mp, firm_ids.p};
-        timed("firm_possible_production", [&] { launch_thread(stream, nF, k1); });
-        SellerProduction k2{firm_view(), edge_view(), mp, sectors.p, sink(), step, firm_ids.p};
+        SellerProduction k2{firm_view(), edge_view(), storage_view(), mp, sectors.p, sink(), step, firm_ids.p};
         timed("seller_production", [&] { launch_seller(stream, nF, book_cap, k2); });
         consumer_join();
         launch_delivery(nullptr);
@@ -1487,7 +1496,12 @@ acc_engine* acc_create_partition(const acc_network* net, const acc_params* param
         if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) fail("acc_create: no CUDA device available (this library has no CPU path)");
         ACC_CUDA(cudaSetDevice(device));
         ACC_CUDA(cudaStreamCreateWithFlags(&E->stream, cudaStreamNonBlocking));
-        ACC_CUDA(cudaStreamCreateWithFlags(&E->side, cudaStreamNonBlocking));
+        {   // the consumers' side stream outranks the main one: their few CTAs of sequential work must become resident when
+            // the first slots free up, not after the sellers' 4 862 CTAs launched beside them have drained
+            int prio_low = 0, prio_high = 0;
+            ACC_CUDA(cudaDeviceGetStreamPriorityRange(&prio_low, &prio_high));
+            ACC_CUDA(cudaStreamCreateWithPriority(&E->side, cudaStreamNonBlocking, prio_high));
+        }
         ACC_CUDA(cudaEventCreateWithFlags(&E->ev_fork, cudaEventDisableTiming));
         ACC_CUDA(cudaEventCreateWithFlags(&E->ev_join, cudaEventDisableTiming));
 #endif

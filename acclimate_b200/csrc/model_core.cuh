@@ -251,24 +251,37 @@ ACC_HD Flow possible_use(const StorageView& st, int s, double dt, bool estimate)
     return fcopy(fadd(stock_over_time(mkflow(st.S_q[s], st.S_v[s]), dt), in));
 }
 
-ACC_HD Flow possible_production(const StorageView& st, const int* list, int n_st, Flow Xstar, double lambda, double beta, i64 var_costs, double dt,
-                                bool estimate) {
-    double p_hat = lambda * beta;
-    i64 ucc = 0;
-    for (int k = 0; k < n_st; ++k) {
+// CapacityManager::get_possible_production_X_hat_intern (CapacityManager.cpp:72-102), one input storage per thread of
+// the group: the unit commodity costs are a sum of int64 Price quanta and the production ratio is a minimum, so neither
+// depends on the order in which the storages are visited -- the result is the sequential loop's, bit for bit.
+struct CapacityTerm {
+    i64 ucc;      // sum of the inputs' unit costs
+    double pmin;  // smallest possible-use ratio seen
+    static ACC_HD CapacityTerm identity() { CapacityTerm r; r.ucc = 0; r.pmin = 1e308; return r; }
+    static ACC_HD CapacityTerm combine(CapacityTerm a, CapacityTerm b) {  // a NaN ratio (0 / 0) never wins, as in `if (tmp < p_hat)`
+        CapacityTerm r; r.ucc = a.ucc + b.ucc; r.pmin = b.pmin < a.pmin ? b.pmin : a.pmin; return r;
+    }
+};
+template <class Ctx>
+ACC_HD Flow possible_production(Ctx& cx, const StorageView& st, const int* list, int n_st, Flow Xstar, double lambda, double beta, i64 var_costs,
+                                double dt, bool estimate) {
+    const CapacityTerm t = cx.template reduce<CapacityTerm>(n_st, [&](int k) {
         const int s = list[k];
         const Flow u = possible_use(st, s, dt, estimate);
+        CapacityTerm r;
         if (estimate) {  // consider_transport_in_production_costs, CapacityManager.cpp:84-86
             const Flow tf = fcopy(mkflow(st.T_q[s], st.T_v[s]));
-            ucc += pmul(flow_price(fcopy(fadd(u, tf))), st.a[s]);
+            r.ucc = pmul(flow_price(fcopy(fadd(u, tf))), st.a[s]);
         } else {
-            ucc += pmul(flow_price(u), st.a[s]);
+            r.ucc = pmul(flow_price(u), st.a[s]);
         }
-        const double tmp = ratio(u.q, st.Istar_q[s]);
-        if (tmp < p_hat) p_hat = tmp;
-    }
+        r.pmin = ratio(u.q, st.Istar_q[s]);
+        return r;
+    });
+    double p_hat = lambda * beta;
+    if (t.pmin < p_hat) p_hat = t.pmin;
     Flow result = fcopy(fmul(Xstar, p_hat));
-    if (result.q > 0) result = set_price(result, ucc + var_costs);
+    if (result.q > 0) result = set_price(result, t.ucc + var_costs);
     return result;
 }
 
@@ -524,7 +537,7 @@ ACC_HD void seller_phase2(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
     const double lambda = fv.lambda[f];
     const Flow Xstar = mkflow(fv.Xstar_q[f], fv.Xstar_v[f]);
     const int s0 = fv.st_off[f];
-    Flow est = possible_production(st, fv.st_list + s0, fv.st_off[f + 1] - s0, Xstar, lambda, fv.beta[f], fv.var_costs[f], mp.dt, true);
+    Flow est = possible_production(cx, st, fv.st_list + s0, fv.st_off[f + 1] - s0, Xstar, lambda, fv.beta[f], fv.var_costs[f], mp.dt, true);
     if (est.q > 0) est = set_price(est, pdiv(flow_price(est), 1.0 - 0.0));  // :617-620
     BookTotals tot;
     tot.sq = fv.bk_sq[f]; tot.sv = fv.bk_sv[f]; tot.cnt = fv.bk_cnt[f]; tot.pmax = fv.bk_pmax[f]; tot.pmin = fv.bk_pmin[f];

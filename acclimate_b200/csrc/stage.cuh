@@ -78,9 +78,11 @@ struct BookPart {
 };
 
 // Stage the book of the connections [e0, e0 + n) of one seller.  Called by all threads of the CTA; `bar` is one
-// mbarrier in static shared memory that this CTA uses once (phase 0).
+// mbarrier in static shared memory that this CTA uses once (phase 0).  `meanwhile()` is called by all threads after the
+// copies were issued and before anyone waits for them.
+template <class Meanwhile>
 __device__ __forceinline__ SellerBook stage_seller_book(unsigned char* smem, int cap, unsigned long long* bar, const i64* D_q, const i64* D_p,
-                                                        const unsigned char* tau, const unsigned char* dom, int e0, int n) {
+                                                        const unsigned char* tau, const unsigned char* dom, int e0, int n, Meanwhile meanwhile) {
     const size_t words = ((size_t)(cap + 2) * sizeof(i64) + 15) / 16 * 16;
     const size_t bytes = ((size_t)cap + 16 + 15) / 16 * 16;
     const BookPart<i64> q(D_q + e0, smem, n), p(D_p + e0, smem + words, n);
@@ -92,6 +94,7 @@ __device__ __forceinline__ SellerBook stage_seller_book(unsigned char* smem, int
         q.issue(bar); p.issue(bar); t.issue(bar); d.issue(bar);
     }
     q.edges(); p.edges(); t.edges(); d.edges();
+    meanwhile();
     mbar_wait(bar, 0);
     __syncthreads();
     SellerBook b;
