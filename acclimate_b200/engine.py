@@ -277,3 +277,36 @@ class Scenario:
             engine.set_agent_forcing(self.lam)
         if changed_n:
             engine.set_entity_passage(self.nu)
+
+
+class EventSeriesScenario:
+    """Per-step forcing grids streamed to the device, the rule of the reference's `event_series` scenario
+    (reference src/scenario/EventSeriesScenario.cpp:45-69): at time index t every firm (sector s, region r) gets the
+    forcing `agent_grid[t, s, r]` (NaN -> 1.0: no forcing) and every geo entity e the passage `entity_grid[t, e]`
+    (negative -> -1: none).  The reference reads the grids from NetCDF files with the dimensions (time, sector, region)
+    and (time, sea_route) (:71-77); here they are arrays -- the file layer is outside the path.  Time indices past the end
+    of a grid leave the last forcing in place, as the reference's reader does when its file ends
+    (src/scenario/ExternalScenario.cpp:83-110)."""
+
+    def __init__(self, arrays, agent_grid=None, entity_grid=None):
+        self.n_agents = int(arrays["meta"][2])
+        at = np.asarray(arrays["agent_type"])
+        self.firms = np.nonzero(at == 1)[0]
+        self.f_sector = np.asarray(arrays["agent_sector"])[self.firms].astype(np.int64)
+        self.f_region = np.asarray(arrays["agent_region"])[self.firms].astype(np.int64)
+        self.agent_grid = None if agent_grid is None else np.asarray(agent_grid, dtype=np.float64)
+        self.entity_grid = None if entity_grid is None else np.asarray(entity_grid, dtype=np.float64)
+        if self.agent_grid is not None and self.agent_grid.ndim != 3:
+            raise ValueError("agent_grid must have the dimensions (time, sector, region)")
+        if self.entity_grid is not None and self.entity_grid.ndim != 2:
+            raise ValueError("entity_grid must have the dimensions (time, geo entity)")
+        self.lam = np.ones(self.n_agents)
+
+    def apply(self, engine, step):
+        if self.agent_grid is not None and step < self.agent_grid.shape[0]:
+            v = self.agent_grid[step][self.f_sector, self.f_region]
+            self.lam[self.firms] = np.where(np.isnan(v), 1.0, v)
+            engine.set_agent_forcing(self.lam)
+        if self.entity_grid is not None and step < self.entity_grid.shape[0]:
+            v = self.entity_grid[step]
+            engine.set_entity_passage(np.ascontiguousarray(np.where(v < 0.0, -1.0, v)))
