@@ -135,19 +135,18 @@ __global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) seller_kernel(K k, 
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     BlockCtx cx(scratch);
     SellerBook book{nullptr, nullptr, nullptr, nullptr};
-    int e0, n;
-    k.range((int)blockIdx.x, &e0, &n);
-    // k.prepare: the seller's possible production (one input storage per lane of the second warp), computed while the
-    // copy engine brings in the book
-    const auto prepare = [&] {
-        if ((threadIdx.x >> 5) == 1) { WarpCtx warp; k.prepare(warp, (int)blockIdx.x); }
-    };
-    if (n > 0 && n <= cap) {
-        book = stage_seller_book(dyn_smem, cap, &bar, k.ev.D_q, k.ev.D_p, k.ev.tau, k.ev.domestic, e0, n, prepare);
-    } else {
-        prepare();
+    if (cap > 0) {
+        if (threadIdx.x == 0) mbar_init(&bar, 1);
         __syncthreads();
     }
+    // k.prepare: the seller's possible production, one input storage per lane of the second warp.  Its chain of dependent
+    // loads (firm -> storage list -> storages) starts at once and runs beside the other warps' work: the seller's range,
+    // handing the book to the copy engine and waiting for it.  The second warp joins them afterwards.
+    if ((threadIdx.x >> 5) == 1) { WarpCtx warp; k.prepare(warp, (int)blockIdx.x); }
+    int e0, n;
+    k.range((int)blockIdx.x, &e0, &n);
+    if (n > 0 && n <= cap) book = stage_seller_book(dyn_smem, cap, &bar, k.ev.D_q, k.ev.D_p, k.ev.tau, k.ev.domestic, e0, n);
+    __syncthreads();
     k(cx, (int)blockIdx.x, book);
 }
 // G > 0: the CTA size is a compile-time constant (K::MAXREG_FIXED registers); G == 0: any CTA size (K::MAXREG)

@@ -67,36 +67,33 @@ struct BookPart {
     __device__ __forceinline__ void issue(unsigned long long* bar) const {
         if (body_bytes) bulk_g2s(dst + head, src + head, body_bytes, bar);
     }
-    __device__ __forceinline__ void edges() const {  // all threads: head and tail elements
+    __device__ __forceinline__ void edges() const {  // first warp: head and tail elements (fewer than 32)
         const int body = (int)(body_bytes / sizeof(T));
-        const int rest = n - body;  // head + tail elements, < 32
-        for (int j = threadIdx.x; j < rest; j += blockDim.x) {
+        const int rest = n - body;  // head + tail elements
+        for (int j = threadIdx.x; j < rest; j += 32) {
             const int i = j < head ? j : body + j;
             dst[i] = src[i];
         }
     }
 };
 
-// Stage the book of the connections [e0, e0 + n) of one seller.  Called by all threads of the CTA; `bar` is one
-// mbarrier in static shared memory that this CTA uses once (phase 0).  `meanwhile()` is called by all threads after the
-// copies were issued and before anyone waits for them.
-template <class Meanwhile>
+// Stage the book of the connections [e0, e0 + n) of one seller.  `bar` is one mbarrier in static shared memory that this
+// CTA uses once (phase 0); the caller has initialised it (mbar_init(bar, 1) by one thread, then a CTA barrier) and puts
+// a CTA barrier behind this call.  Thread 0 hands the four arrays to the copy engine, the first warp moves the few
+// unaligned head / tail elements, every caller waits for the copies.  A warp may arrive late (it works on something else
+// first, see seller_kernel): it then only waits.
 __device__ __forceinline__ SellerBook stage_seller_book(unsigned char* smem, int cap, unsigned long long* bar, const i64* D_q, const i64* D_p,
-                                                        const unsigned char* tau, const unsigned char* dom, int e0, int n, Meanwhile meanwhile) {
+                                                        const unsigned char* tau, const unsigned char* dom, int e0, int n) {
     const size_t words = ((size_t)(cap + 2) * sizeof(i64) + 15) / 16 * 16;
     const size_t bytes = ((size_t)cap + 16 + 15) / 16 * 16;
     const BookPart<i64> q(D_q + e0, smem, n), p(D_p + e0, smem + words, n);
     const BookPart<unsigned char> t(tau + e0, smem + 2 * words, n), d(dom + e0, smem + 2 * words + bytes, n);
-    if (threadIdx.x == 0) mbar_init(bar, 1);
-    __syncthreads();
     if (threadIdx.x == 0) {
         mbar_expect_tx(bar, q.body_bytes + p.body_bytes + t.body_bytes + d.body_bytes);
         q.issue(bar); p.issue(bar); t.issue(bar); d.issue(bar);
     }
-    q.edges(); p.edges(); t.edges(); d.edges();
-    meanwhile();
+    if (threadIdx.x < 32) { q.edges(); p.edges(); t.edges(); d.edges(); }
     mbar_wait(bar, 0);
-    __syncthreads();
     SellerBook b;
     b.q = q.dst; b.p = p.dst; b.tau = t.dst; b.dom = d.dst;
     return b;
