@@ -4,11 +4,13 @@
  * (reference include/optimization.h:123-190, src/model/Consumer.cpp:422).
  * NLopt itself (github.com/stevengj/nlopt, nominal pin v2.7.0, reference
  * CMakeLists.txt:163) is a build-time download of the reference and is NOT
- * available offline, so the oracle links this shim instead.  Names, argument
- * order and result codes follow NLopt's documented API; the implementation
- * behind them is oracle/nlopt_shim/nlopt_shim.cpp.
- * PARITY AT THIS BOUNDARY IS UNPINNED: no upstream NLopt binary or source is
- * available to compare against.
+ * available offline, so the oracle links one of two providers instead:
+ *   oracle/nlopt_kraft  an INDEPENDENT from-scratch restatement of Kraft's SLSQP with NLopt's
+ *                       documented driver logic (includes nothing of the product) -- the parity anchor;
+ *   oracle/nlopt_shim   the product's own solver (csrc/sqp_core.h) behind the same entry points, so
+ *                       that everything AROUND the optimiser can be compared bit for bit.
+ * Names, argument order and result codes follow NLopt's documented API.
+ * No upstream NLopt binary or source is available to compare against.
  */
 #ifndef ORACLE_NLOPT_SHIM_H
 #define ORACLE_NLOPT_SHIM_H
@@ -102,9 +104,13 @@ nlopt_result nlopt_set_local_optimizer(nlopt_opt opt, const nlopt_opt local_opt)
 nlopt_result nlopt_set_population(nlopt_opt opt, unsigned pop);
 const char* nlopt_get_errmsg(nlopt_opt opt);
 
-/* shim-only introspection (not part of NLopt): counters of the last nlopt_optimize call */
+/* provider introspection (not part of NLopt): counters of the last nlopt_optimize call, whole-run statistics
+ * (calls, iterations, evaluations, QP / reset work, largest iteration count), the provider's name */
 int nlopt_shim_last_iterations(nlopt_opt opt);
 int nlopt_shim_last_evals(nlopt_opt opt);
+void nlopt_provider_stats(long long* out5);
+void nlopt_provider_set_group(int group);
+const char* nlopt_provider_name(void);
 
 #ifdef __cplusplus
 }

@@ -171,11 +171,12 @@ struct DenseCallbackEval {
 
 // thread-group size whose reduction order the diagonal solver replays (accsqp_group_for of the network's largest manager)
 static int g_group = ACCSQP_GROUP;
-extern "C" void nlopt_shim_set_group(int group) { g_group = group; }
+extern "C" void nlopt_provider_set_group(int group) { g_group = group; }
+extern "C" const char* nlopt_provider_name(void) { return "shim"; }
 
 // whole-run solver statistics (printed by the harness; serial builds only -- not atomic)
 long long g_stat_calls = 0, g_stat_iters = 0, g_stat_evals = 0, g_stat_qp = 0, g_stat_max_iters = 0;
-extern "C" void nlopt_shim_stats(long long* out) {
+extern "C" void nlopt_provider_stats(long long* out) {
     out[0] = g_stat_calls; out[1] = g_stat_iters; out[2] = g_stat_evals; out[3] = g_stat_qp; out[4] = g_stat_max_iters;
 }
 

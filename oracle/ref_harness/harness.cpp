@@ -42,9 +42,11 @@
 
 #include <unordered_set>
 
-#include "../../acclimate_b200/csrc/purchase_core.cuh"  // pm_kink_slopes: the one definition of the transport penalty's kink
-
-extern "C" void nlopt_shim_stats(long long* out);
+#ifndef ORACLE_NLOPT_KRAFT
+// provider "shim" only (the product's solver behind NLopt's entry points): the one definition of the transport penalty's
+// kink and the solver-group rule.  The provider "kraft" build (make kraft) includes nothing of the product.
+#include "../../acclimate_b200/csrc/purchase_core.cuh"
+#endif
 
 // index of each entry in the "model_f64" array of the network file (acclimate_b200/netfile.py)
 enum ModelParamIdx {
@@ -102,7 +104,6 @@ struct EventRec {
     double value;
 };
 static std::vector<EventRec> g_events;
-extern "C" void nlopt_shim_set_group(int group);
 static std::unordered_set<const void*> g_purchasing_managers;  // which nlopt user data are PurchasingManagers
 static std::int64_t g_step = 0;
 
@@ -328,7 +329,9 @@ class ModelInitializer {
             g_purchasing_managers.insert(st->purchasing_manager.get());
             n_max = std::max(n_max, st->purchasing_manager->business_connections.size());
         }
-        nlopt_shim_set_group(accsqp_group_for(int(n_max)));  // the engine's rule for its solver group (csrc/sqp_core.h)
+#ifndef ORACLE_NLOPT_KRAFT
+        nlopt_provider_set_group(accsqp_group_for(int(n_max)));  // the engine's rule for its solver group (csrc/sqp_core.h)
+#endif
         check_clean();
         // post_initialize, ModelInitializer.cpp:1081-1085
         for (auto& agent : model->economic_agents) agent->initialize();
@@ -358,6 +361,7 @@ class ModelInitializer {
 // The reference's callbacks hand NLopt a gradient that jumps at D_r == target (PurchasingManager.cpp:388-396,432-450).
 // The engine's solver is told where (csrc/purchase_core.cuh PMWork::W); this hook tells the shim the same, from the
 // reference's own objects and with the same formula (acc::pm_kink_slopes), so both run identical arithmetic.
+#ifndef ORACLE_NLOPT_KRAFT
 extern "C" int nlopt_shim_kinks(void* f_data, unsigned n, double* scale, double* target, double* sl, double* sr, double* mid) {
     using namespace acclimate;
     if (g_purchasing_managers.count(f_data) == 0) return 0;
@@ -382,6 +386,7 @@ extern "C" int nlopt_shim_kinks(void* f_data, unsigned n, double* scale, double*
     }
     return 1;
 }
+#endif
 
 // ---- ModelRun members (replacement for src/ModelRun.cpp) -------------------------------------------
 namespace acclimate {
@@ -602,8 +607,8 @@ int main(int argc, char** argv) {
         const double init_s = std::chrono::duration<double>(t1 - t0).count();
         if (std::getenv("ORACLE_SOLVER_STATS") != nullptr) {
             long long st[5];
-            nlopt_shim_stats(st);
-            std::fprintf(stderr, "solver: calls %lld iters %lld evals %lld qp_iters %lld max_iters %lld\n", st[0], st[1], st[2], st[3], st[4]);
+            nlopt_provider_stats(st);
+            std::fprintf(stderr, "solver %s: calls %lld iters %lld evals %lld qp_iters %lld max_iters %lld\n", nlopt_provider_name(), st[0], st[1], st[2], st[3], st[4]);
         }
         std::printf("{\"edges\": %zu, \"steps\": %d, \"threads\": %u, \"init_seconds\": %.6f, \"phase_seconds\": %.6f, \"events\": %zu}\n",
                     acclimate::g_init->edges.size(), cfg.steps, run.thread_count(), init_s, acclimate::g_phase_seconds, g_events.size());

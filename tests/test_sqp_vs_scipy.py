@@ -39,10 +39,10 @@ def shim():
     lib.nlopt_optimize.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.nlopt_shim_set_kinks.argtypes = [C.c_void_p] + [C.POINTER(C.c_double)] * 5
     lib.nlopt_shim_last_evals.argtypes = [C.c_void_p]
-    # position of NLOPT_LD_SLSQP in the enum of oracle/nlopt_shim/nlopt.h
+    # position of NLOPT_LD_SLSQP in the enum of oracle/include/nlopt.h
     names = []
     inside = False
-    for line in open(os.path.join(ROOT, "oracle", "nlopt_shim", "nlopt.h")):
+    for line in open(os.path.join(ROOT, "oracle", "include", "nlopt.h")):
         line = line.split("/*")[0].split("//")[0].strip()
         if line.startswith("typedef enum") and not names:
             inside = True
