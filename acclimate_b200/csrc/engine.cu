@@ -94,6 +94,7 @@ static void launch_block_smem(stream_t, int n, int threads, size_t smem, K k) {
 }
 template <class K>
 static void launch_warps(stream_t s, int n, size_t smem_per_warp, K k) { launch_warp(s, n, smem_per_warp, k); }
+struct DeviceGuard { explicit DeviceGuard(int) {} };
 #else
 typedef cudaStream_t stream_t;
 #define ACC_CUDA(x)                                                                                   \
@@ -114,6 +115,28 @@ static void d2h(void* h, const void* d, size_t b, stream_t s) {
 }
 static void dev_zero(void* d, size_t b, stream_t s) { if (b) ACC_CUDA(cudaMemsetAsync(d, 0, b, s)); }
 static void dev_sync(stream_t s) { ACC_CUDA(cudaStreamSynchronize(s)); }
+// Every C ABI entry makes the engine's device current for its duration (a caller may drive several engines, one per
+// device, from one thread) and puts the caller's device back afterwards.
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int device) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != device) ACC_CUDA(cudaSetDevice(device));
+        else prev = -1;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device (per-context) attribute: what has been configured is
+// remembered per device, not per process.
+static bool smem_needs_config(const void* kernel, size_t bytes) {
+    static std::map<std::pair<int, const void*>, size_t> configured;
+    int dev = 0;
+    ACC_CUDA(cudaGetDevice(&dev));
+    size_t& have = configured[std::make_pair(dev, kernel)];
+    if (bytes <= have) return false;
+    have = bytes;
+    return true;
+}
 
 template <class K>
 __global__ void __launch_bounds__(128) thread_kernel(int n, K k) {
@@ -178,11 +201,7 @@ static void launch_warps(stream_t s, int n, size_t smem_per_warp, K k) {
     if (n <= 0) return;
     smem_per_warp = (smem_per_warp + 15) / 16 * 16;
     const size_t smem = smem_per_warp * K::WARPS;
-    static size_t configured = 0;
-    if (smem > configured) {
-        ACC_CUDA(cudaFuncSetAttribute(warps_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    if (smem_needs_config((const void*)warps_kernel<K>, smem)) ACC_CUDA(cudaFuncSetAttribute(warps_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     warps_kernel<K><<<(n + K::WARPS - 1) / K::WARPS, K::WARPS * 32, smem, s>>>(k, n, (unsigned)smem_per_warp);
     ACC_CUDA(cudaGetLastError());
 }
@@ -202,22 +221,14 @@ template <class K>
 static void launch_seller(stream_t s, int n, int cap, K k) {
     if (n <= 0) return;
     const size_t smem = cap > 0 ? seller_book_bytes(cap) : 0;
-    static size_t configured = 0;
-    if (smem > configured) {
-        ACC_CUDA(cudaFuncSetAttribute(seller_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    if (smem_needs_config((const void*)seller_kernel<K>, smem)) ACC_CUDA(cudaFuncSetAttribute(seller_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     seller_kernel<K><<<n, K::THREADS, smem, s>>>(k, cap);
     ACC_CUDA(cudaGetLastError());
 }
 template <class K>
 static void launch_warp(stream_t s, int n, size_t smem, K k) {
     if (n <= 0) return;
-    static size_t configured = 0;
-    if (smem > configured) {
-        ACC_CUDA(cudaFuncSetAttribute(warp_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    if (smem_needs_config((const void*)warp_kernel<K>, smem)) ACC_CUDA(cudaFuncSetAttribute(warp_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     warp_kernel<K><<<n, 32, smem, s>>>(k);
     ACC_CUDA(cudaGetLastError());
 }
@@ -225,11 +236,9 @@ template <int G, class K>
 static void launch_block_smem(stream_t s, int n, int threads, size_t smem, K k) {
     if (n <= 0) return;
     if (G > 0 && threads != G) fail("launch_block_smem: CTA size does not match the compiled group size");
-    static size_t configured = 0;
-    if (smem > configured) {
+    if (smem_needs_config((const void*)block_smem_kernel<K, G>, smem)) {
         ACC_CUDA(cudaFuncSetAttribute(block_smem_kernel<K, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         ACC_CUDA(cudaFuncSetAttribute(block_smem_kernel<K, G>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        configured = smem;
     }
     block_smem_kernel<K, G><<<n, threads, smem, s>>>(k);
     ACC_CUDA(cudaGetLastError());
@@ -391,8 +400,10 @@ struct StorageDelivery {  // thread per storage
                         }
                         const Flow ovf = fcopy(fsub(total, o));
                         ev.ovf_q[oslot] = ovf.q; ev.ovf_v[oslot] = ovf.v;
-                        if (h + 1 < h1) { ev.conv_q[slot] = o.q; ev.conv_v[slot] = o.v; }
-                        else out = o;
+                        // what passes goes back into the slot: for the next hop, or -- last hop -- as the connection's last delivery
+                        // (the arrival slot is dead until its plane comes round again; read by the output surface)
+                        ev.conv_q[slot] = o.q; ev.conv_v[slot] = o.v;
+                        if (h + 1 == h1) out = o;
                     }
                 }
                 if (FORCED && ev.ship_q != nullptr) ev.ship_q[e] = ship.q;
@@ -500,6 +511,54 @@ struct FirmIncomingDemand {  // CTA per firm: sum of the demand requests it hold
     }
 };
 
+// Per-connection observables of the output surface (thread per connection), all derived from the conveyor:
+//   last shipment   BusinessConnection::last_shipment_Z   plane (t + delay) mod T, t = step of the last production pass
+//   last delivery   BusinessConnection::last_delivery_Z   plane t mod T (what arrived during step t stays there until the
+//                                                         plane comes round again; a forced chain's last hop writes what
+//                                                         it released back into that slot)
+//   in transit      BusinessConnection::get_transport_flow (src/model/BusinessConnection.cpp:162-171): the delay slots
+//                   still under way, planes t+1 .. t+delay, plus the overflow of every hop
+//   flow deficit    get_flow_deficit (:146-155) = Z* (delay + 1) - delivered - in transit
+// idx == nullptr: connections 0..n-1, else the selected ones.  Null outputs are skipped.
+struct EdgeObservables {
+    EdgeView ev; i64 t; const i64* idx;
+    i64* ship_q; double* ship_v; i64* dlv_q; double* dlv_v; i64* tr_q; double* tr_v; i64* def_q;
+    ACC_HD void operator()(int k) const {
+        const i64 e = idx != nullptr ? idx[k] : (i64)k;
+        const int T = ev.T, tau = ev.tau[e];
+        const int p0 = (int)(t % T);
+        if (ship_q != nullptr || ship_v != nullptr) {
+            int pl = p0 + tau;
+            if (pl >= T) pl -= T;
+            const i64 at = (i64)pl * ev.n_edges + e;
+            if (ship_q != nullptr) ship_q[k] = ev.ship_q != nullptr ? ev.ship_q[e] : ev.conv_q[at];
+            if (ship_v != nullptr) ship_v[k] = ev.conv_v[at];
+        }
+        if (dlv_q != nullptr || dlv_v != nullptr) {
+            const i64 at = (i64)p0 * ev.n_edges + e;
+            if (dlv_q != nullptr) dlv_q[k] = ev.conv_q[at];
+            if (dlv_v != nullptr) dlv_v[k] = ev.conv_v[at];
+        }
+        if (tr_q != nullptr || tr_v != nullptr || def_q != nullptr) {
+            Flow sum = mkflow(0, 0.0);
+            for (int j = 1; j <= tau; ++j) {
+                int pl = p0 + j;
+                if (pl >= T) pl -= T;
+                const i64 at = (i64)pl * ev.n_edges + e;
+                sum = fadd(sum, mkflow(ev.conv_q[at], ev.conv_v[at]));
+            }
+            if (ev.ovf_q != nullptr && ev.route[e] >= 0) {
+                const int nh = ev.route_off[ev.route[e] + 1] - ev.route_off[ev.route[e]];
+                for (int h = 0; h < nh; ++h) sum = fadd(sum, mkflow(ev.ovf_q[(i64)h * ev.n_edges + e], ev.ovf_v[(i64)h * ev.n_edges + e]));
+            }
+            sum = fcopy(sum);
+            if (tr_q != nullptr) tr_q[k] = sum.q;
+            if (tr_v != nullptr) tr_v[k] = sum.v;
+            if (def_q != nullptr) def_q[k] = ev.Z_q[e] * (tau + 1) - ev.conv_q[(i64)p0 * ev.n_edges + e] - sum.q;
+        }
+    }
+};
+
 // ---- exchange of a region-partitioned run (thread per halo entry / per agent) ----
 ACC_HD i64 f64_bits(double v) { i64 b; memcpy(&b, &v, sizeof b); return b; }
 ACC_HD double bits_f64(i64 b) { double v; memcpy(&v, &b, sizeof v); return v; }
@@ -573,6 +632,7 @@ struct acc_engine {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 #endif
     i64 step = 0;
+    i64 ship_step = -1;  // step of the last production / distribution pass (its shipments sit on plane (ship_step + tau) mod T)
     i64 launches = 0;
     bool profile = false;
     std::vector<KernelClock> clocks;
@@ -795,6 +855,7 @@ struct acc_engine {
         {
             SellerProduction k{firm_view(), edge_view(), storage_view(), mp, sectors.p, sink(), step, firm_ids.p};
             timed("seller_production", [&] { launch_seller(stream, nF, book_cap, k); });
+            ship_step = step;
         }
         if (halo_send.n) {
             PackFlow k{edge_view(), (int)(step % T), halo_send.p, x_flow_send};
@@ -865,6 +926,7 @@ struct acc_engine {
         consumer_fork();
         SellerProduction k2{firm_view(), edge_view(), storage_view(), mp, sectors.p, sink(), step, firm_ids.p};
         timed("seller_production", [&] { launch_seller(stream, nF, book_cap, k2); });
+        ship_step = step;
         consumer_join();
         launch_delivery(nullptr);
     }
@@ -1045,7 +1107,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
             if (d > 254) fail("transport delay out of range (0..254 steps)");
             tau[e] = (unsigned char)d; route[e] = (int)r;
             if (h1 - h0 > E.h_max) E.h_max = h1 - h0;
-            if (ent_delay[route_ent[h0]] == 0 && d > 0) E.hops_rewrite_shipment = true;
+            if (ent_delay[route_ent[h0]] == 0) E.hops_rewrite_shipment = true;  // a hop may rewrite the slot the shipment sits on
         }
         if (tau[e] > Tmax) Tmax = tau[e];
     }
@@ -1316,25 +1378,41 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
     // connections (file order)
     if (name == "edge_D_q") return I(E.e_D_q);
     if (name == "edge_D_p") return I(E.e_D_p);
-    if (name == "edge_ship_q" || name == "edge_ship_v") {
-        // last shipment of the last completed step t = step-1 sits on plane (t + tau) mod T
-        const bool q = name == "edge_ship_q";
-        const i64 t = E.step - 1;
-        if (q) out.i.assign(E.nE, 0); else out.f.assign(E.nE, 0.0);
+    if (name == "edge_ship_q" || name == "edge_ship_v" || name == "edge_deliv_q" || name == "edge_deliv_v" || name == "edge_transit_q" ||
+        name == "edge_transit_v" || name == "edge_deficit_q") {
+        // derived from the conveyor by a gather kernel (EdgeObservables).  t = step of the last production pass, whether or
+        // not the step has been ticked since (the reference's output sweep runs before Model::tick, src/ModelRun.cpp:198-226).
+        // Before the first step everything is Z*.
+        const bool q = name.back() == 'q';
         out.is_f64 = !q;
+        const i64 t = E.ship_step;
         if (t < 0) {
             std::vector<i64> z = E.e_Z_q.download(s);
-            for (i64 e = 0; e < E.nE; ++e) { if (q) out.i[e] = z[e]; else out.f[e] = flow_qp(z[e], mkp(1.0)).v; }
+            if (q) out.i.assign(E.nE, 0); else out.f.assign(E.nE, 0.0);
+            const bool transit = name.find("transit") != std::string::npos;
+            for (i64 e = 0; e < E.nE; ++e) {
+                const Flow one = flow_qp(z[e], mkp(1.0));
+                Flow f = one;
+                if (transit) { f = mkflow(0, 0.0); for (int k = 0; k < E.h_tau[e]; ++k) f = fadd(f, one); }
+                if (name == "edge_deficit_q") out.i[e] = 0;
+                else if (q) out.i[e] = f.q; else out.f[e] = f.v;
+            }
             return true;
         }
-        if (q && E.e_ship_q.n) { out.i = E.e_ship_q.download(s); return true; }  // kept apart: hops may rewrite the conveyor slot
-        if (!q && E.e_ship_q.n) return false;  // the value of a rewritten shipment is not kept
-        std::vector<i64> hq = q ? E.conv_q.download(s) : std::vector<i64>();
-        std::vector<double> hv = q ? std::vector<double>() : E.conv_v.download(s);
-        for (i64 e = 0; e < E.nE; ++e) {
-            const i64 pl = (t + E.h_tau[e]) % E.T;
-            if (q) out.i[e] = hq[pl * E.nE + e]; else out.f[e] = hv[pl * E.nE + e];
-        }
+        if (name == "edge_ship_v" && E.e_ship_q.n) return false;  // the value of a shipment whose slot a hop rewrote is not kept
+        DBuf<i64> bq; DBuf<double> bv;
+        if (q) bq.alloc(E.nE); else bv.alloc(E.nE);
+        EdgeObservables k{E.edge_view(), t, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+        if (name == "edge_ship_q") k.ship_q = bq.p;
+        else if (name == "edge_ship_v") k.ship_v = bv.p;
+        else if (name == "edge_deliv_q") k.dlv_q = bq.p;
+        else if (name == "edge_deliv_v") k.dlv_v = bv.p;
+        else if (name == "edge_transit_q") k.tr_q = bq.p;
+        else if (name == "edge_transit_v") k.tr_v = bv.p;
+        else k.def_q = bq.p;
+        E.timed("edge_observables", [&] { launch_thread(s, (int)E.nE, k); });
+        if (q) out.i = bq.download(s); else out.f = bv.download(s);
+        bq.free(); bv.free();
         return true;
     }
     // storages (creation order)
@@ -1417,6 +1495,21 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
             if (E.h_agent_type[a] == 1) { out.i[E.h_agent_sector[a]] += q[a]; out.f[E.h_agent_sector[a]] += v[a]; }
         return true;
     }
+    if (name == "sector_demand_q" || name == "sector_demand_v") {
+        // Sector::total_demand_D (src/model/Sector.cpp:36-39): every demand request of the step, by the SELLER's sector
+        DBuf<i64> q; DBuf<double> v;
+        q.alloc(E.nA); v.alloc(E.nA); q.zero(s); v.zero(s);
+        FirmIncomingDemand k{E.edge_view(), E.firm_ids.p, q.p, v.p};
+        E.timed("firm_incoming_demand", [&] { launch_block(s, E.nF, k); });
+        const std::vector<i64> hq = q.download(s);
+        const std::vector<double> hv = v.download(s);
+        q.free(); v.free();
+        out.is_f64 = name == "sector_demand_v";
+        out.i.assign(E.nS, 0); out.f.assign(E.nS, 0.0);
+        for (int a = 0; a < E.nA; ++a)
+            if (E.h_agent_type[a] == 1) { out.i[E.h_agent_sector[a]] += hq[a]; out.f[E.h_agent_sector[a]] += hv[a]; }
+        return true;
+    }
     if (name == "region_export_q" || name == "region_export_v" || name == "region_import_q" || name == "region_import_v" || name == "region_consumption_q"
         || name == "region_consumption_v" || name == "region_gdp_v" || name == "region_gdp_q") {
         std::vector<i64> xq = E.f_exp_q.download(s), iq = E.s_imp_q.download(s), uq = E.s_U_q.download(s);
@@ -1447,6 +1540,7 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
 // C ABI
 // ------------------------------------------------------------------------------------------------
 #define ACC_API_BEGIN try {
+#define ACC_ON_DEVICE(e) acc::DeviceGuard device_guard__((e)->device)
 #define ACC_API_END(failval)                                     \
     }                                                            \
     catch (const acc::EngineError& ex) {                         \
@@ -1462,7 +1556,7 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
 namespace {
 struct StateHeader {
     char magic[8];
-    int64_t n_agents, n_storages, n_edges, planes, step, reg, forcing_used, payload_bytes;
+    int64_t n_agents, n_storages, n_edges, planes, step, reg, forcing_used, payload_bytes, ship_step, event_capacity;
 };
 struct SizeVisitor {
     size_t bytes = 0;
@@ -1493,7 +1587,10 @@ acc_engine* acc_create_partition(const acc_network* net, const acc_params* param
 #ifndef ACC_HOST_EMU
         int count = 0;
         if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) fail("acc_create: no CUDA device available (this library has no CPU path)");
-        ACC_CUDA(cudaSetDevice(device));
+        if (device < 0 || device >= count) fail("acc_create: no such CUDA device");
+#endif
+        acc::DeviceGuard device_guard__(device);
+#ifndef ACC_HOST_EMU
         ACC_CUDA(cudaStreamCreateWithFlags(&E->stream, cudaStreamNonBlocking));
         {   // the consumers' side stream outranks the main one: their few CTAs of sequential work must become resident when
             // the first slots free up, not after the sellers' 4 862 CTAs launched beside them have drained
@@ -1517,8 +1614,9 @@ acc_engine* acc_create_partition(const acc_network* net, const acc_params* param
 
 void acc_destroy(acc_engine* e) {
     if (e == nullptr) return;
+    acc::DeviceGuard* guard = nullptr;
+    try { guard = new acc::DeviceGuard(e->device); } catch (...) {}
 #ifndef ACC_HOST_EMU
-    cudaSetDevice(e->device);
     cudaStreamSynchronize(e->stream);
 #endif
     // DBuf members are plain handles: release them explicitly
@@ -1542,11 +1640,13 @@ void acc_destroy(acc_engine* e) {
     for (DBuf<double>* b : {&e->c_share, &e->c_eshare, &e->c_prev_v, &e->c_budget, &e->c_bshare, &e->c_ebshare, &e->c_utility, &e->c_intra_exp}) b->free();
     e->c_base_q.free(); e->c_prev_q.free();
     delete e;
+    delete guard;
 }
 
 int acc_set_agent_forcing(acc_engine* e, const double* lambda, size_t n) {
     ACC_API_BEGIN
     if (e == nullptr || lambda == nullptr) fail("acc_set_agent_forcing: null argument");
+    ACC_ON_DEVICE(e);
     if (n != (size_t)e->nA) fail("acc_set_agent_forcing: expected one entry per agent");
     h2d(e->a_lambda.p, lambda, n * sizeof(double), e->stream);
     return 0;
@@ -1556,6 +1656,7 @@ int acc_set_agent_forcing(acc_engine* e, const double* lambda, size_t n) {
 int acc_set_entity_passage(acc_engine* e, const double* nu, size_t n) {
     ACC_API_BEGIN
     if (e == nullptr || nu == nullptr) fail("acc_set_entity_passage: null argument");
+    ACC_ON_DEVICE(e);
     if (n != (size_t)e->nEnt) fail("acc_set_entity_passage: expected one entry per geo entity (per region pair for a snapshot without routes)");
     if (!e->forcing_used) {
         bool any = false;
@@ -1571,6 +1672,7 @@ int acc_set_entity_passage(acc_engine* e, const double* nu, size_t n) {
 int acc_phase(acc_engine* e, int phase) {
     ACC_API_BEGIN
     if (e == nullptr) fail("acc_phase: null engine");
+    ACC_ON_DEVICE(e);
     switch (phase) {
         case ACC_PHASE_CONSUMPTION_AND_PRODUCTION: e->phase_cp(); break;
         case ACC_PHASE_EXPECTATION: e->phase_exp(); break;
@@ -1586,6 +1688,7 @@ int acc_set_halo(acc_engine* e, const int64_t* send_edges, size_t n_send, const 
                  void* demand_send, void* demand_recv, void* seller_table) {
     ACC_API_BEGIN
     if (e == nullptr) fail("acc_set_halo: null engine");
+    ACC_ON_DEVICE(e);
     if (!e->partitioned) fail("acc_set_halo: the engine was not created with acc_create_partition");
     if ((n_send && (send_edges == nullptr || flow_send == nullptr || demand_recv == nullptr)) ||
         (n_recv && (recv_edges == nullptr || flow_recv == nullptr || demand_send == nullptr)) || seller_table == nullptr)
@@ -1606,6 +1709,7 @@ int acc_set_halo(acc_engine* e, const int64_t* send_edges, size_t n_send, const 
 int acc_stage(acc_engine* e, int stage) {
     ACC_API_BEGIN
     if (e == nullptr) fail("acc_stage: null engine");
+    ACC_ON_DEVICE(e);
     if (e->partitioned && e->x_sellers == nullptr) fail("acc_stage: call acc_set_halo first");
     switch (stage) {
         case ACC_STAGE_SELL: e->stage_sell(); break;
@@ -1621,6 +1725,7 @@ int acc_stage(acc_engine* e, int stage) {
 int acc_step(acc_engine* e) {
     ACC_API_BEGIN
     if (e == nullptr) fail("acc_step: null engine");
+    ACC_ON_DEVICE(e);
     e->require_single("acc_step");
     e->phase_cp();
     e->phase_exp();
@@ -1633,6 +1738,7 @@ int acc_step(acc_engine* e) {
 int acc_sync(acc_engine* e) {
     ACC_API_BEGIN
     if (e == nullptr) fail("acc_sync: null engine");
+    ACC_ON_DEVICE(e);
     dev_sync(e->stream);
     if (e->mp.utilitarian) {
         int flag = 0;
@@ -1647,8 +1753,10 @@ int acc_sync(acc_engine* e) {
 int acc_drain_events(acc_engine* e, acc_event* buf, size_t cap, size_t* n) {
     ACC_API_BEGIN
     if (e == nullptr || n == nullptr) fail("acc_drain_events: null argument");
+    ACC_ON_DEVICE(e);
     int count = 0;
     d2h(&count, e->ev_count.p, sizeof(int), e->stream);
+    const int raised = count;
     if (count > e->ev_cap) count = e->ev_cap;
     std::vector<Event> h((size_t)count);
     d2h(h.data(), e->ev_buf.p, (size_t)count * sizeof(Event), e->stream);
@@ -1659,11 +1767,32 @@ int acc_drain_events(acc_engine* e, acc_event* buf, size_t cap, size_t* n) {
         if (x.a != y.a) return x.a < y.a;
         return x.b < y.b;
     });
-    const size_t m = std::min(cap, h.size());
-    for (size_t k = 0; k < m && buf != nullptr; ++k) { buf[k].step = h[k].step; buf[k].type = h[k].type; buf[k].a = h[k].a; buf[k].b = h[k].b; buf[k].value = h[k].value; }
     *n = h.size();
-    e->ev_count.zero(e->stream);
+    if (buf == nullptr && cap == 0 && raised <= e->ev_cap) return 0;  // a count query: nothing is taken
+    const size_t m = buf != nullptr ? std::min(cap, h.size()) : 0;
+    for (size_t k = 0; k < m; ++k) { buf[k].step = h[k].step; buf[k].type = h[k].type; buf[k].a = h[k].a; buf[k].b = h[k].b; buf[k].value = h[k].value; }
+    // what did not fit the caller's buffer stays pending (sorted, at the front of the device buffer)
+    const int rest = (int)(h.size() - m);
+    if (rest > 0 && m > 0) h2d(e->ev_buf.p, h.data() + m, (size_t)rest * sizeof(Event), e->stream);
+    h2d(e->ev_count.p, &rest, sizeof(int), e->stream);
     dev_sync(e->stream);
+    if (raised > e->ev_cap)
+        fail("acc_drain_events: " + std::to_string(raised - e->ev_cap) + " events were dropped: more than " + std::to_string(e->ev_cap) +
+             " were raised between two drains (drain every step, or raise the capacity with acc_set_event_capacity)");
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_set_event_capacity(acc_engine* e, size_t capacity) {
+    ACC_API_BEGIN
+    if (e == nullptr) fail("acc_set_event_capacity: null engine");
+    ACC_ON_DEVICE(e);
+    if (capacity < 1 || capacity > ((size_t)1 << 28)) fail("acc_set_event_capacity: capacity out of range");
+    int count = 0;
+    d2h(&count, e->ev_count.p, sizeof(int), e->stream);
+    if (count != 0) fail("acc_set_event_capacity: drain the pending events first");
+    e->ev_cap = (int)capacity;
+    e->ev_buf.alloc(capacity);
     return 0;
     ACC_API_END(-1)
 }
@@ -1671,6 +1800,7 @@ int acc_drain_events(acc_engine* e, acc_event* buf, size_t cap, size_t* n) {
 int acc_read_state(acc_engine* e, const char* name, void* dst, size_t cap_bytes, size_t* n, int* is_f64) {
     ACC_API_BEGIN
     if (e == nullptr || name == nullptr || n == nullptr) fail("acc_read_state: null argument");
+    ACC_ON_DEVICE(e);
     StateArray a;
     if (!read_state(*e, name, a)) fail(std::string("acc_read_state: unknown array '") + name + "'");
     const size_t cnt = a.is_f64 ? a.f.size() : a.i.size();
@@ -1687,6 +1817,7 @@ int acc_read_state(acc_engine* e, const char* name, void* dst, size_t cap_bytes,
 int acc_read(acc_engine* e, const char* group, const char* variable, double* dst, size_t cap, size_t* n) {
     ACC_API_BEGIN
     if (e == nullptr || group == nullptr || variable == nullptr || n == nullptr) fail("acc_read: null argument");
+    ACC_ON_DEVICE(e);
     // observable name -> (state array, kind): kind 'q' quantity (x 1e-3), 'p' price (x 1e-6), 'v' value / plain
     struct Map { const char* group; const char* var; const char* state; char kind; };
     static const Map maps[] = {
@@ -1729,6 +1860,7 @@ int acc_solver_group(const acc_engine* e) { return e ? e->pm_group : -1; }
 int acc_set_solver_group(acc_engine* e, int group) {
     ACC_API_BEGIN
     if (e == nullptr) fail("acc_set_solver_group: null engine");
+    ACC_ON_DEVICE(e);
     if (group < 32 || group > 512 || group % 32 != 0) fail("acc_set_solver_group: the group must be a multiple of 32 in 32..512");
     if (e->step != 0) fail("acc_set_solver_group: only before the first step");
     e->pm_group = group;
@@ -1745,6 +1877,7 @@ void* acc_stream(acc_engine* e) { return e ? (void*)e->stream : nullptr; }
 int acc_state_bytes(acc_engine* e, size_t* bytes) {
     ACC_API_BEGIN
     if (e == nullptr || bytes == nullptr) fail("acc_state_bytes: null argument");
+    ACC_ON_DEVICE(e);
     SizeVisitor v;
     e->visit_state(v);
     *bytes = sizeof(StateHeader) + v.bytes;
@@ -1755,15 +1888,16 @@ int acc_state_bytes(acc_engine* e, size_t* bytes) {
 int acc_save_state(acc_engine* e, void* dst, size_t cap, size_t* written) {
     ACC_API_BEGIN
     if (e == nullptr || dst == nullptr) fail("acc_save_state: null argument");
+    ACC_ON_DEVICE(e);
     SizeVisitor sz;
     e->visit_state(sz);
     const size_t total = sizeof(StateHeader) + sz.bytes;
     if (cap < total) fail("acc_save_state: buffer too small (see acc_state_bytes)");
     acc::dev_sync(e->stream);
     StateHeader h;
-    std::memcpy(h.magic, "ACCSTAT1", 8);
+    std::memcpy(h.magic, "ACCSTAT2", 8);
     h.n_agents = e->nA; h.n_storages = e->nSt; h.n_edges = e->nE; h.planes = e->T; h.step = e->step; h.reg = e->reg;
-    h.forcing_used = e->forcing_used ? 1 : 0; h.payload_bytes = (int64_t)sz.bytes;
+    h.forcing_used = e->forcing_used ? 1 : 0; h.payload_bytes = (int64_t)sz.bytes; h.ship_step = e->ship_step; h.event_capacity = e->ev_cap;
     std::memcpy(dst, &h, sizeof h);
     SaveVisitor v{static_cast<unsigned char*>(dst) + sizeof h, e->stream};
     e->visit_state(v);
@@ -1776,12 +1910,14 @@ int acc_save_state(acc_engine* e, void* dst, size_t cap, size_t* written) {
 int acc_load_state(acc_engine* e, const void* src, size_t bytes) {
     ACC_API_BEGIN
     if (e == nullptr || src == nullptr) fail("acc_load_state: null argument");
+    ACC_ON_DEVICE(e);
     if (bytes < sizeof(StateHeader)) fail("acc_load_state: not a state blob");
     StateHeader h;
     std::memcpy(&h, src, sizeof h);
-    if (std::memcmp(h.magic, "ACCSTAT1", 8) != 0) fail("acc_load_state: not a state blob");
+    if (std::memcmp(h.magic, "ACCSTAT2", 8) != 0) fail("acc_load_state: not a state blob");
     if (h.n_agents != e->nA || h.n_storages != e->nSt || h.n_edges != e->nE || h.planes != e->T)
         fail("acc_load_state: the blob belongs to a different network snapshot");
+    if (h.event_capacity != e->ev_cap) fail("acc_load_state: the blob was saved with another event capacity (acc_set_event_capacity)");
     if (h.forcing_used != 0) e->ensure_forcing_state();
     else if (e->forcing_used) fail("acc_load_state: this engine has used passage forcing, the blob's run had not; load into a fresh engine");
     SizeVisitor sz;
@@ -1791,7 +1927,7 @@ int acc_load_state(acc_engine* e, const void* src, size_t bytes) {
     LoadVisitor v{static_cast<const unsigned char*>(src) + sizeof h, e->stream};
     e->visit_state(v);
     acc::dev_sync(e->stream);
-    e->step = h.step; e->reg = (int)h.reg;
+    e->step = h.step; e->reg = (int)h.reg; e->ship_step = h.ship_step;
     return 0;
     ACC_API_END(-1)
 }
@@ -1805,6 +1941,7 @@ int acc_profile(acc_engine* e, int enable) {
 int acc_kernel_times(acc_engine* e, const char** names, double* ms, int64_t* launches, int cap, int reset) {
     ACC_API_BEGIN
     if (e == nullptr) fail("acc_kernel_times: null engine");
+    ACC_ON_DEVICE(e);
     e->collect_clocks();
     const int cnt = (int)e->clocks.size();
     for (int k = 0; k < cnt && k < cap; ++k) {

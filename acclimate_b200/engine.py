@@ -68,6 +68,7 @@ def load_library(path=None):
     lib.acc_phase.argtypes = [C.c_void_p, C.c_int]
     lib.acc_sync.argtypes = [C.c_void_p]
     lib.acc_drain_events.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+    lib.acc_set_event_capacity.argtypes = [C.c_void_p, C.c_size_t]
     lib.acc_read.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
     lib.acc_read_state.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_int)]
     for name in ("acc_edge_count", "acc_step_count", "acc_launch_count"):
@@ -185,18 +186,24 @@ class Engine:
     def stream(self):
         return self.lib.acc_stream(self.h)
 
-    def drain_events(self):
+    def pending_events(self):
+        """Number of events raised since the last drain (nothing is taken)."""
         n = C.c_size_t(0)
         self._check(self.lib.acc_drain_events(self.h, None, 0, C.byref(n)))
-        # the first call already cleared the device buffer only if n == 0; re-read with a buffer otherwise
         return int(n.value)
 
-    def events(self, cap=1 << 16):
+    def events(self):
+        """Takes all pending events: (step, type, a, b, value), ordered by step, type and indices.  Raises when the engine's
+        event buffer overflowed since the last drain (drain every step, or set_event_capacity)."""
+        cap = max(self.pending_events(), 1)
         buf = (_Event * cap)()
         n = C.c_size_t(0)
         self._check(self.lib.acc_drain_events(self.h, buf, cap, C.byref(n)))
         m = min(cap, int(n.value))
         return [(int(buf[k].step), int(buf[k].type), int(buf[k].a), int(buf[k].b), float(buf[k].value)) for k in range(m)]
+
+    def set_event_capacity(self, capacity):
+        self._check(self.lib.acc_set_event_capacity(self.h, int(capacity)))
 
     def save_state(self):
         """Checkpoint: everything that changes from step to step as one blob (numpy uint8 array); see acc_save_state."""

@@ -39,13 +39,13 @@ class ModelRun:
         self.duration_ms.append(1e3 * (time.perf_counter() - t0))
         for o in self.outputs:                            # outputs->iterate()
             self.series[o].append(e.read(*o))
+        self.events += e.events()                         # ModelRun::event: drained every step (the device buffer is bounded)
         e.phase(PHASE_TICK)                               # model->tick(); ++time
         self.time += 1
 
     def run(self, steps):
         for _ in range(steps):
             self.step()
-        self.events = self.engine.events()
         return {o: np.stack(v) for o, v in self.series.items()}
 
     def close(self):

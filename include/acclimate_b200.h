@@ -166,8 +166,12 @@ int acc_phase(acc_engine* e, int phase);
 /* block until the device has finished all queued phases */
 int acc_sync(acc_engine* e);
 
-/* replaces ModelRun::event (src/ModelRun.cpp:255-275): copies up to cap pending events and clears them */
+/* replaces ModelRun::event (src/ModelRun.cpp:255-275): *n receives the number of pending events; up to cap of them
+ * (ordered by step, type, indices) are copied to buf and removed, the rest stays pending.  buf == NULL with cap == 0
+ * only counts.  The engine buffers 65 536 events between two drains (acc_set_event_capacity changes that): when more
+ * were raised the call delivers what it has and then FAILS, naming the number of events that were dropped. */
 int acc_drain_events(acc_engine* e, acc_event* buf, size_t cap, size_t* n);
+int acc_set_event_capacity(acc_engine* e, size_t capacity);
 
 /* Observable pull, replaces the observe<>() visitor sweep of ArrayOutput::iterate
  * (src/output/ArrayOutput.cpp:479-646): gathers one variable of one group ("firms", "consumers",
