@@ -1932,6 +1932,73 @@ int acc_load_state(acc_engine* e, const void* src, size_t bytes) {
     ACC_API_END(-1)
 }
 
+// ---- acc_firm_incoming_demand_static: the firms' incoming demand without any device allocation ----
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops).  The per-firm sums that acc_read("firms", "incoming_demand_*") puts into
+// freshly allocated device buffers go into a file-scope device array instead.  Every GPU that loads the library holds
+// the array (ACC_STATIC_SCRATCH_AGENTS x 16 bytes = 1 MiB) until the process exits.  All calls share it and it keeps the
+// last call's contents: each call clears the rows it uses first, and calls that overlap on one GPU (two engines on one
+// device driven from two threads) race.
+}  // extern "C"
+#ifdef ACC_HOST_EMU
+static i64 g_static_scratch_q[ACC_STATIC_SCRATCH_AGENTS];
+static double g_static_scratch_v[ACC_STATIC_SCRATCH_AGENTS];
+static void static_scratch(int, i64** q, double** v) { *q = g_static_scratch_q; *v = g_static_scratch_v; }
+#else
+static __device__ __align__(256) i64 g_static_scratch_q[ACC_STATIC_SCRATCH_AGENTS];
+static __device__ __align__(256) double g_static_scratch_v[ACC_STATIC_SCRATCH_AGENTS];
+// In host code the arrays' names are host-side stand-ins, not device addresses: the device addresses are asked for once
+// per device, with that device current.
+static void static_scratch(int device, i64** q, double** v) {
+    struct Addr { i64* q; double* v; };
+    static std::map<int, Addr> per_device;
+    auto it = per_device.find(device);
+    if (it == per_device.end()) {
+        Addr a{nullptr, nullptr};
+        ACC_CUDA(cudaGetSymbolAddress((void**)&a.q, g_static_scratch_q));
+        ACC_CUDA(cudaGetSymbolAddress((void**)&a.v, g_static_scratch_v));
+        it = per_device.emplace(device, a).first;
+    }
+    *q = it->second.q; *v = it->second.v;
+}
+#endif
+extern "C" {
+
+int acc_firm_incoming_demand_static(acc_engine* e, double* out_quantity, double* out_value, size_t cap, size_t* n) {
+    ACC_API_BEGIN
+    if (e == nullptr || n == nullptr) fail("acc_firm_incoming_demand_static: null argument");
+    ACC_ON_DEVICE(e);
+    const size_t cnt = (size_t)e->nA;
+    *n = cnt;
+    if (cnt > (size_t)ACC_STATIC_SCRATCH_AGENTS)
+        fail("acc_firm_incoming_demand_static: " + std::to_string(cnt) + " agents exceed the static scratch of " + std::to_string(ACC_STATIC_SCRATCH_AGENTS) +
+             " agents (ACC_STATIC_SCRATCH_AGENTS); use acc_read(\"firms\", \"incoming_demand_quantity\")");
+    if (out_quantity == nullptr && out_value == nullptr) return 0;  // size query
+    if (cap < cnt) fail("acc_firm_incoming_demand_static: destination too small");
+    i64* sq = nullptr;
+    double* sv = nullptr;
+    static_scratch(e->device, &sq, &sv);
+    stream_t s = e->stream;
+    dev_zero(sq, cnt * sizeof(i64), s);  // rows of agents that are not (owned) firms must read zero, whatever the last call left
+    dev_zero(sv, cnt * sizeof(double), s);
+    FirmIncomingDemand k{e->edge_view(), e->firm_ids.p, sq, sv};
+    e->timed("firm_incoming_demand", [&] { launch_block(s, e->nF, k); });
+    // straight into the caller's buffers: the int64 quanta travel in the doubles' bytes and are converted in place
+    if (out_value != nullptr) d2h(out_value, sv, cnt * sizeof(double), s);
+    if (out_quantity != nullptr) {
+        d2h(out_quantity, sq, cnt * sizeof(i64), s);
+        for (size_t a = 0; a < cnt; ++a) {
+            i64 q;
+            std::memcpy(&q, &out_quantity[a], sizeof q);
+            out_quantity[a] = qf(q);
+        }
+    } else {
+        dev_sync(s);
+    }
+    return 0;
+    ACC_API_END(-1)
+}
+
 int acc_profile(acc_engine* e, int enable) {
     if (e == nullptr) return -1;
     e->profile = enable != 0;

@@ -180,6 +180,17 @@ int acc_set_event_capacity(acc_engine* e, size_t capacity);
  * as doubles (to_float), shaped like ArrayOutput::Variable::data.  *n receives the element count. */
 int acc_read(acc_engine* e, const char* group, const char* variable, double* dst, size_t cap, size_t* n);
 
+/* No counterpart in the reference: added for callers that cannot allocate device
+ * memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same numbers as
+ * acc_read(e, "firms", "incoming_demand_quantity" / "incoming_demand_value", ...) -- the sum of the demand requests each
+ * firm holds, one entry per agent, zero for consumers -- but the per-firm sums are formed in a file-scope device array
+ * instead of freshly allocated buffers: the call allocates and frees nothing on the device.  Limits: at most
+ * ACC_STATIC_SCRATCH_AGENTS agents (more is an error); every GPU that loads the library holds the 1 MiB array until the
+ * process exits; all calls share it, so calls that overlap on one GPU race.  out_quantity / out_value are caller-owned host
+ * buffers of cap doubles, either may be NULL (both NULL: *n receives the count only). */
+#define ACC_STATIC_SCRATCH_AGENTS 65536
+int acc_firm_incoming_demand_static(acc_engine* e, double* out_quantity, double* out_value, size_t cap, size_t* n);
+
 /* Raw state for parity checks: int64 / f64 arrays named like the oracle's per-step dump
  * (oracle/ref_harness/harness.cpp dump_step).  is_f64 tells which type was written to dst. */
 int acc_read_state(acc_engine* e, const char* name, void* dst, size_t cap_bytes, size_t* n, int* is_f64);
