@@ -1426,6 +1426,12 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
     if (name == "sto_S_v") return SF(E.s_S_v);
     if (name == "sto_I_q") return SI(E.s_Il_q);
     if (name == "sto_I_v") return SF(E.s_Il_v);
+    if (name == "sto_Inext_q") {  // Storage::current_input_flow_I() as the oracle dumps it before the tick: input_flow_I[other_register],
+        // the register the storage pass has consumed and zeroed (Storage.cpp:61,90); after the tick it is the one that fills next
+        const bool ticked = E.step != E.ship_step;
+        const bool first = ticked ? E.reg != 0 : E.reg == 0;
+        return SI(first ? E.s_I0_q : E.s_I1_q);
+    }
     if (name == "sto_U_q") return SI(E.s_U_q);
     if (name == "sto_U_v") return SF(E.s_U_v);
     if (name == "sto_Ut_q") return SI(E.s_Ut_q);

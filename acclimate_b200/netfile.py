@@ -6,6 +6,7 @@ reference src/input/ModelInitializer.cpp:94-213,689-700) and the per-step dumps 
 """
 from __future__ import annotations
 
+import gzip
 import struct
 from collections import OrderedDict
 
@@ -46,8 +47,15 @@ SECTOR_PARAMS = [
 ]
 
 
+def _open(path, mode):
+    """Files named *.gz are gzip-compressed (the golden fixtures); the oracle only ever reads plain files."""
+    if str(path).endswith(".gz"):
+        return gzip.GzipFile(path, mode, compresslevel=6, mtime=0) if "w" in mode else gzip.open(path, mode)
+    return open(path, mode)
+
+
 def write(path, arrays):
-    with open(path, "wb") as fp:
+    with _open(path, "wb") as fp:
         fp.write(MAGIC)
         for name, arr in arrays.items():
             arr = np.ascontiguousarray(arr)
@@ -66,7 +74,7 @@ def write(path, arrays):
 
 def read(path, prefix=None):
     out = OrderedDict()
-    with open(path, "rb") as fp:
+    with _open(path, "rb") as fp:
         if fp.read(8) != MAGIC:
             raise ValueError(f"{path}: not an ACCARR1 file")
         while True:
