@@ -145,6 +145,8 @@ class PartitionedEngine(_engine.Engine):
             grp = g_dev.cpu()
         self._check(self.lib.acc_set_solver_group(self.h, int(grp[0])))
         self._stream = None
+        self.time_exchanges = False      # bench.py: CUDA events around every exchange
+        self._exchange_events = []
         if self.tensor_device.type == "cuda":
             self._stream = torch.cuda.ExternalStream(self.stream(), device=self.tensor_device)
             torch.cuda.synchronize(self.tensor_device)  # the exchange buffers were zeroed on torch's stream, not the engine's
@@ -199,13 +201,29 @@ class PartitionedEngine(_engine.Engine):
         else:
             self._step(p)
 
+    def _timed(self, fn, *args):
+        if not (self.time_exchanges and self._stream is not None):
+            return fn(*args)
+        a, b = self.torch.cuda.Event(enable_timing=True), self.torch.cuda.Event(enable_timing=True)
+        a.record(self._stream)
+        fn(*args)
+        b.record(self._stream)
+        self._exchange_events.append((a, b))
+
+    def exchange_ms(self, reset=True):
+        """Device time spent in the three exchanges since the last reset (needs time_exchanges = True and a sync before)."""
+        ms = sum(a.elapsed_time(b) for a, b in self._exchange_events)
+        if reset:
+            self._exchange_events = []
+        return ms
+
     def _step(self, p):
         self._stage(0)  # possible production, production + distribution, pack shipments
-        self._exchange(self.flow_recv, self.flow_send, p.recv_counts, p.send_counts)
+        self._timed(self._exchange, self.flow_recv, self.flow_send, p.recv_counts, p.send_counts)
         self._stage(1)  # unpack shipments, storages + deliveries, expectation, pack supply parameters
-        self._gather_sellers()
+        self._timed(self._gather_sellers)
         self._stage(2)  # unpack supply parameters, purchase, pack demand requests
-        self._exchange(self.demand_recv, self.demand_send, p.send_counts, p.recv_counts)
+        self._timed(self._exchange, self.demand_recv, self.demand_send, p.send_counts, p.recv_counts)
         self._stage(3)  # unpack demand requests, tick
 
     def halo_bytes_per_step(self):
@@ -227,3 +245,40 @@ class PartitionedEngine(_engine.Engine):
         if x.size == self.n_agents:
             return x, p.owned.astype(bool), None
         return x, None, None
+
+
+def state_hash(E, arrays, part=None, group=None):
+    """Order-free 64-bit fingerprint of the demand requests and storage contents of a run, the same number whether the
+    network runs on one engine or split over P parts: sum over connections of (2 gid + 1) D_q plus sum over storages of
+    (2 (sector n_agents + agent) + 1 + 2^40) S_q, modulo 2^64.  A part contributes the connections it buys on and the
+    storages it owns; the parts' sums are added over the process group (as 32-bit halves: no overflow in the collective)."""
+    import numpy as np
+
+    nA = int(np.asarray(arrays["meta"])[2])
+    D = E.read_state("edge_D_q").astype(np.uint64)
+    S = E.read_state("sto_S_q").astype(np.uint64)
+    sa, ss = E.read_state("sto_agent").astype(np.uint64), E.read_state("sto_sector").astype(np.uint64)
+    if part is not None:
+        if part.edge_gid is None:
+            return None
+        mine = part.buys
+        gid = part.edge_gid[mine].astype(np.uint64)
+        D = D[mine]
+        own = part.owned[sa.astype(np.int64)].astype(bool)
+        S, sa, ss = S[own], sa[own], ss[own]
+    else:
+        gid = np.arange(D.size, dtype=np.uint64)
+    h = np.sum((np.uint64(2) * gid + np.uint64(1)) * D, dtype=np.uint64)
+    h += np.sum((np.uint64(2) * (ss * np.uint64(nA) + sa) + np.uint64(1) + np.uint64(1 << 40)) * S, dtype=np.uint64)
+    h = int(h)
+    if part is not None and part.world > 1:
+        import torch
+        import torch.distributed as dist
+
+        t = torch.tensor([h & 0xFFFFFFFF, h >> 32], dtype=torch.int64)
+        if dist.get_backend(group) == "nccl":
+            t = t.cuda()
+        dist.all_reduce(t, group=group)
+        lo, hi = int(t[0]), int(t[1])
+        h = (lo + (hi << 32)) & 0xFFFFFFFFFFFFFFFF
+    return "%016x" % h

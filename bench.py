@@ -3,8 +3,11 @@
 
 A "step" is one full model timestep (consumption & production, expectation, purchase, tick) over every
 BusinessConnection of the network.  Workload at N = 1: BASELINE.json configs[1], the EORA-shaped synthetic MRIO
-(187 regions x 26 sectors, dense, ~24.5 M connections), baseline run.  N > 1: one independent scenario of the ensemble per
-GPU (BASELINE.json configs[4] pattern, no data-path collective), reported as weak scaling.
+(187 regions x 26 sectors, dense, ~24.5 M connections), baseline run.  N > 1: the SAME network split by region over the N
+GPUs, shipment / demand halos and the seller table exchanged over NCCL, reported as strong scaling
+(--mode ensemble: one independent replica per GPU, no data-path collective, weak scaling).  After the timed baseline
+window every run applies the regional shock of configs[2], prints a fingerprint of the state 5 steps in ("state_hash":
+equal at every N) and times the shocked regime ("flood").
 
   python bench.py --gpus N --steps K --warmup W            the CUDA engine through its C ABI
   python bench.py --impl reference ...                      the reference's own model code (oracle/_ref) on the host cores
@@ -188,11 +191,14 @@ def main():
     ap.add_argument("--ref-steps", type=int, default=3)
     ap.add_argument("--reference-small", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--mode", default="ensemble", choices=["ensemble", "partition"],
-                    help="N > 1: one independent member of the same workload per GPU (weak scaling, no collective; default), or ONE network "
-                         "split by region across the GPUs with the shipment / demand halos and the seller table exchanged over NCCL (strong scaling)")
+    ap.add_argument("--mode", default=None, choices=["ensemble", "partition"],
+                    help="N > 1: ONE network split by region across the GPUs, the shipment / demand halos and the seller table exchanged over "
+                         "NCCL (strong scaling; default), or one independent member of the same workload per GPU (weak scaling, no collective)")
+    ap.add_argument("--flood-steps", type=int, default=10, help="timed steps of the shocked window that follows the baseline measurement (0: none)")
     ap.add_argument("--ensemble-shocks", action="store_true", help="ensemble members other than the first get their own regional shock")
     args = ap.parse_args()
+    if args.mode is None:
+        args.mode = "partition" if int(os.environ.get("WORLD_SIZE", "1")) > 1 else "ensemble"
     if args.impl == "reference":
         run_reference(args)
         return
@@ -264,10 +270,23 @@ def main():
         step_no += 1
     ev1.record(stream)
     barrier()
+    if partitioned:
+        E.time_exchanges = True
     ms = ev0.elapsed_time(ev1)
     launches = E.launches - launches0
     ktimes = E.kernel_times(reset=True)
     E.profile(False)
+    exchange_ms = None
+    if partitioned:
+        # a second pass of the same K steps with CUDA events around the three exchanges (kept out of the headline timing:
+        # the extra event records sit on the stream)
+        barrier()
+        for _ in range(args.steps):
+            E.step()
+            step_no += 1
+        barrier()
+        exchange_ms = E.exchange_ms() / args.steps
+        E.time_exchanges = False
 
     # ---- end to end through the C ABI with host buffers: forcing H2D + step + observable D2H every step ----
     lam = torch.ones(E.n_agents, dtype=torch.float64).pin_memory()
@@ -283,6 +302,46 @@ def main():
     e2e_s = time.perf_counter() - t0
     sampler.stop_flag.set()
     sampler.join()
+
+    # ---- untimed epilogue: a regional production-loss shock (BASELINE.json configs[2]: region 17 at half capacity) ----
+    # 5 steps through the onset, then a fingerprint of demand requests and storage contents: the same number at every N
+    # proves the partitioned NCCL path bit-identical to the single-GPU run.  The timed window that follows is the shocked
+    # regime of configs[2] (the purchasing managers iterate; at the baseline they stop after one evaluation).
+    state_hash, flood = None, None
+    if args.config == "eora" and (world == 1 or partitioned):
+        from acclimate_b200 import partition as _partition
+
+        at, ar, ab = (np.asarray(net[k]) for k in ("agent_type", "agent_region", "agent_beta"))
+        lam_shock = np.ones(E.n_agents)
+        hit = (at == 1) & (ar == 17)
+        lam_shock[hit] = 0.5 / ab[hit]
+        E.set_agent_forcing(lam_shock)
+        for _ in range(5):
+            E.step()
+        E.sync()
+        state_hash = _partition.state_hash(E, net, part=E.part if partitioned else None)
+        if args.flood_steps > 0:
+            E.profile(True)
+            E.kernel_times(reset=True)
+            barrier()
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            f0.record(stream)
+            for _ in range(args.flood_steps):
+                E.step()
+            f1.record(stream)
+            barrier()
+            fms = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(fms, op=dist.ReduceOp.MAX)
+            fk = E.kernel_times(reset=True)
+            E.profile(False)
+            evals = E.read_state("sto_solver_evals")
+            if partitioned:
+                evals = evals[E.part.owned[E.read_state("sto_agent")].astype(bool)]
+            flood = {"value": n_edges * args.flood_steps / (float(fms[0]) * 1e-3), "unit": "updates/s", "ms_per_step": float(fms[0]) / args.flood_steps,
+                     "steps": args.flood_steps, "window": "steps 6..%d after the onset of a 50 %% production loss in region 17" % (5 + args.flood_steps),
+                     "evaluations_per_manager_last_step": {"mean": float(evals.mean()), "max": int(evals.max())},
+                     "kernels_ms_per_step": {k: v[0] / args.flood_steps for k, v in fk.items()}}
 
     t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -329,7 +388,12 @@ def main():
             "gpu_launches": launches,
             "roofline": roof,
             "cpu_baseline": cpu,
+            "state_hash": state_hash,
+            "flood": flood,
         }
+        if partitioned:
+            pk = sum(v[0] for k, v in ktimes.items() if k.startswith("pack_") or k.startswith("unpack_")) / args.steps
+            line["partition"] = {"collective_ms": exchange_ms, "pack_ms": pk, "halo_bytes_per_step_this_rank": E.halo_bytes_per_step()}
         print(json.dumps(line))
     E.close()
     if world > 1:

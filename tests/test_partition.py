@@ -87,3 +87,53 @@ def test_halo_lists_pair_up():
         sellers[p.edge_gid[p.sells]] += 1
         buyers[p.edge_gid[p.buys]] += 1
     assert (sellers == 1).all() and (buyers == 1).all()
+
+
+def _hash_worker(rank, world, port, lib, out):
+    import torch.distributed as dist
+
+    from acclimate_b200 import engine, partition
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        net, _, _ = parity.load_case("severe_shock30")
+        E = partition.PartitionedEngine(net, lib_path=lib, tensor_device="cpu")
+        sc = engine.Scenario(net)
+        for t in range(8):
+            sc.apply(E, t)
+            E.step()
+        out.put((rank, partition.state_hash(E, net, part=E.part)))
+        E.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_state_hash_is_partition_invariant(emu_lib):
+    """bench.py's state_hash: the same fingerprint from one engine and from two parts (what the driver compares over N)."""
+    import torch.multiprocessing as mp
+
+    from acclimate_b200 import engine, partition
+
+    net, _, _ = parity.load_case("severe_shock30")
+    E = engine.Engine(net, lib_path=emu_lib)
+    sc = engine.Scenario(net)
+    hashes = []
+    for t in range(8):
+        sc.apply(E, t)
+        E.step()
+        hashes.append(partition.state_hash(E, net))
+    E.close()
+    assert len(set(hashes)) > 4  # the fingerprint follows the state
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_hash_worker, args=(r, 2, port, emu_lib, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = [out.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert {h for _, h in got} == {hashes[-1]}
