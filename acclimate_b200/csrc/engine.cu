@@ -38,6 +38,11 @@
 #include "../../include/acclimate_b200.h"
 #include "purchase_core.cuh"
 #include "consumer_core.cuh"
+#include "observe.cuh"
+
+#ifndef ACC_HOST_EMU
+#include <dlfcn.h>
+#endif
 
 #ifndef ACC_PM_MAXREG_ANY
 #define ACC_PM_MAXREG_ANY 80  // ... at any other group size: two CTAs of 384 threads (748 connections per manager) per SM; measured on a
@@ -245,6 +250,56 @@ static void launch_block_smem(stream_t s, int n, int threads, size_t smem, K k) 
 }
 #endif
 
+#ifndef ACC_HOST_EMU
+// ---- NCCL, bound at run time ----
+// The halo exchanges of a region-partitioned run are NCCL point-to-point groups and one all-gather issued by the engine
+// itself on its own stream (acc_comm_init / acc_step_partitioned).  The library is looked up when the first communicator is
+// made: the copy the process has already loaded (a host that also uses torch.distributed shares torch's), else the system
+// one; an unpartitioned run never needs it.  Prototypes as in nccl.h (2.x: stable since 2.7).
+struct NcclApi {
+    typedef struct ncclComm* comm_t;
+    struct unique_id { char internal[128]; };
+    int (*GetUniqueId)(unique_id*) = nullptr;
+    int (*CommInitRank)(comm_t*, int, unique_id, int) = nullptr;
+    int (*CommDestroy)(comm_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    int (*Send)(const void*, size_t, int, int, comm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, comm_t, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, comm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    enum { Int64 = 4 };
+    static NcclApi& get() {
+        static NcclApi api;
+        if (api.Send != nullptr) return api;
+        void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);
+        if (h == nullptr) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (h == nullptr) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (h == nullptr) fail(std::string("NCCL is not available: ") + dlerror());
+        auto sym = [&](const char* name) {
+            void* p = dlsym(h, name);
+            if (p == nullptr) fail(std::string("NCCL symbol missing: ") + name);
+            return p;
+        };
+        api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(sym("ncclGetUniqueId"));
+        api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
+        api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
+        api.GroupStart = reinterpret_cast<decltype(api.GroupStart)>(sym("ncclGroupStart"));
+        api.GroupEnd = reinterpret_cast<decltype(api.GroupEnd)>(sym("ncclGroupEnd"));
+        api.Recv = reinterpret_cast<decltype(api.Recv)>(sym("ncclRecv"));
+        api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
+        api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
+        api.Send = reinterpret_cast<decltype(api.Send)>(sym("ncclSend"));
+        return api;
+    }
+};
+#define ACC_NCCL(x)                                                                                                  \
+    do {                                                                                                             \
+        const int err__ = (x);                                                                                       \
+        if (err__ != 0) fail(std::string(#x) + ": " + NcclApi::get().GetErrorString(err__));                         \
+    } while (0)
+#endif
+
 template <class T>
 struct DBuf {  // device array with its element count
     T* p = nullptr;
@@ -406,7 +461,7 @@ struct StorageDelivery {  // thread per storage
                         if (h + 1 == h1) out = o;
                     }
                 }
-                if (FORCED && ev.ship_q != nullptr) ev.ship_q[e] = ship.q;
+                if (FORCED && ev.ship_q != nullptr) { ev.ship_q[e] = ship.q; ev.ship_v[e] = ship.v; }
                 in = fadd(in, out);
                 if (!dom_[j]) imp = fadd(imp, out);
                 tq += ship.q - out.q;
@@ -447,7 +502,8 @@ struct Purchase {
     StorageView st; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
     // incoming connections per storage (seller ascending): connection id, seller | delay << 24, Z* (copies in this order:
     // one coalesced read instead of a gather through the connection id)
-    const i64* in_off; const int* in_edge; const int* in_seller; const i64* in_Z; const SellerPub* pub; int n_max; const int* pm_ids;  // pm_ids == nullptr: all
+    // in_seller: seller ROW (SellerTable) | delay << 24
+    const i64* in_off; const int* in_edge; const int* in_seller; const i64* in_Z; SellerTable pubT; int n_max; const int* pm_ids;  // pm_ids == nullptr: all
     i64* dem_q; double* dem_v; double* exp_costs; double* opt_val; double* tpen; int* iters; int* evals;
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const {
@@ -461,7 +517,8 @@ struct Purchase {
         const i64* iz = in_Z + o;
         const EdgeView& E = ev;
         const int T = E.T, plane0 = (int)(step % T);
-        const SellerPub* const pubs = pub;
+        const double* const tf = pubT.f;
+        const i64 ts = pubT.stride;
         const i64 deficit = st.defc[s] - st.dlv_q[s] - st.T_q[s];
         const PMResult r = purchase_one<SEP, STD>(
             cx, nin, [&](int i) { return ie[i]; },
@@ -477,7 +534,12 @@ struct Purchase {
                 g.last_q = (E.ship_q != nullptr ? E.ship_q : conv)[e];  // a select, not a branch: loads of two gathers overlap
                 g.Z_q = iz[i];
                 g.lastD_q = SEP ? E.D_q[e] : 0;
-                g.sp = pubs[g.seller];
+                const double* f = tf + g.seller;  // consecutive connections -> consecutive rows: coalesced field by field
+                double xq = f[SPT_XHAT_Q * ts];
+                memcpy(&g.sp.Xhat_q, &xq, sizeof xq);
+                g.sp.Xhatf = f[SPT_XHATF * ts]; g.sp.Xf = f[SPT_XF * ts]; g.sp.Xexpf = f[SPT_XEXPF * ts]; g.sp.nbarf = f[SPT_NBARF * ts];
+                g.sp.lamXf = f[SPT_LAMXF * ts]; g.sp.c1 = f[SPT_C1 * ts]; g.sp.c2 = f[SPT_C2 * ts]; g.sp.n_co = f[SPT_NCO * ts];
+                g.rr = f[SPT_RR * ts]; g.npeE = f[SPT_NPEE * ts];
                 return g;
             },
             [&](int e) {  // BusinessConnection::get_minimum_passage, BusinessConnection.cpp:69-83
@@ -532,7 +594,7 @@ struct EdgeObservables {
             if (pl >= T) pl -= T;
             const i64 at = (i64)pl * ev.n_edges + e;
             if (ship_q != nullptr) ship_q[k] = ev.ship_q != nullptr ? ev.ship_q[e] : ev.conv_q[at];
-            if (ship_v != nullptr) ship_v[k] = ev.conv_v[at];
+            if (ship_v != nullptr) ship_v[k] = ev.ship_v != nullptr ? ev.ship_v[e] : ev.conv_v[at];
         }
         if (dlv_q != nullptr || dlv_v != nullptr) {
             const i64 at = (i64)p0 * ev.n_edges + e;
@@ -600,12 +662,36 @@ struct PackSellers {  // owned rows as they are, zero elsewhere: an integer SUM 
     }
 };
 struct UnpackSellers {
-    SellerPub* pub; const unsigned char* owned; const i64* table;
+    SellerPub* pub; SellerTable pubT; const unsigned char* owned; const i64* table;
     ACC_HD void operator()(int a) const {
         if (owned[a]) return;
         i64* dst = reinterpret_cast<i64*>(pub + a);
         for (int k = 0; k < ACC_SELLER_WORDS; ++k) dst[k] = table[(i64)a * ACC_SELLER_WORDS + k];
+        publish_seller(pubT, a, pub[a]);
     }
+};
+// the NCCL plane gathers only the rows their owners computed: owned firms in agent order, padded to the largest part
+struct PackSellerRows {
+    const SellerPub* pub; const int* firms; i64* rows;
+    ACC_HD void operator()(int k) const {
+        const i64* src = reinterpret_cast<const i64*>(pub + firms[k]);
+        for (int w = 0; w < ACC_SELLER_WORDS; ++w) rows[(i64)k * ACC_SELLER_WORDS + w] = src[w];
+    }
+};
+struct UnpackSellerRows {  // thread per (part, row): firms of every part in agent order; the own part's rows are skipped
+    SellerPub* pub; SellerTable pubT; const int* part_firms; const int* part_off; int n_parts, rank, max_rows; const i64* rows;
+    ACC_HD void operator()(int i) const {
+        const int p = i / max_rows, k = i - p * max_rows;
+        if (p == rank || k >= part_off[p + 1] - part_off[p]) return;
+        const int a = part_firms[part_off[p] + k];
+        i64* dst = reinterpret_cast<i64*>(pub + a);
+        for (int w = 0; w < ACC_SELLER_WORDS; ++w) dst[w] = rows[((i64)p * max_rows + k) * ACC_SELLER_WORDS + w];
+        publish_seller(pubT, a, pub[a]);
+    }
+};
+struct RepublishSellers {  // the field-major twin of the seller records, rebuilt from them (after a checkpoint was loaded)
+    const SellerPub* pub; SellerTable pubT;
+    ACC_HD void operator()(int a) const { publish_seller(pubT, a, pub[a]); }
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -658,6 +744,16 @@ struct acc_engine {
     DBuf<i64> f_cap_q, f_Xhat_q, f_est_q, f_X_q, f_Xexp_q, f_nbar, f_cutoff, f_desired_q, f_sumD_q, f_bk_sq, f_bk_cnt, f_bk_pmax, f_bk_pmin, f_exp_q;
     DBuf<double> f_cap_v, f_Xhat_v, f_est_v, f_X_v, f_Xexp_v, f_C, f_R, f_sumD_v, f_bk_sv, f_exp_v;
     DBuf<SellerPub> pub;
+    DBuf<double> pubT;         // field-major twin of pub over the seller rows (SellerTable)
+    DBuf<int> seller_row;      // agent -> seller row (firms in sector-major order), -1 for consumers
+    DBuf<int> row_firm;        // seller row -> agent
+    // output surface (acc_observe): buyer of every connection, storage of every (sector, agent), staging buffers
+    DBuf<int> e_to, sto_of;
+    DBuf<double> obs_out;
+    DBuf<i64> obs_idx, obs_inc_q;
+    DBuf<double> obs_inc_v;
+    int max_storages = 0;      // most input storages of one agent
+    std::vector<int> h_row_firm;  // seller row -> agent
     // storages
     DBuf<i64> s_S_q, s_I0_q, s_I1_q, s_Il_q, s_U_q, s_Ut_q, s_T_q, s_dlv_q, s_imp_q, s_Istar_q, s_Sstar_q, s_defc, s_dem_q;
     DBuf<double> s_S_v, s_I0_v, s_I1_v, s_Il_v, s_U_v, s_Ut_v, s_T_v, s_imp_v, s_Istar_v, s_Sstar_v, s_a, s_dem_v, s_exp_costs, s_opt_val, s_tpen;
@@ -667,6 +763,7 @@ struct acc_engine {
     DBuf<int> e_seller_off, e_route, route_off, route_ent;
     DBuf<unsigned char> ent_delay;
     DBuf<i64> e_ship_q;
+    DBuf<double> e_ship_v;
     int nEnt = 0, h_max = 1;
     bool hops_rewrite_shipment = false;  // some route starts with a zero-delay entity
     DBuf<i64> e_D_q, e_D_p, e_Z_q, conv_q, e_ovf_q;
@@ -689,7 +786,16 @@ struct acc_engine {
     DBuf<unsigned char> owned;
     DBuf<int> pm_ids;
     DBuf<i64> halo_send, halo_recv;
-    i64 *x_flow_send = nullptr, *x_flow_recv = nullptr, *x_dem_send = nullptr, *x_dem_recv = nullptr, *x_sellers = nullptr;  // caller-owned
+    i64 *x_flow_send = nullptr, *x_flow_recv = nullptr, *x_dem_send = nullptr, *x_dem_recv = nullptr, *x_sellers = nullptr;  // caller-owned ...
+    DBuf<i64> own_flow_send, own_flow_recv, own_dem_send, own_dem_recv, own_sellers;  // ... or the engine's own (acc_set_halo with null buffers)
+    // NCCL plane (acc_comm_init): the engine exchanges the halos itself
+    int comm_rank = -1, comm_world = 0, comm_max_rows = 0;
+    std::vector<i64> comm_send_cnt, comm_recv_cnt, comm_send_off, comm_recv_off;
+    DBuf<int> comm_part_firms, comm_part_off;
+    DBuf<i64> comm_rows_send, comm_rows_recv;
+#ifndef ACC_HOST_EMU
+    NcclApi::comm_t comm = nullptr;
+#endif
     // events
     DBuf<Event> ev_buf;
     DBuf<int> ev_count;
@@ -707,7 +813,7 @@ struct acc_engine {
         v(s_S_v); v(s_I0_v); v(s_I1_v); v(s_Il_v); v(s_U_v); v(s_Ut_v); v(s_T_v); v(s_imp_v); v(s_dem_v); v(s_exp_costs); v(s_opt_val); v(s_tpen);
         v(s_iters); v(s_evals);
         v(e_D_q); v(e_D_p); v(conv_q); v(conv_v);
-        v(e_ovf_q); v(e_ovf_v); v(e_ship_q);  // empty until passage forcing is used
+        v(e_ovf_q); v(e_ovf_v); v(e_ship_q); v(e_ship_v);  // empty until passage forcing is used
         v(c_prev_q); v(c_prev_v); v(c_utility);
         v(ev_count); v(ev_buf);
     }
@@ -715,7 +821,7 @@ struct acc_engine {
         if (forcing_used) return;
         e_ovf_q.alloc((size_t)nE * h_max); e_ovf_v.alloc((size_t)nE * h_max);
         e_ovf_q.zero(stream); e_ovf_v.zero(stream);
-        if (hops_rewrite_shipment) { e_ship_q.alloc((size_t)nE); e_ship_q.zero(stream); }
+        if (hops_rewrite_shipment) { e_ship_q.alloc((size_t)nE); e_ship_q.zero(stream); e_ship_v.alloc((size_t)nE); e_ship_v.zero(stream); }
         forcing_used = true;
     }
 
@@ -723,6 +829,7 @@ struct acc_engine {
 #ifndef ACC_HOST_EMU
         for (auto& c : clocks)
             for (auto& pr : c.pending) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+        if (comm != nullptr) NcclApi::get().CommDestroy(comm);
         if (ev_fork) cudaEventDestroy(ev_fork);
         if (ev_join) cudaEventDestroy(ev_join);
         if (side) cudaStreamDestroy(side);
@@ -745,6 +852,7 @@ struct acc_engine {
     FirmView firm_view() {
         FirmView v;
         v.pub = pub.p;
+        v.pubT = seller_table();
         v.Xstar_q = f_Xstar_q.p; v.Xstar_v = f_Xstar_v.p; v.beta = a_beta.p; v.lambda = a_lambda.p; v.sector = a_sector.p; v.region = a_region.p;
         v.type = a_type.p; v.markup_eff = f_markup_eff.p; v.var_costs = f_var_costs.p; v.st_off = a_st_off.p; v.st_list = a_st_list.p;
         v.cap_q = f_cap_q.p; v.cap_v = f_cap_v.p; v.Xhat_q = f_Xhat_q.p; v.Xhat_v = f_Xhat_v.p; v.est_q = f_est_q.p; v.est_v = f_est_v.p;
@@ -754,12 +862,18 @@ struct acc_engine {
         v.exp_q = f_exp_q.p; v.exp_v = f_exp_v.p;
         return v;
     }
+    SellerTable seller_table() {
+        SellerTable t;
+        t.f = pubT.p; t.row = seller_row.p; t.stride = (i64)h_row_firm.size();
+        return t;
+    }
     EdgeView edge_view() {
         EdgeView v;
         v.seller_off = e_seller_off.p; v.D_q = e_D_q.p; v.D_p = e_D_p.p; v.Z_q = e_Z_q.p; v.tau = e_tau.p; v.domestic = e_dom.p; v.route = e_route.p; v.route_off = route_off.p; v.route_ent = route_ent.p; v.ent_delay = ent_delay.p;
         v.conv_q = conv_q.p; v.conv_v = conv_v.p; v.n_edges = nE; v.T = T;
         v.ovf_q = forcing_used ? e_ovf_q.p : nullptr; v.ovf_v = forcing_used ? e_ovf_v.p : nullptr; v.nu = forcing_used ? nu.p : nullptr;
         v.ship_q = e_ship_q.n ? e_ship_q.p : nullptr;
+        v.ship_v = e_ship_v.n ? e_ship_v.p : nullptr;
         return v;
     }
     ConsumerView consumer_view() {
@@ -787,8 +901,10 @@ struct acc_engine {
     template <class Fn>
     void timed(const char* name, Fn fn) { timed_on(stream, name, fn); }
     template <class Fn>
-    void timed_on(stream_t on, const char* name, Fn fn) {
-        ++launches;
+    void timed_comm(const char* name, Fn fn) { timed_on(stream, name, fn, false); }  // a collective: clocked, not counted as a kernel launch
+    template <class Fn>
+    void timed_on(stream_t on, const char* name, Fn fn, bool kernel = true) {
+        if (kernel) ++launches;
 #ifndef ACC_HOST_EMU
         if (profile) {
             const int id = clock_id(name);
@@ -883,15 +999,18 @@ struct acc_engine {
     template <bool SEP, bool STD, int G>
     void launch_purchase() {
         constexpr bool DVAL = G > 0;  // the base group keeps the D_r summands; the large groups trade them for a second CTA per SM
-        Purchase<SEP, STD, DVAL> k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, in_Z.p, pub.p, n_max,
+        Purchase<SEP, STD, DVAL> k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, in_Z.p, seller_table(), n_max,
                              partitioned ? pm_ids.p : nullptr, s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
         timed("purchase", [&] { launch_block_smem<G>(stream, partitioned ? n_pm : nSt, pm_group, pm_workspace_bytes(n_max, SEP, DVAL), k); });
     }
     void stage_purchase() {
         if (partitioned && x_sellers != nullptr) {
-            UnpackSellers k{pub.p, owned.p, x_sellers};
+            UnpackSellers k{pub.p, seller_table(), owned.p, x_sellers};
             timed("unpack_sellers", [&] { launch_thread(stream, nA, k); });
         }
+        purchase_and_pack();
+    }
+    void purchase_and_pack() {
         // One CTA of pm_group threads per purchasing manager, all its vectors in shared memory.  The group size is part
         // of the arithmetic (reduction order): ACCSQP_GROUP, or accsqp_group_for(largest manager) -- the same rule the
         // oracle's host context follows.
@@ -916,6 +1035,58 @@ struct acc_engine {
             timed("unpack_demand", [&] { launch_thread(stream, (int)halo_send.n, k); });
         }
         tick();
+    }
+#ifndef ACC_HOST_EMU
+    // all-to-all of (2 x int64) entries grouped by peer: one NCCL point-to-point group on the engine's stream
+    void exchange_halo(const i64* send, const std::vector<i64>& scnt, const std::vector<i64>& soff, i64* recv, const std::vector<i64>& rcnt,
+                       const std::vector<i64>& roff) {
+        NcclApi& nc = NcclApi::get();
+        ACC_NCCL(nc.GroupStart());
+        for (int p = 0; p < comm_world; ++p) {
+            if (p == comm_rank) continue;
+            if (scnt[p]) ACC_NCCL(nc.Send(send + 2 * soff[p], (size_t)(2 * scnt[p]), NcclApi::Int64, p, comm, stream));
+            if (rcnt[p]) ACC_NCCL(nc.Recv(recv + 2 * roff[p], (size_t)(2 * rcnt[p]), NcclApi::Int64, p, comm, stream));
+        }
+        ACC_NCCL(nc.GroupEnd());
+        ++collectives;
+    }
+#endif
+    i64 collectives = 0;
+    // One timestep of a region-partitioned run with the engine doing its own exchanges (NCCL on the engine's stream):
+    //   sellers' pass -> shipments to the buyers' parts -> storages, deliveries, expectation -> all-gather of the owned
+    //   sellers' records -> purchase -> demand requests to the sellers' parts -> tick
+    void step_partitioned() {
+#ifdef ACC_HOST_EMU
+        fail("acc_step_partitioned: the emulation has no NCCL; drive the stages with acc_stage");
+#else
+        if (comm == nullptr) fail("acc_step_partitioned: call acc_comm_init first");
+        NcclApi& nc = NcclApi::get();
+        stage_sell();
+        timed_comm("exchange_flow", [&] { exchange_halo(x_flow_send, comm_send_cnt, comm_send_off, x_flow_recv, comm_recv_cnt, comm_recv_off); });
+        {   // stage_deliver without the full-table pack
+            if (halo_recv.n) {
+                UnpackFlow k{edge_view(), (int)(step % T), halo_recv.p, x_flow_recv};
+                timed("unpack_flow", [&] { launch_thread(stream, (int)halo_recv.n, k); });
+            }
+            consumer_join();
+            launch_delivery(owned.p);
+            SellerExpectation k{firm_view(), edge_view(), storage_view(), mp, sectors.p, sink(), firm_ids.p};
+            timed("seller_expectation", [&] { launch_warp(stream, nF, 0, k); });
+            PackSellerRows pk{pub.p, firm_ids.p, comm_rows_send.p};
+            timed("pack_sellers", [&] { launch_thread(stream, nF, pk); });
+        }
+        timed_comm("exchange_sellers", [&] {
+            ACC_NCCL(nc.AllGather(comm_rows_send.p, comm_rows_recv.p, (size_t)comm_max_rows * ACC_SELLER_WORDS, NcclApi::Int64, comm, stream));
+            ++collectives;
+        });
+        {
+            UnpackSellerRows k{pub.p, seller_table(), comm_part_firms.p, comm_part_off.p, comm_world, comm_rank, comm_max_rows, comm_rows_recv.p};
+            timed("unpack_sellers", [&] { launch_thread(stream, comm_world * comm_max_rows, k); });
+        }
+        purchase_and_pack();
+        timed_comm("exchange_demand", [&] { exchange_halo(x_dem_send, comm_recv_cnt, comm_recv_off, x_dem_recv, comm_send_cnt, comm_send_off); });
+        stage_close();
+#endif
     }
     void require_single(const char* what) {
         if (partitioned) fail(std::string(what) + ": this engine is one part of a region-partitioned run; drive it with acc_stage and exchange the halos in between");
@@ -1171,11 +1342,20 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
         X_q[a] = Xstar_q[a]; X_v[a] = Xstar_v[a];
     }
     E.nF = (int)firm_ids.size();
+    // seller rows: all firms (of every part: a buyer reads the record of any seller), sector-major, agent-minor
+    std::vector<int> seller_row(nA, -1);
+    {
+        std::vector<int> by_sector(all_firms);
+        std::stable_sort(by_sector.begin(), by_sector.end(), [&](int x, int y) { return a_sector[x] < a_sector[y]; });
+        for (size_t r = 0; r < by_sector.size(); ++r) seller_row[by_sector[r]] = (int)r;
+        E.h_row_firm = by_sector;
+        if (by_sector.size() >= ((size_t)1 << 24)) fail("more than 2^24 firms");
+    }
 
     // ---- buyer-side lists ----
     std::vector<i64> in_off(nSt + 1, 0);
     for (int k = 0; k < nSt; ++k) in_off[k + 1] = in_off[k] + in_cnt[k + 1];
-    std::vector<int> in_edge(nE), in_seller(nE);  // in_seller: seller agent | delay << 24
+    std::vector<int> in_edge(nE), in_seller(nE);  // in_seller: seller row | delay << 24
     std::vector<i64> in_Z(nE);
     if (nA >= (1 << 24)) fail("more than 2^24 agents");
     {
@@ -1183,7 +1363,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
         for (i64 e = 0; e < nE; ++e) {  // file order == seller ascending
             const int st = cid2s[e_cid[e]];
             in_edge[fill[st]] = (int)e;
-            in_seller[fill[st]] = (int)((unsigned)net.edge_from[e] | ((unsigned)tau[e] << 24));
+            in_seller[fill[st]] = (int)((unsigned)seller_row[net.edge_from[e]] | ((unsigned)tau[e] << 24));
             in_Z[fill[st]] = Zq[e];
             ++fill[st];
         }
@@ -1218,6 +1398,18 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
                          &E.f_bk_pmin, &E.f_exp_q}) { b->alloc(nA); b->zero(s); }
     for (DBuf<double>* b : {&E.f_cap_v, &E.f_Xhat_v, &E.f_Xexp_v, &E.f_C, &E.f_R, &E.f_sumD_v, &E.f_bk_sv, &E.f_exp_v}) { b->alloc(nA); b->zero(s); }
     E.pub.alloc(nA); E.pub.zero(s);
+    E.pubT.alloc((size_t)SPT_FIELDS * E.h_row_firm.size()); E.pubT.zero(s);
+    E.seller_row.upload(seller_row, s);
+    E.row_firm.upload(E.h_row_firm, s);
+    {
+        std::vector<int> e_to(nE);
+        for (i64 e = 0; e < nE; ++e) e_to[e] = (int)net.edge_to[e];
+        E.e_to.upload(e_to, s);
+        std::vector<int> sto_of((size_t)nS * nA, -1);
+        for (int k = 0; k < nSt; ++k) sto_of[(size_t)st_sector[k] * nA + st_agent[k]] = k;
+        E.sto_of.upload(sto_of, s);
+        for (i64 a = 0; a < nA; ++a) E.max_storages = std::max(E.max_storages, a_st_off[a + 1] - a_st_off[a]);
+    }
 
     E.s_agent.upload(st_agent, s); E.s_sector.upload(st_sector, s);
     E.s_Istar_q.upload(Istar_q, s); E.s_Istar_v.upload(Istar_v, s); E.s_Sstar_q.upload(Sstar_q, s); E.s_Sstar_v.upload(Sstar_v, s);
@@ -1399,7 +1591,6 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
             }
             return true;
         }
-        if (name == "edge_ship_v" && E.e_ship_q.n) return false;  // the value of a shipment whose slot a hop rewrote is not kept
         DBuf<i64> bq; DBuf<double> bv;
         if (q) bq.alloc(E.nE); else bv.alloc(E.nE);
         EdgeObservables k{E.edge_view(), t, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -1558,6 +1749,194 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
         return failval;                                          \
     }
 
+
+// ---- acc_observe: the output surface with selection (ArrayOutput::iterate, src/output/ArrayOutput.cpp:479-646) ----
+namespace acc {
+struct ObsName { const char* name; int id; };
+static const ObsName k_agent_names[] = {
+    {"business_connections", AV_BUSINESS_CONNECTIONS}, {"consumption_quantity", AV_CONSUMPTION_Q}, {"consumption_value", AV_CONSUMPTION_V},
+    {"demand_quantity", AV_DEMAND_Q}, {"demand_value", AV_DEMAND_V}, {"input_flow_quantity", AV_INPUT_FLOW_Q}, {"input_flow_value", AV_INPUT_FLOW_V},
+    {"storage_quantity", AV_STORAGE_Q}, {"storage_value", AV_STORAGE_V}};
+static const ObsName k_firm_names[] = {
+    {"communicated_possible_production_quantity", FV_COMMUNICATED_POSSIBLE_PRODUCTION_Q}, {"communicated_possible_production_value", FV_COMMUNICATED_POSSIBLE_PRODUCTION_V},
+    {"desired_production_capacity", FV_DESIRED_PRODUCTION_CAPACITY}, {"direct_loss_quantity", FV_DIRECT_LOSS_Q}, {"direct_loss_value", FV_DIRECT_LOSS_V},
+    {"expected_offer_price", FV_EXPECTED_OFFER_PRICE}, {"expected_production_quantity", FV_EXPECTED_PRODUCTION_Q}, {"expected_production_value", FV_EXPECTED_PRODUCTION_V},
+    {"forcing", FV_FORCING}, {"incoming_demand_quantity", FV_INCOMING_DEMAND_Q}, {"incoming_demand_value", FV_INCOMING_DEMAND_V}, {"offer_price", FV_OFFER_PRICE},
+    {"production_quantity", FV_PRODUCTION_Q}, {"production_value", FV_PRODUCTION_V}, {"production_capacity", FV_PRODUCTION_CAPACITY},
+    {"possible_production_capacity", FV_POSSIBLE_PRODUCTION_CAPACITY}, {"tax", FV_TAX}, {"total_loss_quantity", FV_TOTAL_LOSS_Q}, {"total_loss_value", FV_TOTAL_LOSS_V},
+    {"total_production_costs", FV_TOTAL_PRODUCTION_COSTS}, {"total_revenue", FV_TOTAL_REVENUE}, {"total_value_loss", FV_TOTAL_VALUE_LOSS},
+    {"unit_production_costs", FV_UNIT_PRODUCTION_COSTS}};
+static const ObsName k_consumer_names[] = {{"utility", CV_UTILITY}, {"local_optimal_utility", CV_LOCAL_OPTIMAL_UTILITY}};
+static const ObsName k_storage_names[] = {
+    {"business_connections", SV_BUSINESS_CONNECTIONS}, {"content_quantity", SV_CONTENT_Q}, {"content_value", SV_CONTENT_V}, {"demand_quantity", SV_DEMAND_Q},
+    {"demand_value", SV_DEMAND_V}, {"desired_used_flow_quantity", SV_DESIRED_USED_FLOW_Q}, {"desired_used_flow_value", SV_DESIRED_USED_FLOW_V},
+    {"expected_costs", SV_EXPECTED_COSTS}, {"input_flow_quantity", SV_INPUT_FLOW_Q}, {"input_flow_value", SV_INPUT_FLOW_V}, {"optimized_value", SV_OPTIMIZED_VALUE},
+    {"possible_use_quantity", SV_POSSIBLE_USE_Q}, {"possible_use_value", SV_POSSIBLE_USE_V}, {"purchase_quantity", SV_PURCHASE_Q}, {"purchase_value", SV_PURCHASE_V},
+    {"shipment_quantity", SV_SHIPMENT_Q}, {"shipment_value", SV_SHIPMENT_V}, {"storage_demand_quantity", SV_STORAGE_DEMAND_Q},
+    {"storage_demand_value", SV_STORAGE_DEMAND_V}, {"total_transport_penalty", SV_TOTAL_TRANSPORT_PENALTY}, {"use_quantity", SV_USE_Q}, {"use_value", SV_USE_V},
+    {"used_flow_quantity", SV_USED_FLOW_Q}, {"used_flow_value", SV_USED_FLOW_V}};
+static const ObsName k_flow_names[] = {
+    {"initial_flow_quantity", XV_INITIAL_FLOW_Q}, {"initial_flow_value", XV_INITIAL_FLOW_V}, {"demand_request_quantity", XV_DEMAND_REQUEST_Q},
+    {"demand_request_value", XV_DEMAND_REQUEST_V}, {"flow_deficit", XV_FLOW_DEFICIT}, {"flow_mean_quantity", XV_FLOW_MEAN_Q}, {"flow_mean_value", XV_FLOW_MEAN_V},
+    {"received_flow_quantity", XV_RECEIVED_FLOW_Q}, {"received_flow_value", XV_RECEIVED_FLOW_V}, {"sent_flow_quantity", XV_SENT_FLOW_Q},
+    {"sent_flow_value", XV_SENT_FLOW_V}, {"total_flow_quantity", XV_TOTAL_FLOW_Q}, {"total_flow_value", XV_TOTAL_FLOW_V}, {"minimum_passage", XV_MINIMUM_PASSAGE}};
+template <size_t N>
+static int find_obs(const ObsName (&table)[N], const char* name) {
+    for (size_t k = 0; k < N; ++k) if (std::strcmp(table[k].name, name) == 0) return table[k].id;
+    return -1;
+}
+
+// copies a selection to the device (checked against `limit`); returns the device pointer or null for "all"
+static const i64* stage_selection(acc_engine& E, const int64_t* idx, size_t n, i64 limit, size_t offset, const char* what) {
+    if (n == 0) return nullptr;
+    if (idx == nullptr) fail(std::string("acc_observe: null selection of ") + what);
+    for (size_t k = 0; k < n; ++k) if (idx[k] < 0 || idx[k] >= limit) fail(std::string("acc_observe: selected ") + what + " out of range");
+    if (E.obs_idx.n < offset + n) {
+        DBuf<i64> bigger;
+        bigger.alloc(std::max<size_t>(offset + n, 2 * E.obs_idx.n));
+        E.obs_idx.free();
+        E.obs_idx = bigger;
+    }
+    std::vector<i64> h(idx, idx + n);
+    h2d(E.obs_idx.p + offset, h.data(), n * sizeof(i64), E.stream);
+    dev_sync(E.stream);
+    return E.obs_idx.p + offset;
+}
+
+static void observe(acc_engine& E, const std::string& group, const char* var, const int64_t* idx0, size_t n0, const int64_t* idx1, size_t n1, double* dst,
+                    size_t cap, size_t* n) {
+    stream_t s = E.stream;
+    auto out_buffer = [&](size_t cells) {
+        if (E.obs_out.n < cells) { E.obs_out.free(); E.obs_out.alloc(cells); }
+        return E.obs_out.p;
+    };
+    auto deliver = [&](size_t cells) { d2h(dst, E.obs_out.p, cells * sizeof(double), s); };
+    if (group == "firms" || group == "consumers") {
+        const bool firms = group == "firms";
+        int id = find_obs(k_agent_names, var);
+        if (id < 0) id = firms ? find_obs(k_firm_names, var) : find_obs(k_consumer_names, var);
+        if (id < 0) fail("acc_observe: unknown observable " + group + "/" + var);
+        if (n1 != 0) fail("acc_observe: " + group + " take one selection (agents)");
+        const size_t cells = n0 ? n0 : (size_t)E.nA;
+        *n = cells;
+        if (dst == nullptr) return;
+        if (cap < cells) fail("acc_observe: destination too small");
+        const i64* sel = stage_selection(E, idx0, n0, E.nA, 0, "agent");
+        if (id == FV_INCOMING_DEMAND_Q || id == FV_INCOMING_DEMAND_V) {
+            if (E.obs_inc_q.n == 0) { E.obs_inc_q.alloc(E.nA); E.obs_inc_v.alloc(E.nA); }
+            E.obs_inc_q.zero(s); E.obs_inc_v.zero(s);
+            FirmIncomingDemand k{E.edge_view(), E.firm_ids.p, E.obs_inc_q.p, E.obs_inc_v.p};
+            E.timed("firm_incoming_demand", [&] { launch_block(s, E.nF, k); });
+        }
+        ObserveAgents k{id, firms ? 1 : 0, sel, E.firm_view(), E.storage_view(), E.mp, E.in_off.p, E.s_dem_q.p, E.s_dem_v.p, E.obs_inc_q.p, E.obs_inc_v.p,
+                        E.mp.utilitarian ? E.c_utility.p : nullptr, out_buffer(cells)};
+        E.timed("observe_agents", [&] { launch_thread(s, (int)cells, k); });
+        deliver(cells);
+        return;
+    }
+    if (group == "storages") {
+        const int id = find_obs(k_storage_names, var);
+        if (id < 0) fail("acc_observe: unknown observable storages/" + std::string(var));
+        if (n0 != 0) fail("acc_observe: storages cannot be selected by sector (nor can the reference's output, ArrayOutput.cpp:575); select agents with idx1");
+        const size_t n_sel = n1 ? n1 : (size_t)E.nA;
+        const size_t cells = (size_t)E.nS * n_sel;
+        *n = cells;
+        if (dst == nullptr) return;
+        if (cap < cells) fail("acc_observe: destination too small");
+        if (cells >= (size_t)0x7fffffff) fail("acc_observe: selection too large");
+        if ((id == SV_SHIPMENT_Q || id == SV_SHIPMENT_V) && E.ship_step < 0) fail("acc_observe: no timestep has run yet");
+        const i64* sel = stage_selection(E, idx1, n1, E.nA, 0, "agent");
+        ObserveStorages k{id, (int)n_sel, E.nA, sel, E.sto_of.p, E.storage_view(), E.edge_view(), E.mp, E.ship_step, E.in_off.p, E.in_edge.p, E.s_dem_q.p,
+                          E.s_dem_v.p, E.s_exp_costs.p, E.s_opt_val.p, E.s_tpen.p, out_buffer(cells)};
+        E.timed("observe_storages", [&] { launch_thread(s, (int)cells, k); });
+        deliver(cells);
+        return;
+    }
+    if (group == "flows") {
+        const int id = find_obs(k_flow_names, var);
+        if (id < 0) fail("acc_observe: unknown observable flows/" + std::string(var));
+        if (n0 != 0 && n1 != 0) fail("acc_observe: selection on both source agent and target agent not supported (as in the reference, ArrayOutput.cpp:469-471)");
+        if (E.partitioned) fail("acc_observe: flows of a region-partitioned engine are read per part with acc_read_state");
+        const size_t rows = n0 ? n0 : (size_t)E.nA, cols = n1 ? n1 : (size_t)E.nA;
+        const size_t cells = rows * cols;
+        *n = cells;
+        if (dst == nullptr) return;
+        if (cap < cells) fail("acc_observe: destination too small");
+        if (cells >= (size_t)0x7fffffff) fail("acc_observe: selection too large: select source or target agents");
+        if (E.ship_step < 0) fail("acc_observe: no timestep has run yet");
+        double* out = out_buffer(cells);
+        ObsFill fill{out};
+        E.timed("observe_fill", [&] { launch_thread(s, (int)cells, fill); });
+        if (n1 == 0) {
+            const i64* sel = stage_selection(E, idx0, n0, E.nA, 0, "agent");
+            ObserveFlowsFrom k{id, (int)cols, sel, E.edge_view(), E.ship_step, E.a_type.p, E.e_to.p, out};
+            E.timed("observe_flows", [&] { launch_block(s, (int)rows, k); });
+        } else {
+            const i64* sel = stage_selection(E, idx1, n1, E.nA, 0, "agent");
+            ObserveFlowsTo k{id, (int)cols, E.max_storages, sel, E.edge_view(), E.ship_step, E.a_st_off.p, E.a_st_list.p, E.in_off.p, E.in_edge.p, E.in_seller.p,
+                             E.row_firm.p, out};
+            E.timed("observe_flows", [&] { launch_block(s, (int)(cols * (size_t)E.max_storages), k); });
+        }
+        deliver(cells);
+        return;
+    }
+    if (group == "sectors" || group == "regions") {
+        // a few dozen to a few hundred cells: folded on the host in the reference's serial order from per-agent / per-storage arrays
+        const bool sectors = group == "sectors";
+        const std::string v = var;
+        std::string state;
+        char kind = 'v';
+        if (sectors) {
+            if (v == "total_production_quantity") { state = "sector_production_q"; kind = 'q'; }
+            else if (v == "total_production_value") state = "sector_production_v";
+            else if (v == "total_demand_quantity") { state = "sector_demand_q"; kind = 'q'; }
+            else if (v == "total_demand_value") state = "sector_demand_v";
+            else if (v == "offer_price") { state = "sector_production_q"; kind = 'P'; }
+        } else {
+            static const char* names[] = {"import", "export", "consumption", "gdp"};
+            for (const char* nm : names) {
+                if (v == std::string(nm) + "_quantity") { state = std::string("region_") + nm + "_q"; kind = 'q'; }
+                if (v == std::string(nm) + "_value") state = std::string("region_") + nm + "_v";
+            }
+        }
+        // GeoEntity::observe on a region (include/model/GeoEntity.h:64-80): the transport chain links registered AT the region.  Routes
+        // of a snapshot lead over connections, ports and sea areas, never through a region, so a region holds no link: Flow(0.0)
+        const bool no_links = !sectors && (v == "total_flow_quantity" || v == "total_flow_value" || v == "total_outflow_quantity" || v == "total_outflow_value");
+        if (state.empty() && !no_links) fail("acc_observe: unknown observable " + group + "/" + v);
+        if (n1 != 0) fail("acc_observe: " + group + " take one selection");
+        const i64 limit = sectors ? E.nS : E.nR;
+        const size_t cells = n0 ? n0 : (size_t)limit;
+        *n = cells;
+        if (dst == nullptr) return;
+        if (cap < cells) fail("acc_observe: destination too small");
+        for (size_t k = 0; k < n0; ++k) if (idx0[k] < 0 || idx0[k] >= limit) fail("acc_observe: selection out of range");
+        if (no_links) { for (size_t k = 0; k < cells; ++k) dst[k] = 0.0; return; }
+        StateArray a, b;
+        if (!read_state(E, state, a)) fail("acc_observe: internal mapping error");
+        if (kind == 'P' && !read_state(E, "sector_production_v", b)) fail("acc_observe: internal mapping error");
+        for (size_t k = 0; k < cells; ++k) {
+            const size_t j = n0 ? (size_t)idx0[k] : k;
+            // the consumers' sector produces and sells nothing: its sums are the empty Flow the reference reports too
+            if (kind == 'q') dst[k] = qf(a.i[j]);
+            else if (kind == 'P') dst[k] = pf(flow_price(mkflow(a.i[j], b.f[j])));  // Sector.h:78-80: total_production_X().get_price()
+            else dst[k] = a.f[j];
+        }
+        return;
+    }
+    fail("acc_observe: unknown group '" + group + "' (firms, consumers, sectors, regions, storages, flows)");
+}
+}  // namespace acc
+
+extern "C" int acc_observe(acc_engine* e, const char* group, const char* variable, const int64_t* idx0, size_t n0, const int64_t* idx1, size_t n1, double* dst,
+                           size_t cap, size_t* n) {
+    ACC_API_BEGIN
+    if (e == nullptr || group == nullptr || variable == nullptr || n == nullptr) fail("acc_observe: null argument");
+    ACC_ON_DEVICE(e);
+    acc::observe(*e, group, variable, idx0, n0, idx1, n1, dst, cap, n);
+    return 0;
+    ACC_API_END(-1)
+}
+
 // ---- state checkpoint: blob header and the visitors over acc_engine::visit_state ----
 namespace {
 struct StateHeader {
@@ -1639,9 +2018,11 @@ void acc_destroy(acc_engine* e) {
     for (DBuf<int>* b : {&e->a_type, &e->a_sector, &e->a_region, &e->a_st_off, &e->a_st_list, &e->firm_ids, &e->s_agent, &e->s_sector, &e->s_iters,
                          &e->s_evals, &e->e_seller_off, &e->e_route, &e->route_off, &e->route_ent, &e->ell_width, &e->ell_edge, &e->in_edge, &e->in_seller, &e->ev_count})
         b->free();
-    e->e_tau.free(); e->e_dom.free(); e->sectors.free(); e->pub.free(); e->ev_buf.free();
-    e->ent_delay.free(); e->e_ship_q.free();
+    e->e_tau.free(); e->e_dom.free(); e->sectors.free(); e->pub.free(); e->pubT.free(); e->seller_row.free(); e->row_firm.free(); e->e_to.free(); e->sto_of.free(); e->obs_out.free(); e->obs_idx.free(); e->obs_inc_q.free(); e->obs_inc_v.free(); e->ev_buf.free();
+    e->ent_delay.free(); e->e_ship_q.free(); e->e_ship_v.free();
     e->owned.free(); e->pm_ids.free(); e->halo_send.free(); e->halo_recv.free();
+    for (DBuf<i64>* b : {&e->own_flow_send, &e->own_flow_recv, &e->own_dem_send, &e->own_dem_recv, &e->own_sellers, &e->comm_rows_send, &e->comm_rows_recv}) b->free();
+    e->comm_part_firms.free(); e->comm_part_off.free();
     for (DBuf<int>* b : {&e->cons_ids, &e->c_order_cnt, &e->c_order, &e->c_order_basket, &e->fatal}) b->free();
     for (DBuf<double>* b : {&e->c_share, &e->c_eshare, &e->c_prev_v, &e->c_budget, &e->c_bshare, &e->c_ebshare, &e->c_utility, &e->c_intra_exp}) b->free();
     e->c_base_q.free(); e->c_prev_q.free();
@@ -1696,9 +2077,17 @@ int acc_set_halo(acc_engine* e, const int64_t* send_edges, size_t n_send, const 
     if (e == nullptr) fail("acc_set_halo: null engine");
     ACC_ON_DEVICE(e);
     if (!e->partitioned) fail("acc_set_halo: the engine was not created with acc_create_partition");
-    if ((n_send && (send_edges == nullptr || flow_send == nullptr || demand_recv == nullptr)) ||
-        (n_recv && (recv_edges == nullptr || flow_recv == nullptr || demand_send == nullptr)) || seller_table == nullptr)
-        fail("acc_set_halo: null list or exchange buffer");
+    if ((n_send && send_edges == nullptr) || (n_recv && recv_edges == nullptr)) fail("acc_set_halo: null list");
+    const bool own_buffers = flow_send == nullptr && flow_recv == nullptr && demand_send == nullptr && demand_recv == nullptr && seller_table == nullptr;
+    if (own_buffers) {  // the engine keeps the exchange buffers itself (the NCCL plane of acc_step_partitioned needs no caller's)
+        e->own_flow_send.alloc(2 * n_send); e->own_dem_recv.alloc(2 * n_send); e->own_flow_recv.alloc(2 * n_recv); e->own_dem_send.alloc(2 * n_recv);
+        e->own_sellers.alloc((size_t)e->nA * ACC_SELLER_WORDS);
+        for (DBuf<i64>* b : {&e->own_flow_send, &e->own_dem_recv, &e->own_flow_recv, &e->own_dem_send, &e->own_sellers}) b->zero(e->stream);
+        flow_send = e->own_flow_send.p; flow_recv = e->own_flow_recv.p; demand_send = e->own_dem_send.p; demand_recv = e->own_dem_recv.p;
+        seller_table = e->own_sellers.p;
+    }
+    if ((n_send && (flow_send == nullptr || demand_recv == nullptr)) || (n_recv && (flow_recv == nullptr || demand_send == nullptr)) || seller_table == nullptr)
+        fail("acc_set_halo: null exchange buffer (pass all five, or none to let the engine allocate them)");
     if (n_send >= (size_t)0x7fffffff || n_recv >= (size_t)0x7fffffff) fail("acc_set_halo: halo too large");
     for (size_t k = 0; k < n_send; ++k) if (send_edges[k] < 0 || send_edges[k] >= e->nE) fail("acc_set_halo: send connection out of range");
     for (size_t k = 0; k < n_recv; ++k) if (recv_edges[k] < 0 || recv_edges[k] >= e->nE) fail("acc_set_halo: receive connection out of range");
@@ -1711,6 +2100,75 @@ int acc_set_halo(acc_engine* e, const int64_t* send_edges, size_t n_send, const 
     return 0;
     ACC_API_END(-1)
 }
+
+int acc_comm_unique_id(void* id) {
+    ACC_API_BEGIN
+    if (id == nullptr) fail("acc_comm_unique_id: null argument");
+#ifdef ACC_HOST_EMU
+    fail("acc_comm_unique_id: the emulation has no NCCL");
+#else
+    NcclApi::unique_id u;
+    ACC_NCCL(NcclApi::get().GetUniqueId(&u));
+    std::memcpy(id, &u, sizeof u);
+#endif
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_comm_init(acc_engine* e, const void* id, int rank, int world, const int32_t* agent_part, const int64_t* send_counts, const int64_t* recv_counts) {
+    ACC_API_BEGIN
+    if (e == nullptr || id == nullptr || agent_part == nullptr || send_counts == nullptr || recv_counts == nullptr) fail("acc_comm_init: null argument");
+    ACC_ON_DEVICE(e);
+    if (!e->partitioned || e->x_sellers == nullptr) fail("acc_comm_init: create the engine with acc_create_partition and call acc_set_halo first");
+    if (world < 1 || rank < 0 || rank >= world) fail("acc_comm_init: rank / world out of range");
+#ifdef ACC_HOST_EMU
+    fail("acc_comm_init: the emulation has no NCCL; drive the stages with acc_stage");
+#else
+    if (e->comm != nullptr) fail("acc_comm_init: the engine has a communicator already");
+    // how the halo lists split over the peers (they are grouped by peer, acc_set_halo)
+    e->comm_send_cnt.assign(send_counts, send_counts + world); e->comm_recv_cnt.assign(recv_counts, recv_counts + world);
+    e->comm_send_off.assign(world + 1, 0); e->comm_recv_off.assign(world + 1, 0);
+    for (int p = 0; p < world; ++p) {
+        if (send_counts[p] < 0 || recv_counts[p] < 0 || (p == rank && (send_counts[p] || recv_counts[p]))) fail("acc_comm_init: bad halo counts");
+        e->comm_send_off[p + 1] = e->comm_send_off[p] + send_counts[p];
+        e->comm_recv_off[p + 1] = e->comm_recv_off[p] + recv_counts[p];
+    }
+    if ((size_t)e->comm_send_off[world] != e->halo_send.n || (size_t)e->comm_recv_off[world] != e->halo_recv.n)
+        fail("acc_comm_init: the per-peer counts do not add up to the halo lists of acc_set_halo");
+    // the firms of every part, in agent order: rows of the sellers' all-gather
+    std::vector<int> part_off(world + 1, 0), part_firms;
+    for (int p = 0; p < world; ++p) {
+        for (int a = 0; a < e->nA; ++a) {
+            if (agent_part[a] < 0 || agent_part[a] >= world) fail("acc_comm_init: agent_part out of range");
+            if (agent_part[a] == p && e->h_agent_type[a] == 1) part_firms.push_back(a);
+        }
+        part_off[p + 1] = (int)part_firms.size();
+        e->comm_max_rows = std::max(e->comm_max_rows, part_off[p + 1] - part_off[p]);
+    }
+    if (part_off[rank + 1] - part_off[rank] != e->nF) fail("acc_comm_init: agent_part does not match the ownership mask the engine was created with");
+    e->comm_part_firms.upload(part_firms, e->stream); e->comm_part_off.upload(part_off, e->stream);
+    e->comm_rows_send.alloc((size_t)e->comm_max_rows * ACC_SELLER_WORDS); e->comm_rows_send.zero(e->stream);
+    e->comm_rows_recv.alloc((size_t)world * e->comm_max_rows * ACC_SELLER_WORDS); e->comm_rows_recv.zero(e->stream);
+    dev_sync(e->stream);
+    NcclApi::unique_id u;
+    std::memcpy(&u, id, sizeof u);
+    e->comm_rank = rank; e->comm_world = world;
+    ACC_NCCL(NcclApi::get().CommInitRank(&e->comm, world, u, rank));
+#endif
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_step_partitioned(acc_engine* e) {
+    ACC_API_BEGIN
+    if (e == nullptr) fail("acc_step_partitioned: null engine");
+    ACC_ON_DEVICE(e);
+    e->step_partitioned();
+    return 0;
+    ACC_API_END(-1)
+}
+
+int64_t acc_collective_count(const acc_engine* e) { return e ? e->collectives : -1; }
 
 int acc_stage(acc_engine* e, int stage) {
     ACC_API_BEGIN
@@ -1934,6 +2392,11 @@ int acc_load_state(acc_engine* e, const void* src, size_t bytes) {
     e->visit_state(v);
     acc::dev_sync(e->stream);
     e->step = h.step; e->reg = (int)h.reg; e->ship_step = h.ship_step;
+    {   // the field-major twin of the seller records is derived state: rebuild it from the loaded records
+        RepublishSellers k{e->pub.p, e->seller_table()};
+        launch_thread(e->stream, e->nA, k);
+        acc::dev_sync(e->stream);
+    }
     return 0;
     ACC_API_END(-1)
 }

@@ -298,11 +298,43 @@ struct SellerPub {
     double n_co;      // estimate_marginal_production_costs at the seller's production with n_c un-rounded (:323-326)
 };
 
+// The same record once more, field-major over the firms in SECTOR-MAJOR order ("seller rows": the firms of one sector are
+// consecutive).  A purchasing manager's connections all lead to sellers of one sector, in ascending agent order, so a warp
+// that gathers the records of consecutive connections reads consecutive rows: every field is one coalesced 8-byte read per
+// lane instead of 32 strided 72-byte rows.  Two values every buyer would derive from the record alone are stored with it
+// (expected_production / production and the extension penalty at the expected production, PurchasingManager.cpp:334-349,
+// :279-289 -- both for an unforced route, minimum passage 1; a buyer behind a throttled route recomputes them).
+enum { SPT_XHAT_Q = 0, SPT_XHATF, SPT_XF, SPT_XEXPF, SPT_NBARF, SPT_LAMXF, SPT_C1, SPT_C2, SPT_NCO, SPT_RR, SPT_NPEE, SPT_FIELDS };
+struct SellerTable {
+    double* f;        // [SPT_FIELDS][stride]; field SPT_XHAT_Q holds the int64's bits
+    const int* row;   // agent -> seller row (-1: not a firm)
+    i64 stride;
+};
+ACC_HD double spt_ratio(double Xe, double X) { return (X > 0.0) ? Xe / X : 0.0; }
+ACC_HD double spt_extension_penalty(double c1, double Xe, double lamXf) {
+    return (Xe > lamXf && Xe > 0.0) ? stdmax(0.0, c1 * (Xe - lamXf) * (Xe - lamXf)) / Xe : 0.0;
+}
+ACC_HD void publish_seller(const SellerTable& t, int agent, const SellerPub& pb) {
+    if (t.f == nullptr) return;
+    const int r = t.row[agent];
+    if (r < 0) return;
+    double* f = t.f + r;
+    i64 bits = pb.Xhat_q;
+    double xq;
+    memcpy(&xq, &bits, sizeof xq);
+    f[SPT_XHAT_Q * t.stride] = xq; f[SPT_XHATF * t.stride] = pb.Xhatf; f[SPT_XF * t.stride] = pb.Xf; f[SPT_XEXPF * t.stride] = pb.Xexpf;
+    f[SPT_NBARF * t.stride] = pb.nbarf; f[SPT_LAMXF * t.stride] = pb.lamXf; f[SPT_C1 * t.stride] = pb.c1; f[SPT_C2 * t.stride] = pb.c2;
+    f[SPT_NCO * t.stride] = pb.n_co;
+    f[SPT_RR * t.stride] = spt_ratio(pb.Xexpf, pb.Xf);
+    f[SPT_NPEE * t.stride] = spt_extension_penalty(pb.c1, pb.Xexpf, pb.lamXf);
+}
+
 // ------------------------------------------------------------------------------------------------
 // Per-firm state
 // ------------------------------------------------------------------------------------------------
 struct FirmView {
     SellerPub* pub;                 // published after the expectation phase, read by the purchasing phase
+    SellerTable pubT;               // ... and its field-major twin
     const i64* Xstar_q; const double* Xstar_v; const double* beta; const double* lambda; const int* sector; const int* region; const int* type;
     const i64* markup_eff; const i64* var_costs;  // SalesManager::get_initial_markup / get_initial_unit_variable_production_costs
     const int* st_off; const int* st_list;        // the agent's input storages, reference container order
@@ -334,7 +366,7 @@ struct EdgeView {
     i64 n_edges; int T;
     i64* ovf_q; double* ovf_v;      // overflow per (hop, connection): [hop][n_edges] (null until passage forcing is used)
     const double* nu;               // passage per geo entity (null until used; < 0: none)
-    i64* ship_q;                    // last shipment (only kept apart when hops may rewrite its conveyor slot, else null)
+    i64* ship_q; double* ship_v;    // last shipment (only kept apart when hops may rewrite its conveyor slot, else null)
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -450,7 +482,7 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
             int pl = plane_now + tau[i];  // (step + delay) mod T without the division: delay < T
             if (pl >= T) pl -= T;
             ev.conv_q[(i64)pl * ev.n_edges + e0 + i] = 0;
-            if (ev.ship_q != nullptr) ev.ship_q[e0 + i] = 0;
+            if (ev.ship_q != nullptr) { ev.ship_q[e0 + i] = 0; ev.ship_v[e0 + i] = 0.0; }
             ev.conv_v[(i64)pl * ev.n_edges + e0 + i] = 0.0;
         });
     } else {
@@ -499,7 +531,7 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
             int pl = plane_now + tau[i];  // (step + delay) mod T without the division: delay < T
             if (pl >= T) pl -= T;
             ev.conv_q[(i64)pl * ev.n_edges + e0 + i] = z.q;           // BusinessConnection::push_flow_Z -> first transport link
-            if (ev.ship_q != nullptr) ev.ship_q[e0 + i] = z.q;        // last_shipment_Z, kept apart when hops rewrite the slot
+            if (ev.ship_q != nullptr) { ev.ship_q[e0 + i] = z.q; ev.ship_v[e0 + i] = z.v; }  // last_shipment_Z, kept apart when hops rewrite the slot
             ev.conv_v[(i64)pl * ev.n_edges + e0 + i] = z.v;
             if (!dom[i]) { r.eq = z.q; r.ev = z.v; }                  // Region::add_export_Z, BusinessConnection.cpp:91-93
             return r;
@@ -626,6 +658,7 @@ ACC_HD void seller_phase2(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
         const double ncf = xh.v / qf(xh.q);  // get_price_float(); only read when Xhat_q > 0
         pb.n_co = (pb.Xf <= pb.lamXf) ? ncf : ncf + pb.c2 * (pb.Xf - pb.lamXf);
         fv.pub[f] = pb;
+        publish_seller(fv.pubT, f, pb);
     }
     // Firm::iterate_expectation, Firm.cpp:65-73: sum_demand_requests_D was zeroed two lines earlier
     // (SalesManager.cpp:623), so the desired production is the expected production

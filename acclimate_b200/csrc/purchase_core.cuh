@@ -52,23 +52,27 @@ ACC_HD double pm_scaled_slope(double slope, double z_over_u) { return slope * z_
 // Slot-major: the V f64 values of connection slot r are contiguous, so one index computation per slot serves every
 // vector (the vector is a compile-time offset) and one base register serves them all.  With an even V one f64 of
 // padding follows every eight slots, which keeps the 16 eight-byte accesses of a half-warp on different banks.
-// V = 19: 9 of the solver (x, x0, g, a, d, b, gl, xbest, xu) + 8 price-curve values + the two summands of the ordered
-// sums; 20 with deviation_penalty (the penalty target is then the last demand request instead of Z*).  Connection ids
-// are a separate int vector.
-// DVAL = false drops the D_r summand (the ordered sum then recomputes x_r Z*_r on the way): one vector less, which is
-// what lets two CTAs of the large solver groups (748 connections: 111 KB instead of 117 KB) share an SM.
+// V = 20: 9 of the solver (x, x0, g, a, d, b, gl, xbest, xu) + 8 price-curve values + the two summands of the ordered
+// sums + the x tolerance; one more with deviation_penalty (the penalty target is then the last demand request instead of
+// Z*).  Connection ids are a separate int vector.
+// DVAL = false drops the D_r summand (the ordered sum then recomputes x_r Z*_r on the way) and the x tolerance (divided
+// out where it is tested): two vectors less, which is what lets two CTAs of the large solver groups (748 connections:
+// 111 KB instead of 123 KB) share an SM.
+// Number of f64 per slot for a given number of vectors: a multiple of four would put lanes i and i + 4 of a half-warp on the
+// same banks whatever the padding (stride 8 i words mod 32), so it gets one unused f64 per slot.
+ACC_HD constexpr int pm_slot_doubles(int vectors) { return vectors % 4 == 0 ? vectors + 1 : vectors; }
 template <int V>
 ACC_HD int pm_slot_off(int i) { return (V % 2 == 0) ? i * V + (i >> 3) : i * V; }
 ACC_HD size_t pm_workspace_bytes(int n_max, bool separate_target, bool dval) {
-    const int v = 18 + (separate_target ? 1 : 0) + (dval ? 1 : 0);
+    const int v = pm_slot_doubles(18 + (separate_target ? 1 : 0) + (dval ? 2 : 0));
     const size_t doubles = (size_t)n_max * v + (v % 2 == 0 ? (size_t)(n_max >> 3) + 1 : 0);
     return doubles * sizeof(double) + (size_t)n_max * sizeof(int);
 }
 
 template <bool SEP, bool STD, bool DVAL>
 struct PMWorkT {
-    enum { V = 18 + (SEP ? 1 : 0) + (DVAL ? 1 : 0), TGT = SEP ? V - 1 : 9, COL_X = 0, COL_X0 = 1, COL_G = 2, COL_ZF = 9, COL_TERM = 17, COL_DVAL = 18,
-           HAS_DVAL = DVAL ? 1 : 0 };
+    enum { NVEC = 18 + (SEP ? 1 : 0) + (DVAL ? 2 : 0), V = pm_slot_doubles(NVEC), TGT = SEP ? NVEC - 1 : 9, COL_X = 0, COL_X0 = 1, COL_G = 2, COL_ZF = 9, COL_TERM = 17, COL_DVAL = 18,
+           COL_TOL = 19, HAS_DVAL = DVAL ? 1 : 0 };
     template <int K>
     struct Col {
         double* base;
@@ -79,10 +83,11 @@ struct PMWorkT {
         Col<8> xu;                            // upper bounds (lower bounds are all zero, :620)
         Col<9> zf;                            // x tolerance = quantum of the demand request over the variable's scale (:640-644)
         Col<TGT> tgt;                         // kink position in D_r
+        Col<COL_TOL> tolv;                    // (only with DVAL) the x tolerance, divided out once in the set-up pass
         double tol_c;
         PMParams pp;
         ACC_HD double lower(int) const { return 0.0; }
-        ACC_HD double tol(int i) const { return tol_c / zf[i]; }
+        ACC_HD double tol(int i) const { return DVAL ? tolv[i] : tol_c / zf[i]; }
         // kink of the transport penalty (sqp_core.h "Kinks"); a[i] = -(Z*_i / U*) is the constraint gradient
         ACC_HD bool kinked() const { return true; }
         ACC_HD int kside(int i, double xi) const { const double D = xi * zf[i], t = tgt[i]; return D < t ? -1 : (D > t ? 1 : 0); }
@@ -109,7 +114,7 @@ struct PMWorkT {
     ACC_HD void carve(unsigned char* mem, int n_max) {
         double* p = reinterpret_cast<double*>(mem);
         w.x.base = p; w.x0.base = p; w.g.base = p; w.a.base = p; w.d.base = p; w.b.base = p; w.gl.base = p; w.xbest.base = p;
-        w.xu.base = p; w.zf.base = p; w.tgt.base = p;
+        w.xu.base = p; w.zf.base = p; w.tgt.base = p; w.tolv.base = p;
         zf.base = p; tgt.base = p; addX.base = p; Xhatf.base = p; lamXf.base = p; c2.base = p; base.base = p; n_co.base = p;
         slope.base = p; term.base = p; dval.base = p;
         eid = reinterpret_cast<int*>(mem + pm_workspace_bytes(n_max, SEP, DVAL) - (size_t)n_max * sizeof(int));
@@ -251,11 +256,12 @@ struct PMResult {
 // The caller's `gather(i)` resolves it; the group contexts call it for two connections of a thread before either is
 // worked on (reduce_staged), so the dependent loads of both are in flight together.
 struct PMGather {
-    int e, seller;   // connection id, seller agent of the i-th incoming connection (seller ascending)
+    int e, seller;   // connection id, seller row (SellerTable) of the i-th incoming connection (seller ascending)
     i64 last_q;      // last shipment on the connection (:346)
     i64 Z_q;         // initial flow Z*
     i64 lastD_q;     // last demand request (read with deviation_penalty only)
     SellerPub sp;    // the seller's published supply parameters (SalesManager.h:38-43)
+    double rr, npeE; // expected production / production and the extension penalty at the expected production, for minimum passage 1
 };
 
 // Inputs of one purchasing manager, gathered by the caller-provided accessors:
@@ -288,10 +294,11 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, Gather gather, Mi
         k.eid[r] = e;
         if (sp.Xhat_q <= 0) return 0;                                           // :604-605
         const double nu = min_passage(e);
+        const bool open_route = nu == 1.0;                                      // then nu * x == x bit for bit and the seller's own values apply
         const double Xe = nu * sp.Xexpf;                                        // expected_production, :334-341
         const double X = sp.Xf;
         const double Zl = qf(in.last_q);
-        const double rr = (X > 0.0) ? Xe / X : 0.0;
+        const double rr = open_route ? in.rr : spt_ratio(Xe, X);
         const double add = rr * (X - Zl);                                       // expected_additional_production, :343-349
         double Xmax = sp.Xhatf;
         Xmax *= nu;                                                             // :612-614
@@ -309,8 +316,8 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, Gather gather, Mi
         // n_r constants, :279-289 (penalty terms only divided out inside the production extension)
         const double Dmin = stdmax(0.0, lamXf - add);
         const double Xmin = Dmin + add;
-        double npeE = 0.0, npeMin = 0.0;
-        if (Xe > lamXf && Xe > 0.0) npeE = stdmax(0.0, sp.c1 * (Xe - lamXf) * (Xe - lamXf)) / Xe;
+        double npeMin = 0.0;
+        const double npeE = open_route ? in.npeE : spt_extension_penalty(sp.c1, Xe, lamXf);
         if (Xmin > lamXf && Xmin > 0.0) npeMin = stdmax(0.0, sp.c1 * (Xmin - lamXf) * (Xmin - lamXf)) / Xmin;
         const double nbar_min = sp.nbarf - npeE + npeMin;
         // E_n_r's four cases collapse to  base [+ pen(X_new)/X_new]  with base = n_bar [- pen(X_exp)/X_exp]
@@ -323,6 +330,7 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, Gather gather, Mi
         k.w.xu[r] = upper / zf;
         k.w.x[r] = stdmin(upper, stdmax(0.0, Xe - add)) / zf;
         k.w.a[r] = -(zf / pp.Uf);
+        if (PW::HAS_DVAL) k.w.tolv[r] = k.w.tol_c / zf;
         return dmax;
     };
     // the same pass counts the connections that take part and sums their D_r_max (integers: any order)

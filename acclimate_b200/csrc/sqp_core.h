@@ -126,6 +126,11 @@ struct Sum3 {
     static SQP_HD Sum3 identity() { Sum3 r; r.a = 0.0; r.b = 0.0; r.c = 0.0; return r; }
     static SQP_HD Sum3 combine(Sum3 x, Sum3 y) { Sum3 r; r.a = x.a + y.a; r.b = x.b + y.b; r.c = x.c + y.c; return r; }
 };
+struct Sum4 {
+    double a, b, c, d;
+    static SQP_HD Sum4 identity() { Sum4 r; r.a = 0.0; r.b = 0.0; r.c = 0.0; r.d = 0.0; return r; }
+    static SQP_HD Sum4 combine(Sum4 x, Sum4 y) { Sum4 r; r.a = x.a + y.a; r.b = x.b + y.b; r.c = x.c + y.c; r.d = x.d + y.d; return r; }
+};
 struct MinMax {
     double lo, hi;
     static SQP_HD MinMax identity() { MinMax r; r.lo = 1e308; r.hi = -1e308; return r; }
@@ -185,9 +190,15 @@ SQP_HD Sum2 qp_range_term(const W& w, int i) {
 // of a per-coordinate objective computes it on the way, see sqp_eval_pass), else null.
 // `lambda_start`: where the root-find begins -- the multiplier of the previous SQP iteration (psi is piecewise linear and
 // Newton's steps exact between breakpoints, so starting next to the root saves passes; 0 for the first iteration).
+// `step_sums` / `have_sums`: every pass of the root-find forms the whole step d(lambda) anyway, so it also stores it in w.d and
+// returns the three sums the driver needs from the step (a.d, number of coordinates whose step reaches the x tolerance, model
+// change of the objective g.d + kink terms).  When the root-find ends on a pass at the returned multiplier -- every exit but
+// the exhausted iteration cap -- the driver needs no pass of its own to form the step.
 template <class Ctx, class W>
-SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, bool* d_ready, const Sum2* known_range, double lambda_start) {
+SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, bool* d_ready, const Sum2* known_range, double lambda_start,
+                       Sum3* step_sums, bool* have_sums) {
     *d_ready = false;
+    *have_sums = false;
     const bool kinked = w.kinked();
     if (ctype == CON_NONE) return 0.0;
     const double target = -c;  // want a^T d = target
@@ -236,16 +247,23 @@ SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, boo
     bool prev_valid = false;
     bool converged = false;
     int it = 0;
+    Sum4 ps = Sum4::identity();
     for (; it < 200; ++it) {
-        // psi and its slope at lambda
-        const Sum2 ps = cx.template reduce<Sum2>(n, [&](int i) {
+        // psi and its slope at lambda; the step itself and the driver's sums on the way
+        ps = cx.template reduce<Sum4>(n, [&](int i) {
             bool smooth;
             const double t = qp_free_step(w, i, lambda, kinked, &smooth);
             const double lo = ACCSQP_LO(w, i), hi = ACCSQP_HI(w, i);
-            Sum2 r;
-            if (t <= lo) { r.a = w.a[i] * lo; r.b = 0.0; }
-            else if (t >= hi) { r.a = w.a[i] * hi; r.b = 0.0; }
-            else { r.a = w.a[i] * t; r.b = smooth ? w.a[i] * w.a[i] * w.b[i] : 0.0; }
+            Sum4 r;
+            double di;
+            if (t <= lo) { di = lo; r.b = 0.0; }
+            else if (t >= hi) { di = hi; r.b = 0.0; }
+            else { di = t; r.b = smooth ? w.a[i] * w.a[i] * w.b[i] : 0.0; }
+            r.a = w.a[i] * di;
+            w.d[i] = di;
+            r.c = (fabs(di) < w.tol(i)) ? 0.0 : 1.0;
+            r.d = w.g[i] * di;
+            if (kinked) r.d += kink_phi(w, i, w.x[i] + di) - kink_phi(w, i, w.x[i]);  // model decrease incl. the kink term
             return r;
         });
         const double psi = c + ps.a, slope = ps.b;
@@ -271,6 +289,11 @@ SQP_HD double qp_solve(Ctx& cx, int n, int ctype, double c, W& w, Stats& st, boo
         }
         lambda = next;
     }
+    if (it < 200) {  // the last pass ran at the multiplier that is returned: w.d holds its step
+        *d_ready = true;
+        *have_sums = true;
+        step_sums->a = ps.a; step_sums->b = ps.c; step_sums->c = ps.d;
+    }
     st.qp_iters += it;
     if (!converged) st.qp_inexact += 1;
     return lambda;
@@ -295,24 +318,48 @@ struct EvalTraits {
     enum { PER_COORD = 0 };
 };
 
+// contribution of coordinate i to the driver's first multiplier estimate (see sqp_minimize): a_i g_i and a_i^2 next to the range
+template <class W>
+SQP_HD Sum4 qp_start_term(const W& w, int i) {
+    const Sum2 rg = qp_range_term(w, i);
+    Sum4 r; r.a = rg.a; r.b = rg.b; r.c = w.a[i] * w.g[i]; r.d = w.a[i] * w.a[i]; return r;
+}
+
 // x_i <- newx(i) for every coordinate, objective / constraint / gradient there, smooth part of the gradient in w.g.
-// Returns true when *range holds the attainable range of a^T d at the new x.
+// Returns true when *range holds the attainable range of a^T d at the new x.  With `start` not null (the first evaluation
+// of a run) the range comes with the two sums of the multiplier estimate, whichever way the objective is evaluated.
 template <class Ctx, class Eval, class W, class NewX>
-SQP_HD bool sqp_eval_pass(Ctx& cx, Eval& ev, W& w, int n, bool kinked, NewX newx, double* F, double* c, Sum2* range) {
+SQP_HD bool sqp_eval_pass(Ctx& cx, Eval& ev, W& w, int n, bool kinked, NewX newx, double* F, double* c, Sum2* range, Sum4* start = nullptr) {
     if constexpr (EvalTraits<Eval>::PER_COORD != 0) {
-        *range = cx.template reduce<Sum2>(n, [&](int i) {
-            const double xi = newx(i);
-            w.x[i] = xi;
-            ev.coord(i, xi);
-            if (kinked) w.g[i] -= kink_sigma(w, i, xi);
-            return qp_range_term(w, i);
-        });
+        if (start != nullptr) {
+            *start = cx.template reduce<Sum4>(n, [&](int i) {
+                const double xi = newx(i);
+                w.x[i] = xi;
+                ev.coord(i, xi);
+                if (kinked) w.g[i] -= kink_sigma(w, i, xi);
+                return qp_start_term(w, i);
+            });
+            range->a = start->a; range->b = start->b;
+        } else {
+            *range = cx.template reduce<Sum2>(n, [&](int i) {
+                const double xi = newx(i);
+                w.x[i] = xi;
+                ev.coord(i, xi);
+                if (kinked) w.g[i] -= kink_sigma(w, i, xi);
+                return qp_range_term(w, i);
+            });
+        }
         ev.finish(w.x, F, c);
         return true;
     } else {
         cx.foreach(n, [&](int i) { w.x[i] = newx(i); });
         ev(w.x, true, F, c);
         if (kinked) cx.foreach(n, [&](int i) { w.g[i] -= kink_sigma(w, i, w.x[i]); });  // keep the smooth part only
+        if (start != nullptr) {
+            *start = cx.template reduce<Sum4>(n, [&](int i) { return qp_start_term(w, i); });
+            range->a = start->a; range->b = start->b;
+            return true;
+        }
         return false;
     }
 }
@@ -333,6 +380,7 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
     const bool kinked = w.kinked();
     double F = 0.0, c = 0.0;
     Sum2 range;
+    Sum4 start;
     // NLopt clips the start point into the box; the first point is the best one so far
     bool have_range = sqp_eval_pass(cx, ev, w, n, kinked, [&](int i) {
         double xi = w.x[i];
@@ -341,7 +389,7 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
         w.b[i] = 1.0;
         w.xbest[i] = xi;
         return xi;
-    }, &F, &c, &range);
+    }, &F, &c, &range, &start);
     st.evals = 1;
     double viol = con_violation(p.ctype, c);
     bool feasible = viol <= p.ctol;
@@ -349,7 +397,9 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
     st.minf = F;
 
     bool b_identity = true;
-    double lambda_prev = 0.0;
+    // Where the first root-find starts: with the identity model and no bound or kink in the way the QP's multiplier is
+    // (a.g - c) / a.a exactly; the later ones start at their predecessor's multiplier.
+    double lambda_prev = (p.ctype == CON_EQ && start.d > 0.0) ? (start.c - c) / start.d : 0.0;
     double mu = 0.0;      // merit penalty parameter
     int ireset = 0;
     int ret = SQP_SUCCESS;
@@ -357,21 +407,22 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
     while (ret == SQP_SUCCESS) {
         ++st.iters;
         if (p.max_iter > 0 && st.iters > p.max_iter) { ret = SQP_FAILURE; break; }
-        bool d_ready = false;
-        const double lambda = qp_solve(cx, n, p.ctype, c, w, st, &d_ready, have_range ? &range : nullptr, lambda_prev);
+        bool d_ready = false, have_sums = false;
+        Sum3 sd;
+        const double lambda = qp_solve(cx, n, p.ctype, c, w, st, &d_ready, have_range ? &range : nullptr, lambda_prev, &sd, &have_sums);
         lambda_prev = lambda;
-        // One pass forms the step, the Lagrangian gradient at the old point with the new multiplier (Kraft: v), saves
-        // the old point and returns three sums: a.d (linearised constraint), the number of coordinates whose step
-        // reaches the x tolerance, and the model's first-order change of the objective g.d (+ change of the kink terms).
-        const Sum3 sd = cx.template reduce<Sum3>(n, [&](int i) {
-            const double di = d_ready ? w.d[i] : qp_step(w, i, lambda, kinked);
-            w.d[i] = di;
-            w.gl[i] = w.g[i] - lambda * w.a[i];
-            w.x0[i] = w.x[i];
-            Sum3 r; r.a = w.a[i] * di; r.b = (fabs(di) < w.tol(i)) ? 0.0 : 1.0; r.c = w.g[i] * di;
-            if (kinked) r.c += kink_phi(w, i, w.x[i] + di) - kink_phi(w, i, w.x[i]);  // model decrease incl. the kink term
-            return r;
-        });
+        // The step, its linearised constraint a.d, the number of coordinates whose step reaches the x tolerance and the model's
+        // first-order change of the objective g.d (+ change of the kink terms) come out of the root-find's last pass; only a
+        // vertex solution or an exhausted root-find leaves them to a pass of its own.
+        if (!have_sums) {
+            sd = cx.template reduce<Sum3>(n, [&](int i) {
+                const double di = d_ready ? w.d[i] : qp_step(w, i, lambda, kinked);
+                w.d[i] = di;
+                Sum3 r; r.a = w.a[i] * di; r.b = (fabs(di) < w.tol(i)) ? 0.0 : 1.0; r.c = w.g[i] * di;
+                if (kinked) r.c += kink_phi(w, i, w.x[i] + di) - kink_phi(w, i, w.x[i]);  // model decrease incl. the kink term
+                return r;
+            });
+        }
         const double cres = (p.ctype == CON_NONE) ? 0.0 : c + sd.a;
         // Step test (Kraft's convergence test is on the size of the QP step as well): when the full step is below the
         // x tolerance in every coordinate, no line search result can move x by a tolerance -- stop here instead of
@@ -405,6 +456,10 @@ SQP_HD int sqp_minimize(Ctx& cx, Eval& ev, W& w, const Params& p, Stats& st) {
             ++line;
             h3 = alpha * h3;
             have_range = sqp_eval_pass(cx, ev, w, n, kinked, [&](int i) {
+                if (line == 1) {  // the old point and the Lagrangian gradient there with the new multiplier (Kraft: v), before x and g move
+                    w.gl[i] = w.g[i] - lambda * w.a[i];
+                    w.x0[i] = w.x[i];
+                }
                 const double si = alpha * w.d[i];
                 w.d[i] = si;
                 double xi = w.x0[i] + si;

@@ -234,6 +234,22 @@ class Engine:
         self._check(self.lib.acc_read(self.h, group.encode(), variable.encode(), out.ctypes.data, out.size, C.byref(n)))
         return out
 
+    def observe(self, group, variable, select_from=None, select_to=None, out=None):
+        """acc_observe: one observable of one group, shaped like ArrayOutput's data of one timestep (NaN where there is no
+        object).  select_from / select_to: agent (sector, region) indices -- the reference's select_* of an `outputs:` entry."""
+        lib = self.lib
+        lib.acc_observe.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]
+        i0 = None if select_from is None else np.ascontiguousarray(select_from, dtype=np.int64)
+        i1 = None if select_to is None else np.ascontiguousarray(select_to, dtype=np.int64)
+        a0 = (i0.ctypes.data, i0.size) if i0 is not None else (None, 0)
+        a1 = (i1.ctypes.data, i1.size) if i1 is not None else (None, 0)
+        n = C.c_size_t(0)
+        if out is None:
+            self._check(lib.acc_observe(self.h, group.encode(), variable.encode(), a0[0], a0[1], a1[0], a1[1], None, 0, C.byref(n)))
+            out = np.empty(int(n.value), dtype=np.float64)
+        self._check(lib.acc_observe(self.h, group.encode(), variable.encode(), a0[0], a0[1], a1[0], a1[1], out.ctypes.data, out.size, C.byref(n)))
+        return out[: int(n.value)]
+
     def profile(self, enable=True):
         self._check(self.lib.acc_profile(self.h, 1 if enable else 0))
 

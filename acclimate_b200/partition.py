@@ -101,7 +101,10 @@ class PartitionedEngine(_engine.Engine):
     """One part of a region-partitioned model.  Needs an initialised torch.distributed process group with one rank
     per part (NCCL for the CUDA library; the CPU tests drive the emulation library over gloo)."""
 
-    def __init__(self, arrays, region_owner=None, device=0, lib_path=None, group=None, tensor_device=None, local=False):
+    def __init__(self, arrays, region_owner=None, device=0, lib_path=None, group=None, tensor_device=None, local=False, plane=None):
+        """plane: "nccl" -- the engine exchanges its halos itself (acc_comm_init / acc_step_partitioned: NCCL from C++ on the
+        engine's stream; default when the process group's backend is NCCL); "host" -- this class moves the exchange buffers
+        between the four stages with torch.distributed (gloo in the CPU tests, where the emulation library has no NCCL)."""
         import torch
         import torch.distributed as dist
 
@@ -124,17 +127,39 @@ class PartitionedEngine(_engine.Engine):
         if tensor_device is None:
             tensor_device = "cuda:%d" % device
         self.tensor_device = torch.device(tensor_device)
+        if plane is None:
+            plane = "nccl" if (world > 1 and dist.get_backend(group) == "nccl" and self.tensor_device.type == "cuda") else "host"
+        self.plane = plane
         p = self.part
         ns, nr = int(p.send_edges.size), int(p.recv_edges.size)
-        mk = lambda rows, cols: torch.zeros((rows, cols), dtype=torch.int64, device=self.tensor_device)
-        self.flow_send, self.flow_recv = mk(ns, 2), mk(nr, 2)
-        self.demand_send, self.demand_recv = mk(nr, 2), mk(ns, 2)
-        self.seller_table = mk(self.n_agents, SELLER_WORDS)
         self._send_ids = np.ascontiguousarray(p.send_edges)
         self._recv_ids = np.ascontiguousarray(p.recv_edges)
-        self._check(self.lib.acc_set_halo(self.h, self._send_ids.ctypes.data, ns, self._recv_ids.ctypes.data, nr, self.flow_send.data_ptr(),
-                                          self.flow_recv.data_ptr(), self.demand_send.data_ptr(), self.demand_recv.data_ptr(),
-                                          self.seller_table.data_ptr()))
+        if plane == "nccl":
+            # the engine keeps the exchange buffers and talks to its peers itself: nothing of the data plane is left here
+            self._check(self.lib.acc_set_halo(self.h, self._send_ids.ctypes.data, ns, self._recv_ids.ctypes.data, nr, None, None, None, None, None))
+            ident = torch.zeros(128, dtype=torch.uint8)
+            if rank == 0:
+                buf = (C.c_ubyte * 128)()
+                lib.acc_comm_unique_id.argtypes = [C.c_void_p]
+                self._check(lib.acc_comm_unique_id(buf))
+                ident = torch.tensor(list(buf), dtype=torch.uint8)
+            ident = ident.to(self.tensor_device)
+            dist.broadcast(ident, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+            raw = bytes(ident.cpu().tolist())
+            part32 = np.ascontiguousarray(p.agent_part, dtype=np.int32)
+            sc = np.ascontiguousarray(p.send_counts, dtype=np.int64)
+            rc = np.ascontiguousarray(p.recv_counts, dtype=np.int64)
+            lib.acc_comm_init.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+            lib.acc_step_partitioned.argtypes = [C.c_void_p]
+            self._check(lib.acc_comm_init(self.h, raw, rank, world, part32.ctypes.data, sc.ctypes.data, rc.ctypes.data))
+        else:
+            mk = lambda rows, cols: torch.zeros((rows, cols), dtype=torch.int64, device=self.tensor_device)
+            self.flow_send, self.flow_recv = mk(ns, 2), mk(nr, 2)
+            self.demand_send, self.demand_recv = mk(nr, 2), mk(ns, 2)
+            self.seller_table = mk(self.n_agents, SELLER_WORDS)
+            self._check(self.lib.acc_set_halo(self.h, self._send_ids.ctypes.data, ns, self._recv_ids.ctypes.data, nr, self.flow_send.data_ptr(),
+                                              self.flow_recv.data_ptr(), self.demand_send.data_ptr(), self.demand_recv.data_ptr(),
+                                              self.seller_table.data_ptr()))
         # one solver group size for all parts: the reduction order is part of the arithmetic
         lib.acc_solver_group.argtypes = [C.c_void_p]
         lib.acc_set_solver_group.argtypes = [C.c_void_p, C.c_int]
@@ -195,6 +220,9 @@ class PartitionedEngine(_engine.Engine):
     def step(self):
         """One timestep: four engine stages with the three exchanges between them, all ordered on the engine's stream."""
         p = self.part
+        if self.plane == "nccl":
+            self._check(self.lib.acc_step_partitioned(self.h))
+            return
         if self._stream is not None:
             with self.torch.cuda.stream(self._stream):
                 self._step(p)
@@ -227,6 +255,8 @@ class PartitionedEngine(_engine.Engine):
         self._stage(3)  # unpack demand requests, tick
 
     def halo_bytes_per_step(self):
+        """bytes this rank sends + receives per step: two halos of 16 B per cross connection and the sellers' records (the
+        all-gather of owned rows in the NCCL plane, the full-table all-reduce in the host plane)"""
         p = self.part
         return 2 * 16 * (int(p.send_edges.size) + int(p.recv_edges.size)) + 8 * SELLER_WORDS * self.n_agents
 

@@ -143,6 +143,27 @@ int acc_set_halo(acc_engine* e, const int64_t* send_edges, size_t n_send, const 
 enum { ACC_STAGE_SELL = 0, ACC_STAGE_DELIVER = 1, ACC_STAGE_PURCHASE = 2, ACC_STAGE_CLOSE = 3 };
 int acc_stage(acc_engine* e, int stage);
 
+/* ---- the same run with the engine exchanging its halos itself: NCCL from C++, no host code in the data plane ----
+ * (no counterpart in the reference, which is shared-memory only)  One rank makes the 128-byte NCCL id and hands
+ * it to the others by any means (MPI, a file, torch.distributed ...); every rank then joins with acc_comm_init, which also
+ * says how the halo lists of acc_set_halo split over the peers (send_counts / recv_counts [world], entries grouped by peer
+ * in rank order) and which part owns each agent (agent_part [n_agents], the same on every rank).  acc_set_halo may be
+ * given five NULL buffers: the engine then allocates the exchange buffers itself.
+ * acc_step_partitioned = one timestep: the four stages of acc_stage with, between them, on the engine's stream,
+ *   shipments:       one ncclSend / ncclRecv group with the peers (16 bytes per cross connection),
+ *   supply records:  ncclAllGather of the rows each part's own firms published (72 bytes per firm; not the zero-padded full
+ *                    table of the acc_stage protocol),
+ *   demand requests: one ncclSend / ncclRecv group.
+ * NCCL is bound at run time (dlopen of libnccl.so.2, the copy already in the process first): an unpartitioned run does not
+ * need it.  A P-part run is bit-identical to the one-engine run. */
+#define ACC_COMM_ID_BYTES 128
+int acc_comm_unique_id(void* id);
+int acc_comm_init(acc_engine* e, const void* id, int rank, int world, const int32_t* agent_part, const int64_t* send_counts,
+                  const int64_t* recv_counts);
+int acc_step_partitioned(acc_engine* e);
+/* collectives (point-to-point groups and all-gathers) the engine has issued since acc_comm_init */
+int64_t acc_collective_count(const acc_engine* e);
+
 /* Threads that solve one purchasing manager's optimisation.  The order of the solver's reductions -- part of its
  * floating-point arithmetic -- follows from it, so all parts of a partitioned run must agree: each part derives the
  * value from its own largest manager, the caller takes the maximum over the parts and sets it everywhere before the
@@ -179,6 +200,20 @@ int acc_set_event_capacity(acc_engine* e, size_t capacity);
  * observables split into <name>_quantity / <name>_value as ArrayOutput.cpp:58-66 does) into dst
  * as doubles (to_float), shaped like ArrayOutput::Variable::data.  *n receives the element count. */
 int acc_read(acc_engine* e, const char* group, const char* variable, double* dst, size_t cap, size_t* n);
+
+/* The same pull with SELECTION and the reference's array shapes -- what ArrayOutput::iterate writes for one timestep
+ * (src/output/ArrayOutput.cpp:479-646; the observable lists are the observe<>() visitors of include/model/EconomicAgent.h:70-96,
+ * Firm.h:78-153, Consumer.h:98-110, Sector.h:73-90, Region.h, Storage.h:90-150, BusinessConnection.h:79-115):
+ *   "firms", "consumers"   [n0 or n_agents]            idx0 = agents; agents of the other kind are NaN
+ *   "sectors", "regions"   [n0 or n_sectors/n_regions] idx0 = sectors / regions
+ *   "storages"             [n_sectors][n1 or n_agents] idx1 = agents (no selection by sector, as in the reference, :575)
+ *   "flows"                [n0 or n_agents][n1 or n_agents]  idx0 = selling agents OR idx1 = buying agents (not both, :469-471)
+ * Cells without an object (no storage of that sector, no connection between the two agents) are NaN (:170).  The cells are
+ * gathered by kernels on the device -- only the selected ones are touched, nothing else of the state moves -- and arrive in
+ * dst (caller-owned, cap doubles) in one copy; dst == NULL only reports the size in *n.  Valid after the purchase phase of a
+ * step, before or after its tick. */
+int acc_observe(acc_engine* e, const char* group, const char* variable, const int64_t* idx0, size_t n0, const int64_t* idx1, size_t n1,
+                double* dst, size_t cap, size_t* n);
 
 /* No counterpart in the reference: added for callers that cannot allocate device
  * memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same numbers as

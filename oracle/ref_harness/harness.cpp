@@ -17,6 +17,8 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <limits>
+#include <map>
 #include <memory>
 #include <string>
 #include <vector>
@@ -37,6 +39,7 @@
 #include "model/SalesManager.h"
 #include "model/Sector.h"
 #include "model/Storage.h"
+#include "model/TransportChainLink.h"
 #include "nlopt.h"
 #include "openmp.h"
 
@@ -88,6 +91,7 @@ struct HarnessConfig {
     std::string dump_path;
     int dump_every = 1;
     bool dump_edges = true;
+    bool dump_observables = false;  // --observe: every observable of the reference's observe<>() visitors, shaped like ArrayOutput's data
     const std::vector<std::int64_t>& I(const char* n) const { return net.at(n).i; }
     const std::vector<double>& F(const char* n) const { return net.at(n).f; }
 };
@@ -461,6 +465,67 @@ static void apply_scenario(Model* model) {
     }
 }
 
+// ---- the reference's OUTPUT SURFACE: every observable its observe<Observer, H>() visitors offer (include/model/*.h),
+// collected the way ArrayOutput does (src/output/ArrayOutput.cpp:115-158: Flow / Stock split into <name>_quantity and
+// <name>_value, everything through to_float) into arrays shaped like ArrayOutput::Variable::data of ONE timestep
+// (ArrayOutput::iterate, :479-646): firms / consumers [agents], sectors, regions, storages [sectors][agents],
+// flows [agent_from][agent_to]; cells nothing writes stay NaN (:170).
+struct ObsDump {
+    struct H {
+        static constexpr const char* hash(const char* s) { return s; }
+    };
+    std::map<std::string, std::vector<double>> data;
+    std::string group;
+    std::size_t size = 0, index = 0;
+    std::vector<double>& col(const std::string& name) {
+        auto it = data.find(name);
+        if (it == data.end()) it = data.emplace(name, std::vector<double>(size, std::numeric_limits<double>::quiet_NaN())).first;
+        return it->second;
+    }
+    template<typename Function>
+    auto set(const char* name, Function&& f) ->
+        typename std::enable_if<!std::is_same<decltype(f()), Flow>::value && !std::is_same<decltype(f()), Stock>::value, bool>::type {
+        col(group + ":" + name)[index] = to_float(f());
+        return true;
+    }
+    template<typename Function>
+    auto set(const char* name, Function&& f) ->
+        typename std::enable_if<std::is_same<decltype(f()), Flow>::value || std::is_same<decltype(f()), Stock>::value, bool>::type {
+        const auto& v = f();
+        col(group + ":" + name + "_quantity")[index] = to_float(v.get_quantity());
+        col(group + ":" + name + "_value")[index] = to_float(v.get_value());
+        return true;
+    }
+    template<typename T>
+    void collect(const T* v, std::size_t index_p) {
+        index = index_p;
+        v->template observe<ObsDump, H>(*this);
+    }
+    void begin(const char* g, std::size_t n) { group = g; size = n; }
+};
+
+static void dump_observables(accio::Writer& out, Model* model, const std::string& P) {
+    ObsDump o;
+    const auto& A = model->economic_agents;
+    const std::size_t nA = A.size(), nS = model->sectors.size(), nR = model->regions.size();
+    o.begin("firms", nA);
+    for (std::size_t i = 0; i < nA; ++i) if (A[i]->is_firm()) o.collect(A[i]->as_firm(), i);
+    o.begin("consumers", nA);
+    for (std::size_t i = 0; i < nA; ++i) if (A[i]->is_consumer()) o.collect(A[i]->as_consumer(), i);
+    o.begin("sectors", nS);
+    for (std::size_t i = 0; i < nS; ++i) o.collect(model->sectors[i], i);
+    o.begin("regions", nR);
+    for (std::size_t i = 0; i < nR; ++i) o.collect(model->regions[i], i);
+    o.begin("storages", nS * nA);
+    for (std::size_t i = 0; i < nA; ++i)
+        for (const auto& storage : A[i]->input_storages) o.collect(storage.get(), storage->sector->id.index() * nA + i);
+    o.begin("flows", nA * nA);
+    for (std::size_t i = 0; i < nA; ++i)
+        if (A[i]->is_firm())
+            for (const auto& bc : A[i]->as_firm()->sales_manager->business_connections) o.collect(bc.get(), i * nA + bc->buyer->storage->economic_agent->id.index());
+    for (const auto& kv : o.data) out.put(P + "obs:" + kv.first, kv.second);
+}
+
 static void dump_step(accio::Writer& out, Model* model, std::int64_t t, bool with_edges) {
     char pre[32];
     std::snprintf(pre, sizeof(pre), "t%05ld/", long(t));
@@ -532,6 +597,7 @@ static void dump_step(accio::Writer& out, Model* model, std::int64_t t, bool wit
     put_i("region_consumption_q", nr, [&](std::size_t k) { return qi(model->regions[k]->consumption_C().get_quantity()); });
     put_f("region_consumption_v", nr, [&](std::size_t k) { return to_float(model->regions[k]->consumption_C().get_value()); });
     put_f("region_gdp_v", nr, [&](std::size_t k) { return to_float(model->regions[k]->get_gdp().get_value()); });
+    if (g_cfg->dump_observables) dump_observables(out, model, P);
 }
 
 // the time loop: same order of calls as src/ModelRun.cpp:153-229
@@ -585,7 +651,7 @@ void ModelRun::run() {
 
 int main(int argc, char** argv) {
     if (argc < 3) {
-        std::fprintf(stderr, "usage: %s <network.acc> <steps> [dump.acc] [--every k] [--no-edges]\n", argv[0]);
+        std::fprintf(stderr, "usage: %s <network.acc> <steps> [dump.acc] [--every k] [--no-edges] [--observe]\n", argv[0]);
         return 1;
     }
     try {
@@ -596,6 +662,7 @@ int main(int argc, char** argv) {
             const std::string a = argv[i];
             if (a == "--every" && i + 1 < argc) cfg.dump_every = std::atoi(argv[++i]);
             else if (a == "--no-edges") cfg.dump_edges = false;
+            else if (a == "--observe") cfg.dump_observables = true;
             else cfg.dump_path = a;
         }
         settings::SettingsNode node;

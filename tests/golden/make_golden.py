@@ -164,6 +164,15 @@ def cases():
     # its start value, which NLopt -- and oracle/nlopt_kraft with it -- rejects as NLOPT_INVALID_ARGS: the reference aborts the
     # run there ("optimization failed, ... (for 3 consumption goods)", Consumer.cpp:497-502); the shim clips the start value
     yield "events18", a, 18, {"no_kraft": True}
+    # the OUTPUT SURFACE: every observable of the reference's observe<>() visitors (firms, consumers, sectors, regions, storages,
+    # flows), collected by the oracle the way ArrayOutput does, at three steps of a run with a shock, multi-hop routes and
+    # passage forcing on them (overflow, minimum passage < 1) and utilitarian consumers
+    a = synth.make_network(regions=5, sectors=3, seed=23, max_delay=3)
+    info = synth.add_routes(a, seed=23, hubs=2)
+    synth.add_shock(a, 1, 6, 2, 0.4)
+    synth.add_entity_passage(a, 2, 7, info["hub_loc"][0], 0.5)
+    synth.add_entity_passage(a, 3, 5, info["access"][1], 0.3)
+    yield "observe10", a, 10, {"no_kraft": True, "observe": True, "full_steps": [0, 4, 9]}
     if "eora_flood4" in sys.argv[1:]:  # only on request: minutes of oracle time, 20 GB of memory
         yield "eora_flood4", synth_network("eora_flood4"), 4, {"no_kraft": True, "full_steps": [], "synth": True}
 
@@ -179,11 +188,12 @@ def synth_network(name):
     raise KeyError(name)
 
 
-def run_oracle(flavour, net, steps, tmp):
+def run_oracle(flavour, net, steps, tmp, observe=False):
     npath, dpath = os.path.join(tmp, "n.acc"), os.path.join(tmp, "d_%s.acc" % flavour)
     if not os.path.exists(npath):
         netfile.write(npath, net)
-    r = subprocess.run([ORACLE[flavour], npath, str(steps), dpath], capture_output=True, text=True, env=dict(os.environ, ORACLE_SOLVER_STATS="1"))
+    r = subprocess.run([ORACLE[flavour], npath, str(steps), dpath] + (["--observe"] if observe else []), capture_output=True, text=True,
+                       env=dict(os.environ, ORACLE_SOLVER_STATS="1"))
     if r.returncode != 0:
         raise RuntimeError("oracle (%s) failed: %s" % (flavour, r.stderr[-2000:]))
     return netfile.read(dpath), r.stderr.strip().splitlines()[-1]
@@ -207,6 +217,8 @@ def build_fixture(flavour, net, steps, dump, opts):
             continue
         if full is None or int(t[1:]) in full:
             out[k] = v
+        elif base.startswith("obs:"):
+            continue  # observables are kept at the full steps only
         else:
             out["chk/" + k] = checksum(v)
     if full is not None:
@@ -225,7 +237,7 @@ def main():
             for flavour in ("shim", "kraft"):
                 if flavour == "kraft" and opts.get("no_kraft"):
                     continue
-                dump, stats = run_oracle(flavour, net, steps, tmp)
+                dump, stats = run_oracle(flavour, net, steps, tmp, observe=bool(opts.get("observe")))
                 path = os.path.join(GOLDEN, "%s.%s.acc.gz" % (name, flavour))
                 netfile.write(path, build_fixture(flavour, net, steps, dump, opts))
                 ev = dump["events"].reshape(-1, 4)

@@ -24,9 +24,8 @@ CASES = ["small_shock12", "severe_shock30", "passage25", "outage25", "flags20", 
 LOOSE = {"region_import_v", "region_export_v", "region_gdp_v"}
 # per-connection in-transit value: the reference folds a queue in ring-position order, the engine in travel order
 TRANSIT = {"edge_transit_v"}
-# (case, array) the engine does not keep: the VALUE of a shipment whose conveyor slot a zero-delay hop rewrote (the
-# quantity is kept apart, DESIGN.md "Multi-hop routes"); nothing else may be missing
-UNAVAILABLE = {("routes25", "edge_ship_v")}
+# (case, array) the engine does not keep: nothing may be missing
+UNAVAILABLE = set()
 EV_ROUNDOFF = 14
 
 
