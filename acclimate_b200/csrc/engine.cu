@@ -31,6 +31,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <map>
 #include <string>
 #include <vector>
@@ -39,6 +40,7 @@
 #include "purchase_core.cuh"
 #include "consumer_core.cuh"
 #include "observe.cuh"
+#include "ingest.cuh"
 
 #ifndef ACC_HOST_EMU
 #include <dlfcn.h>
@@ -304,11 +306,12 @@ template <class T>
 struct DBuf {  // device array with its element count
     T* p = nullptr;
     size_t n = 0;
+    bool borrowed = false;  // the array belongs to another engine (the immutable tables of an ensemble member, acc_fork)
     void alloc(size_t count) { free(); n = count; p = static_cast<T*>(dev_alloc(count * sizeof(T))); }
     void upload(const std::vector<T>& h, stream_t s) { alloc(h.size()); h2d(p, h.data(), h.size() * sizeof(T), s); }
     void zero(stream_t s) { dev_zero(p, n * sizeof(T), s); }
     std::vector<T> download(stream_t s) const { std::vector<T> h(n); d2h(h.data(), p, n * sizeof(T), s); return h; }
-    void free() { if (p) dev_free(p); p = nullptr; n = 0; }
+    void free() { if (p && !borrowed) dev_free(p); p = nullptr; n = 0; borrowed = false; }
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -817,6 +820,27 @@ struct acc_engine {
         v(c_prev_q); v(c_prev_v); v(c_utility);
         v(ev_count); v(ev_buf);
     }
+    // every device array of the engine (acc_destroy releases them, acc_fork shares the ones visit_state does not name)
+    template <class V>
+    void visit_all(V& v) {
+        visit_state(v);
+        v(sectors); v(a_type); v(a_sector); v(a_region); v(a_st_off); v(a_st_list); v(firm_ids); v(a_beta);
+        v(f_Xstar_q); v(f_markup_eff); v(f_var_costs); v(f_Xstar_v);
+        v(pubT); v(seller_row); v(row_firm); v(e_to); v(sto_of); v(obs_out); v(obs_idx); v(obs_inc_q); v(obs_inc_v);
+        v(s_Istar_q); v(s_Sstar_q); v(s_defc); v(s_Istar_v); v(s_Sstar_v); v(s_a); v(s_agent); v(s_sector);
+        v(e_seller_off); v(e_route); v(route_off); v(route_ent); v(ent_delay); v(e_Z_q); v(e_tau); v(e_dom);
+        v(ell_off); v(in_off); v(ell_width); v(ell_edge); v(in_edge); v(in_seller); v(in_Z);
+        v(cons_ids); v(c_order_cnt); v(c_order); v(c_order_basket); v(fatal);
+        v(c_share); v(c_eshare); v(c_budget); v(c_bshare); v(c_ebshare); v(c_intra_exp); v(c_base_q);
+        v(owned); v(pm_ids); v(halo_send); v(halo_recv);
+        v(own_flow_send); v(own_flow_recv); v(own_dem_send); v(own_dem_recv); v(own_sellers);
+        v(comm_part_firms); v(comm_part_off); v(comm_rows_send); v(comm_rows_recv);
+    }
+    // ensemble members (acc_fork): a member shares its parent's immutable tables; the parent's memory lives until the last member is gone
+    acc_engine* parent = nullptr;
+    int members = 0;
+    bool zombie = false;
+
     void ensure_forcing_state() {  // overflow per (hop, connection) exists from the first non-negative passage on
         if (forcing_used) return;
         e_ovf_q.alloc((size_t)nE * h_max); e_ovf_v.alloc((size_t)nE * h_max);
@@ -1937,6 +1961,103 @@ extern "C" int acc_observe(acc_engine* e, const char* group, const char* variabl
     ACC_API_END(-1)
 }
 
+
+// ---- acc_ingest_table: threshold filter + clean_network fix point on the device (csrc/ingest.cuh) ----
+extern "C" int acc_ingest_table(int device, int64_t n_agents, int64_t n_sectors, const int64_t* agent_type, const int64_t* agent_sector, const float* flows,
+                                double threshold, double time_factor, int no_self_supply, uint8_t* agent_alive, int64_t* n_edges, int64_t* edge_from,
+                                int64_t* edge_to, int64_t* edge_zq, size_t cap_edges, int64_t* sweeps, int64_t* removed) {
+    ACC_API_BEGIN
+    if (agent_type == nullptr || agent_sector == nullptr || flows == nullptr || n_edges == nullptr) fail("acc_ingest_table: null argument");
+    if (n_agents <= 0 || n_sectors <= 0 || n_agents * n_agents >= (int64_t)0x7fffffff) fail("acc_ingest_table: table size out of range");
+#ifndef ACC_HOST_EMU
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) fail("acc_ingest_table: no CUDA device available (this library has no CPU path)");
+    if (device < 0 || device >= count) fail("acc_ingest_table: no such CUDA device");
+#endif
+    acc::DeviceGuard device_guard__(device);
+    stream_t s = nullptr;
+#ifndef ACC_HOST_EMU
+    ACC_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    struct StreamOwner { stream_t s; ~StreamOwner() { cudaStreamDestroy(s); } } stream_owner{s};
+#endif
+    const i64 nA = n_agents;
+    const int nS = (int)n_sectors;
+    std::vector<int> h_type(nA), h_sector(nA);
+    for (i64 a = 0; a < nA; ++a) {
+        h_type[a] = (int)agent_type[a]; h_sector[a] = (int)agent_sector[a];
+        if (h_sector[a] < 0 || h_sector[a] >= nS) fail("acc_ingest_table: agent sector out of range");
+    }
+    DBuf<int> d_type, d_sector, d_nout, d_nst, d_cnt;
+    DBuf<float> d_table;
+    DBuf<i64> d_Z, d_X, d_in, d_found, d_rows, d_off, d_from, d_to, d_zq;
+    DBuf<unsigned char> d_alive, d_self;
+    struct Release {
+        std::vector<std::function<void()>> f;
+        ~Release() { for (auto& g : f) g(); }
+    } rel;
+    auto own = [&](auto& b) { rel.f.push_back([&b] { b.free(); }); };
+    own(d_type); own(d_sector); own(d_nout); own(d_nst); own(d_cnt); own(d_table); own(d_Z); own(d_X); own(d_in); own(d_found); own(d_rows); own(d_off);
+    own(d_from); own(d_to); own(d_zq); own(d_alive); own(d_self);
+    d_type.upload(h_type, s); d_sector.upload(h_sector, s);
+    d_table.alloc((size_t)(nA * nA)); h2d(d_table.p, flows, (size_t)(nA * nA) * sizeof(float), s);
+    d_Z.alloc((size_t)(nA * nA)); d_X.alloc(nA); d_in.alloc(nA); d_nout.alloc(nA); d_nst.alloc(nA); d_cnt.alloc((size_t)nS * nA); d_alive.alloc(nA); d_self.alloc(nA);
+    d_found.alloc(1); d_rows.alloc(nA);
+    IngestView v{nA, nS, d_type.p, d_sector.p, d_Z.p, d_X.p, d_in.p, d_nout.p, d_nst.p, d_cnt.p, d_alive.p, d_self.p};
+    {
+        IngestFilter k{v, d_table.p, threshold, time_factor, mkq(threshold * time_factor), no_self_supply};
+        launch_thread(s, (int)(nA * nA), k);
+        IngestStats st{v};
+        launch_block(s, (int)nA, st);
+    }
+    // the reference's sweeps, replayed exactly: find the first removable agent at or after the cursor, take it out, go on behind it
+    i64 n_sweeps = 0, n_removed = 0;
+    for (;;) {
+        ++n_sweeps;
+        i64 cursor = 0, in_sweep = 0;
+        while (cursor < nA) {
+            i64 found = nA;
+            h2d(d_found.p, &found, sizeof found, s);
+            IngestFindFirst ff{v, cursor, d_found.p};
+            launch_thread(s, (int)(nA - cursor), ff);
+            d2h(&found, d_found.p, sizeof found, s);
+            if (found >= nA) break;
+            IngestRemove rm{v, found};
+            launch_block(s, 1, rm);
+            ++in_sweep;
+            cursor = found + 1;
+        }
+        n_removed += in_sweep;
+        if (in_sweep == 0) break;
+    }
+    {
+        IngestCount k{v, d_rows.p};
+        launch_block(s, (int)nA, k);
+    }
+    std::vector<i64> rows = d_rows.download(s), off(nA + 1, 0);
+    for (i64 a = 0; a < nA; ++a) off[a + 1] = off[a] + rows[a];
+    *n_edges = off[nA];
+    if (sweeps) *sweeps = n_sweeps;
+    if (removed) *removed = n_removed;
+    if (agent_alive != nullptr) {
+        std::vector<unsigned char> al = d_alive.download(s);
+        std::memcpy(agent_alive, al.data(), (size_t)nA);
+    }
+    if (edge_from != nullptr || edge_to != nullptr || edge_zq != nullptr) {
+        if (edge_from == nullptr || edge_to == nullptr || edge_zq == nullptr) fail("acc_ingest_table: pass all three connection arrays or none");
+        if (cap_edges < (size_t)off[nA]) fail("acc_ingest_table: connection arrays too small (call with NULL arrays first to learn the count)");
+        if (off[nA] == 0) fail("No economic agents present");  // ModelInitializer.cpp:296-298
+        d_off.upload(off, s);
+        d_from.alloc((size_t)off[nA]); d_to.alloc((size_t)off[nA]); d_zq.alloc((size_t)off[nA]);
+        IngestEmit k{v, d_off.p, d_from.p, d_to.p, d_zq.p};
+        launch_block(s, (int)nA, k);
+        d2h(edge_from, d_from.p, (size_t)off[nA] * sizeof(i64), s);
+        d2h(edge_to, d_to.p, (size_t)off[nA] * sizeof(i64), s);
+        d2h(edge_zq, d_zq.p, (size_t)off[nA] * sizeof(i64), s);
+    }
+    return 0;
+    ACC_API_END(-1)
+}
+
 // ---- state checkpoint: blob header and the visitors over acc_engine::visit_state ----
 namespace {
 struct StateHeader {
@@ -1955,6 +2076,37 @@ struct LoadVisitor {
     const unsigned char* src; acc::stream_t s;
     template <class T> void operator()(acc::DBuf<T>& b) { if (b.n) { acc::h2d(b.p, src, b.n * sizeof(T), s); src += b.n * sizeof(T); } }
 };
+}  // namespace
+
+namespace {
+struct FreeVisitor {
+    template <class T> void operator()(acc::DBuf<T>& b) { b.free(); }
+};
+struct BorrowVisitor {
+    template <class T> void operator()(acc::DBuf<T>& b) { b.borrowed = true; }
+};
+struct CloneVisitor {  // the member gets its own copy of a state array, filled with the parent's current contents
+    acc::stream_t s;
+    template <class T> void operator()(acc::DBuf<T>& b) {
+        const T* src = b.p;
+        const size_t n = b.n;
+        b.p = nullptr; b.n = 0; b.borrowed = false;
+        if (n == 0) return;
+        b.alloc(n);
+#ifdef ACC_HOST_EMU
+        std::memcpy(b.p, src, n * sizeof(T));
+#else
+        ACC_CUDA(cudaMemcpyAsync(b.p, src, n * sizeof(T), cudaMemcpyDeviceToDevice, s));
+#endif
+    }
+};
+void release_engine(acc_engine* e) {
+    FreeVisitor fv;
+    e->visit_all(fv);
+    acc_engine* parent = e->parent;
+    delete e;
+    if (parent != nullptr && --parent->members == 0 && parent->zombie) release_engine(parent);
+}
 }  // namespace
 
 extern "C" {
@@ -2004,30 +2156,59 @@ void acc_destroy(acc_engine* e) {
 #ifndef ACC_HOST_EMU
     cudaStreamSynchronize(e->stream);
 #endif
-    // DBuf members are plain handles: release them explicitly
-    for (DBuf<i64>* b : {&e->f_Xstar_q, &e->f_markup_eff, &e->f_var_costs, &e->f_cap_q, &e->f_Xhat_q, &e->f_est_q, &e->f_X_q, &e->f_Xexp_q, &e->f_nbar,
-                         &e->f_cutoff, &e->f_desired_q, &e->f_sumD_q, &e->f_bk_sq, &e->f_bk_cnt, &e->f_bk_pmax, &e->f_bk_pmin, &e->f_exp_q, &e->s_S_q,
-                         &e->s_I0_q, &e->s_I1_q, &e->s_Il_q, &e->s_U_q, &e->s_Ut_q, &e->s_T_q, &e->s_dlv_q, &e->s_imp_q, &e->s_Istar_q, &e->s_Sstar_q,
-                         &e->s_defc, &e->s_dem_q, &e->e_D_q, &e->e_D_p, &e->e_Z_q, &e->conv_q, &e->e_ovf_q, &e->ell_off, &e->in_off, &e->in_Z})
-        b->free();
-    for (DBuf<double>* b : {&e->a_beta, &e->a_lambda, &e->f_Xstar_v, &e->f_cap_v, &e->f_Xhat_v, &e->f_est_v, &e->f_X_v, &e->f_Xexp_v, &e->f_C, &e->f_R,
-                            &e->f_sumD_v, &e->f_bk_sv, &e->f_exp_v, &e->s_S_v, &e->s_I0_v, &e->s_I1_v, &e->s_Il_v, &e->s_U_v, &e->s_Ut_v, &e->s_T_v,
-                            &e->s_imp_v, &e->s_Istar_v, &e->s_Sstar_v, &e->s_a, &e->s_dem_v, &e->s_exp_costs, &e->s_opt_val, &e->s_tpen, &e->conv_v,
-                            &e->e_ovf_v, &e->nu})
-        b->free();
-    for (DBuf<int>* b : {&e->a_type, &e->a_sector, &e->a_region, &e->a_st_off, &e->a_st_list, &e->firm_ids, &e->s_agent, &e->s_sector, &e->s_iters,
-                         &e->s_evals, &e->e_seller_off, &e->e_route, &e->route_off, &e->route_ent, &e->ell_width, &e->ell_edge, &e->in_edge, &e->in_seller, &e->ev_count})
-        b->free();
-    e->e_tau.free(); e->e_dom.free(); e->sectors.free(); e->pub.free(); e->pubT.free(); e->seller_row.free(); e->row_firm.free(); e->e_to.free(); e->sto_of.free(); e->obs_out.free(); e->obs_idx.free(); e->obs_inc_q.free(); e->obs_inc_v.free(); e->ev_buf.free();
-    e->ent_delay.free(); e->e_ship_q.free(); e->e_ship_v.free();
-    e->owned.free(); e->pm_ids.free(); e->halo_send.free(); e->halo_recv.free();
-    for (DBuf<i64>* b : {&e->own_flow_send, &e->own_flow_recv, &e->own_dem_send, &e->own_dem_recv, &e->own_sellers, &e->comm_rows_send, &e->comm_rows_recv}) b->free();
-    e->comm_part_firms.free(); e->comm_part_off.free();
-    for (DBuf<int>* b : {&e->cons_ids, &e->c_order_cnt, &e->c_order, &e->c_order_basket, &e->fatal}) b->free();
-    for (DBuf<double>* b : {&e->c_share, &e->c_eshare, &e->c_prev_v, &e->c_budget, &e->c_bshare, &e->c_ebshare, &e->c_utility, &e->c_intra_exp}) b->free();
-    e->c_base_q.free(); e->c_prev_q.free();
-    delete e;
+    if (e->members > 0) e->zombie = true;  // ensemble members still read this engine's tables: released with the last of them
+    else release_engine(e);
     delete guard;
+}
+
+/* acc_fork: an ensemble member.  The new engine SHARES the parent's immutable tables (topology, Z*, delays, the buyer-side lists:
+ * everything acc_save_state does not name) and owns a copy of the state, taken as the parent has it now.  Members and parent
+ * are stepped, forced and read independently (each on its own stream); many scenarios of one network cost one topology. */
+acc_engine* acc_fork(acc_engine* parent) {
+    acc_engine* E = nullptr;
+    try {
+        if (parent == nullptr) fail("acc_fork: null engine");
+        if (parent->partitioned) fail("acc_fork: a part of a region-partitioned run cannot be forked");
+        acc::DeviceGuard device_guard__(parent->device);
+        acc::dev_sync(parent->stream);
+        acc_engine* root = parent->parent != nullptr ? parent->parent : parent;  // members of a member share the same tables
+        E = new acc_engine(*parent);
+        E->stream = nullptr; E->side = nullptr;
+#ifndef ACC_HOST_EMU
+        E->ev_fork = nullptr; E->ev_join = nullptr; E->comm = nullptr;
+#endif
+        E->clocks.clear(); E->launches = 0; E->profile = false;
+        E->parent = nullptr; E->members = 0; E->zombie = false;
+        BorrowVisitor bv;
+        E->visit_all(bv);
+#ifndef ACC_HOST_EMU
+        ACC_CUDA(cudaStreamCreateWithFlags(&E->stream, cudaStreamNonBlocking));
+        int prio_low = 0, prio_high = 0;
+        ACC_CUDA(cudaDeviceGetStreamPriorityRange(&prio_low, &prio_high));
+        ACC_CUDA(cudaStreamCreateWithPriority(&E->side, cudaStreamNonBlocking, prio_high));
+        ACC_CUDA(cudaEventCreateWithFlags(&E->ev_fork, cudaEventDisableTiming));
+        ACC_CUDA(cudaEventCreateWithFlags(&E->ev_join, cudaEventDisableTiming));
+#endif
+        CloneVisitor cv{E->stream};
+        E->visit_state(cv);
+        cv(E->pubT); cv(E->fatal);  // derived / scratch state that changes with the steps
+        for (acc::DBuf<double>* b : {&E->obs_out, &E->obs_inc_v}) { b->p = nullptr; b->n = 0; b->borrowed = false; }
+        for (acc::DBuf<i64>* b : {&E->obs_idx, &E->obs_inc_q}) { b->p = nullptr; b->n = 0; b->borrowed = false; }
+        acc::dev_sync(E->stream);
+        E->parent = root;
+        root->members += 1;
+        return E;
+    } catch (const acc::EngineError& ex) {
+        acc::g_last_error = ex.msg;
+    } catch (const std::exception& ex) {
+        acc::g_last_error = ex.what();
+    }
+    if (E != nullptr) {
+        FreeVisitor fv;
+        E->visit_all(fv);
+        delete E;
+    }
+    return nullptr;
 }
 
 int acc_set_agent_forcing(acc_engine* e, const double* lambda, size_t n) {

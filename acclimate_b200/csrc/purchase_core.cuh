@@ -244,6 +244,15 @@ struct CountSum {
     static ACC_HD CountSum combine(CountSum a, CountSum b) { CountSum r; r.n = a.n + b.n; r.s = a.s + b.s; return r; }
 };
 
+struct WriteBack {  // sums of the write-back pass: demand quantity (exact), expected costs, transport penalty, demand value
+    i64 q;
+    double costs, pen, value;
+    static ACC_HD WriteBack identity() { WriteBack r; r.q = 0; r.costs = 0.0; r.pen = 0.0; r.value = 0.0; return r; }
+    static ACC_HD WriteBack combine(WriteBack a, WriteBack b) {
+        WriteBack r; r.q = a.q + b.q; r.costs = a.costs + b.costs; r.pen = a.pen + b.pen; r.value = a.value + b.value; return r;
+    }
+};
+
 struct PMResult {
     Flow demand;           // demand_D_
     double expected_costs; // expected_costs_
@@ -372,8 +381,10 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, Gather gather, Mi
     }
     res.optimized = (-st.minf) * pp.Uf;  // unscaled_objective(opt.optimized_value()), :509
 
-    // distribute demand requests, :704-737
-    const i64 dq = cx.isum(n, [&](int r) {
+    // distribute demand requests, :704-737.  The three value sums of this pass (expected costs, transport penalty, value of
+    // the demand) are observables only -- nothing of the model reads them back (include/model/Storage.h:108-140) -- so they are
+    // folded in the group's fixed reduction order with the integer sum of the requests, not in a strictly sequential chain.
+    const WriteBack wb = cx.template reduce<WriteBack>(n, [&](int r) {
         const double D = k.w.xbest[r] * k.zf[r];
         const i64 q = mkq(D);
         // with deviation_penalty the penalty target is last_demand_request_D, which the reference has already
@@ -382,14 +393,12 @@ ACC_HD PMResult purchase_one(Ctx& cx, int nin, InEdge in_edge, Gather gather, Mi
         const CurvePoint cp = curve_at<STD>(k, pp, r, D);
         const i64 p = q > 0 ? mkp(cp.n) : 0;
         send_D(k.eid[r], q, p);
-        k.term[r] = cp.n * D + cp.tp;
-        k.w.x0[r] = cp.tp;
-        k.w.g[r] = q > 0 ? q_times_p(q, p) : 0.0;
-        return q;
+        WriteBack t;
+        t.q = q; t.costs = cp.n * D + cp.tp; t.pen = cp.tp; t.value = q > 0 ? q_times_p(q, p) : 0.0;
+        return t;
     });
-    double sums[3];
-    cx.template seqsum<3>(n, [&](int r, int j) { return k.at(r, j == 0 ? PW::COL_TERM : (j == 1 ? PW::COL_X0 : PW::COL_G)); }, sums);
-    const double costs = sums[0], pen = sums[1], dv = sums[2];
+    const i64 dq = wb.q;
+    const double costs = wb.costs, pen = wb.pen, dv = wb.value;
     res.demand = mkflow(dq, dv);
     res.expected_costs = costs;
     res.penalty = pen;

@@ -147,6 +147,19 @@ class Engine:
         if rc != 0:
             raise EngineError(self.lib.acc_last_error().decode())
 
+    def fork(self):
+        """acc_fork: an ensemble member -- shares this engine's network tables on the device, owns a copy of its current state."""
+        self.lib.acc_fork.restype = C.c_void_p
+        self.lib.acc_fork.argtypes = [C.c_void_p]
+        h = self.lib.acc_fork(self.h)
+        if not h:
+            raise EngineError(self.lib.acc_last_error().decode())
+        member = object.__new__(type(self))
+        member.lib, member._keep = self.lib, self._keep
+        member.n_sectors, member.n_regions, member.n_agents, member.n_edges = self.n_sectors, self.n_regions, self.n_agents, self.n_edges
+        member.h = h
+        return member
+
     def close(self):
         if getattr(self, "h", None):
             self.lib.acc_destroy(self.h)
@@ -204,6 +217,12 @@ class Engine:
 
     def set_event_capacity(self, capacity):
         self._check(self.lib.acc_set_event_capacity(self.h, int(capacity)))
+
+    def state_bytes(self):
+        """Size of the state blob (acc_state_bytes): what one more ensemble member costs in device memory."""
+        n = C.c_size_t(0)
+        self._check(self.lib.acc_state_bytes(self.h, C.byref(n)))
+        return int(n.value)
 
     def save_state(self):
         """Checkpoint: everything that changes from step to step as one blob (numpy uint8 array); see acc_save_state."""

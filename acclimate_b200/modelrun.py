@@ -27,6 +27,34 @@ class ModelRun:
         self.events = []
         self.duration_ms = []  # the reference's model/duration observable (ModelRun.cpp:192-194)
         self.time = 0
+        self.sinks = []        # (pulls, sink) pairs of a settings document's `outputs:` section
+        self.start_time = 0.0
+        self.delta_t = 1.0
+
+    @classmethod
+    def from_settings(cls, doc, network, sector_names, region_names, device=0, lib_path=None, flows=None):
+        """The reference's entry point (src/main.cpp:58-124 -> ModelRun::ModelRun, src/ModelRun.cpp:77-150) on a settings document:
+        `network` is the snapshot (or, with `flows`, the agents of a candidate MRIO table that is filtered by network.threshold and
+        cleaned on the device first, acclimate_b200/ingest.py); model / sectors / firms / consumers / scenario / outputs come from
+        the document (acclimate_b200/settings.py).  Returns (run, number of timesteps)."""
+        from . import ingest, output, settings
+
+        st = doc if isinstance(doc, settings.Settings) else settings.Settings(doc)
+        net = st.apply_to(network, sector_names, region_names) if flows is None else dict(network)
+        if flows is not None:
+            seed = dict(network)
+            seed["model_f64"] = st.model_params()
+            net, _ = ingest.ingest_table(seed, flows, float(st.doc.get("network", {}).get("threshold", 0.0)), device=device, lib_path=lib_path)
+            net = st.apply_to(net, sector_names, region_names)
+        run = cls(net, device=device, lib_path=lib_path)
+        start, _, basedate = st.run_window()
+        run.start_time, run.delta_t = start, float(st.doc["model"]["delta_t"])
+        for _, fmt, path, pulls in st.output_plan(net, sector_names, region_names):
+            if fmt == "progress":
+                continue
+            sink = output.ArraySink() if fmt == "array" else output.NetCDFSink(path, net, sector_names, region_names, basedate=basedate)
+            run.sinks.append((pulls, sink))
+        return run, st.steps()
 
     def step(self):
         e = self.engine
@@ -39,7 +67,13 @@ class ModelRun:
         self.duration_ms.append(1e3 * (time.perf_counter() - t0))
         for o in self.outputs:                            # outputs->iterate()
             self.series[o].append(e.read(*o))
-        self.events += e.events()                         # ModelRun::event: drained every step (the device buffer is bounded)
+        new_events = e.events()                           # ModelRun::event: drained every step (the device buffer is bounded)
+        self.events += new_events
+        if self.sinks:
+            from . import output
+
+            for pulls, sink in self.sinks:                # ArrayOutput::iterate / NetCDFOutput::iterate: gathered on the device
+                sink.write(self.start_time + self.time * self.delta_t, output.pull(e, pulls), new_events)
         e.phase(PHASE_TICK)                               # model->tick(); ++time
         self.time += 1
 
@@ -49,4 +83,6 @@ class ModelRun:
         return {o: np.stack(v) for o, v in self.series.items()}
 
     def close(self):
+        for _, sink in self.sinks:
+            sink.close()
         self.engine.close()

@@ -196,6 +196,9 @@ def main():
                          "NCCL (strong scaling; default), or one independent member of the same workload per GPU (weak scaling, no collective)")
     ap.add_argument("--flood-steps", type=int, default=10, help="timed steps of the shocked window that follows the baseline measurement (0: none)")
     ap.add_argument("--ensemble-shocks", action="store_true", help="ensemble members other than the first get their own regional shock")
+    ap.add_argument("--members", type=int, default=8, help="scenario ensemble on ONE GPU after the headline run (BASELINE.json configs[4] pattern): this many "
+                                                            "acc_fork members share the network tables, each with its own seeded regional shock (0: none)")
+    ap.add_argument("--member-steps", type=int, default=5)
     args = ap.parse_args()
     if args.mode is None:
         args.mode = "partition" if int(os.environ.get("WORLD_SIZE", "1")) > 1 else "ensemble"
@@ -308,6 +311,11 @@ def main():
     sampler.stop_flag.set()
     sampler.join()
 
+    # a member at the baseline state, taken before the shocked epilogue: the scenario ensemble below grows from it
+    base_member = None
+    if args.config == "eora" and world == 1 and args.members > 1:
+        base_member = E.fork()
+
     # ---- untimed epilogue: a regional production-loss shock (BASELINE.json configs[2]: region 17 at half capacity) ----
     # 5 steps through the onset, then a fingerprint of demand requests and storage contents: the same number at every N
     # proves the partitioned NCCL path bit-identical to the single-GPU run.  The timed window that follows is the shocked
@@ -347,6 +355,53 @@ def main():
                      "steps": args.flood_steps, "window": "steps 6..%d after the onset of a 50 %% production loss in region 17" % (5 + args.flood_steps),
                      "evaluations_per_manager_last_step": {"mean": float(evals.mean()), "max": int(evals.max())},
                      "kernels_ms_per_step": {k: v[0] / args.flood_steps for k, v in fk.items()}}
+
+    # ---- scenario ensemble (BASELINE.json configs[4]: 1 024 shock scenarios on the EORA shape, 128 per GPU) ----
+    # M members resident on this GPU at a time (a wave): ONE copy of the network tables, M copies of the state, every member with
+    # its own seeded shock (region and remaining capacity), stepped concurrently on their own streams.
+    ensemble = None
+    if base_member is not None:
+        rng = np.random.default_rng(20260105)
+        free_b, _ = torch.cuda.mem_get_info()
+        state_b = E.state_bytes()
+        M = max(1, min(args.members, 1 + int(free_b * 0.9 // state_b)))
+        members = [base_member] + [base_member.fork() for _ in range(M - 1)]
+        at, ar, ab = (np.asarray(net[k]) for k in ("agent_type", "agent_region", "agent_beta"))
+        R = int(net["meta"][1])
+        shocks = []
+        for m in members:
+            region, cap = int(rng.integers(0, R)), float(rng.uniform(0.2, 0.8))
+            lam_m = np.ones(E.n_agents)
+            hit_m = (at == 1) & (ar == region)
+            lam_m[hit_m] = cap / ab[hit_m]
+            m.set_agent_forcing(lam_m)
+            shocks.append((region, round(cap, 3)))
+        for m in members:  # onset step, untimed
+            m.step()
+        for m in members:
+            m.sync()
+        streams = [torch.cuda.ExternalStream(m.stream(), device=torch.device("cuda", local_rank)) for m in members]
+        torch.cuda.synchronize()
+        e0 = [torch.cuda.Event(enable_timing=True) for _ in members]
+        e1 = [torch.cuda.Event(enable_timing=True) for _ in members]
+        for k, m in enumerate(members):
+            e0[k].record(streams[k])
+        for _ in range(args.member_steps):
+            for m in members:
+                m.step()
+        for k, m in enumerate(members):
+            e1[k].record(streams[k])
+        torch.cuda.synchronize()
+        ens_ms = max(e0[0].elapsed_time(e1[k]) for k in range(M))
+        prints = {"%016x" % (int(np.sum(m.read_state("firm_X_q").astype(np.uint64) * (2 * np.arange(E.n_agents, dtype=np.uint64) + 1), dtype=np.uint64))) for m in members}
+        rate = n_edges * M * args.member_steps / (ens_ms * 1e-3)
+        ensemble = {"value": rate, "unit": "updates/s", "members_resident": M, "steps": args.member_steps, "ms_per_member_step": ens_ms / (M * args.member_steps),
+                    "scenario_steps_per_s": M * args.member_steps / (ens_ms * 1e-3), "distinct_states": len(prints), "shocks": shocks[:4],
+                    "state_bytes_per_member": state_b, "network_tables": "shared (acc_fork)",
+                    "configs4_estimate_s": 1024 * 1095 / 8 / (M * args.member_steps / (ens_ms * 1e-3)),
+                    "note": "shocked regime (every member inside its shock window); configs[4] = 1 024 scenarios x 1 095 steps over 8 GPUs in waves of members_resident"}
+        for m in members:
+            m.close()
 
     t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -397,6 +452,7 @@ def main():
             "cpu_baseline": cpu,
             "state_hash": state_hash,
             "flood": flood,
+            "ensemble": ensemble,
         }
         if partitioned:
             pk = sum(v[0] for k, v in ktimes.items() if k.startswith("pack_") or k.startswith("unpack_")) / args.steps

@@ -107,11 +107,33 @@ typedef struct {
     double value;
 } acc_event;
 
+/* ---- network ingest: the step BEFORE the path, on the device ----
+ * Replaces the dense branch of ModelInitializer::build_agent_network_from_table (src/input/ModelInitializer.cpp:832-834,
+ * :947-965), initialize_connection's self-supply rule (:187-190) and clean_network (:215-299): flows[n_agents][n_agents] are
+ * annual flows as float (row = selling agent), a cell becomes a connection when  flow > threshold  and its quantised
+ * per-timestep flow  round(FlowQuantity(flow) * time_factor)  exceeds the quantised per-timestep threshold; then firms without
+ * value added, buyers or inputs (and consumers without inputs) are removed in the reference's sweep order until nothing
+ * changes.  agent_alive[n_agents] (may be NULL) tells who is left; the surviving connections come back seller-major, buyer
+ * ascending, in ORIGINAL agent numbers (edge_* may be NULL: *n_edges then only reports how many there are).  The caller
+ * renumbers the survivors and hands the result to acc_create (acclimate_b200/ingest.py does). */
+int acc_ingest_table(int device, int64_t n_agents, int64_t n_sectors, const int64_t* agent_type, const int64_t* agent_sector, const float* flows,
+                     double threshold, double time_factor, int no_self_supply, uint8_t* agent_alive, int64_t* n_edges, int64_t* edge_from,
+                     int64_t* edge_to, int64_t* edge_zq, size_t cap_edges, int64_t* sweeps, int64_t* removed);
+
 /* replaces Model::Model + ModelInitializer::initialize + Model::start
  * (include/model/Model.h:62,72; src/ModelRun.cpp:108-116,163-168) */
 acc_engine* acc_create(const acc_network* net, const acc_params* params, int device);
 /* replaces ~Model */
 void acc_destroy(acc_engine* e);
+
+/* ---- ensembles of scenarios on one network (BASELINE.json configs[4]; SURVEY 8e "replicate topology once per GPU, batch state
+ * along a scenario axis") ----
+ * No counterpart in the reference, which runs one scenario per process.  acc_fork makes an ensemble MEMBER: a new engine on the
+ * parent's device that shares the parent's immutable tables -- the network itself: connections, Z*, delays, routes, both
+ * buyer-side lists, agent and sector constants -- and owns only the state (what acc_save_state names), copied from the parent
+ * as it is at the time of the call.  Parent and members are then forced, stepped and read independently, each on its own
+ * stream; the shared tables are released when the last engine that uses them is destroyed, in whatever order. */
+acc_engine* acc_fork(acc_engine* parent);
 
 /* ---- region-partitioned run: one engine per device, each owning the agents of a block of regions ----
  * The reference parallelises the same loops over agents with OpenMP on shared memory (src/model/Model.cpp:59-118);

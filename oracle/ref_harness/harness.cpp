@@ -91,6 +91,7 @@ struct HarnessConfig {
     std::string dump_path;
     int dump_every = 1;
     bool dump_edges = true;
+    std::string ingest_out;         // --ingest <out.acc>: candidate flow table -> threshold filter -> clean_network; dumps the survivors, no run
     bool dump_observables = false;  // --observe: every observable of the reference's observe<>() visitors, shaped like ArrayOutput's data
     const std::vector<std::int64_t>& I(const char* n) const { return net.at(n).i; }
     const std::vector<double>& F(const char* n) const { return net.at(n).f; }
@@ -300,12 +301,36 @@ class ModelInitializer {
         }
         }
         // connections: initialize_connection, ModelInitializer.cpp:187-213
-        const auto& ef = cfg.I("edge_from");
-        const auto& et = cfg.I("edge_to");
-        const auto& ez = cfg.I("edge_zq");
+        std::vector<std::int64_t> t_from, t_to, t_zq;
+        const bool ingest = !cfg.ingest_out.empty();
+        if (ingest) {
+            // the dense branch of build_agent_network_from_table, ModelInitializer.cpp:832-834,947-965: annual flows as float,
+            // kept when  *d > flow_threshold && flow > daily_flow_threshold  with flow = round(FlowQuantity(*d) * time_factor)
+            const auto& table = cfg.F("flows_f32");  // values exactly representable as float, row = source agent
+            const FloatType flow_threshold = cfg.F("threshold").at(0);
+            const FloatType time_factor = cfg.F("time_factor").at(0);
+            const FlowQuantity daily_flow_threshold = round(FlowQuantity(flow_threshold * time_factor));
+            if (table.size() != n_agents * n_agents) throw std::runtime_error("flows_f32 must hold n_agents x n_agents values");
+            for (std::size_t i = 0; i < n_agents; ++i) {
+                if (!agents[i]->is_firm()) continue;
+                for (std::size_t j = 0; j < n_agents; ++j) {
+                    const float d = float(table[i * n_agents + j]);
+                    const FlowQuantity flow = round(FlowQuantity(d) * time_factor);
+                    if (d > flow_threshold && flow > daily_flow_threshold) {
+                        if (model->no_self_supply() && i == j) continue;  // initialize_connection, :188-190
+                        t_from.push_back(std::int64_t(i)); t_to.push_back(std::int64_t(j));
+                        t_zq.push_back(iround(to_float(flow) / FlowQuantity::precision));
+                    }
+                }
+            }
+        }
+        const auto& ef = ingest ? t_from : cfg.I("edge_from");
+        const auto& et = ingest ? t_to : cfg.I("edge_to");
+        const auto& ez = ingest ? t_zq : cfg.I("edge_zq");
         const auto& cel = cfg.F("consumer_elasticity");
-        edges.reserve(n_edges);
-        for (std::size_t e = 0; e < n_edges; ++e) {
+        const std::size_t n_edges_used = ingest ? t_from.size() : n_edges;
+        edges.reserve(n_edges_used);
+        for (std::size_t e = 0; e < n_edges_used; ++e) {
             Firm* firm_from = agents[ef[e]]->as_firm();
             EconomicAgent* to = agents[et[e]];
             if (model->no_self_supply() && static_cast<void*>(firm_from) == static_cast<void*>(to)) {
@@ -336,9 +361,84 @@ class ModelInitializer {
 #ifndef ORACLE_NLOPT_KRAFT
         nlopt_provider_set_group(accsqp_group_for(int(n_max)));  // the engine's rule for its solver group (csrc/sqp_core.h)
 #endif
+        if (ingest) {
+            clean_network();
+            dump_survivors(ef, et, ez);
+            return;
+        }
         check_clean();
         // post_initialize, ModelInitializer.cpp:1081-1085
         for (auto& agent : model->economic_agents) agent->initialize();
+    }
+
+    // clean_network, ModelInitializer.cpp:215-299, restated around the reference's own mutators (Storage::subtract_initial_flow_Z_star,
+    // PurchasingManager / SalesManager::remove_business_connection, Firm::subtract_initial_production_X_star): sweeps over the
+    // agents in order; a firm without value added, buyers or inputs (a lone self-supply connection does not count) is taken out
+    // at once -- its buyers' storages and its suppliers' production shrink before the next agent is looked at -- and the
+    // sweeps repeat until one removes nothing.
+    std::size_t clean_sweeps = 0;
+    void clean_network() {
+        for (;;) {
+            ++clean_sweeps;
+            std::vector<EconomicAgent*> to_remove;
+            for (auto& ea : model->economic_agents) {
+                if (ea->is_firm()) {
+                    Firm* firm = ea->as_firm();
+                    FlowQuantity input(0.0);
+                    for (const auto& is : firm->input_storages) input = input + is->initial_input_flow_I_star().get_quantity();
+                    const FloatType value_added = to_float(firm->initial_production_X_star().get_quantity() - input);
+                    const bool self = firm->self_supply_connection() != nullptr;
+                    const auto& out = firm->sales_manager->business_connections;
+                    if (value_added <= 0.0 || out.empty() || (out.size() == 1 && self) || firm->input_storages.empty() || (firm->input_storages.size() == 1 && self)) {
+                        for (auto& bc : firm->sales_manager->business_connections) {            // :253-260: the buyers lose this input
+                            if (bc->buyer == nullptr) throw std::runtime_error("Buyer invalid");
+                            if (!bc->buyer->storage->subtract_initial_flow_Z_star(bc->initial_flow_Z_star())) bc->buyer->remove_business_connection(bc.get());
+                        }
+                        for (auto& storage : firm->input_storages) {                            // :263-271: the suppliers lose this buyer
+                            for (auto& bc : storage->purchasing_manager->business_connections) {
+                                if (bc->seller == nullptr) throw std::runtime_error("Seller invalid");
+                                bc->seller->firm->subtract_initial_production_X_star(bc->initial_flow_Z_star());
+                                bc->seller->remove_business_connection(bc.get());
+                            }
+                        }
+                        firm->sector->firms.remove(firm);
+                        firm->region->economic_agents.remove(ea.get());
+                        to_remove.push_back(ea.get());
+                    }
+                } else if (ea->input_storages.empty()) {                                        // :279-286
+                    ea->region->economic_agents.remove(ea.get());
+                    to_remove.push_back(ea.get());
+                }
+            }
+            if (to_remove.empty()) break;
+            for (auto* gone : to_remove)
+                for (auto& slot : agents) if (slot == gone) slot = nullptr;
+            model->economic_agents.remove(to_remove);
+        }
+    }
+    // what is left: agents by their index in the candidate list, connections that still link a living seller to a living storage
+    void dump_survivors(const std::vector<std::int64_t>& ef, const std::vector<std::int64_t>& et, const std::vector<std::int64_t>& ez) {
+        accio::Writer out(cfg.ingest_out);
+        std::vector<std::int64_t> alive(agents.size(), 0), o_from, o_to, o_zq, xstar(agents.size(), 0);
+        for (std::size_t a = 0; a < agents.size(); ++a) {
+            if (agents[a] == nullptr) continue;
+            alive[a] = 1;
+            if (agents[a]->is_firm()) {
+                xstar[a] = iround(to_float(agents[a]->as_firm()->initial_production_X_star().get_quantity()) / FlowQuantity::precision);
+                for (const auto& bc : agents[a]->as_firm()->sales_manager->business_connections) {
+                    const EconomicAgent* buyer = bc->buyer->storage->economic_agent;
+                    std::size_t b = 0;
+                    while (b < agents.size() && agents[b] != buyer) ++b;
+                    o_from.push_back(std::int64_t(a)); o_to.push_back(std::int64_t(b));
+                    o_zq.push_back(iround(to_float(bc->initial_flow_Z_star().get_quantity()) / FlowQuantity::precision));
+                }
+            }
+        }
+        (void)ef; (void)et; (void)ez;
+        out.put("agent_alive", alive);
+        out.put("edge_from", o_from); out.put("edge_to", o_to); out.put("edge_zq", o_zq);
+        out.put("firm_Xstar_q", xstar);
+        out.put("sweeps", std::vector<std::int64_t>{std::int64_t(clean_sweeps)});
     }
 
     // clean_network (ModelInitializer.cpp:215-299) must be a no-op for a valid snapshot: the generator guarantees it.
@@ -663,12 +763,14 @@ int main(int argc, char** argv) {
             if (a == "--every" && i + 1 < argc) cfg.dump_every = std::atoi(argv[++i]);
             else if (a == "--no-edges") cfg.dump_edges = false;
             else if (a == "--observe") cfg.dump_observables = true;
+            else if (a == "--ingest" && i + 1 < argc) cfg.ingest_out = argv[++i];
             else cfg.dump_path = a;
         }
         settings::SettingsNode node;
         node.cfg = &cfg;
         const auto t0 = std::chrono::high_resolution_clock::now();
         acclimate::ModelRun run(node);
+        if (!cfg.ingest_out.empty()) return 0;  // ingest only: the survivors have been written
         const auto t1 = std::chrono::high_resolution_clock::now();
         run.run();
         const double init_s = std::chrono::duration<double>(t1 - t0).count();
