@@ -269,6 +269,7 @@ struct NcclApi {
     int (*Send)(const void*, size_t, int, int, comm_t, cudaStream_t) = nullptr;
     int (*Recv)(void*, size_t, int, int, comm_t, cudaStream_t) = nullptr;
     int (*AllGather)(const void*, void*, size_t, int, comm_t, cudaStream_t) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, comm_t, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
     enum { Int64 = 4 };
     static NcclApi& get() {
@@ -291,6 +292,7 @@ struct NcclApi {
         api.Recv = reinterpret_cast<decltype(api.Recv)>(sym("ncclRecv"));
         api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
         api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
+        api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
         api.Send = reinterpret_cast<decltype(api.Send)>(sym("ncclSend"));
         return api;
     }
@@ -555,7 +557,7 @@ struct Purchase {
                 }
                 return m;
             },
-            [&](int e, i64 q, i64 p) { E.D_q[e] = q; E.D_p[e] = p; }, k, mp, sectors[st.sector[s]], st.Istar_q[s], st.Sstar_q[s],
+            [&](int e, i64 q, i64 p) { E.D_q[e] = q; E.D_p[e] = p; peer_store_demand(E, e, q, p); }, k, mp, sectors[st.sector[s]], st.Istar_q[s], st.Sstar_q[s],
             st.S_q[s], st.Ut_q[s], deficit, events, st.sector[s], st.agent[s]);
         if (cx.leader()) {
             dem_q[s] = r.demand.q; dem_v[s] = r.demand.v; exp_costs[s] = r.expected_costs; opt_val[s] = r.optimized; tpen[s] = r.penalty;
@@ -796,6 +798,13 @@ struct acc_engine {
     std::vector<i64> comm_send_cnt, comm_recv_cnt, comm_send_off, comm_recv_off;
     DBuf<int> comm_part_firms, comm_part_off;
     DBuf<i64> comm_rows_send, comm_rows_recv;
+    // peer stores (acc_comm_enable_peer_stores): the other parts' arrays mapped over NVLink, the connections' ids there
+    bool peer_stores = false;
+    DBuf<signed char> x_peer;
+    DBuf<int> x_rid;
+    DBuf<PeerTable> peer_table;
+    DBuf<i64> barrier_word;
+    std::vector<void*> ipc_opened;
 #ifndef ACC_HOST_EMU
     NcclApi::comm_t comm = nullptr;
 #endif
@@ -835,6 +844,7 @@ struct acc_engine {
         v(owned); v(pm_ids); v(halo_send); v(halo_recv);
         v(own_flow_send); v(own_flow_recv); v(own_dem_send); v(own_dem_recv); v(own_sellers);
         v(comm_part_firms); v(comm_part_off); v(comm_rows_send); v(comm_rows_recv);
+        v(x_peer); v(x_rid); v(peer_table); v(barrier_word);
     }
     // ensemble members (acc_fork): a member shares its parent's immutable tables; the parent's memory lives until the last member is gone
     acc_engine* parent = nullptr;
@@ -853,6 +863,7 @@ struct acc_engine {
 #ifndef ACC_HOST_EMU
         for (auto& c : clocks)
             for (auto& pr : c.pending) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+        for (void* q : ipc_opened) cudaIpcCloseMemHandle(q);
         if (comm != nullptr) NcclApi::get().CommDestroy(comm);
         if (ev_fork) cudaEventDestroy(ev_fork);
         if (ev_join) cudaEventDestroy(ev_join);
@@ -898,6 +909,7 @@ struct acc_engine {
         v.ovf_q = forcing_used ? e_ovf_q.p : nullptr; v.ovf_v = forcing_used ? e_ovf_v.p : nullptr; v.nu = forcing_used ? nu.p : nullptr;
         v.ship_q = e_ship_q.n ? e_ship_q.p : nullptr;
         v.ship_v = e_ship_v.n ? e_ship_v.p : nullptr;
+        v.x_peer = peer_stores ? x_peer.p : nullptr; v.x_rid = peer_stores ? x_rid.p : nullptr; v.peers = peer_stores ? peer_table.p : nullptr;
         return v;
     }
     ConsumerView consumer_view() {
@@ -997,7 +1009,7 @@ struct acc_engine {
             timed("seller_production", [&] { launch_seller(stream, nF, book_cap, k); });
             ship_step = step;
         }
-        if (halo_send.n) {
+        if (halo_send.n && !peer_stores) {
             PackFlow k{edge_view(), (int)(step % T), halo_send.p, x_flow_send};
             timed("pack_flow", [&] { launch_thread(stream, (int)halo_send.n, k); });
         }
@@ -1048,7 +1060,7 @@ struct acc_engine {
         } else {
             launch_purchase<false, false, 0>();
         }
-        if (halo_recv.n) {
+        if (halo_recv.n && !peer_stores) {
             PackDemand pk{edge_view(), halo_recv.p, x_dem_send};
             timed("pack_demand", [&] { launch_thread(stream, (int)halo_recv.n, pk); });
         }
@@ -1075,6 +1087,14 @@ struct acc_engine {
         ++collectives;
     }
 #endif
+#ifndef ACC_HOST_EMU
+    // all parts have reached this point of their streams, and the peer stores of the kernels before it are visible: a
+    // one-word all-reduce (kernel boundaries make the stores visible system-wide, the collective orders the parts)
+    void cross_barrier() {
+        ACC_NCCL(NcclApi::get().AllReduce(barrier_word.p, barrier_word.p + 1, 1, NcclApi::Int64, 0 /* ncclSum */, comm, stream));
+        ++collectives;
+    }
+#endif
     i64 collectives = 0;
     // One timestep of a region-partitioned run with the engine doing its own exchanges (NCCL on the engine's stream):
     //   sellers' pass -> shipments to the buyers' parts -> storages, deliveries, expectation -> all-gather of the owned
@@ -1086,7 +1106,8 @@ struct acc_engine {
         if (comm == nullptr) fail("acc_step_partitioned: call acc_comm_init first");
         NcclApi& nc = NcclApi::get();
         stage_sell();
-        timed_comm("exchange_flow", [&] { exchange_halo(x_flow_send, comm_send_cnt, comm_send_off, x_flow_recv, comm_recv_cnt, comm_recv_off); });
+        if (peer_stores) timed_comm("barrier_shipments", [&] { cross_barrier(); });  // every part's shipments have landed on its buyers' conveyors
+        else timed_comm("exchange_flow", [&] { exchange_halo(x_flow_send, comm_send_cnt, comm_send_off, x_flow_recv, comm_recv_cnt, comm_recv_off); });
         {   // stage_deliver without the full-table pack
             if (halo_recv.n) {
                 UnpackFlow k{edge_view(), (int)(step % T), halo_recv.p, x_flow_recv};
@@ -1108,7 +1129,8 @@ struct acc_engine {
             timed("unpack_sellers", [&] { launch_thread(stream, comm_world * comm_max_rows, k); });
         }
         purchase_and_pack();
-        timed_comm("exchange_demand", [&] { exchange_halo(x_dem_send, comm_recv_cnt, comm_recv_off, x_dem_recv, comm_send_cnt, comm_send_off); });
+        if (peer_stores) timed_comm("barrier_demand", [&] { cross_barrier(); });  // every part's demand requests have landed in its sellers' books
+        else timed_comm("exchange_demand", [&] { exchange_halo(x_dem_send, comm_recv_cnt, comm_recv_off, x_dem_recv, comm_send_cnt, comm_send_off); });
         stage_close();
 #endif
     }
@@ -2338,6 +2360,86 @@ int acc_comm_init(acc_engine* e, const void* id, int rank, int world, const int3
 #endif
     return 0;
     ACC_API_END(-1)
+}
+
+int acc_comm_enable_peer_stores(acc_engine* e) {
+    ACC_API_BEGIN
+    if (e == nullptr) fail("acc_comm_enable_peer_stores: null engine");
+    ACC_ON_DEVICE(e);
+#ifdef ACC_HOST_EMU
+    fail("acc_comm_enable_peer_stores: the emulation has no peer memory");
+#else
+    if (e->comm == nullptr) fail("acc_comm_enable_peer_stores: call acc_comm_init first");
+    if (e->peer_stores) return 0;
+    if (e->step != 0) fail("acc_comm_enable_peer_stores: only before the first step");
+    if (e->x_flow_recv != e->own_flow_recv.p || e->x_dem_recv != e->own_dem_recv.p)
+        fail("acc_comm_enable_peer_stores: the receive buffers must be the engine's own (pass NULL buffers to acc_set_halo)");
+    const int world = e->comm_world, rank = e->comm_rank;
+    if (world > ACC_MAX_PARTS) fail("acc_comm_enable_peer_stores: more parts than ACC_MAX_PARTS");
+    NcclApi& nc = NcclApi::get();
+    stream_t s = e->stream;
+    // every part tells the others where its two receive buffers are (IPC handles) and how its halo lists split over the parts:
+    // the k-th entry this part sends to part p is the k-th entry p receives from it (both lists are in global order), so its
+    // position in p's buffer is p's offset for this part + k -- no per-connection id has to travel
+    struct Hello { i64 send_cnt[ACC_MAX_PARTS], recv_cnt[ACC_MAX_PARTS]; cudaIpcMemHandle_t h[2]; };
+    static_assert(sizeof(Hello) % 8 == 0, "exchanged as int64 words");
+    Hello mine;
+    std::memset(&mine, 0, sizeof mine);
+    for (int p = 0; p < world; ++p) { mine.send_cnt[p] = e->comm_send_cnt[p]; mine.recv_cnt[p] = e->comm_recv_cnt[p]; }
+    void* arrays[2] = {e->own_flow_recv.p, e->own_dem_recv.p};
+    for (int k = 0; k < 2; ++k) ACC_CUDA(cudaIpcGetMemHandle(&mine.h[k], arrays[k]));
+    DBuf<i64> d_hello, d_all;
+    const size_t words = sizeof(Hello) / 8;
+    d_hello.alloc(words); d_all.alloc(words * world);
+    h2d(d_hello.p, &mine, sizeof mine, s);
+    ACC_NCCL(nc.AllGather(d_hello.p, d_all.p, words, NcclApi::Int64, e->comm, s));
+    std::vector<Hello> all(world);
+    d2h(all.data(), d_all.p, sizeof(Hello) * world, s);
+    d_hello.free(); d_all.free();
+    // (the only collective of this call is behind us: a part that cannot map its peers fails alone, nobody hangs)
+    PeerTable pt;
+    std::memset(&pt, 0, sizeof pt);
+    for (int p = 0; p < world; ++p) {
+        if (all[p].recv_cnt[rank] != e->comm_send_cnt[p] || all[p].send_cnt[rank] != e->comm_recv_cnt[p])
+            fail("acc_comm_enable_peer_stores: the parts' halo lists do not match");
+        void* ptr[2];
+        for (int k = 0; k < 2; ++k) {
+            if (p == rank) { ptr[k] = arrays[k]; continue; }
+            ACC_CUDA(cudaIpcOpenMemHandle(&ptr[k], all[p].h[k], cudaIpcMemLazyEnablePeerAccess));
+            e->ipc_opened.push_back(ptr[k]);
+        }
+        pt.flow_recv[p] = static_cast<i64*>(ptr[0]); pt.dem_recv[p] = static_cast<i64*>(ptr[1]);
+    }
+    std::vector<i64> hs = e->halo_send.download(s), hr = e->halo_recv.download(s);
+    std::vector<signed char> xp((size_t)e->nE, (signed char)-1);
+    std::vector<int> xr((size_t)e->nE, 0);
+    for (int p = 0; p < world; ++p) {
+        if (p == rank) continue;
+        i64 their_recv_off = 0, their_send_off = 0;  // where this part's entries start in p's receive buffers
+        for (int q = 0; q < rank; ++q) { their_recv_off += all[p].recv_cnt[q]; their_send_off += all[p].send_cnt[q]; }
+        for (i64 k = 0; k < e->comm_send_cnt[p]; ++k) {  // shipments to p: p's flow_recv, in p's receive order
+            const i64 edge = hs[e->comm_send_off[p] + k];
+            xp[edge] = (signed char)p; xr[edge] = (int)(their_recv_off + k);
+        }
+        for (i64 k = 0; k < e->comm_recv_cnt[p]; ++k) {  // demand requests to p: p's dem_recv, in p's send order
+            const i64 edge = hr[e->comm_recv_off[p] + k];
+            xp[edge] = (signed char)p; xr[edge] = (int)(their_send_off + k);
+        }
+    }
+    e->x_peer.upload(xp, s); e->x_rid.upload(xr, s);
+    e->peer_table.upload(std::vector<PeerTable>(1, pt), s);
+    e->barrier_word.alloc(2); e->barrier_word.zero(s);
+    dev_sync(s);
+    e->peer_stores = true;
+#endif
+    return 0;
+    ACC_API_END(-1)
+}
+
+int acc_comm_disable_peer_stores(acc_engine* e) {
+    if (e == nullptr) return -1;
+    e->peer_stores = false;
+    return 0;
 }
 
 int acc_step_partitioned(acc_engine* e) {

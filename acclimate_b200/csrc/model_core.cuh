@@ -352,6 +352,20 @@ struct FirmView {
     i64* exp_q; double* exp_v;      // non-domestic shipments of this step (region export)
 };
 
+// Peer memory of a region-partitioned run (acc_comm_enable_peer_stores): the other parts' halo receive buffers, mapped into this
+// device's address space over NVLink (CUDA IPC).  A kernel that produces a shipment or a demand request for a connection whose
+// other end lives on another part stores the 16-byte entry straight into that part's receive buffer, at the entry's position
+// in the halo order, next to its local store: no pack kernel and no collective -- the transfer rides under the producing
+// kernel; the receiving part applies the buffer with its unpack kernel once a cross-part barrier says everything has landed.
+#define ACC_MAX_PARTS 16
+struct PeerTable {
+    i64* flow_recv[ACC_MAX_PARTS];  // [n_recv_p][2] shipments (quantity, value bits) part p receives
+    i64* dem_recv[ACC_MAX_PARTS];   // [n_send_p][2] demand requests (quantity, price) part p receives
+};
+struct alignas(16) HaloEntry {
+    i64 a, b;
+};
+
 // Connection arrays in CSR-by-seller order
 struct EdgeView {
     const int* seller_off;          // [n_agents + 1]
@@ -367,7 +381,27 @@ struct EdgeView {
     i64* ovf_q; double* ovf_v;      // overflow per (hop, connection): [hop][n_edges] (null until passage forcing is used)
     const double* nu;               // passage per geo entity (null until used; < 0: none)
     i64* ship_q; double* ship_v;    // last shipment (only kept apart when hops may rewrite its conveyor slot, else null)
+    // peer stores (null: none): part that holds the other end of each connection (-1: this one) and the entry's position in that
+    // part's receive buffer
+    const signed char* x_peer; const int* x_rid; const PeerTable* peers;
 };
+// the shipment on connection e also goes into the receive buffer of the part that owns the buyer (one 16-byte store)
+ACC_HD void peer_store_shipment(const EdgeView& ev, i64 e, Flow z) {
+    if (ev.x_peer == nullptr) return;
+    const int p = ev.x_peer[e];
+    if (p < 0) return;
+    HaloEntry h;
+    h.a = z.q; memcpy(&h.b, &z.v, sizeof h.b);
+    reinterpret_cast<HaloEntry*>(ev.peers->flow_recv[p])[ev.x_rid[e]] = h;
+}
+ACC_HD void peer_store_demand(const EdgeView& ev, i64 e, i64 q, i64 pr) {
+    if (ev.x_peer == nullptr) return;
+    const int p = ev.x_peer[e];
+    if (p < 0) return;
+    HaloEntry h;
+    h.a = q; h.b = pr;
+    reinterpret_cast<HaloEntry*>(ev.peers->dem_recv[p])[ev.x_rid[e]] = h;
+}
 
 // ------------------------------------------------------------------------------------------------
 // Phase 1, one seller: production X, offer price, cutoff price (calc_supply_distribution_scenario,
@@ -484,6 +518,7 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
             ev.conv_q[(i64)pl * ev.n_edges + e0 + i] = 0;
             if (ev.ship_q != nullptr) { ev.ship_q[e0 + i] = 0; ev.ship_v[e0 + i] = 0.0; }
             ev.conv_v[(i64)pl * ev.n_edges + e0 + i] = 0.0;
+            peer_store_shipment(ev, (i64)e0 + i, mkflow(0, 0.0));
         });
     } else {
         const i64 h = half_width(mp, sp.dn, fv.beta[f]);
@@ -533,6 +568,7 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
             ev.conv_q[(i64)pl * ev.n_edges + e0 + i] = z.q;           // BusinessConnection::push_flow_Z -> first transport link
             if (ev.ship_q != nullptr) { ev.ship_q[e0 + i] = z.q; ev.ship_v[e0 + i] = z.v; }  // last_shipment_Z, kept apart when hops rewrite the slot
             ev.conv_v[(i64)pl * ev.n_edges + e0 + i] = z.v;
+            peer_store_shipment(ev, (i64)e0 + i, z);
             if (!dom[i]) { r.eq = z.q; r.ev = z.v; }                  // Region::add_export_Z, BusinessConnection.cpp:91-93
             return r;
         });

@@ -101,7 +101,7 @@ class PartitionedEngine(_engine.Engine):
     """One part of a region-partitioned model.  Needs an initialised torch.distributed process group with one rank
     per part (NCCL for the CUDA library; the CPU tests drive the emulation library over gloo)."""
 
-    def __init__(self, arrays, region_owner=None, device=0, lib_path=None, group=None, tensor_device=None, local=False, plane=None):
+    def __init__(self, arrays, region_owner=None, device=0, lib_path=None, group=None, tensor_device=None, local=False, plane=None, peer_stores=True):
         """plane: "nccl" -- the engine exchanges its halos itself (acc_comm_init / acc_step_partitioned: NCCL from C++ on the
         engine's stream; default when the process group's backend is NCCL); "host" -- this class moves the exchange buffers
         between the four stages with torch.distributed (gloo in the CPU tests, where the emulation library has no NCCL)."""
@@ -152,6 +152,15 @@ class PartitionedEngine(_engine.Engine):
             lib.acc_comm_init.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
             lib.acc_step_partitioned.argtypes = [C.c_void_p]
             self._check(lib.acc_comm_init(self.h, raw, rank, world, part32.ctypes.data, sc.ctypes.data, rc.ctypes.data))
+            self.peer_stores = False
+            if peer_stores:
+                lib.acc_comm_enable_peer_stores.argtypes = [C.c_void_p]
+                ok = torch.tensor([1 if lib.acc_comm_enable_peer_stores(self.h) == 0 else 0], dtype=torch.int64, device=self.tensor_device)
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+                self.peer_stores = int(ok[0]) == 1
+                if not self.peer_stores:  # some part could not map its peers: everybody stays with the NCCL exchanges
+                    lib.acc_comm_disable_peer_stores.argtypes = [C.c_void_p]
+                    lib.acc_comm_disable_peer_stores(self.h)
         else:
             mk = lambda rows, cols: torch.zeros((rows, cols), dtype=torch.int64, device=self.tensor_device)
             self.flow_send, self.flow_recv = mk(ns, 2), mk(nr, 2)

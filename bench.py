@@ -196,6 +196,7 @@ def main():
                          "NCCL (strong scaling; default), or one independent member of the same workload per GPU (weak scaling, no collective)")
     ap.add_argument("--flood-steps", type=int, default=10, help="timed steps of the shocked window that follows the baseline measurement (0: none)")
     ap.add_argument("--ensemble-shocks", action="store_true", help="ensemble members other than the first get their own regional shock")
+    ap.add_argument("--no-peer-stores", action="store_true", help="partitioned run: exchange the halos with NCCL send/recv groups instead of peer stores")
     ap.add_argument("--members", type=int, default=8, help="scenario ensemble on ONE GPU after the headline run (BASELINE.json configs[4] pattern): this many "
                                                             "acc_fork members share the network tables, each with its own seeded regional shock (0: none)")
     ap.add_argument("--member-steps", type=int, default=5)
@@ -231,13 +232,13 @@ def main():
 
         owner = partition.assign_regions_uniform(int(os.environ.get("ACC_X4_REGIONS", synth.CONFIGS["x4"]["regions"])), world)
         net, workload = make_network(args, rank, part=(owner, rank))
-        E = partition.PartitionedEngine(net, region_owner=owner, device=local_rank, local=True)
+        E = partition.PartitionedEngine(net, region_owner=owner, device=local_rank, local=True, peer_stores=not args.no_peer_stores)
         n_edges = E.part.global_edges
     elif partitioned:
         from acclimate_b200 import partition
 
         net, workload = make_network(args, rank)
-        E = partition.PartitionedEngine(net, device=local_rank)
+        E = partition.PartitionedEngine(net, device=local_rank, peer_stores=not args.no_peer_stores)
         n_edges = int(net["meta"][3])  # the whole network; this rank holds E.n_edges of them (owned seller or owned buyer)
     else:
         net, workload = make_network(args, rank)
@@ -283,8 +284,8 @@ def main():
     exchange_ms = None
     if nccl_plane:
         # the engine issues the collectives itself (acc_step_partitioned) and clocks them like its kernels
-        exchange_ms = sum(v[0] for k, v in ktimes.items() if k.startswith("exchange_")) / args.steps
-        ktimes = {k: v for k, v in ktimes.items() if not k.startswith("exchange_")}
+        exchange_ms = sum(v[0] for k, v in ktimes.items() if k.startswith("exchange_") or k.startswith("barrier_")) / args.steps
+        ktimes = {k: v for k, v in ktimes.items() if not (k.startswith("exchange_") or k.startswith("barrier_"))}
     elif partitioned:
         # a second pass of the same K steps with CUDA events around the three exchanges (kept out of the headline timing:
         # the extra event records sit on the stream)
@@ -457,7 +458,9 @@ def main():
         if partitioned:
             pk = sum(v[0] for k, v in ktimes.items() if k.startswith("pack_") or k.startswith("unpack_")) / args.steps
             line["partition"] = {"collective_ms": exchange_ms, "pack_ms": pk, "halo_bytes_per_step_this_rank": E.halo_bytes_per_step(),
-                                 "data_plane": "acc_step_partitioned (C++, NCCL)" if nccl_plane else "acc_stage + torch.distributed"}
+                                 "data_plane": ("acc_step_partitioned (C++): halos stored into the peers' memory by the producing kernels over NVLink (CUDA IPC), "
+                                                "2 one-word all-reduces + 1 all-gather of seller records per step" if getattr(E, "peer_stores", False)
+                                                else "acc_step_partitioned (C++, NCCL send/recv groups)") if nccl_plane else "acc_stage + torch.distributed"}
         print(json.dumps(line))
     E.close()
     if world > 1:

@@ -183,6 +183,18 @@ int acc_comm_unique_id(void* id);
 int acc_comm_init(acc_engine* e, const void* id, int rank, int world, const int32_t* agent_part, const int64_t* send_counts,
                   const int64_t* recv_counts);
 int acc_step_partitioned(acc_engine* e);
+/* Peer stores (call once after acc_comm_init, before the first step; all parts; needs the engine-owned exchange buffers of
+ * acc_set_halo(..., NULL x 5)).  The parts map each other's halo RECEIVE buffers into their address spaces (CUDA IPC over
+ * NVLink / NVSwitch); from then on the kernel that produces a shipment or a demand request for a connection whose other end
+ * lives on another part stores the 16-byte entry straight into that part's receive buffer, at its position in the halo order,
+ * next to its local store.  The pack kernels and the two NCCL send / receive groups of acc_step_partitioned disappear: the
+ * transfer rides under the sellers' pass and under the purchasing kernel, and two one-word all-reduces per step order the
+ * parts (all shipments landed / all demand requests landed) before the receiving part applies its buffer.  Results are
+ * unchanged bit for bit.  Fails (and leaves the NCCL exchanges in place) where peer access is not possible. */
+int acc_comm_enable_peer_stores(acc_engine* e);
+/* All parts must run the same protocol: when the call failed on ANY part (the caller agrees on that, e.g. with a MIN all-reduce
+ * of the return codes, which also orders the parts before the first step), every part calls this and the NCCL exchanges stay. */
+int acc_comm_disable_peer_stores(acc_engine* e);
 /* collectives (point-to-point groups and all-gathers) the engine has issued since acc_comm_init */
 int64_t acc_collective_count(const acc_engine* e);
 
