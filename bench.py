@@ -188,7 +188,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="eora", choices=["eora", "eora_flood", "small", "x4", "wide"])
-    ap.add_argument("--ref-steps", type=int, default=3)
+    ap.add_argument("--ref-steps", type=int, default=10, help="--impl reference: at most this many timed steps (a step of the full network takes ~1.6 s on 16 cores)")
     ap.add_argument("--reference-small", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--mode", default=None, choices=["ensemble", "partition"],
@@ -309,6 +309,26 @@ def main():
         step_no += 1
     E.sync()
     e2e_s = time.perf_counter() - t0
+    # ---- the same loop with an OUTPUT-SIZED pull every step: all storages' contents ([sectors][agents]) and the flows
+    # of one region's sellers ([26 firms][agents]) through acc_observe -- gathered on the device, one copy each ----
+    e2e_outputs = None
+    if not partitioned and args.config in ("eora", "small"):
+        firms17 = np.nonzero((np.asarray(net["agent_type"]) == 1) & (np.asarray(net["agent_region"]) == min(17, E.n_regions - 1)))[0]
+        buf_s = np.empty(E.n_sectors * E.n_agents)
+        buf_f = np.empty(firms17.size * E.n_agents)
+        barrier()
+        t0o = time.perf_counter()
+        for _ in range(args.steps):
+            E.set_agent_forcing(lam.numpy())
+            E.step()
+            E.observe("storages", "content_quantity", out=buf_s)
+            E.observe("flows", "sent_flow_quantity", select_from=firms17, out=buf_f)
+            step_no += 1
+        E.sync()
+        o_s = time.perf_counter() - t0o
+        e2e_outputs = {"value": n_edges * args.steps / o_s, "unit": "updates/s", "ms_per_step": 1e3 * o_s / args.steps,
+                       "d2h_bytes_per_step": int(buf_s.nbytes + buf_f.nbytes),
+                       "call": "acc_step + acc_observe(storages/content_quantity, all) + acc_observe(flows/sent_flow_quantity, sellers of one region) per step"}
     sampler.stop_flag.set()
     sampler.join()
 
@@ -454,6 +474,7 @@ def main():
             "state_hash": state_hash,
             "flood": flood,
             "ensemble": ensemble,
+            "e2e_outputs": e2e_outputs,
         }
         if partitioned:
             pk = sum(v[0] for k, v in ktimes.items() if k.startswith("pack_") or k.startswith("unpack_")) / args.steps
