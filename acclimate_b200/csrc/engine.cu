@@ -503,7 +503,9 @@ struct Purchase {
     // any group size: 512 threads still fit; base group (96 threads, compile-time): 96 registers = 6 CTAs of 3 warps per
     // SM (5 warps on a scheduler: 16384 / (5 * 32) = 102).  80 registers would admit the 7 CTAs the shared memory allows
     // but spill: measured 3.22 ms against 3.10 ms on the EORA shape
-    enum { MAXREG = ACC_PM_MAXREG_ANY, MAXREG_FIXED = ACC_PM_MAXREG_FIXED };
+    // (a compile-time LARGE group -- the 384 threads of the 748-connection managers of the 4x network -- keeps the 80 registers
+    // that let two of its CTAs share an SM; it is told apart by the dropped D_r vector)
+    enum { MAXREG = ACC_PM_MAXREG_ANY, MAXREG_FIXED = DVAL ? ACC_PM_MAXREG_FIXED : ACC_PM_MAXREG_ANY };
     StorageView st; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
     // incoming connections per storage (seller ascending): connection id, seller | delay << 24, Z* (copies in this order:
     // one coalesced read instead of a gather through the connection id)
@@ -1032,9 +1034,8 @@ struct acc_engine {
             timed("pack_sellers", [&] { launch_thread(stream, nA, k); });
         }
     }
-    template <bool SEP, bool STD, int G>
+    template <bool SEP, bool STD, int G, bool DVAL = (G > 0)>  // the base group keeps the D_r summands; the large groups trade them for a second CTA per SM
     void launch_purchase() {
-        constexpr bool DVAL = G > 0;  // the base group keeps the D_r summands; the large groups trade them for a second CTA per SM
         Purchase<SEP, STD, DVAL> k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, in_Z.p, seller_table(), n_max,
                              partitioned ? pm_ids.p : nullptr, s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
         timed("purchase", [&] { launch_block_smem<G>(stream, partitioned ? n_pm : nSt, pm_group, pm_workspace_bytes(n_max, SEP, DVAL), k); });
@@ -1054,6 +1055,7 @@ struct acc_engine {
         const bool std_pen = mp.quadratic_penalty != 0 && mp.relative_penalty != 0 && !dev;
         if (std_pen) {
             if (pm_group == ACCSQP_GROUP) launch_purchase<false, true, ACCSQP_GROUP>();
+            else if (pm_group == 384) launch_purchase<false, true, 384, false>();  // 748 connections per manager (BASELINE.json configs[3]): 748x3 probe 1.30 -> 0.98 ms
             else launch_purchase<false, true, 0>();
         } else if (dev) {
             launch_purchase<true, false, 0>();

@@ -148,9 +148,9 @@ def run_reference(args):
 
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu --set full capture of this
-    same workload (profiles/r01_traffic.json names the summary it was read from); None when no capture is on file."""
+    same workload (profiles/r02_traffic.json names the summary it was read from); None when no capture is on file."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
             return json.load(f)[kernel]["dram_bytes_per_launch"]
     except (OSError, KeyError, ValueError):
         return None

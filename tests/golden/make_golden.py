@@ -173,6 +173,12 @@ def cases():
     synth.add_entity_passage(a, 2, 7, info["hub_loc"][0], 0.5)
     synth.add_entity_passage(a, 3, 5, info["access"][1], 0.3)
     yield "observe10", a, 10, {"no_kraft": True, "observe": True, "full_steps": [0, 4, 9]}
+    if "flood40_1095" in sys.argv[1:]:  # only on request: a quarter of an hour of oracle time
+        # BASELINE.json configs[2] as specified -- regional production loss from step 10 to 24, THREE YEARS of daily steps -- on a
+        # 40 x 26 cut of the EORA generator (1.1 M connections; the full network would keep the serial reference busy for a day):
+        # every 15th step as checksums of all per-storage / per-firm / region / sector arrays, plus the recovery series in full
+        yield "flood40_1095", synth_network("flood40_1095"), 1095, {"no_kraft": True, "full_steps": [], "synth": True, "no_edges": True,
+                                                                    "oracle_args": ["--every", "15", "--no-edges"], "keep_full": ["region_gdp_v", "firm_X_q"]}
     if "eora_flood4" in sys.argv[1:]:  # only on request: minutes of oracle time, 20 GB of memory
         yield "eora_flood4", synth_network("eora_flood4"), 4, {"no_kraft": True, "full_steps": [], "synth": True}
 
@@ -185,14 +191,18 @@ def synth_network(name):
         a = synth.make_config("eora")
         synth.add_shock(a, 1, 3, 17, 0.5)
         return a
+    if name == "flood40_1095":
+        a = synth.make_network(regions=40, sectors=26, seed=20260101 + 3)
+        synth.add_shock(a, 10, 24, 17, 0.5)
+        return a
     raise KeyError(name)
 
 
-def run_oracle(flavour, net, steps, tmp, observe=False):
+def run_oracle(flavour, net, steps, tmp, observe=False, extra=()):
     npath, dpath = os.path.join(tmp, "n.acc"), os.path.join(tmp, "d_%s.acc" % flavour)
     if not os.path.exists(npath):
         netfile.write(npath, net)
-    r = subprocess.run([ORACLE[flavour], npath, str(steps), dpath] + (["--observe"] if observe else []), capture_output=True, text=True,
+    r = subprocess.run([ORACLE[flavour], npath, str(steps), dpath] + (["--observe"] if observe else []) + list(extra), capture_output=True, text=True,
                        env=dict(os.environ, ORACLE_SOLVER_STATS="1"))
     if r.returncode != 0:
         raise RuntimeError("oracle (%s) failed: %s" % (flavour, r.stderr[-2000:]))
@@ -215,7 +225,7 @@ def build_fixture(flavour, net, steps, dump, opts):
             continue
         if flavour == "kraft" and base not in KRAFT_KEEP:
             continue
-        if full is None or int(t[1:]) in full:
+        if full is None or int(t[1:]) in full or base in opts.get("keep_full", ()):
             out[k] = v
         elif base.startswith("obs:"):
             continue  # observables are kept at the full steps only
@@ -237,7 +247,7 @@ def main():
             for flavour in ("shim", "kraft"):
                 if flavour == "kraft" and opts.get("no_kraft"):
                     continue
-                dump, stats = run_oracle(flavour, net, steps, tmp, observe=bool(opts.get("observe")))
+                dump, stats = run_oracle(flavour, net, steps, tmp, observe=bool(opts.get("observe")), extra=opts.get("oracle_args", ()))
                 path = os.path.join(GOLDEN, "%s.%s.acc.gz" % (name, flavour))
                 netfile.write(path, build_fixture(flavour, net, steps, dump, opts))
                 ev = dump["events"].reshape(-1, 4)
