@@ -50,6 +50,9 @@
 #define ACC_PM_MAXREG_ANY 80  // ... at any other group size: two CTAs of 384 threads (748 connections per manager) per SM; measured on a
                               // 748x3 network: 1.81 ms with 112 registers (one CTA per SM), 1.30 ms with 80
 #endif
+#ifndef ACC_PM_PREFETCH_AHEAD
+#define ACC_PM_PREFETCH_AHEAD 444  // purchasing managers ahead whose connection lists are prefetched into the L2 (half a wave of 6 CTAs x 148 SMs)
+#endif
 #ifndef ACC_PM_MAXREG_FIXED
 #define ACC_PM_MAXREG_FIXED 96  // registers per thread of the purchase kernel at the base group size (see struct Purchase)
 #endif
@@ -158,8 +161,10 @@ __global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) block_kernel(K k) {
 }
 // One CTA per seller; `cap` > 0: the seller's demand book is staged in dynamic shared memory first (csrc/stage.cuh),
 // books larger than `cap` connections are read in place.
+// `ahead` > 0: while this CTA waits for its own book, one thread asks the copy engine to bring the book of the seller `ahead`
+// CTAs further on -- the one a CTA of the next wave will take on this SM -- into the L2, so that its bulk copy is fed from there.
 template <class K>
-__global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) seller_kernel(K k, int cap) {
+__global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) seller_kernel(K k, int cap, int ahead) {
     __shared__ __align__(16) unsigned char scratch[ACC_BLOCK_SCRATCH_BYTES];
     __shared__ __align__(8) unsigned long long bar;
     extern __shared__ __align__(16) unsigned char dyn_smem[];
@@ -175,6 +180,16 @@ __global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) seller_kernel(K k, 
     if ((threadIdx.x >> 5) == 1) { WarpCtx warp; k.prepare(warp, (int)blockIdx.x); }
     int e0, n;
     k.range((int)blockIdx.x, &e0, &n);
+    if (ahead > 0 && threadIdx.x == 64 && blockIdx.x + ahead < gridDim.x) {
+        int e2, n2;
+        k.range((int)blockIdx.x + ahead, &e2, &n2);
+        if (n2 > 0 && n2 <= cap) {
+            prefetch_l2(k.ev.D_q + e2, (size_t)n2 * sizeof(i64));
+            prefetch_l2(k.ev.D_p + e2, (size_t)n2 * sizeof(i64));
+            prefetch_l2(k.ev.tau + e2, (size_t)n2);
+            prefetch_l2(k.ev.domestic + e2, (size_t)n2);
+        }
+    }
     if (n > 0 && n <= cap) book = stage_seller_book(dyn_smem, cap, &bar, k.ev.D_q, k.ev.D_p, k.ev.tau, k.ev.domestic, e0, n);
     __syncthreads();
     k(cx, (int)blockIdx.x, book);
@@ -229,7 +244,18 @@ static void launch_seller(stream_t s, int n, int cap, K k) {
     if (n <= 0) return;
     const size_t smem = cap > 0 ? seller_book_bytes(cap) : 0;
     if (smem_needs_config((const void*)seller_kernel<K>, smem)) ACC_CUDA(cudaFuncSetAttribute(seller_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    seller_kernel<K><<<n, K::THREADS, smem, s>>>(k, cap);
+    int ahead = 0;
+    if (cap > 0) {  // half a wave of CTAs ahead (measured on the EORA shape: none 0.521 ms, 148 ahead 0.504, 296 ahead 0.512, 592 ahead 0.539)
+        static std::map<int, int> sms;
+        int dev = 0;
+        ACC_CUDA(cudaGetDevice(&dev));
+        if (sms.find(dev) == sms.end()) { int v = 0; ACC_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev)); sms[dev] = v; }
+        ahead = sms[dev] * K::MIN_BLOCKS / 2;
+#ifdef ACC_SELLER_PREFETCH_AHEAD
+        ahead = ACC_SELLER_PREFETCH_AHEAD;
+#endif
+    }
+    seller_kernel<K><<<n, K::THREADS, smem, s>>>(k, cap, ahead);
     ACC_CUDA(cudaGetLastError());
 }
 template <class K>
@@ -512,8 +538,21 @@ struct Purchase {
     // in_seller: seller ROW (SellerTable) | delay << 24
     const i64* in_off; const int* in_edge; const int* in_seller; const i64* in_Z; SellerTable pubT; int n_max; const int* pm_ids;  // pm_ids == nullptr: all
     i64* dem_q; double* dem_v; double* exp_costs; double* opt_val; double* tpen; int* iters; int* evals;
+    int n_items, ahead;  // ahead > 0: the last thread asks for the connection lists of the manager `ahead` items further on (L2 prefetch)
     template <class Ctx>
     ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const {
+#if defined(__CUDA_ARCH__)
+        if (ahead > 0 && threadIdx.x == blockDim.x - 1 && item + ahead < n_items) {
+            // the three static lists of a manager further down the grid are streamed from HBM once per step: by the time a CTA takes
+            // that manager they wait in the L2
+            const int s2 = pm_ids != nullptr ? pm_ids[item + ahead] : item + ahead;
+            const i64 o2 = in_off[s2];
+            const size_t n2 = (size_t)(in_off[s2 + 1] - o2);
+            prefetch_l2(in_edge + o2, n2 * sizeof(int));
+            prefetch_l2(in_seller + o2, n2 * sizeof(int));
+            prefetch_l2(in_Z + o2, n2 * sizeof(i64));
+        }
+#endif
         const int s = pm_ids != nullptr ? pm_ids[item] : item;
         PMWorkT<SEP, STD, DVAL> k;
         k.carve(smem, n_max);
@@ -1037,7 +1076,8 @@ struct acc_engine {
     template <bool SEP, bool STD, int G, bool DVAL = (G > 0)>  // the base group keeps the D_r summands; the large groups trade them for a second CTA per SM
     void launch_purchase() {
         Purchase<SEP, STD, DVAL> k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, in_Z.p, seller_table(), n_max,
-                             partitioned ? pm_ids.p : nullptr, s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p};
+                             partitioned ? pm_ids.p : nullptr, s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p,
+                             partitioned ? n_pm : nSt, ACC_PM_PREFETCH_AHEAD};
         timed("purchase", [&] { launch_block_smem<G>(stream, partitioned ? n_pm : nSt, pm_group, pm_workspace_bytes(n_max, SEP, DVAL), k); });
     }
     void stage_purchase() {

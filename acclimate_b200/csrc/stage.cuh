@@ -38,6 +38,12 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                  "r"(smem_addr(bar))
                  : "memory");
 }
+// asks the copy engine to bring [p, p + bytes) into the L2 (no destination: a later bulk copy or load then finds it there)
+__device__ __forceinline__ void prefetch_l2(const void* p, size_t bytes) {
+    const size_t a = reinterpret_cast<size_t>(p) & ~(size_t)15;
+    const size_t end = (reinterpret_cast<size_t>(p) + bytes + 15) & ~(size_t)15;
+    if (end > a) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a), "r"((unsigned)(end - a)) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
     asm volatile(
         "{\n"
