@@ -9,11 +9,14 @@
 //   :381-433  optimiser set-up (local SLSQP; the global MLSL path is not provided)
 //   :455-503  consumption_optimize: result codes -> events
 //   :510-523  consume_optimisation_result
-// The utility couples all goods of a consumer, so objective, gradient and constraint are evaluated by the group's
-// leader in the reference's own operation order (every intermediate of the autodiff chain is reproduced, which makes
-// the host-side emulation bit-identical to the reference's autodiff; the CUDA pow() may differ from glibc's in the
-// last bit).  The optimiser is csrc/sqp_dense.h (dense BFGS model: the utility is not separable), strictly sequential
-// code that the leader runs alone -- the same code oracle/nlopt_shim runs for every objective without described kinks.
+// The utility couples all goods of a consumer; objective, gradient and constraint follow the reference's own operation
+// order (every intermediate of the autodiff chain is reproduced, which makes the host-side emulation bit-identical to the
+// reference's autodiff; the CUDA pow() may differ from glibc's in the last bit).  The optimiser is csrc/sqp_dense.h (dense
+// BFGS model: the utility is not separable).  The whole warp runs it: the same scalar control flow on every lane, the
+// element-wise work -- BFGS update, Cholesky columns, matrix-vector products, bound multipliers, the pow() of every good --
+// shared out over the lanes, recurrences in one lane; every ELEMENT is still computed by one thread with the operations
+// of a sequential loop in the same order, so the bits equal those of the serial run of the same code in oracle/nlopt_shim
+// (which uses it for every objective without described kinks).
 #pragma once
 
 #include "model_core.cuh"

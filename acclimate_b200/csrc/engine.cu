@@ -148,6 +148,25 @@ static bool smem_needs_config(const void* kernel, size_t bytes) {
     return true;
 }
 
+// Cross-part barrier over peer memory (acc_comm_enable_peer_stores): thread p announces this part's epoch in part p's counter
+// array and waits until part p has announced the same epoch here.  The fence orders the peer stores of the kernels before it
+// (same stream) ahead of the announcement; the waiting side's later kernels see them.  A wait that lasts seconds (a part died)
+// ends with an error flag instead of hanging the GPU.
+__global__ void cross_barrier_kernel(PeerTable pt, int rank, int world, unsigned long long epoch, int* timed_out) {
+    const int p = (int)threadIdx.x;
+    if (p >= world || p == rank) return;
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(pt.flags[p] + rank), "l"(epoch) : "memory");
+    const unsigned long long* mine = pt.flags[rank] + p;
+    const long long t0 = clock64();
+    for (;;) {
+        unsigned long long seen;
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(seen) : "l"(mine) : "memory");
+        if (seen >= epoch) break;
+        if (clock64() - t0 > 20000000000LL) { *timed_out = 1; break; }  // ~10 s
+    }
+}
+
 template <class K>
 __global__ void __launch_bounds__(128) thread_kernel(int n, K k) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -845,6 +864,11 @@ struct acc_engine {
     DBuf<int> x_rid;
     DBuf<PeerTable> peer_table;
     DBuf<i64> barrier_word;
+    DBuf<unsigned long long> barrier_flags;  // this part's arrival counters (written by the peers)
+    DBuf<int> barrier_timeout;
+    PeerTable h_peers;
+    unsigned long long barrier_epoch = 0;
+    bool flag_barrier = false;
     std::vector<void*> ipc_opened;
 #ifndef ACC_HOST_EMU
     NcclApi::comm_t comm = nullptr;
@@ -885,7 +909,7 @@ struct acc_engine {
         v(owned); v(pm_ids); v(halo_send); v(halo_recv);
         v(own_flow_send); v(own_flow_recv); v(own_dem_send); v(own_dem_recv); v(own_sellers);
         v(comm_part_firms); v(comm_part_off); v(comm_rows_send); v(comm_rows_recv);
-        v(x_peer); v(x_rid); v(peer_table); v(barrier_word);
+        v(x_peer); v(x_rid); v(peer_table); v(barrier_word); v(barrier_flags); v(barrier_timeout);
     }
     // ensemble members (acc_fork): a member shares its parent's immutable tables; the parent's memory lives until the last member is gone
     acc_engine* parent = nullptr;
@@ -1133,6 +1157,12 @@ struct acc_engine {
     // all parts have reached this point of their streams, and the peer stores of the kernels before it are visible: a
     // one-word all-reduce (kernel boundaries make the stores visible system-wide, the collective orders the parts)
     void cross_barrier() {
+        if (flag_barrier) {  // counters in peer memory: a few microseconds instead of a collective's launch
+            ++barrier_epoch;
+            cross_barrier_kernel<<<1, ACC_MAX_PARTS, 0, stream>>>(h_peers, comm_rank, comm_world, barrier_epoch, barrier_timeout.p);
+            ACC_CUDA(cudaGetLastError());
+            return;
+        }
         ACC_NCCL(NcclApi::get().AllReduce(barrier_word.p, barrier_word.p + 1, 1, NcclApi::Int64, 0 /* ncclSum */, comm, stream));
         ++collectives;
     }
@@ -2423,13 +2453,16 @@ int acc_comm_enable_peer_stores(acc_engine* e) {
     // every part tells the others where its two receive buffers are (IPC handles) and how its halo lists split over the parts:
     // the k-th entry this part sends to part p is the k-th entry p receives from it (both lists are in global order), so its
     // position in p's buffer is p's offset for this part + k -- no per-connection id has to travel
-    struct Hello { i64 send_cnt[ACC_MAX_PARTS], recv_cnt[ACC_MAX_PARTS]; cudaIpcMemHandle_t h[2]; };
+    struct Hello { i64 send_cnt[ACC_MAX_PARTS], recv_cnt[ACC_MAX_PARTS]; cudaIpcMemHandle_t h[3]; };
     static_assert(sizeof(Hello) % 8 == 0, "exchanged as int64 words");
     Hello mine;
     std::memset(&mine, 0, sizeof mine);
     for (int p = 0; p < world; ++p) { mine.send_cnt[p] = e->comm_send_cnt[p]; mine.recv_cnt[p] = e->comm_recv_cnt[p]; }
-    void* arrays[2] = {e->own_flow_recv.p, e->own_dem_recv.p};
-    for (int k = 0; k < 2; ++k) ACC_CUDA(cudaIpcGetMemHandle(&mine.h[k], arrays[k]));
+    e->barrier_flags.alloc(ACC_MAX_PARTS); e->barrier_flags.zero(s);
+    e->barrier_timeout.alloc(1); e->barrier_timeout.zero(s);
+    dev_sync(s);
+    void* arrays[3] = {e->own_flow_recv.p, e->own_dem_recv.p, e->barrier_flags.p};
+    for (int k = 0; k < 3; ++k) ACC_CUDA(cudaIpcGetMemHandle(&mine.h[k], arrays[k]));
     DBuf<i64> d_hello, d_all;
     const size_t words = sizeof(Hello) / 8;
     d_hello.alloc(words); d_all.alloc(words * world);
@@ -2444,13 +2477,14 @@ int acc_comm_enable_peer_stores(acc_engine* e) {
     for (int p = 0; p < world; ++p) {
         if (all[p].recv_cnt[rank] != e->comm_send_cnt[p] || all[p].send_cnt[rank] != e->comm_recv_cnt[p])
             fail("acc_comm_enable_peer_stores: the parts' halo lists do not match");
-        void* ptr[2];
-        for (int k = 0; k < 2; ++k) {
+        void* ptr[3];
+        for (int k = 0; k < 3; ++k) {
             if (p == rank) { ptr[k] = arrays[k]; continue; }
             ACC_CUDA(cudaIpcOpenMemHandle(&ptr[k], all[p].h[k], cudaIpcMemLazyEnablePeerAccess));
             e->ipc_opened.push_back(ptr[k]);
         }
         pt.flow_recv[p] = static_cast<i64*>(ptr[0]); pt.dem_recv[p] = static_cast<i64*>(ptr[1]);
+        pt.flags[p] = static_cast<unsigned long long*>(ptr[2]);
     }
     std::vector<i64> hs = e->halo_send.download(s), hr = e->halo_recv.download(s);
     std::vector<signed char> xp((size_t)e->nE, (signed char)-1);
@@ -2472,6 +2506,8 @@ int acc_comm_enable_peer_stores(acc_engine* e) {
     e->peer_table.upload(std::vector<PeerTable>(1, pt), s);
     e->barrier_word.alloc(2); e->barrier_word.zero(s);
     dev_sync(s);
+    e->h_peers = pt;
+    e->flag_barrier = std::getenv("ACC_NCCL_BARRIER") == nullptr;  // ACC_NCCL_BARRIER=1: one-word all-reduces instead (for comparison)
     e->peer_stores = true;
 #endif
     return 0;
@@ -2529,6 +2565,13 @@ int acc_sync(acc_engine* e) {
     if (e == nullptr) fail("acc_sync: null engine");
     ACC_ON_DEVICE(e);
     dev_sync(e->stream);
+#ifndef ACC_HOST_EMU
+    if (e->flag_barrier && e->barrier_timeout.n) {
+        int late = 0;
+        d2h(&late, e->barrier_timeout.p, sizeof(int), e->stream);
+        if (late) fail("acc_sync: a cross-part barrier waited for more than ten seconds: another part of the run has stopped");
+    }
+#endif
     if (e->mp.utilitarian) {
         int flag = 0;
         d2h(&flag, e->fatal.p, sizeof(int), e->stream);

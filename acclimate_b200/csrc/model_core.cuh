@@ -3,9 +3,11 @@
 // intermediate of the reference (Price, FlowQuantity, Quantity) is re-quantised at the same point.
 //
 // Scope of the restatement (what acc_create accepts, everything else is rejected with an error):
-//   naive_expectations = true, respect_markup_in_production_extension = false (the reference never assigns
-//   it, parameters.h:46), tax = 0 (Government is dead code at the pinned commit), local SLSQP purchasing
-//   optimisation only, one transport hop per connection (const / csv / centroids transport).
+//   naive_expectations true or false (with or without always_extend_expected_demand_curve: seller_phase2 carries the
+//   demand-curve extension and its bisection), respect_markup_in_production_extension = false (the reference never
+//   assigns it, parameters.h:46), tax = 0 (Government is dead code at the pinned commit), local SLSQP purchasing
+//   optimisation only, transport as one connection per region pair (const / csv / centroids) or as multi-hop routes
+//   over geo entities ("network": per-hop delay, passage forcing and overflow, applied in the delivery pass).
 #pragma once
 
 #include "coop.cuh"
@@ -361,6 +363,7 @@ struct FirmView {
 struct PeerTable {
     i64* flow_recv[ACC_MAX_PARTS];  // [n_recv_p][2] shipments (quantity, value bits) part p receives
     i64* dem_recv[ACC_MAX_PARTS];   // [n_send_p][2] demand requests (quantity, price) part p receives
+    unsigned long long* flags[ACC_MAX_PARTS];  // [ACC_MAX_PARTS] arrival counters of part p, one per announcing part (cross-part barrier)
 };
 struct alignas(16) HaloEntry {
     i64 a, b;
