@@ -20,6 +20,7 @@ PHASE_CP, PHASE_EXP, PHASE_PUR, PHASE_TICK = 0, 1, 2, 3
 class ModelRun:
     def __init__(self, network, outputs=(), device=0, lib_path=None):
         """network: snapshot arrays (synth.make_network / netfile.read); outputs: iterable of (group, variable) names."""
+        self.network = network
         self.engine = engine.Engine(network, device=device, lib_path=lib_path)
         self.scenario = engine.Scenario(network)
         self.outputs = list(outputs)
@@ -32,23 +33,38 @@ class ModelRun:
         self.delta_t = 1.0
 
     @classmethod
-    def from_settings(cls, doc, network, sector_names, region_names, device=0, lib_path=None, flows=None):
+    def from_settings(cls, doc, network, sector_names, region_names, device=0, lib_path=None, flows=None, entity_names=None):
         """The reference's entry point (src/main.cpp:58-124 -> ModelRun::ModelRun, src/ModelRun.cpp:77-150) on a settings document:
         `network` is the snapshot (or, with `flows`, the agents of a candidate MRIO table that is filtered by network.threshold and
-        cleaned on the device first, acclimate_b200/ingest.py); model / sectors / firms / consumers / scenario / outputs come from
+        cleaned on the device first, acclimate_b200/ingest.py; with network = None the table, the agents and the names are read from
+        the document's network.file, acclimate_b200/mrio.py); model / sectors / firms / consumers / scenario / outputs come from
         the document (acclimate_b200/settings.py).  Returns (run, number of timesteps)."""
         from . import ingest, output, settings
 
         st = doc if isinstance(doc, settings.Settings) else settings.Settings(doc)
+        nw = st.doc.get("network", {}) or {}
+        if network is None:                                # build_agent_network, ModelInitializer.cpp:822-976: the table file
+            from . import mrio
+
+            if nw.get("type") != "netcdf" or "file" not in nw or "threshold" not in nw:
+                raise settings.SettingsError("without a snapshot the document needs network.type = netcdf, network.file and network.threshold")
+            tb = mrio.read_table(nw["file"])
+            network, flows = mrio.seed_network(tb, st.doc.get("transport")), tb["flows"]
+            sector_names, region_names = tb["sector_names"], tb["region_names"]
         net = st.apply_to(network, sector_names, region_names) if flows is None else dict(network)
         if flows is not None:
             seed = dict(network)
             seed["model_f64"] = st.model_params()
-            net, _ = ingest.ingest_table(seed, flows, float(st.doc.get("network", {}).get("threshold", 0.0)), device=device, lib_path=lib_path)
+            net, _ = ingest.ingest_table(seed, flows, float(nw.get("threshold", 0.0)), device=device, lib_path=lib_path)
             net = st.apply_to(net, sector_names, region_names)
         run = cls(net, device=device, lib_path=lib_path)
         start, _, basedate = st.run_window()
         run.start_time, run.delta_t = start, float(st.doc["model"]["delta_t"])
+        if st.doc["scenario"]["type"] == "event_series" and "forcing" in st.doc["scenario"]:
+            from . import forcing                          # ModelRun.cpp:124-126: the forcing files of scenario.forcing
+
+            run.scenario = forcing.EventSeriesFiles(net, sector_names, region_names, st.doc["scenario"], entity_names=entity_names,
+                                                    start_time=start, delta_t=run.delta_t)
         for _, fmt, path, pulls in st.output_plan(net, sector_names, region_names):
             if fmt == "progress":
                 continue
@@ -85,4 +101,6 @@ class ModelRun:
     def close(self):
         for _, sink in self.sinks:
             sink.close()
+        if hasattr(self.scenario, "close"):
+            self.scenario.close()                          # ExternalScenario::end
         self.engine.close()

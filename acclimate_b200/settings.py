@@ -84,7 +84,7 @@ SECTOR_KEYS = {  # sectors.<name>|ALL.<key> (ModelInitializer.cpp:159-180) -> sn
 TRANSPORT_TYPES = {"aviation": 0, "immediate": 1, "roadsea": 2}  # Sector::map_transport_type, src/model/Sector.cpp:65-78
 FIRM_KEYS = {"possible_overcapacity_ratio"}
 CONSUMER_KEYS = {"consumer_baskets", "inter_basket_substitution_coefficient", "bool_utilitarian", "consumption_price_elasticity"}
-SCENARIO_KEYS = {"type", "start", "stop", "basedate", "baseyear", "events", "seed", "forcings", "forcing"}
+SCENARIO_KEYS = {"type", "start", "stop", "basedate", "baseyear", "events", "seed", "forcings", "forcing", "parameters"}
 OUTPUT_KEYS = {"format", "file", "observables", "events", "flush", "only_current_timestep"}
 GROUPS = ("model", "firms", "consumers", "sectors", "regions", "locations", "storages", "flows")
 SELECTORS = {  # ArrayOutput.cpp:200-470: which select_* keys a group takes and whether they pick the first or second index
@@ -283,7 +283,7 @@ class Settings:
         nR = len(region_names)
         forcing, passage = [], []
         if sc["type"] == "event_series":
-            return np.zeros((0, 4)), np.zeros((0, 4))  # grids are streamed by engine.EventSeriesScenario
+            return np.zeros((0, 4)), np.zeros((0, 4))  # records are streamed: forcing.EventSeriesFiles / engine.EventSeriesScenario
         for ev in sc.get("events", []) or []:
             if ev.get("type") != "shock":
                 continue  # Scenario::iterate only acts on shocks (:163-172)
