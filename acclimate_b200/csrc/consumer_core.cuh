@@ -146,9 +146,16 @@ struct CtxPar {
     template <class F> ACC_HD void single(F f) const { cx.single(f); }
 };
 
-// returns false when the optimiser failed outright (the reference throws, Consumer.cpp:497-502)
+// What a solve leaves behind (consumer_one) for consumer_apply: the solve only READS model state, so it can run ahead of the step
+// it belongs to -- as soon as the storages of the previous step are final -- while nothing the rest of that step reads has changed.
+struct ConsumerStage {
+    i64* q; double* v;   // per storage: optimised consumption
+    double* utility;     // per agent
+    int* ret;            // per agent: the solver's return code
+};
+
 template <class Ctx>
-ACC_HD bool consumer_one(Ctx& cx, int a, const ConsumerView& cv, const StorageView& st, const ModelP& mp, const EventSink& events, unsigned char* smem,
+ACC_HD void consumer_one(Ctx& cx, int a, const ConsumerView& cv, const StorageView& st, const ModelP& mp, const ConsumerStage& out, unsigned char* smem,
                          int n_max) {
     const int s0 = cv.st_off[a];
     const int n = cv.st_off[a + 1] - s0;
@@ -192,17 +199,30 @@ ACC_HD bool consumer_one(Ctx& cx, int a, const ConsumerView& cv, const StorageVi
     accsqp::Stats stt;
     CtxPar<Ctx> par{cx};
     const int ret = accsqp::sqp_minimize_dense(par, ev, k.w, sp, stt);
-    if (cx.leader()) {  // consumption_optimize, :455-503
-        if (ret == accsqp::SQP_ROUNDOFF_LIMITED) events.push(EV_OPTIMIZER_ROUNDOFF_LIMITED, a, -1, (double)NAN);
-        else if (ret == accsqp::SQP_MAXEVAL_REACHED) events.push(EV_OPTIMIZER_MAXITER, a, -1, (double)NAN);
-        cv.utility[a] = -stt.minf;
-    }
-    // consume_optimisation_result, :510-523: desired use = use = previous consumption = optimised consumption
+    if (cx.leader()) { out.ret[a] = ret; out.utility[a] = -stt.minf; }
     cx.foreach(n, [&](int i) {
         const int s = cv.st_list[s0 + i];
         const Flow cons = fcopy(flow_qp(qmul_l(k.w.xbest[i], cv.base_q[s]), (i64)k.price[i]));
-        st.Ut_q[s] = cons.q; st.Ut_v[s] = cons.v;
-        cv.prev_q[s] = cons.q; cv.prev_v[s] = cons.v;
+        out.q[s] = cons.q; out.v[s] = cons.v;
+    });
+}
+
+// The step's own part of Consumer::iterate_consumption_and_production, one group per consumer: events of consumption_optimize
+// (:455-503) and consume_optimisation_result (:510-523): desired use = use = previous consumption = optimised consumption.
+// Returns false when the optimiser failed outright (the reference throws, Consumer.cpp:497-502).
+template <class Ctx>
+ACC_HD bool consumer_apply(Ctx& cx, int a, const ConsumerView& cv, const StorageView& st, const ConsumerStage& in, const EventSink& events) {
+    const int ret = in.ret[a];
+    if (cx.leader()) {
+        if (ret == accsqp::SQP_ROUNDOFF_LIMITED) events.push(EV_OPTIMIZER_ROUNDOFF_LIMITED, a, -1, (double)NAN);
+        else if (ret == accsqp::SQP_MAXEVAL_REACHED) events.push(EV_OPTIMIZER_MAXITER, a, -1, (double)NAN);
+        cv.utility[a] = in.utility[a];
+    }
+    const int s0 = cv.st_off[a];
+    cx.foreach(cv.st_off[a + 1] - s0, [&](int i) {
+        const int s = cv.st_list[s0 + i];
+        st.Ut_q[s] = in.q[s]; st.Ut_v[s] = in.v[s];
+        cv.prev_q[s] = in.q[s]; cv.prev_v[s] = in.v[s];
     });
     return ret != accsqp::SQP_FAILURE;
 }

@@ -533,11 +533,16 @@ struct StorageDelivery {  // thread per storage
 #endif
 struct ConsumerUtility {
     enum { WARPS = ACC_CONSUMER_WARPS };
-    ConsumerView cv; StorageView st; ModelP mp; EventSink events; int n_max; int* fatal;
+    ConsumerView cv; StorageView st; ModelP mp; ConsumerStage out; int n_max;
     template <class Ctx>
-    ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const {
-        const bool ok = consumer_one(cx, cv.cons_ids[item], cv, st, mp, events, smem, n_max);
-        if (!ok && cx.leader()) *fatal = 1;
+    ACC_HD void operator()(Ctx& cx, int item, unsigned char* smem) const { consumer_one(cx, cv.cons_ids[item], cv, st, mp, out, smem, n_max); }
+};
+struct ConsumerApply {  // warp per consumer: the solve's results become the step's desired use
+    enum { WARPS = 8 };
+    ConsumerView cv; StorageView st; ConsumerStage in; EventSink events; int* fatal;
+    template <class Ctx>
+    ACC_HD void operator()(Ctx& cx, int item, unsigned char*) const {
+        if (!consumer_apply(cx, cv.cons_ids[item], cv, st, in, events) && cx.leader()) *fatal = 1;
     }
 };
 
@@ -845,6 +850,9 @@ struct acc_engine {
     DBuf<int> cons_ids, c_order_cnt, c_order, c_order_basket, fatal;
     DBuf<double> c_share, c_eshare, c_prev_v, c_budget, c_bshare, c_ebshare, c_utility, c_intra_exp;
     DBuf<i64> c_base_q, c_prev_q;
+    // results of the consumers' solve until consumer_apply takes them; ahead_step: the step the solve in flight (or done) belongs to
+    DBuf<i64> c_nx_q; DBuf<double> c_nx_v, c_nx_util; DBuf<int> c_nx_ret;
+    i64 ahead_step = -1;
     // region partition (empty = the engine owns every agent)
     bool partitioned = false;
     int n_pm = 0;  // purchasing managers of owned agents
@@ -904,7 +912,7 @@ struct acc_engine {
         v(s_Istar_q); v(s_Sstar_q); v(s_defc); v(s_Istar_v); v(s_Sstar_v); v(s_a); v(s_agent); v(s_sector);
         v(e_seller_off); v(e_route); v(route_off); v(route_ent); v(ent_delay); v(e_Z_q); v(e_tau); v(e_dom);
         v(ell_off); v(in_off); v(ell_width); v(ell_edge); v(in_edge); v(in_seller); v(in_Z);
-        v(cons_ids); v(c_order_cnt); v(c_order); v(c_order_basket); v(fatal);
+        v(cons_ids); v(c_order_cnt); v(c_order); v(c_order_basket); v(fatal); v(c_nx_q); v(c_nx_v); v(c_nx_util); v(c_nx_ret);
         v(c_share); v(c_eshare); v(c_budget); v(c_bshare); v(c_ebshare); v(c_intra_exp); v(c_base_q);
         v(owned); v(pm_ids); v(halo_send); v(halo_recv);
         v(own_flow_send); v(own_flow_recv); v(own_dem_send); v(own_dem_recv); v(own_sellers);
@@ -1049,10 +1057,20 @@ struct acc_engine {
             StorageDelivery<false> k{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p, own};
             timed("storage_delivery", [&] { launch_thread(stream, nSt, k); });
         }
+        consumer_ahead();  // the storages are final for this step: the consumers' solve of the next step starts here
     }
-    void consumer_fork() {
+    // The solve of step t reads the storages as the delivery pass of step t - 1 left them and nothing else that changes, and
+    // writes only its own result arrays, so it is started right behind that delivery pass (`ahead`: with the input-flow registers
+    // already seen the way step t will see them) and runs beside the sellers' expectation pass and the purchasing managers of
+    // step t - 1.  consumer_join applies the results where Consumer::iterate_consumption_and_production would have computed
+    // them.  Whatever rewrites state from outside (acc_load_state, forcing) drops a solve made ahead: it is repeated in place.
+    ConsumerStage consumer_stage() { return ConsumerStage{c_nx_q.p, c_nx_v.p, c_nx_util.p, c_nx_ret.p}; }
+    void consumer_fork(bool ahead = false) {
         if (!mp.utilitarian || nC == 0) return;
-        ConsumerUtility k{consumer_view(), storage_view(), mp, sink(), c_n_max, fatal.p};
+        if (!ahead && ahead_step == step) return;  // solved behind the previous step's delivery pass
+        if (ahead) reg = 1 - reg;
+        ConsumerUtility k{consumer_view(), storage_view(), mp, consumer_stage(), c_n_max};
+        if (ahead) reg = 1 - reg;
 #ifndef ACC_HOST_EMU
         ACC_CUDA(cudaEventRecord(ev_fork, stream));
         ACC_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
@@ -1061,10 +1079,19 @@ struct acc_engine {
 #ifndef ACC_HOST_EMU
         ACC_CUDA(cudaEventRecord(ev_join, side));
 #endif
+        ahead_step = ahead ? step + 1 : step;
     }
     void consumer_join() {
+        if (!mp.utilitarian || nC == 0) return;
 #ifndef ACC_HOST_EMU
-        if (mp.utilitarian && nC != 0) ACC_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
+        ACC_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
+#endif
+        ConsumerApply k{consumer_view(), storage_view(), consumer_stage(), sink(), fatal.p};
+        timed("consumer_apply", [&] { launch_warps(stream, nC, 0, k); });
+    }
+    void consumer_ahead() {
+#ifndef ACC_NO_CONSUMER_AHEAD
+        consumer_fork(true);
 #endif
     }
     void stage_sell() {
@@ -1640,6 +1667,8 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
         E.c_bshare.upload(bshare, s); E.c_ebshare.upload(ebshare, s); E.c_intra_exp.upload(intra_exp, s);
         E.c_base_q.upload(base_q, s); E.c_prev_q.upload(prev_q, s);
         E.c_utility.alloc(nA); E.c_utility.zero(s);
+        E.c_nx_q.alloc(nSt); E.c_nx_v.alloc(nSt); E.c_nx_util.alloc(nA); E.c_nx_ret.alloc(nA);
+        E.c_nx_q.zero(s); E.c_nx_v.zero(s); E.c_nx_util.zero(s); E.c_nx_ret.zero(s);
     }
     E.fatal.alloc(1); E.fatal.zero(s);
     E.in_off.upload(in_off, s); E.in_edge.upload(in_edge, s); E.in_seller.upload(in_seller, s); E.in_Z.upload(in_Z, s);
@@ -1770,6 +1799,11 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
     // agents
     if (name == "agent_forcing") return F(E.a_lambda);
     if (name == "consumer_utility" && E.mp.utilitarian) return F(E.c_utility);
+    if (name == "consumer_solver_ret" && E.mp.utilitarian) {  // return code of the last utility optimisation per agent (csrc/sqp_core.h)
+        std::vector<int> h = E.c_nx_ret.download(s);
+        out.i.assign(h.begin(), h.end()); out.is_f64 = false;
+        return true;
+    }
     if (name == "firm_X_q") return I(E.f_X_q);
     if (name == "firm_X_v") return F(E.f_X_v);
     if (name == "firm_Xhat_q") return I(E.f_Xhat_q);
@@ -2249,6 +2283,7 @@ void acc_destroy(acc_engine* e) {
     try { guard = new acc::DeviceGuard(e->device); } catch (...) {}
 #ifndef ACC_HOST_EMU
     cudaStreamSynchronize(e->stream);
+    if (e->side) cudaStreamSynchronize(e->side);
 #endif
     if (e->members > 0) e->zombie = true;  // ensemble members still read this engine's tables: released with the last of them
     else release_engine(e);
@@ -2265,6 +2300,7 @@ acc_engine* acc_fork(acc_engine* parent) {
         if (parent->partitioned) fail("acc_fork: a part of a region-partitioned run cannot be forked");
         acc::DeviceGuard device_guard__(parent->device);
         acc::dev_sync(parent->stream);
+        if (parent->side) acc::dev_sync(parent->side);
         acc_engine* root = parent->parent != nullptr ? parent->parent : parent;  // members of a member share the same tables
         E = new acc_engine(*parent);
         E->stream = nullptr; E->side = nullptr;
@@ -2286,6 +2322,8 @@ acc_engine* acc_fork(acc_engine* parent) {
         CloneVisitor cv{E->stream};
         E->visit_state(cv);
         cv(E->pubT); cv(E->fatal);  // derived / scratch state that changes with the steps
+        cv(E->c_nx_q); cv(E->c_nx_v); cv(E->c_nx_util); cv(E->c_nx_ret);
+        E->ahead_step = -1;         // the member repeats the consumers' solve of its next step on its own copy of the state
         for (acc::DBuf<double>* b : {&E->obs_out, &E->obs_inc_v}) { b->p = nullptr; b->n = 0; b->borrowed = false; }
         for (acc::DBuf<i64>* b : {&E->obs_idx, &E->obs_inc_q}) { b->p = nullptr; b->n = 0; b->borrowed = false; }
         acc::dev_sync(E->stream);
@@ -2566,6 +2604,7 @@ int acc_sync(acc_engine* e) {
     ACC_ON_DEVICE(e);
     dev_sync(e->stream);
 #ifndef ACC_HOST_EMU
+    if (e->side) dev_sync(e->side);  // the consumers' solve of the next step, started behind this step's delivery pass
     if (e->flag_barrier && e->barrier_timeout.n) {
         int late = 0;
         d2h(&late, e->barrier_timeout.p, sizeof(int), e->stream);
@@ -2760,6 +2799,7 @@ int acc_load_state(acc_engine* e, const void* src, size_t bytes) {
     e->visit_state(v);
     acc::dev_sync(e->stream);
     e->step = h.step; e->reg = (int)h.reg; e->ship_step = h.ship_step;
+    e->ahead_step = -1;  // a consumers' solve made ahead belonged to the state that has just been replaced
     {   // the field-major twin of the seller records is derived state: rebuild it from the loaded records
         RepublishSellers k{e->pub.p, e->seller_table()};
         launch_thread(e->stream, e->nA, k);
@@ -2835,6 +2875,71 @@ int acc_firm_incoming_demand_static(acc_engine* e, double* out_quantity, double*
     return 0;
     ACC_API_END(-1)
 }
+
+#ifdef ACC_DEBUG_API
+// Debugging aids, compiled into variant builds only (scripts/consumer_replay.py): what one consumer's utility optimisation reads
+// from the model state, per input storage in input_storages order -- content (q, v), arrived input flow (q, v), previous
+// consumption (q, v) -- can be taken from one engine and replayed on another (the host emulation) for that consumer alone.
+int acc_debug_consumer_inputs(acc_engine* e, int agent, double* buf, size_t cap, size_t* n) {
+    ACC_API_BEGIN
+    ACC_ON_DEVICE(e);
+    stream_t s = e->stream;
+    dev_sync(s);
+    if (e->side) dev_sync(e->side);
+    std::vector<int> off = e->a_st_off.download(s), list = e->a_st_list.download(s);
+    const int s0 = off[agent], cnt = off[agent + 1] - s0;
+    *n = (size_t)cnt * 6;
+    if (buf == nullptr) return 0;
+    if (cap < *n) fail("acc_debug_consumer_inputs: buffer too small");
+    const StorageView v = e->storage_view();
+    std::vector<i64> Sq = e->s_S_q.download(s), pq = e->c_prev_q.download(s);
+    std::vector<double> Sv = e->s_S_v.download(s), pv = e->c_prev_v.download(s);
+    std::vector<i64> Iq = (v.Ip_q == e->s_I0_q.p ? e->s_I0_q : e->s_I1_q).download(s);
+    std::vector<double> Iv = (v.Ip_v == e->s_I0_v.p ? e->s_I0_v : e->s_I1_v).download(s);
+    for (int i = 0; i < cnt; ++i) {
+        const int st = list[s0 + i];
+        double* o = buf + 6 * (size_t)i;
+        o[0] = (double)Sq[st]; o[1] = Sv[st]; o[2] = (double)Iq[st]; o[3] = Iv[st]; o[4] = (double)pq[st]; o[5] = pv[st];
+    }
+    return 0;
+    ACC_API_END(-1)
+}
+int acc_debug_consumer_replay(acc_engine* e, int agent, const double* buf, size_t n, int* ret, double* x_out) {
+    ACC_API_BEGIN
+    ACC_ON_DEVICE(e);
+    stream_t s = e->stream;
+    dev_sync(s);
+    if (e->side) dev_sync(e->side);
+    std::vector<int> off = e->a_st_off.download(s), list = e->a_st_list.download(s), ids = e->cons_ids.download(s);
+    const int s0 = off[agent], cnt = off[agent + 1] - s0;
+    if (n != (size_t)cnt * 6) fail("acc_debug_consumer_replay: wrong number of values");
+    int item = -1;
+    for (size_t k = 0; k < ids.size(); ++k) if (ids[k] == agent) item = (int)k;
+    if (item < 0) fail("acc_debug_consumer_replay: not a consumer of this engine");
+    const StorageView v = e->storage_view();
+    for (int i = 0; i < cnt; ++i) {
+        const int st = list[s0 + i];
+        const double* o = buf + 6 * (size_t)i;
+        const i64 Sq = (i64)o[0], Iq = (i64)o[2], pq = (i64)o[4];
+        h2d(e->s_S_q.p + st, &Sq, sizeof Sq, s); h2d(e->s_S_v.p + st, &o[1], sizeof(double), s);
+        h2d(const_cast<i64*>(v.Ip_q) + st, &Iq, sizeof Iq, s); h2d(const_cast<double*>(v.Ip_v) + st, &o[3], sizeof(double), s);
+        h2d(e->c_prev_q.p + st, &pq, sizeof pq, s); h2d(e->c_prev_v.p + st, &o[5], sizeof(double), s);
+    }
+    dev_sync(s);
+    ConsumerView cv = e->consumer_view();
+    cv.cons_ids = e->cons_ids.p + item;
+    ConsumerUtility k{cv, e->storage_view(), e->mp, e->consumer_stage(), e->c_n_max};
+    launch_warps(s, 1, consumer_workspace_bytes(e->c_n_max), k);
+    dev_sync(s);
+    std::vector<int> r = e->c_nx_ret.download(s);
+    std::vector<i64> q = e->c_nx_q.download(s);
+    *ret = r[agent];
+    if (x_out != nullptr) for (int i = 0; i < cnt; ++i) x_out[i] = (double)q[list[s0 + i]];
+    e->ahead_step = -1;
+    return 0;
+    ACC_API_END(-1)
+}
+#endif
 
 int acc_profile(acc_engine* e, int enable) {
     if (e == nullptr) return -1;

@@ -191,6 +191,7 @@ SQP_HD int sqp_minimize_dense(Par& par, Eval& ev, DenseWork& w, const Params& p,
     bool b_identity = true;
     double mu = 0.0;
     int ireset = 0;
+    int stalled = 0;  // line searches in a row that ran out of trials without the sufficient decrease
     int ret = SQP_SUCCESS;
     while (ret == SQP_SUCCESS) {
         ++st.iters;
@@ -256,11 +257,17 @@ SQP_HD int sqp_minimize_dense(Par& par, Eval& ev, DenseWork& w, const Params& p,
             if (p.maxeval > 0 && st.evals >= p.maxeval) { ret = SQP_MAXEVAL_REACHED; break; }
             const double tt = F + mu * con_violation(p.ctype, c);
             const double h1 = tt - t0;
-            if (h1 <= h3 / 10.0 || line > 10) break;
+            if (h1 <= h3 / 10.0) { stalled = 0; break; }
+            if (line > 10) { ++stalled; break; }
             const double cand = h3 / (2.0 * (h3 - h1));
             alpha = cand > 0.1 ? cand : 0.1;
         }
         if (ret != SQP_SUCCESS) break;
+        // Twenty line searches in a row without the sufficient decrease: the merit function moves in its last digits only (an
+        // objective at its optimum to 1e-12 with steps of a few xtol left, the multiplier equal to the penalty weight) and the
+        // iteration would crawl on until max_iter.  NLopt calls this "roundoff errors limited progress"; the best point stands.
+        // (A handful of such searches in a row do occur in ordinary solves that then go on to meet xtol.)
+        if (stalled >= 20) { ret = SQP_ROUNDOFF_LIMITED; break; }
         bool moved = false;
         for (int i = 0; i < n; ++i) if (!(fabs(w.x[i] - w.x0[i]) < w.xtol[i])) moved = true;
         if (!moved) { ret = SQP_XTOL_REACHED; break; }
