@@ -205,7 +205,7 @@ __global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) seller_kernel(K k, 
         if (n2 > 0 && n2 <= cap) {
             prefetch_l2(k.ev.D_q + e2, (size_t)n2 * sizeof(i64));
             prefetch_l2(k.ev.D_p + e2, (size_t)n2 * sizeof(i64));
-            prefetch_l2(k.ev.tau + e2, (size_t)n2);
+            prefetch_l2(k.ev.slotw + e2, (size_t)n2 * sizeof(unsigned));
             prefetch_l2(k.ev.domestic + e2, (size_t)n2);
         }
     }
@@ -401,7 +401,7 @@ struct SellerExpectation {  // warp per firm
 template <bool FORCED>  // FORCED: passage forcing has been used, the chain of hops with its overflows is walked
 struct StorageDelivery {  // thread per storage
     StorageView st; FirmView fv; EdgeView ev; ModelP mp; const SectorP* sectors; EventSink events; i64 step;
-    const i64* ell_off; const int* ell_width; const int* ell_edge; const unsigned char* owned;  // owned == nullptr: every agent
+    const i64* ell_off; const int* ell_width; const int* ell_edge; const unsigned* ell_slotw; const unsigned char* owned;  // owned == nullptr: every agent
     ACC_HD void operator()(int s) const {
         const int a = st.agent[s];
         if (owned != nullptr && !owned[a]) return;
@@ -434,9 +434,7 @@ struct StorageDelivery {  // thread per storage
         const int slice = s >> 5, lane = s & 31;
         const i64 base = ell_off[slice];
         const int width = ell_width[slice];
-        const int T = ev.T;
-        const int plane_now = (int)(step % T);
-        const i64 now = (i64)plane_now * ev.n_edges;
+        const ConveyorRings& rg = ev.rings;
         Flow in = mkflow(0, 0.0);
         Flow imp = mkflow(0, 0.0);
         i64 tq = st.T_q[s];
@@ -447,26 +445,30 @@ struct StorageDelivery {  // thread per storage
         enum { U = 8 };
         for (int k0 = 0; k0 < width; k0 += U) {
             int e_[U], tau_[U];
+            unsigned w_[U];
             Flow front_[U], ship_[U];
             unsigned char dom_[U];
 #pragma unroll
-            for (int j = 0; j < U; ++j) e_[j] = (k0 + j < width) ? ell_edge[base + (i64)(k0 + j) * 32 + lane] : -1;
-#pragma unroll
             for (int j = 0; j < U; ++j) {
-                const int e = e_[j] < 0 ? 0 : e_[j];
-                tau_[j] = ev.tau[e];
-                dom_[j] = ev.domestic[e];
-                front_[j] = mkflow(ev.conv_q[now + e], ev.conv_v[now + e]);
+                const bool have = k0 + j < width;
+                e_[j] = have ? ell_edge[base + (i64)(k0 + j) * 32 + lane] : -1;
+                w_[j] = ell_slotw[base + (i64)(have ? k0 + j : 0) * 32 + lane];  // padding cells hold connection -1 and the word of connection 0
             }
 #pragma unroll
             for (int j = 0; j < U; ++j) {
                 const int e = e_[j] < 0 ? 0 : e_[j];
+                const unsigned w = w_[j];
+                tau_[j] = ring_tau(rg, w);
+                dom_[j] = ev.domestic[e];
+                const i64 at = ring_slot_front(rg, w);
+                front_[j] = mkflow(ev.conv_q[at], ev.conv_v[at]);
+            }
+#pragma unroll
+            for (int j = 0; j < U; ++j) {
                 ship_[j] = front_[j];
                 if (tau_[j] != 0) {
-                    int pj = plane_now + tau_[j];  // (step + delay) mod T without the division: delay < T
-                    if (pj >= T) pj -= T;
-                    const i64 pl = (i64)pj * ev.n_edges;
-                    ship_[j] = mkflow(ev.conv_q[pl + e], ev.conv_v[pl + e]);
+                    const i64 at = ring_slot_last(rg, w_[j]);
+                    ship_[j] = mkflow(ev.conv_q[at], ev.conv_v[at]);
                 }
             }
 #pragma unroll
@@ -489,9 +491,7 @@ struct StorageDelivery {  // thread per storage
                     for (int h = h0; h < h1; ++h) {
                         const int ent = ev.route_ent[h];
                         rem -= ev.ent_delay[ent];
-                        int ps = plane_now + rem;
-                        if (ps >= T) ps -= T;
-                        const i64 slot = (i64)ps * ev.n_edges + e;
+                        const i64 slot = ring_slot(rg, w_[j], rem);
                         const i64 oslot = (i64)(h - h0) * ev.n_edges + e;
                         const Flow fr = mkflow(ev.conv_q[slot], ev.conv_v[slot]);
                         const double nu = ev.nu[ent];
@@ -560,7 +560,7 @@ struct Purchase {
     // incoming connections per storage (seller ascending): connection id, seller | delay << 24, Z* (copies in this order:
     // one coalesced read instead of a gather through the connection id)
     // in_seller: seller ROW (SellerTable) | delay << 24
-    const i64* in_off; const int* in_edge; const int* in_seller; const i64* in_Z; SellerTable pubT; int n_max; const int* pm_ids;  // pm_ids == nullptr: all
+    const i64* in_off; const int* in_edge; const int* in_seller; const unsigned* in_slotw; const i64* in_Z; SellerTable pubT; int n_max; const int* pm_ids;  // pm_ids == nullptr: all
     i64* dem_q; double* dem_v; double* exp_costs; double* opt_val; double* tpen; int* iters; int* evals;
     int n_items, ahead;  // ahead > 0: the last thread asks for the connection lists of the manager `ahead` items further on (L2 prefetch)
     template <class Ctx>
@@ -574,6 +574,7 @@ struct Purchase {
             const size_t n2 = (size_t)(in_off[s2 + 1] - o2);
             prefetch_l2(in_edge + o2, n2 * sizeof(int));
             prefetch_l2(in_seller + o2, n2 * sizeof(int));
+            prefetch_l2(in_slotw + o2, n2 * sizeof(unsigned));
             prefetch_l2(in_Z + o2, n2 * sizeof(i64));
         }
 #endif
@@ -584,9 +585,9 @@ struct Purchase {
         const int nin = (int)(in_off[s + 1] - o);
         const int* ie = in_edge + o;
         const int* is = in_seller + o;
+        const unsigned* iw = in_slotw + o;
         const i64* iz = in_Z + o;
         const EdgeView& E = ev;
-        const int T = E.T, plane0 = (int)(step % T);
         const double* const tf = pubT.f;
         const i64 ts = pubT.stride;
         const i64 deficit = st.defc[s] - st.dlv_q[s] - st.T_q[s];
@@ -598,10 +599,9 @@ struct Purchase {
                 const unsigned st_ = (unsigned)is[i];
                 g.seller = (int)(st_ & 0xffffffu);
                 const int e = g.e;
-                int plane = plane0 + (int)(st_ >> 24);  // the conveyor plane of the last shipment: (step + delay) mod T
-                if (plane >= T) plane -= T;
-                const i64* conv = E.conv_q + (i64)plane * E.n_edges;
-                g.last_q = (E.ship_q != nullptr ? E.ship_q : conv)[e];  // a select, not a branch: loads of two gathers overlap
+                // the last shipment: the slot of time step + delay in the connection's conveyor ring
+                const i64 at = E.ship_q != nullptr ? (i64)e : ring_slot_last(E.rings, iw[i]);
+                g.last_q = (E.ship_q != nullptr ? E.ship_q : E.conv_q)[at];  // a select, not a branch: loads of two gathers overlap
                 g.Z_q = iz[i];
                 g.lastD_q = SEP ? E.D_q[e] : 0;
                 const double* f = tf + g.seller;  // consecutive connections -> consecutive rows: coalesced field by field
@@ -657,26 +657,22 @@ struct EdgeObservables {
     i64* ship_q; double* ship_v; i64* dlv_q; double* dlv_v; i64* tr_q; double* tr_v; i64* def_q;
     ACC_HD void operator()(int k) const {
         const i64 e = idx != nullptr ? idx[k] : (i64)k;
-        const int T = ev.T, tau = ev.tau[e];
-        const int p0 = (int)(t % T);
+        const int tau = ev.tau[e];
+        const unsigned w = ev.slotw[e];
+        const i64 at0 = ring_slot_time(ev.rings, w, t);
         if (ship_q != nullptr || ship_v != nullptr) {
-            int pl = p0 + tau;
-            if (pl >= T) pl -= T;
-            const i64 at = (i64)pl * ev.n_edges + e;
+            const i64 at = ring_slot_time(ev.rings, w, t + tau);
             if (ship_q != nullptr) ship_q[k] = ev.ship_q != nullptr ? ev.ship_q[e] : ev.conv_q[at];
             if (ship_v != nullptr) ship_v[k] = ev.ship_v != nullptr ? ev.ship_v[e] : ev.conv_v[at];
         }
         if (dlv_q != nullptr || dlv_v != nullptr) {
-            const i64 at = (i64)p0 * ev.n_edges + e;
-            if (dlv_q != nullptr) dlv_q[k] = ev.conv_q[at];
-            if (dlv_v != nullptr) dlv_v[k] = ev.conv_v[at];
+            if (dlv_q != nullptr) dlv_q[k] = ev.conv_q[at0];
+            if (dlv_v != nullptr) dlv_v[k] = ev.conv_v[at0];
         }
         if (tr_q != nullptr || tr_v != nullptr || def_q != nullptr) {
             Flow sum = mkflow(0, 0.0);
             for (int j = 1; j <= tau; ++j) {
-                int pl = p0 + j;
-                if (pl >= T) pl -= T;
-                const i64 at = (i64)pl * ev.n_edges + e;
+                const i64 at = ring_slot_time(ev.rings, w, t + j);
                 sum = fadd(sum, mkflow(ev.conv_q[at], ev.conv_v[at]));
             }
             if (ev.ovf_q != nullptr && ev.route[e] >= 0) {
@@ -686,7 +682,7 @@ struct EdgeObservables {
             sum = fcopy(sum);
             if (tr_q != nullptr) tr_q[k] = sum.q;
             if (tr_v != nullptr) tr_v[k] = sum.v;
-            if (def_q != nullptr) def_q[k] = ev.Z_q[e] * (tau + 1) - ev.conv_q[(i64)p0 * ev.n_edges + e] - sum.q;
+            if (def_q != nullptr) def_q[k] = ev.Z_q[e] * (tau + 1) - ev.conv_q[at0] - sum.q;
         }
     }
 };
@@ -694,24 +690,19 @@ struct EdgeObservables {
 // ---- exchange of a region-partitioned run (thread per halo entry / per agent) ----
 ACC_HD i64 f64_bits(double v) { i64 b; memcpy(&b, &v, sizeof b); return b; }
 ACC_HD double bits_f64(i64 b) { double v; memcpy(&v, &b, sizeof v); return v; }
-ACC_HD i64 conveyor_slot(const EdgeView& ev, int plane_now, i64 e) {  // slot of plane (step + delay) mod T, plane_now = step mod T
-    int pl = plane_now + ev.tau[e];
-    if (pl >= ev.T) pl -= ev.T;
-    return (i64)pl * ev.n_edges + e;
-}
 struct PackFlow {  // shipment of this step: the conveyor slot it was written to
-    EdgeView ev; int plane_now; const i64* ids; i64* buf;
+    EdgeView ev; const i64* ids; i64* buf;
     ACC_HD void operator()(int i) const {
         const i64 e = ids[i];
-        const i64 at = conveyor_slot(ev, plane_now, e);
+        const i64 at = ring_slot_last(ev.rings, ev.slotw[e]);
         buf[2 * (i64)i] = ev.conv_q[at]; buf[2 * (i64)i + 1] = f64_bits(ev.conv_v[at]);
     }
 };
 struct UnpackFlow {
-    EdgeView ev; int plane_now; const i64* ids; const i64* buf;
+    EdgeView ev; const i64* ids; const i64* buf;
     ACC_HD void operator()(int i) const {
         const i64 e = ids[i];
-        const i64 at = conveyor_slot(ev, plane_now, e);
+        const i64 at = ring_slot_last(ev.rings, ev.slotw[e]);
         ev.conv_q[at] = buf[2 * (i64)i]; ev.conv_v[at] = bits_f64(buf[2 * (i64)i + 1]);
     }
 };
@@ -843,6 +834,10 @@ struct acc_engine {
     // buyer-side lists
     DBuf<i64> ell_off, in_off;
     DBuf<int> ell_width, ell_edge, in_edge, in_seller;
+    DBuf<unsigned> e_slotw, ell_slotw, in_slotw;  // conveyor words (ring << 24 | rank) in connection order and in both buyer-side orders
+    ConveyorRings rings;                          // groups of equal delay (phase filled in per view)
+    int n_rings = 0;
+    i64 conv_slots = 0;
     DBuf<i64> in_Z;
     // utilitarian consumers (nested-CES utility optimisation)
     int nC = 0, nB = 0, c_n_max = 0;
@@ -911,7 +906,7 @@ struct acc_engine {
         v(pubT); v(seller_row); v(row_firm); v(e_to); v(sto_of); v(obs_out); v(obs_idx); v(obs_inc_q); v(obs_inc_v);
         v(s_Istar_q); v(s_Sstar_q); v(s_defc); v(s_Istar_v); v(s_Sstar_v); v(s_a); v(s_agent); v(s_sector);
         v(e_seller_off); v(e_route); v(route_off); v(route_ent); v(ent_delay); v(e_Z_q); v(e_tau); v(e_dom);
-        v(ell_off); v(in_off); v(ell_width); v(ell_edge); v(in_edge); v(in_seller); v(in_Z);
+        v(ell_off); v(in_off); v(ell_width); v(ell_edge); v(in_edge); v(in_seller); v(in_Z); v(e_slotw); v(ell_slotw); v(in_slotw);
         v(cons_ids); v(c_order_cnt); v(c_order); v(c_order_basket); v(fatal); v(c_nx_q); v(c_nx_v); v(c_nx_util); v(c_nx_ret);
         v(c_share); v(c_eshare); v(c_budget); v(c_bshare); v(c_ebshare); v(c_intra_exp); v(c_base_q);
         v(owned); v(pm_ids); v(halo_send); v(halo_recv);
@@ -979,6 +974,13 @@ struct acc_engine {
         EdgeView v;
         v.seller_off = e_seller_off.p; v.D_q = e_D_q.p; v.D_p = e_D_p.p; v.Z_q = e_Z_q.p; v.tau = e_tau.p; v.domestic = e_dom.p; v.route = e_route.p; v.route_off = route_off.p; v.route_ent = route_ent.p; v.ent_delay = ent_delay.p;
         v.conv_q = conv_q.p; v.conv_v = conv_v.p; v.n_edges = nE; v.T = T;
+        v.slotw = e_slotw.p; v.rings = rings;
+        for (int r = 0; r < n_rings; ++r) {
+            const int L = rings.len[r], ph = (int)(step % (i64)L);
+            v.rings.phase[r] = (unsigned char)ph;
+            v.rings.front[r] = rings.base[r] + (i64)ph * rings.count[r];
+            v.rings.last[r] = rings.base[r] + (i64)(ph == 0 ? L - 1 : ph - 1) * rings.count[r];
+        }
         v.ovf_q = forcing_used ? e_ovf_q.p : nullptr; v.ovf_v = forcing_used ? e_ovf_v.p : nullptr; v.nu = forcing_used ? nu.p : nullptr;
         v.ship_q = e_ship_q.n ? e_ship_q.p : nullptr;
         v.ship_v = e_ship_v.n ? e_ship_v.p : nullptr;
@@ -1051,10 +1053,10 @@ struct acc_engine {
     // stream next to the sellers' production / distribution pass; the storage pass waits for both.
     void launch_delivery(const unsigned char* own) {
         if (forcing_used) {
-            StorageDelivery<true> k{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p, own};
+            StorageDelivery<true> k{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p, ell_slotw.p, own};
             timed("storage_delivery", [&] { launch_thread(stream, nSt, k); });
         } else {
-            StorageDelivery<false> k{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p, own};
+            StorageDelivery<false> k{storage_view(), firm_view(), edge_view(), mp, sectors.p, sink(), step, ell_off.p, ell_width.p, ell_edge.p, ell_slotw.p, own};
             timed("storage_delivery", [&] { launch_thread(stream, nSt, k); });
         }
         consumer_ahead();  // the storages are final for this step: the consumers' solve of the next step starts here
@@ -1102,13 +1104,13 @@ struct acc_engine {
             ship_step = step;
         }
         if (halo_send.n && !peer_stores) {
-            PackFlow k{edge_view(), (int)(step % T), halo_send.p, x_flow_send};
+            PackFlow k{edge_view(), halo_send.p, x_flow_send};
             timed("pack_flow", [&] { launch_thread(stream, (int)halo_send.n, k); });
         }
     }
     void stage_deliver() {
         if (halo_recv.n) {
-            UnpackFlow k{edge_view(), (int)(step % T), halo_recv.p, x_flow_recv};
+            UnpackFlow k{edge_view(), halo_recv.p, x_flow_recv};
             timed("unpack_flow", [&] { launch_thread(stream, (int)halo_recv.n, k); });
         }
         consumer_join();
@@ -1126,7 +1128,7 @@ struct acc_engine {
     }
     template <bool SEP, bool STD, int G, bool DVAL = (G > 0)>  // the base group keeps the D_r summands; the large groups trade them for a second CTA per SM
     void launch_purchase() {
-        Purchase<SEP, STD, DVAL> k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, in_Z.p, seller_table(), n_max,
+        Purchase<SEP, STD, DVAL> k{storage_view(), edge_view(), mp, sectors.p, sink(), step, in_off.p, in_edge.p, in_seller.p, in_slotw.p, in_Z.p, seller_table(), n_max,
                              partitioned ? pm_ids.p : nullptr, s_dem_q.p, s_dem_v.p, s_exp_costs.p, s_opt_val.p, s_tpen.p, s_iters.p, s_evals.p,
                              partitioned ? n_pm : nSt, ACC_PM_PREFETCH_AHEAD};
         timed("purchase", [&] { launch_block_smem<G>(stream, partitioned ? n_pm : nSt, pm_group, pm_workspace_bytes(n_max, SEP, DVAL), k); });
@@ -1209,7 +1211,7 @@ struct acc_engine {
         else timed_comm("exchange_flow", [&] { exchange_halo(x_flow_send, comm_send_cnt, comm_send_off, x_flow_recv, comm_recv_cnt, comm_recv_off); });
         {   // stage_deliver without the full-table pack
             if (halo_recv.n) {
-                UnpackFlow k{edge_view(), (int)(step % T), halo_recv.p, x_flow_recv};
+                UnpackFlow k{edge_view(), halo_recv.p, x_flow_recv};
                 timed("unpack_flow", [&] { launch_thread(stream, (int)halo_recv.n, k); });
             }
             consumer_join();
@@ -1428,6 +1430,36 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
         if (tau[e] > Tmax) Tmax = tau[e];
     }
     E.T = Tmax + 1;
+    // ---- conveyor rings: connections of equal delay, in connection order; at most 2^24 per group ----
+    std::vector<unsigned> slotw(nE);
+    {
+        std::vector<i64> per_delay(Tmax + 1, 0);
+        for (i64 e = 0; e < nE; ++e) ++per_delay[tau[e]];
+        const i64 cap = (i64)1 << 24;
+        std::vector<int> first_ring(Tmax + 1, -1);
+        int nr = 0;
+        i64 slots = 0;
+        std::memset(&E.rings, 0, sizeof E.rings);
+        for (int d = 0; d <= Tmax; ++d) {
+            if (per_delay[d] == 0) continue;
+            first_ring[d] = nr;
+            for (i64 left = per_delay[d]; left > 0; left -= cap) {
+                if (nr >= ACC_MAX_RINGS) fail("more than " + std::to_string((int)ACC_MAX_RINGS) + " conveyor ring groups (distinct delays, 2^24 connections each): partition the network");
+                E.rings.base[nr] = slots;
+                E.rings.count[nr] = (int)std::min(left, cap);
+                E.rings.len[nr] = (unsigned char)(d + 1);
+                slots += (i64)(d + 1) * E.rings.count[nr];
+                ++nr;
+            }
+        }
+        E.n_rings = nr;
+        E.conv_slots = slots;
+        std::vector<i64> seen(Tmax + 1, 0);
+        for (i64 e = 0; e < nE; ++e) {
+            const i64 k = seen[tau[e]]++;
+            slotw[e] = ((unsigned)(first_ring[tau[e]] + (int)(k >> 24)) << 24) | (unsigned)(k & (cap - 1));
+        }
+    }
 
     // ---- initial state (Storage::add_initial_flow_Z_star, Firm::add_initial_production_X_star) ----
     std::vector<i64> Xstar_q(nA, 0), Istar_q(nSt, 0), Sstar_q(nSt, 0), defc(nSt, 0), T_q(nSt, 0);
@@ -1501,6 +1533,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
     std::vector<i64> in_off(nSt + 1, 0);
     for (int k = 0; k < nSt; ++k) in_off[k + 1] = in_off[k] + in_cnt[k + 1];
     std::vector<int> in_edge(nE), in_seller(nE);  // in_seller: seller row | delay << 24
+    std::vector<unsigned> in_slotw(nE);
     std::vector<i64> in_Z(nE);
     if (nA >= (1 << 24)) fail("more than 2^24 agents");
     {
@@ -1510,6 +1543,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
             in_edge[fill[st]] = (int)e;
             in_seller[fill[st]] = (int)((unsigned)seller_row[net.edge_from[e]] | ((unsigned)tau[e] << 24));
             in_Z[fill[st]] = Zq[e];
+            in_slotw[fill[st]] = slotw[e];
             ++fill[st];
         }
     }
@@ -1527,9 +1561,13 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
         ell_off[sl + 1] = ell_off[sl] + (i64)w * 32;
     }
     std::vector<int> ell_edge(ell_off[n_slices], -1);
+    std::vector<unsigned> ell_slotw(ell_off[n_slices], slotw[0]);  // padding cells: a valid word (the loads are issued before the cell is tested)
     for (int k = 0; k < nSt; ++k) {
         const int sl = k >> 5, lane = k & 31;
-        for (i64 j = in_off[k]; j < in_off[k + 1]; ++j) ell_edge[ell_off[sl] + (j - in_off[k]) * 32 + lane] = in_edge[j];
+        for (i64 j = in_off[k]; j < in_off[k + 1]; ++j) {
+            ell_edge[ell_off[sl] + (j - in_off[k]) * 32 + lane] = in_edge[j];
+            ell_slotw[ell_off[sl] + (j - in_off[k]) * 32 + lane] = in_slotw[j];
+        }
     }
 
     // ---- upload ----
@@ -1578,26 +1616,26 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
         std::vector<i64> p1(nE, mkp(1.0));
         E.e_D_q.upload(Zq, s); E.e_D_p.upload(p1, s);
     }
-    {   // delay queues start full of Z* (TransportChainLink.cpp:49)
-        const i64 T = E.T;
-        E.conv_q.alloc((size_t)(T * nE)); E.conv_v.alloc((size_t)(T * nE));
+    {   // delay queues start full of Z* (TransportChainLink.cpp:49): the slots of times 0 .. tau - 1 of every ring, one ring group at a time
+        E.conv_q.alloc((size_t)E.conv_slots); E.conv_v.alloc((size_t)E.conv_slots);
         E.conv_q.zero(s); E.conv_v.zero(s);
-        std::vector<i64> pq(nE);
-        std::vector<double> pv(nE);
-        for (i64 k = 0; k < T; ++k) {
-            bool any = false;
-            for (i64 e = 0; e < nE; ++e) {
-                // plane T-1 also holds the "last shipment" of connections whose queue is shorter: last_shipment_Z = Z*
-                const bool init = k < tau[e];
-                pq[e] = init ? Zq[e] : 0;
-                pv[e] = init ? flow_qp(Zq[e], mkp(1.0)).v : 0.0;
-                any = any || init;
+        std::vector<std::vector<i64>> members(E.n_rings);
+        for (int r = 0; r < E.n_rings; ++r) members[r].reserve(E.rings.count[r]);
+        for (i64 e = 0; e < nE; ++e) members[slotw[e] >> 24].push_back(e);  // connection order == rank order
+        std::vector<i64> pq;
+        std::vector<double> pv;
+        for (int r = 0; r < E.n_rings; ++r) {
+            const i64 cnt = E.rings.count[r];
+            const int d = (int)E.rings.len[r] - 1;
+            if (d == 0) continue;
+            pq.resize(cnt); pv.resize(cnt);
+            for (i64 k = 0; k < cnt; ++k) { pq[k] = Zq[members[r][k]]; pv[k] = flow_qp(pq[k], mkp(1.0)).v; }
+            for (int i = 0; i < d; ++i) {
+                h2d(E.conv_q.p + E.rings.base[r] + (i64)i * cnt, pq.data(), cnt * sizeof(i64), s);
+                h2d(E.conv_v.p + E.rings.base[r] + (i64)i * cnt, pv.data(), cnt * sizeof(double), s);
             }
-            if (any) {
-                h2d(E.conv_q.p + k * nE, pq.data(), nE * sizeof(i64), s);
-                h2d(E.conv_v.p + k * nE, pv.data(), nE * sizeof(double), s);
-                dev_sync(s);
-            }
+            dev_sync(s);
+            std::vector<i64>().swap(members[r]);
         }
     }
     if (mp.utilitarian) {
@@ -1673,6 +1711,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
     E.fatal.alloc(1); E.fatal.zero(s);
     E.in_off.upload(in_off, s); E.in_edge.upload(in_edge, s); E.in_seller.upload(in_seller, s); E.in_Z.upload(in_Z, s);
     E.ell_off.upload(ell_off, s); E.ell_width.upload(ell_width, s); E.ell_edge.upload(ell_edge, s);
+    E.e_slotw.upload(slotw, s); E.ell_slotw.upload(ell_slotw, s); E.in_slotw.upload(in_slotw, s);
     E.ev_buf.alloc(E.ev_cap); E.ev_count.alloc(1); E.ev_count.zero(s);
     E.nu.alloc((size_t)E.nEnt + 1);
     dev_sync(s);

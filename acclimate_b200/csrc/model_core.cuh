@@ -369,6 +369,42 @@ struct alignas(16) HaloEntry {
     i64 a, b;
 };
 
+// The conveyor: every connection owns a ring of tau + 1 slots (the delay queue of its transport chain plus the slot of the
+// shipment under way to it).  Connections of equal delay form a RING GROUP stored plane by plane -- [tau + 1][connections of
+// the group] --, so that neighbouring connections of a seller (neighbouring buyers: same region, same delay) still sit side by
+// side in every plane.  A connection's word `ring << 24 | rank` names its group and its position in the group's planes (a
+// group holds at most 2^24 connections; larger ones are split).  Memory is 16 * sum(tau + 1) bytes instead of 16 * T * E for
+// dense planes of the longest delay.  The table travels by value with the kernel arguments.
+enum { ACC_MAX_RINGS = 64 };
+struct ConveyorRings {
+    // for the step the view was made for: the plane of what arrives now (time step) and of this step's shipment (time step + tau)
+    i64 front[ACC_MAX_RINGS];
+    i64 last[ACC_MAX_RINGS];
+    i64 base[ACC_MAX_RINGS];             // first slot of the group
+    int count[ACC_MAX_RINGS];            // connections in the group
+    unsigned char len[ACC_MAX_RINGS];    // tau + 1
+    unsigned char phase[ACC_MAX_RINGS];  // step mod (tau + 1)
+};
+ACC_HD int ring_tau(const ConveyorRings& rg, unsigned w) { return (int)rg.len[w >> 24] - 1; }
+// slot of time step + k, 0 <= k <= tau (k = 0: what arrives now; k = tau: the shipment of this step)
+ACC_HD i64 ring_slot(const ConveyorRings& rg, unsigned w, int k) {
+    const unsigned r = w >> 24;
+    const int L = rg.len[r];
+    int i = (int)rg.phase[r] + k;
+    if (i >= L) i -= L;
+    return rg.base[r] + (i64)i * rg.count[r] + (i64)(w & 0xffffffu);
+}
+ACC_HD i64 ring_slot_front(const ConveyorRings& rg, unsigned w) { return rg.front[w >> 24] + (i64)(w & 0xffffffu); }  // k = 0
+ACC_HD i64 ring_slot_last(const ConveyorRings& rg, unsigned w) { return rg.last[w >> 24] + (i64)(w & 0xffffffu); }    // k = tau
+// slot of an absolute time u (any sign): for reads outside the step's kernels
+ACC_HD i64 ring_slot_time(const ConveyorRings& rg, unsigned w, i64 u) {
+    const unsigned r = w >> 24;
+    const i64 L = rg.len[r];
+    i64 i = u % L;
+    if (i < 0) i += L;
+    return rg.base[r] + i * rg.count[r] + (i64)(w & 0xffffffu);
+}
+
 // Connection arrays in CSR-by-seller order
 struct EdgeView {
     const int* seller_off;          // [n_agents + 1]
@@ -379,8 +415,10 @@ struct EdgeView {
     const int* route;               // route of the connection (-1: immediate / domestic, no geo entity)
     const int* route_off; const int* route_ent;  // route -> its geo entities in travel order (TransportChainLink chain)
     const unsigned char* ent_delay; // delay of each geo entity
-    i64* conv_q; double* conv_v;    // conveyor planes [T][n_edges]: plane (t + tau) mod T receives the shipment of step t
-    i64 n_edges; int T;
+    i64* conv_q; double* conv_v;    // conveyor slots (ConveyorRings): slot (t + tau) mod (tau + 1) of a connection's ring receives the shipment of step t
+    const unsigned* slotw;          // ring << 24 | rank of every connection
+    ConveyorRings rings;
+    i64 n_edges; int T;             // T = longest delay + 1
     i64* ovf_q; double* ovf_v;      // overflow per (hop, connection): [hop][n_edges] (null until passage forcing is used)
     const double* nu;               // passage per geo entity (null until used; < 0: none)
     i64* ship_q; double* ship_v;    // last shipment (only kept apart when hops may rewrite its conveyor slot, else null)
@@ -508,19 +546,16 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
     }
 
     // ---- distribute, :140-251 ----
-    const int T = ev.T;
-    const int plane_now = (int)(step % T);
-    const unsigned char* tau = book.q != nullptr ? book.tau : ev.tau + e0;
+    const unsigned* slotw = ev.slotw + e0;
     const unsigned char* dom = book.q != nullptr ? book.dom : ev.domestic + e0;
     double R = 0.0;
     i64 exq = 0; double exv = 0.0;
     if (X.q <= 0) {
         cx.foreach(n, [&](int i) {
-            int pl = plane_now + tau[i];  // (step + delay) mod T without the division: delay < T
-            if (pl >= T) pl -= T;
-            ev.conv_q[(i64)pl * ev.n_edges + e0 + i] = 0;
+            const i64 at = ring_slot_last(ev.rings, slotw[i]);
+            ev.conv_q[at] = 0;
             if (ev.ship_q != nullptr) { ev.ship_q[e0 + i] = 0; ev.ship_v[e0 + i] = 0.0; }
-            ev.conv_v[(i64)pl * ev.n_edges + e0 + i] = 0.0;
+            ev.conv_v[at] = 0.0;
             peer_store_shipment(ev, (i64)e0 + i, mkflow(0, 0.0));
         });
     } else {
@@ -566,11 +601,10 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
                     }
                 }
             }
-            int pl = plane_now + tau[i];  // (step + delay) mod T without the division: delay < T
-            if (pl >= T) pl -= T;
-            ev.conv_q[(i64)pl * ev.n_edges + e0 + i] = z.q;           // BusinessConnection::push_flow_Z -> first transport link
+            const i64 at = ring_slot_last(ev.rings, slotw[i]);
+            ev.conv_q[at] = z.q;                                      // BusinessConnection::push_flow_Z -> first transport link
             if (ev.ship_q != nullptr) { ev.ship_q[e0 + i] = z.q; ev.ship_v[e0 + i] = z.v; }  // last_shipment_Z, kept apart when hops rewrite the slot
-            ev.conv_v[(i64)pl * ev.n_edges + e0 + i] = z.v;
+            ev.conv_v[at] = z.v;
             peer_store_shipment(ev, (i64)e0 + i, z);
             if (!dom[i]) { r.eq = z.q; r.ev = z.v; }                  // Region::add_export_Z, BusinessConnection.cpp:91-93
             return r;

@@ -41,11 +41,9 @@ struct ObsFill {  // ArrayOutput::resize_data: everything starts as NaN
     ACC_HD void operator()(int i) const { out[i] = ACC_OBS_NAN; }
 };
 
-// last shipment of connection e: the conveyor slot of plane (t + delay) mod T, t = step of the last production pass
+// last shipment of connection e: the slot of time t + delay in its conveyor ring, t = step of the last production pass
 ACC_HD Flow obs_last_shipment(const EdgeView& ev, i64 t, i64 e) {
-    int pl = (int)(t % ev.T) + ev.tau[e];
-    if (pl >= ev.T) pl -= ev.T;
-    const i64 at = (i64)pl * ev.n_edges + e;
+    const i64 at = ring_slot_time(ev.rings, ev.slotw[e], t + ev.tau[e]);
     return ev.ship_q != nullptr ? mkflow(ev.ship_q[e], ev.ship_v[e]) : mkflow(ev.conv_q[at], ev.conv_v[at]);
 }
 
@@ -173,8 +171,9 @@ struct ObserveStorages {
 
 // one connection's observable; t = step of the last production pass
 ACC_HD double observe_connection(int var, const EdgeView& ev, i64 t, i64 e) {
-    const int T = ev.T, tau = ev.tau[e];
-    const int p0 = (int)(t % T);
+    const int tau = ev.tau[e];
+    const unsigned w = ev.slotw[e];
+    const i64 at0 = ring_slot_time(ev.rings, w, t);  // what arrived at step t
     switch (var) {
         case XV_INITIAL_FLOW_Q: return qf(ev.Z_q[e]);
         case XV_INITIAL_FLOW_V: return flow_q(ev.Z_q[e]).v;
@@ -182,8 +181,8 @@ ACC_HD double observe_connection(int var, const EdgeView& ev, i64 t, i64 e) {
         case XV_DEMAND_REQUEST_V: return ev.D_q[e] > 0 ? q_times_p(ev.D_q[e], ev.D_p[e]) : 0.0;
         case XV_SENT_FLOW_Q: return qf(obs_last_shipment(ev, t, e).q);
         case XV_SENT_FLOW_V: return obs_last_shipment(ev, t, e).v;
-        case XV_RECEIVED_FLOW_Q: return qf(ev.conv_q[(i64)p0 * ev.n_edges + e]);
-        case XV_RECEIVED_FLOW_V: return ev.conv_v[(i64)p0 * ev.n_edges + e];
+        case XV_RECEIVED_FLOW_Q: return qf(ev.conv_q[at0]);
+        case XV_RECEIVED_FLOW_V: return ev.conv_v[at0];
         case XV_MINIMUM_PASSAGE: {  // BusinessConnection::get_minimum_passage, BusinessConnection.cpp:69-83
             double m = 1.0;
             if (ev.nu != nullptr && ev.route[e] >= 0)
@@ -196,12 +195,10 @@ ACC_HD double observe_connection(int var, const EdgeView& ev, i64 t, i64 e) {
         default: break;
     }
     // what is under way: the delay slots of planes t+1 .. t+delay plus the overflow of every hop (get_transport_flow, :162-171)
-    const Flow dlv = mkflow(ev.conv_q[(i64)p0 * ev.n_edges + e], ev.conv_v[(i64)p0 * ev.n_edges + e]);
+    const Flow dlv = mkflow(ev.conv_q[at0], ev.conv_v[at0]);
     Flow sum = mkflow(0, 0.0);
     for (int j = 1; j <= tau; ++j) {
-        int pl = p0 + j;
-        if (pl >= T) pl -= T;
-        const i64 at = (i64)pl * ev.n_edges + e;
+        const i64 at = ring_slot_time(ev.rings, w, t + j);
         sum = fadd(sum, mkflow(ev.conv_q[at], ev.conv_v[at]));
     }
     if (ev.ovf_q != nullptr && ev.route[e] >= 0) {

@@ -314,8 +314,9 @@ def main():
     e2e_outputs = None
     if not partitioned and args.config in ("eora", "small"):
         firms17 = np.nonzero((np.asarray(net["agent_type"]) == 1) & (np.asarray(net["agent_region"]) == min(17, E.n_regions - 1)))[0]
-        buf_s = np.empty(E.n_sectors * E.n_agents)
-        buf_f = np.empty(firms17.size * E.n_agents)
+        # pinned host buffers, like the forcing upload: the copy engine writes them without a staging copy of the driver's
+        buf_s = torch.empty(E.n_sectors * E.n_agents, dtype=torch.float64, pin_memory=True).numpy()
+        buf_f = torch.empty(firms17.size * E.n_agents, dtype=torch.float64, pin_memory=True).numpy()
         barrier()
         t0o = time.perf_counter()
         for _ in range(args.steps):

@@ -1,0 +1,12 @@
+# A/B on one box: the committed kernels (variants/libacc_head.so) against the working tree's, same bench, alternating
+B="python bench.py --steps 20 --warmup 3 --no-cpu-baseline --flood-steps 0 --members 0"
+for i in 1 2; do
+  for L in variants/libacc_head.so acclimate_b200/libacclimate_b200.so $EXTRA_LIBS; do
+    ACCLIMATE_B200_LIB=$L timeout 300 $B 2>/dev/null | python -c "
+import sys, json
+for l in sys.stdin:
+    if l.startswith('{'):
+        d=json.loads(l); k=d['roofline']['kernels_ms_per_step']; print('$L', round(d['ms_per_step'],4), {n: round(v,4) for n,v in k.items()})
+"
+  done
+done
