@@ -1435,7 +1435,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
     {
         std::vector<i64> per_delay(Tmax + 1, 0);
         for (i64 e = 0; e < nE; ++e) ++per_delay[tau[e]];
-        const i64 cap = (i64)1 << 24;
+        const i64 cap = (i64)1 << ACC_RING_RANK_BITS;
         std::vector<int> first_ring(Tmax + 1, -1);
         int nr = 0;
         i64 slots = 0;
@@ -1457,7 +1457,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
         std::vector<i64> seen(Tmax + 1, 0);
         for (i64 e = 0; e < nE; ++e) {
             const i64 k = seen[tau[e]]++;
-            slotw[e] = ((unsigned)(first_ring[tau[e]] + (int)(k >> 24)) << 24) | (unsigned)(k & (cap - 1));
+            slotw[e] = ((unsigned)(first_ring[tau[e]] + (int)(k >> ACC_RING_RANK_BITS)) << ACC_RING_RANK_BITS) | (unsigned)(k & (cap - 1));
         }
     }
 
@@ -1621,7 +1621,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
         E.conv_q.zero(s); E.conv_v.zero(s);
         std::vector<std::vector<i64>> members(E.n_rings);
         for (int r = 0; r < E.n_rings; ++r) members[r].reserve(E.rings.count[r]);
-        for (i64 e = 0; e < nE; ++e) members[slotw[e] >> 24].push_back(e);  // connection order == rank order
+        for (i64 e = 0; e < nE; ++e) members[ring_of(slotw[e])].push_back(e);  // connection order == rank order
         std::vector<i64> pq;
         std::vector<double> pv;
         for (int r = 0; r < E.n_rings; ++r) {

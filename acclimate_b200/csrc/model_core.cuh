@@ -375,7 +375,12 @@ struct alignas(16) HaloEntry {
 // side in every plane.  A connection's word `ring << 24 | rank` names its group and its position in the group's planes (a
 // group holds at most 2^24 connections; larger ones are split).  Memory is 16 * sum(tau + 1) bytes instead of 16 * T * E for
 // dense planes of the longest delay.  The table travels by value with the kernel arguments.
+#ifndef ACC_RING_RANK_BITS
+#define ACC_RING_RANK_BITS 24  // (a test build lowers it to run the split of large groups on a small network)
+#endif
 enum { ACC_MAX_RINGS = 64 };
+ACC_HD unsigned ring_of(unsigned w) { return w >> ACC_RING_RANK_BITS; }
+ACC_HD i64 rank_of(unsigned w) { return (i64)(w & ((1u << ACC_RING_RANK_BITS) - 1u)); }
 struct ConveyorRings {
     // for the step the view was made for: the plane of what arrives now (time step) and of this step's shipment (time step + tau)
     i64 front[ACC_MAX_RINGS];
@@ -385,24 +390,24 @@ struct ConveyorRings {
     unsigned char len[ACC_MAX_RINGS];    // tau + 1
     unsigned char phase[ACC_MAX_RINGS];  // step mod (tau + 1)
 };
-ACC_HD int ring_tau(const ConveyorRings& rg, unsigned w) { return (int)rg.len[w >> 24] - 1; }
+ACC_HD int ring_tau(const ConveyorRings& rg, unsigned w) { return (int)rg.len[ring_of(w)] - 1; }
 // slot of time step + k, 0 <= k <= tau (k = 0: what arrives now; k = tau: the shipment of this step)
 ACC_HD i64 ring_slot(const ConveyorRings& rg, unsigned w, int k) {
-    const unsigned r = w >> 24;
+    const unsigned r = ring_of(w);
     const int L = rg.len[r];
     int i = (int)rg.phase[r] + k;
     if (i >= L) i -= L;
-    return rg.base[r] + (i64)i * rg.count[r] + (i64)(w & 0xffffffu);
+    return rg.base[r] + (i64)i * rg.count[r] + rank_of(w);
 }
-ACC_HD i64 ring_slot_front(const ConveyorRings& rg, unsigned w) { return rg.front[w >> 24] + (i64)(w & 0xffffffu); }  // k = 0
-ACC_HD i64 ring_slot_last(const ConveyorRings& rg, unsigned w) { return rg.last[w >> 24] + (i64)(w & 0xffffffu); }    // k = tau
+ACC_HD i64 ring_slot_front(const ConveyorRings& rg, unsigned w) { return rg.front[ring_of(w)] + rank_of(w); }  // k = 0
+ACC_HD i64 ring_slot_last(const ConveyorRings& rg, unsigned w) { return rg.last[ring_of(w)] + rank_of(w); }    // k = tau
 // slot of an absolute time u (any sign): for reads outside the step's kernels
 ACC_HD i64 ring_slot_time(const ConveyorRings& rg, unsigned w, i64 u) {
-    const unsigned r = w >> 24;
+    const unsigned r = ring_of(w);
     const i64 L = rg.len[r];
     i64 i = u % L;
     if (i < 0) i += L;
-    return rg.base[r] + i * rg.count[r] + (i64)(w & 0xffffffu);
+    return rg.base[r] + i * rg.count[r] + rank_of(w);
 }
 
 // Connection arrays in CSR-by-seller order
