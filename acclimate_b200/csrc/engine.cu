@@ -85,11 +85,11 @@ static void launch_thread(stream_t, int n, K k) { for (int i = 0; i < n; ++i) k(
 template <class K>
 static void launch_block(stream_t, int n, K k) { for (int i = 0; i < n; ++i) { HostCtx cx(K::THREADS); k(cx, i); } }
 template <class K>
-static void launch_seller(stream_t, int n, int, K k) {
+static void launch_seller(stream_t, int n, int, int, K k) {
     for (int i = 0; i < n; ++i) {
         HostCtx warp(32), cx(K::THREADS);
         k.prepare(warp, i);
-        k(cx, i, SellerBook{nullptr, nullptr, nullptr, nullptr});
+        k(cx, i, SellerBook{nullptr, nullptr, nullptr, nullptr, 0});
     }
 }
 template <class K>
@@ -183,12 +183,12 @@ __global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) block_kernel(K k) {
 // `ahead` > 0: while this CTA waits for its own book, one thread asks the copy engine to bring the book of the seller `ahead`
 // CTAs further on -- the one a CTA of the next wave will take on this SM -- into the L2, so that its bulk copy is fed from there.
 template <class K>
-__global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) seller_kernel(K k, int cap, int ahead) {
+__global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) seller_kernel(K k, int cap, int ahead, int perm_slots) {
     __shared__ __align__(16) unsigned char scratch[ACC_BLOCK_SCRATCH_BYTES];
     __shared__ __align__(8) unsigned long long bar;
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     BlockCtx cx(scratch);
-    SellerBook book{nullptr, nullptr, nullptr, nullptr};
+    SellerBook book{nullptr, nullptr, nullptr, nullptr, 0};
     if (cap > 0) {
         if (threadIdx.x == 0) mbar_init(&bar, 1);
         __syncthreads();
@@ -209,7 +209,11 @@ __global__ void __launch_bounds__(K::THREADS, K::MIN_BLOCKS) seller_kernel(K k, 
             prefetch_l2(k.ev.domestic + e2, (size_t)n2);
         }
     }
-    if (n > 0 && n <= cap) book = stage_seller_book(dyn_smem, cap, &bar, k.ev.D_q, k.ev.D_p, k.ev.tau, k.ev.domestic, e0, n);
+    if (n > 0 && n <= cap) book = stage_seller_book(dyn_smem, cap, &bar, k.ev.D_q, k.ev.D_p, k.ev.domestic, e0, n);
+    if (perm_slots > 0) {  // room for a sort of the seller's connections behind the book (ordered_range_sums)
+        book.perm16 = reinterpret_cast<unsigned short*>(dyn_smem + (cap > 0 ? seller_book_bytes(cap) : 0));
+        book.perm_slots = perm_slots;
+    }
     __syncthreads();
     k(cx, (int)blockIdx.x, book);
 }
@@ -259,9 +263,9 @@ static void launch_block(stream_t s, int n, K k) {
     ACC_CUDA(cudaGetLastError());
 }
 template <class K>
-static void launch_seller(stream_t s, int n, int cap, K k) {
+static void launch_seller(stream_t s, int n, int cap, int perm_slots, K k) {
     if (n <= 0) return;
-    const size_t smem = cap > 0 ? seller_book_bytes(cap) : 0;
+    const size_t smem = (cap > 0 ? seller_book_bytes(cap) : 0) + (size_t)perm_slots * sizeof(unsigned short);
     if (smem_needs_config((const void*)seller_kernel<K>, smem)) ACC_CUDA(cudaFuncSetAttribute(seller_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int ahead = 0;
     if (cap > 0) {  // half a wave of CTAs ahead (measured on the EORA shape: none 0.521 ms, 148 ahead 0.504, 296 ahead 0.512, 592 ahead 0.539)
@@ -274,7 +278,7 @@ static void launch_seller(stream_t s, int n, int cap, K k) {
         ahead = ACC_SELLER_PREFETCH_AHEAD;
 #endif
     }
-    seller_kernel<K><<<n, K::THREADS, smem, s>>>(k, cap, ahead);
+    seller_kernel<K><<<n, K::THREADS, smem, s>>>(k, cap, ahead, perm_slots);
     ACC_CUDA(cudaGetLastError());
 }
 template <class K>
@@ -788,6 +792,7 @@ struct acc_engine {
     int nA = 0, nS = 0, nR = 0, nSt = 0, nF = 0, n_max = 0, T = 1;
     int pm_group = ACCSQP_GROUP;  // threads per purchasing manager
     int book_cap = 0;             // largest seller's number of connections when its demand book fits the shared-memory budget, else 0
+    int perm_slots = 0;           // 16-bit sort slots behind the book (power of two >= the largest seller) when they fit as well, else 0
     i64 nE = 0;
     ModelP mp;
     std::vector<SectorP> h_sectors;
@@ -834,6 +839,7 @@ struct acc_engine {
     // buyer-side lists
     DBuf<i64> ell_off, in_off;
     DBuf<int> ell_width, ell_edge, in_edge, in_seller;
+    DBuf<int> e_sort;  // scratch of the sellers' pass: a seller's connections in sorted order (model_core.cuh ordered_range_sums)
     DBuf<unsigned> e_slotw, ell_slotw, in_slotw;  // conveyor words (ring << 24 | rank) in connection order and in both buyer-side orders
     ConveyorRings rings;                          // groups of equal delay (phase filled in per view)
     int n_rings = 0;
@@ -906,7 +912,7 @@ struct acc_engine {
         v(pubT); v(seller_row); v(row_firm); v(e_to); v(sto_of); v(obs_out); v(obs_idx); v(obs_inc_q); v(obs_inc_v);
         v(s_Istar_q); v(s_Sstar_q); v(s_defc); v(s_Istar_v); v(s_Sstar_v); v(s_a); v(s_agent); v(s_sector);
         v(e_seller_off); v(e_route); v(route_off); v(route_ent); v(ent_delay); v(e_Z_q); v(e_tau); v(e_dom);
-        v(ell_off); v(in_off); v(ell_width); v(ell_edge); v(in_edge); v(in_seller); v(in_Z); v(e_slotw); v(ell_slotw); v(in_slotw);
+        v(ell_off); v(in_off); v(ell_width); v(ell_edge); v(in_edge); v(in_seller); v(in_Z); v(e_slotw); v(ell_slotw); v(in_slotw); v(e_sort);
         v(cons_ids); v(c_order_cnt); v(c_order); v(c_order_basket); v(fatal); v(c_nx_q); v(c_nx_v); v(c_nx_util); v(c_nx_ret);
         v(c_share); v(c_eshare); v(c_budget); v(c_bshare); v(c_ebshare); v(c_intra_exp); v(c_base_q);
         v(owned); v(pm_ids); v(halo_send); v(halo_recv);
@@ -974,7 +980,7 @@ struct acc_engine {
         EdgeView v;
         v.seller_off = e_seller_off.p; v.D_q = e_D_q.p; v.D_p = e_D_p.p; v.Z_q = e_Z_q.p; v.tau = e_tau.p; v.domestic = e_dom.p; v.route = e_route.p; v.route_off = route_off.p; v.route_ent = route_ent.p; v.ent_delay = ent_delay.p;
         v.conv_q = conv_q.p; v.conv_v = conv_v.p; v.n_edges = nE; v.T = T;
-        v.slotw = e_slotw.p; v.rings = rings;
+        v.slotw = e_slotw.p; v.rings = rings; v.sort_scratch = e_sort.p;
         for (int r = 0; r < n_rings; ++r) {
             const int L = rings.len[r], ph = (int)(step % (i64)L);
             v.rings.phase[r] = (unsigned char)ph;
@@ -1100,7 +1106,7 @@ struct acc_engine {
         consumer_fork();
         {
             SellerProduction k{firm_view(), edge_view(), storage_view(), mp, sectors.p, sink(), step, firm_ids.p};
-            timed("seller_production", [&] { launch_seller(stream, nF, book_cap, k); });
+            timed("seller_production", [&] { launch_seller(stream, nF, book_cap, perm_slots, k); });
             ship_step = step;
         }
         if (halo_send.n && !peer_stores) {
@@ -1243,7 +1249,7 @@ struct acc_engine {
         require_single("acc_phase");
         consumer_fork();
         SellerProduction k2{firm_view(), edge_view(), storage_view(), mp, sectors.p, sink(), step, firm_ids.p};
-        timed("seller_production", [&] { launch_seller(stream, nF, book_cap, k2); });
+        timed("seller_production", [&] { launch_seller(stream, nF, book_cap, perm_slots, k2); });
         ship_step = step;
         consumer_join();
         launch_delivery(nullptr);
@@ -1348,6 +1354,12 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
         int out_max = 0;
         for (i64 a = 0; a < nA; ++a) out_max = std::max(out_max, seller_off[a + 1] - seller_off[a]);
         E.book_cap = seller_book_bytes(out_max) <= ACC_SELLER_BOOK_BUDGET ? out_max : 0;
+        {   // the sort scratch of ordered_range_sums: in shared memory when it fits next to the book (or alone, for books read in place)
+            int N = 1;
+            while (N < out_max) N <<= 1;
+            const size_t with = (E.book_cap > 0 ? seller_book_bytes(E.book_cap) : 0) + (size_t)N * sizeof(unsigned short);
+            E.perm_slots = (N <= 32768 && with <= ACC_SELLER_BOOK_BUDGET) ? N : 0;
+        }
     }
     const int nSt = (int)c_agent.size();
     E.nSt = nSt;
@@ -1712,6 +1724,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
     E.in_off.upload(in_off, s); E.in_edge.upload(in_edge, s); E.in_seller.upload(in_seller, s); E.in_Z.upload(in_Z, s);
     E.ell_off.upload(ell_off, s); E.ell_width.upload(ell_width, s); E.ell_edge.upload(ell_edge, s);
     E.e_slotw.upload(slotw, s); E.ell_slotw.upload(ell_slotw, s); E.in_slotw.upload(in_slotw, s);
+    E.e_sort.alloc(2 * (size_t)nE); E.e_sort.zero(s);
     E.ev_buf.alloc(E.ev_cap); E.ev_count.alloc(1); E.ev_count.zero(s);
     E.nu.alloc((size_t)E.nEnt + 1);
     dev_sync(s);
@@ -2361,7 +2374,7 @@ acc_engine* acc_fork(acc_engine* parent) {
         CloneVisitor cv{E->stream};
         E->visit_state(cv);
         cv(E->pubT); cv(E->fatal);  // derived / scratch state that changes with the steps
-        cv(E->c_nx_q); cv(E->c_nx_v); cv(E->c_nx_util); cv(E->c_nx_ret);
+        cv(E->c_nx_q); cv(E->c_nx_v); cv(E->c_nx_util); cv(E->c_nx_ret); cv(E->e_sort);
         E->ahead_step = -1;         // the member repeats the consumers' solve of its next step on its own copy of the state
         for (acc::DBuf<double>* b : {&E->obs_out, &E->obs_inc_v}) { b->p = nullptr; b->n = 0; b->borrowed = false; }
         for (acc::DBuf<i64>* b : {&E->obs_idx, &E->obs_inc_q}) { b->p = nullptr; b->n = 0; b->borrowed = false; }

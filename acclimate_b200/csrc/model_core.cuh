@@ -427,6 +427,7 @@ struct EdgeView {
     i64* ovf_q; double* ovf_v;      // overflow per (hop, connection): [hop][n_edges] (null until passage forcing is used)
     const double* nu;               // passage per geo entity (null until used; < 0: none)
     i64* ship_q; double* ship_v;    // last shipment (only kept apart when hops may rewrite its conveyor slot, else null)
+    int* sort_scratch;              // [2 n_edges]: a seller's connections in the reference's sorted order, when a pass needs it (ordered_range_sums)
     // peer stores (null: none): part that holds the other end of each connection (-1: this one) and the entry's position in that
     // part's receive buffer
     const signed char* x_peer; const int* x_rid; const PeerTable* peers;
@@ -464,14 +465,100 @@ struct DistTotals {
 };
 struct ShipTotals {
     double rev; i64 eq; double ev;
-    static ACC_HD ShipTotals identity() { ShipTotals r; r.rev = 0.0; r.eq = 0; r.ev = 0.0; return r; }
-    static ACC_HD ShipTotals combine(ShipTotals a, ShipTotals b) { ShipTotals r; r.rev = a.rev + b.rev; r.eq = a.eq + b.eq; r.ev = a.ev + b.ev; return r; }
+    i64 doubt;  // shipments whose pro-rata quantity lies so close to a rounding boundary that the order of the sums behind it may decide
+    static ACC_HD ShipTotals identity() { ShipTotals r; r.rev = 0.0; r.eq = 0; r.ev = 0.0; r.doubt = 0; return r; }
+    static ACC_HD ShipTotals combine(ShipTotals a, ShipTotals b) {
+        ShipTotals r; r.rev = a.rev + b.rev; r.eq = a.eq + b.eq; r.ev = a.ev + b.ev; r.doubt = a.doubt + b.doubt; return r;
+    }
 };
+// Is f / precision (as f * inv) within `slack` (in quanta) of a half-integer, i.e. can a perturbation of that size change round()?
+ACC_HD bool near_rounding_boundary(double f, double inv, double slack) {
+    const double y = fabs(f * inv);
+    const double fr = y - floor(y);
+    return fabs(fr - 0.5) <= slack + 1e-9;
+}
 
 // cheapest_price_range_half_width, SalesManager.cpp:151-159 (each typed step re-quantised)
 ACC_HD i64 half_width(const ModelP& mp, i64 dn, double beta) {
     if (mp.generic_width) return pdiv(pmul(pmul(pdiv(dn, 2.0), beta - 1), beta - 1), beta);
     return pdiv(mp.width, 2.0);
+}
+
+// Demand of the cheapest price range as the reference accumulates it (SalesManager.cpp:163-185): two DOUBLE sums -- quantity and
+// value -- over the connections in the order calc_production_X has sorted them into (price descending, then quantity descending,
+// :104-127; connections with equal price and quantity contribute equal summands, so their mutual order does not matter).  The
+// engine does not sort (every decision of the scan is taken on int64 totals) and sums values in its fixed tree order,
+// which agrees with the reference to ~1e-16 -- not enough where the pro-rata formula (:216-224) lands on an exact half quantum:
+// at the onset of a shock from the baseline all prices are equal, a firm at half capacity ships q / 2 to every buyer, and for
+// every odd q the last bits of the two sums decide which way round() goes (found by the three-year flood run: one shipment in
+// 27 000 off by a quantum at step 10).  seller_phase1 therefore bounds how far its sums can lie from the reference's ((n + 16)
+// unit roundoffs, both being sums of positive terms), carries the bound through the three roundings that depend on them (average
+// price, price shift, every shipment) and, if any of them comes within the bound of a rounding boundary, takes the sums in the
+// reference's order instead: the range's connections are sorted (a bitonic network over 16-bit indices in the CTA's shared memory
+// -- over the seller's slice of a per-connection scratch array where the launch had no room for them --, connections outside the
+// range as sentinels at the end; comparisons read the staged book), then added up left to right.  O(n log^2 n) for a seller in doubt -- every shocked seller at a shock's onset, about one in a thousand otherwise.
+ACC_HD int ordered_range_slots(int n) { int N = 1; while (N < n) N <<= 1; return N; }  // < 2 n: the scratch holds two ints per connection
+// where the permutation lives: the CTA's shared memory when the launch provided room for it (16-bit entries), else global scratch
+struct PermGlobal {
+    int* p;
+    ACC_HD int get(int i) const { return p[i]; }
+    ACC_HD void set(int i, int v) const { p[i] = v; }
+};
+struct PermShared {
+    unsigned short* p;
+    ACC_HD int get(int i) const { const unsigned short v = p[i]; return v == 0xffffu ? -1 : (int)v; }
+    ACC_HD void set(int i, int v) const { p[i] = v < 0 ? (unsigned short)0xffffu : (unsigned short)v; }
+};
+template <class Ctx, class Perm>
+ACC_HD void ordered_range_sums(Ctx& cx, int n, const i64* Dq, const i64* Dp, i64 cutoff, i64 h, int m, Perm perm, double (&rs)[2]) {
+    const int N = ordered_range_slots(n);
+    cx.foreach(N, [&](int i) {
+        int v = -1;
+        if (i < n) {
+            const i64 d = Dp[i] - cutoff;
+            if (Dq[i] > 0 && (d < 0 ? -d : d) < h) v = i;
+        }
+        perm.set(i, v);
+    });
+    // strict total order: sentinels last, equal keys by connection (any order of equal keys gives the same sums)
+    auto before = [&](int a, int b) {
+        if (a < 0) return false;
+        if (b < 0) return true;
+        const i64 pa = Dp[a], pb = Dp[b];
+        if (pa != pb) return pa > pb;
+        const i64 qa = Dq[a], qb = Dq[b];
+        if (qa != qb) return qa > qb;
+        return a < b;
+    };
+    for (int k = 2; k <= N; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            cx.sync();
+            // eight pairs per turn, all of their loads first: a thread's stores to perm would otherwise order its next loads behind them
+            enum { B = 8 };
+            cx.foreach((N / 2 + B - 1) / B, [&](int g) {
+                int a[B], b[B];
+#pragma unroll
+                for (int u = 0; u < B; ++u) {
+                    const int t = g * B + u;
+                    const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));  // the pair's lower index: bit j clear
+                    a[u] = t < N / 2 ? perm.get(i) : -1;
+                    b[u] = t < N / 2 ? perm.get(i | j) : -1;
+                }
+#pragma unroll
+                for (int u = 0; u < B; ++u) {
+                    const int t = g * B + u;
+                    const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                    const bool ascending = (i & k) == 0;
+                    if (t < N / 2 && (ascending ? before(b[u], a[u]) : before(a[u], b[u]))) { perm.set(i, b[u]); perm.set(i | j, a[u]); }
+                }
+            });
+        }
+    }
+    cx.sync();
+    cx.template seqsum<2>(m, [&](int r, int k) {
+        const int i = perm.get(r);
+        return k == 0 ? qf(Dq[i]) : q_times_p(Dq[i], Dp[i]);
+    }, rs);
 }
 
 template <class Ctx>
@@ -577,43 +664,73 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
         });
         const i64 P = X.q - dt_.fq;                                   // production_cheapest_price_range, :197-198
         const bool prorata = dt_.rcnt > 0 && dt_.rq > P;              // :199
-        i64 shift = 0, seller_price = 0;
-        double den = 1.0;
-        if (prorata) {
-            const i64 pmax_r = cutoff + h, pmin_r = cutoff - h;
-            const i64 avg = mkp(dt_.rv / qf(dt_.rq));                 // :206
-            const i64 cand = mkp((q_times_p(P, pmax_r) - q_times_p(dt_.rq, avg)) / qf(dt_.rq - P));  // :207-209
-            shift = cand > (0 - pmin_r) ? cand : (0 - pmin_r);
-            seller_price = mkp((X.v - dt_.fv) / qf(P));               // :211-212
-            den = q_times_p(dt_.rq, shift) + dt_.rv;                  // :220
-        }
-        const ShipTotals st_ = cx.template reduce<ShipTotals>(n, [&](int i) {
-            ShipTotals r = ShipTotals::identity();
-            const i64 q = Dq[i];
-            Flow z = mkflow(0, 0.0);
-            if (q > 0) {
-                const i64 p = Dp[i];
-                const i64 d = p - cutoff;
-                if (d >= h) {
-                    z = flow_qp(q, p);                                // :170
-                } else if ((d < 0 ? -d : d) < h) {
-                    if (prorata) {                                    // :216-224
-                        const i64 zq = mkq(qf(P) * (q_times_p(q, shift) + q_times_p(q, p)) / den);
-                        z = fcopy(flow_qp(zq, mp.preserve_seller_price ? seller_price : p));
-                        r.rev = z.v;
-                    } else {
-                        z = flow_qp(q, p);                            // :234
-                    }
+        // demand_cheapest_price_range / demand_value_cheapest_price_range (:176-177): the engine's sums first; `exact` once they
+        // have been taken in the reference's order (see ordered_range_sums)
+        double rq_f = qf(dt_.rq), rv_f = dt_.rv;
+        bool exact = ev.sort_scratch == nullptr;
+        const double kappa = (double)(n + 16) * 0x1p-53;              // relative distance of either sum from the reference's
+        ShipTotals st_ = ShipTotals::identity();
+        for (;;) {
+            i64 shift = 0, seller_price = 0;
+            double den = 1.0, ship_slack = 0.0;
+            bool doubt = false;
+            if (prorata) {
+                const i64 pmax_r = cutoff + h, pmin_r = cutoff - h;
+                const double ratio = rv_f / rq_f;
+                const i64 avg = mkp(ratio);                           // :206
+                const double num = q_times_p(P, pmax_r) - rq_f * pf(avg), den2 = rq_f - qf(P);
+                const double c = num / den2;
+                const i64 cand = mkp(c);                              // :207-209
+                shift = cand > (0 - pmin_r) ? cand : (0 - pmin_r);
+                seller_price = mkp((X.v - dt_.fv) / qf(P));           // :211-212
+                den = rq_f * pf(shift) + rv_f;                        // :220
+                if (!exact) {
+                    const double dc = 2.0 * kappa * (rq_f * pf(avg) + fabs(c) * rq_f) / fabs(den2);
+                    doubt = near_rounding_boundary(ratio, 1e6, 4.0 * kappa * ratio * 1e6) || near_rounding_boundary(c, 1e6, dc * 1e6);
+                    ship_slack = 2.0 * kappa * (rq_f * fabs(pf(shift)) + rv_f) / den;  // relative, of every pro-rata quantity
                 }
             }
-            const i64 at = ring_slot_last(ev.rings, slotw[i]);
-            ev.conv_q[at] = z.q;                                      // BusinessConnection::push_flow_Z -> first transport link
-            if (ev.ship_q != nullptr) { ev.ship_q[e0 + i] = z.q; ev.ship_v[e0 + i] = z.v; }  // last_shipment_Z, kept apart when hops rewrite the slot
-            ev.conv_v[at] = z.v;
-            peer_store_shipment(ev, (i64)e0 + i, z);
-            if (!dom[i]) { r.eq = z.q; r.ev = z.v; }                  // Region::add_export_Z, BusinessConnection.cpp:91-93
-            return r;
-        });
+            if (!doubt) {
+                st_ = cx.template reduce<ShipTotals>(n, [&](int i) {
+                    ShipTotals r = ShipTotals::identity();
+                    const i64 q = Dq[i];
+                    Flow z = mkflow(0, 0.0);
+                    if (q > 0) {
+                        const i64 p = Dp[i];
+                        const i64 d = p - cutoff;
+                        if (d >= h) {
+                            z = flow_qp(q, p);                        // :170
+                        } else if ((d < 0 ? -d : d) < h) {
+                            if (prorata) {                            // :216-224
+                                const double x = qf(P) * (q_times_p(q, shift) + q_times_p(q, p)) / den;
+                                if (!exact && near_rounding_boundary(x, 1e3, ship_slack * x * 1e3)) r.doubt = 1;
+                                const i64 zq = mkq(x);
+                                z = fcopy(flow_qp(zq, mp.preserve_seller_price ? seller_price : p));
+                                r.rev = z.v;
+                            } else {
+                                z = flow_qp(q, p);                    // :234
+                            }
+                        }
+                    }
+                    const i64 at = ring_slot_last(ev.rings, slotw[i]);
+                    ev.conv_q[at] = z.q;                              // BusinessConnection::push_flow_Z -> first transport link
+                    if (ev.ship_q != nullptr) { ev.ship_q[e0 + i] = z.q; ev.ship_v[e0 + i] = z.v; }  // last_shipment_Z, kept apart when hops rewrite the slot
+                    ev.conv_v[at] = z.v;
+                    peer_store_shipment(ev, (i64)e0 + i, z);
+                    if (!dom[i]) { r.eq = z.q; r.ev = z.v; }          // Region::add_export_Z, BusinessConnection.cpp:91-93
+                    return r;
+                });
+                doubt = st_.doubt != 0;
+            }
+            if (!doubt || exact) break;
+            double rs[2];
+            if (book.perm16 != nullptr && ordered_range_slots(n) <= book.perm_slots)
+                ordered_range_sums(cx, n, Dq, Dp, cutoff, h, (int)dt_.rcnt, PermShared{book.perm16}, rs);
+            else
+                ordered_range_sums(cx, n, Dq, Dp, cutoff, h, (int)dt_.rcnt, PermGlobal{ev.sort_scratch + 2 * (i64)e0}, rs);
+            rq_f = rs[0]; rv_f = rs[1];
+            exact = true;                                             // ... and the shipments are written once more
+        }
         if (dt_.rcnt > 0 && prorata) R = dt_.fv + st_.rev;            // :214,225
         else R = X.v;                                                 // :231,241
         exq = st_.eq; exv = st_.ev;

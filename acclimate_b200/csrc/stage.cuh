@@ -3,7 +3,7 @@
 // SalesManager::distribute_production and calc_supply_distribution_scenario (reference src/model/SalesManager.cpp:140-423)
 // walk the seller's demand requests several times (totals, the price scan, the cheapest-price-range totals, the
 // shipments).  A seller's connections are contiguous (CSR by seller), so ONE thread hands the whole book to the copy
-// engine -- four 1-D bulk copies (quantity, price, delay, domestic flag) that complete on an mbarrier -- and every pass
+// engine -- three 1-D bulk copies (quantity, price, domestic flag) that complete on an mbarrier -- and every pass
 // then runs out of shared memory: HBM sees each demand request once, and the number of loads in flight no longer
 // depends on how many warps are resident.
 #pragma once
@@ -14,14 +14,15 @@ namespace acc {
 
 // what seller_phase1 reads per connection; null pointers = read the global arrays
 struct SellerBook {
-    const i64* q; const i64* p; const unsigned char* tau; const unsigned char* dom;
+    const i64* q; const i64* p; const unsigned char* dom;
+    unsigned short* perm16; int perm_slots;  // shared-memory scratch for a sort of the seller's connections (model_core.cuh ordered_range_sums), or null
 };
 
 ACC_HD size_t seller_book_bytes(int cap) {
-    // two i64 arrays with one element of slack (16-byte phase of the source), two byte arrays with 16 bytes of slack
+    // two i64 arrays with one element of slack (16-byte phase of the source), one byte array with 16 bytes of slack
     const size_t words = ((size_t)(cap + 2) * sizeof(i64) + 15) / 16 * 16;
     const size_t bytes = ((size_t)cap + 16 + 15) / 16 * 16;
-    return 2 * words + 2 * bytes;
+    return 2 * words + bytes;
 }
 
 #if defined(__CUDACC__)
@@ -85,23 +86,22 @@ struct BookPart {
 
 // Stage the book of the connections [e0, e0 + n) of one seller.  `bar` is one mbarrier in static shared memory that this
 // CTA uses once (phase 0); the caller has initialised it (mbar_init(bar, 1) by one thread, then a CTA barrier) and puts
-// a CTA barrier behind this call.  Thread 0 hands the four arrays to the copy engine, the first warp moves the few
+// a CTA barrier behind this call.  Thread 0 hands the three arrays to the copy engine, the first warp moves the few
 // unaligned head / tail elements, every caller waits for the copies.  A warp may arrive late (it works on something else
 // first, see seller_kernel): it then only waits.
 __device__ __forceinline__ SellerBook stage_seller_book(unsigned char* smem, int cap, unsigned long long* bar, const i64* D_q, const i64* D_p,
-                                                        const unsigned char* tau, const unsigned char* dom, int e0, int n) {
+                                                        const unsigned char* dom, int e0, int n) {
     const size_t words = ((size_t)(cap + 2) * sizeof(i64) + 15) / 16 * 16;
-    const size_t bytes = ((size_t)cap + 16 + 15) / 16 * 16;
     const BookPart<i64> q(D_q + e0, smem, n), p(D_p + e0, smem + words, n);
-    const BookPart<unsigned char> t(tau + e0, smem + 2 * words, n), d(dom + e0, smem + 2 * words + bytes, n);
+    const BookPart<unsigned char> d(dom + e0, smem + 2 * words, n);
     if (threadIdx.x == 0) {
-        mbar_expect_tx(bar, q.body_bytes + p.body_bytes + t.body_bytes + d.body_bytes);
-        q.issue(bar); p.issue(bar); t.issue(bar); d.issue(bar);
+        mbar_expect_tx(bar, q.body_bytes + p.body_bytes + d.body_bytes);
+        q.issue(bar); p.issue(bar); d.issue(bar);
     }
-    if (threadIdx.x < 32) { q.edges(); p.edges(); t.edges(); d.edges(); }
+    if (threadIdx.x < 32) { q.edges(); p.edges(); d.edges(); }
     mbar_wait(bar, 0);
     SellerBook b;
-    b.q = q.dst; b.p = p.dst; b.tau = t.dst; b.dom = d.dst;
+    b.q = q.dst; b.p = p.dst; b.dom = d.dst; b.perm16 = nullptr; b.perm_slots = 0;
     return b;
 }
 #endif
