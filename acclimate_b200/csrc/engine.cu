@@ -839,6 +839,7 @@ struct acc_engine {
     // buyer-side lists
     DBuf<i64> ell_off, in_off;
     DBuf<int> ell_width, ell_edge, in_edge, in_seller;
+    DBuf<int> f_sorted;  // per firm: the last sellers' pass took the pro-rata sums in sorted order (diagnostic, read_state "firm_sorted_sums")
     DBuf<int> e_sort;  // scratch of the sellers' pass: a seller's connections in sorted order (model_core.cuh ordered_range_sums)
     DBuf<unsigned> e_slotw, ell_slotw, in_slotw;  // conveyor words (ring << 24 | rank) in connection order and in both buyer-side orders
     ConveyorRings rings;                          // groups of equal delay (phase filled in per view)
@@ -912,7 +913,7 @@ struct acc_engine {
         v(pubT); v(seller_row); v(row_firm); v(e_to); v(sto_of); v(obs_out); v(obs_idx); v(obs_inc_q); v(obs_inc_v);
         v(s_Istar_q); v(s_Sstar_q); v(s_defc); v(s_Istar_v); v(s_Sstar_v); v(s_a); v(s_agent); v(s_sector);
         v(e_seller_off); v(e_route); v(route_off); v(route_ent); v(ent_delay); v(e_Z_q); v(e_tau); v(e_dom);
-        v(ell_off); v(in_off); v(ell_width); v(ell_edge); v(in_edge); v(in_seller); v(in_Z); v(e_slotw); v(ell_slotw); v(in_slotw); v(e_sort);
+        v(ell_off); v(in_off); v(ell_width); v(ell_edge); v(in_edge); v(in_seller); v(in_Z); v(e_slotw); v(ell_slotw); v(in_slotw); v(e_sort); v(f_sorted);
         v(cons_ids); v(c_order_cnt); v(c_order); v(c_order_basket); v(fatal); v(c_nx_q); v(c_nx_v); v(c_nx_util); v(c_nx_ret);
         v(c_share); v(c_eshare); v(c_budget); v(c_bshare); v(c_ebshare); v(c_intra_exp); v(c_base_q);
         v(owned); v(pm_ids); v(halo_send); v(halo_recv);
@@ -968,7 +969,7 @@ struct acc_engine {
         v.X_q = f_X_q.p; v.X_v = f_X_v.p; v.Xexp_q = f_Xexp_q.p; v.Xexp_v = f_Xexp_v.p; v.nbar = f_nbar.p; v.cutoff = f_cutoff.p;
         v.C = f_C.p; v.R = f_R.p; v.desired_q = f_desired_q.p; v.sumD_q = f_sumD_q.p; v.sumD_v = f_sumD_v.p;
         v.bk_sq = f_bk_sq.p; v.bk_sv = f_bk_sv.p; v.bk_cnt = f_bk_cnt.p; v.bk_pmax = f_bk_pmax.p; v.bk_pmin = f_bk_pmin.p;
-        v.exp_q = f_exp_q.p; v.exp_v = f_exp_v.p;
+        v.exp_q = f_exp_q.p; v.exp_v = f_exp_v.p; v.sorted = f_sorted.p;
         return v;
     }
     SellerTable seller_table() {
@@ -1725,6 +1726,7 @@ static void build(acc_engine& E, const acc_network& net, const acc_params& par, 
     E.ell_off.upload(ell_off, s); E.ell_width.upload(ell_width, s); E.ell_edge.upload(ell_edge, s);
     E.e_slotw.upload(slotw, s); E.ell_slotw.upload(ell_slotw, s); E.in_slotw.upload(in_slotw, s);
     E.e_sort.alloc(2 * (size_t)nE); E.e_sort.zero(s);
+    E.f_sorted.alloc((size_t)nA); E.f_sorted.zero(s);
     E.ev_buf.alloc(E.ev_cap); E.ev_count.alloc(1); E.ev_count.zero(s);
     E.nu.alloc((size_t)E.nEnt + 1);
     dev_sync(s);
@@ -1853,6 +1855,11 @@ static bool read_state(acc_engine& E, const std::string& name, StateArray& out) 
     if (name == "consumer_utility" && E.mp.utilitarian) return F(E.c_utility);
     if (name == "consumer_solver_ret" && E.mp.utilitarian) {  // return code of the last utility optimisation per agent (csrc/sqp_core.h)
         std::vector<int> h = E.c_nx_ret.download(s);
+        out.i.assign(h.begin(), h.end()); out.is_f64 = false;
+        return true;
+    }
+    if (name == "firm_sorted_sums") {  // diagnostic: sellers whose last pro-rata distribution needed the reference's summation order
+        std::vector<int> h = E.f_sorted.download(s);
         out.i.assign(h.begin(), h.end()); out.is_f64 = false;
         return true;
     }
@@ -2374,7 +2381,7 @@ acc_engine* acc_fork(acc_engine* parent) {
         CloneVisitor cv{E->stream};
         E->visit_state(cv);
         cv(E->pubT); cv(E->fatal);  // derived / scratch state that changes with the steps
-        cv(E->c_nx_q); cv(E->c_nx_v); cv(E->c_nx_util); cv(E->c_nx_ret); cv(E->e_sort);
+        cv(E->c_nx_q); cv(E->c_nx_v); cv(E->c_nx_util); cv(E->c_nx_ret); cv(E->e_sort); cv(E->f_sorted);
         E->ahead_step = -1;         // the member repeats the consumers' solve of its next step on its own copy of the state
         for (acc::DBuf<double>* b : {&E->obs_out, &E->obs_inc_v}) { b->p = nullptr; b->n = 0; b->borrowed = false; }
         for (acc::DBuf<i64>* b : {&E->obs_idx, &E->obs_inc_q}) { b->p = nullptr; b->n = 0; b->borrowed = false; }

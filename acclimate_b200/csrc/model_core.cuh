@@ -352,6 +352,7 @@ struct FirmView {
     i64* sumD_q; double* sumD_v;    // sum_demand_requests_D at the start of the step
     i64* bk_sq; double* bk_sv; i64* bk_cnt; i64* bk_pmax; i64* bk_pmin;  // demand book totals, reused by the expectation phase
     i64* exp_q; double* exp_v;      // non-domestic shipments of this step (region export)
+    int* sorted;                    // 1 where this step's pro-rata distribution took its sums in the reference's sorted order (diagnostic)
 };
 
 // Peer memory of a region-partitioned run (acc_comm_enable_peer_stores): the other parts' halo receive buffers, mapped into this
@@ -521,14 +522,12 @@ ACC_HD void ordered_range_sums(Ctx& cx, int n, const i64* Dq, const i64* Dp, i64
         perm.set(i, v);
     });
     // strict total order: sentinels last, equal keys by connection (any order of equal keys gives the same sums)
+    // (no early exits: the four loads of a pair are unconditional, so those of the eight pairs of a turn can be in flight together)
     auto before = [&](int a, int b) {
-        if (a < 0) return false;
-        if (b < 0) return true;
-        const i64 pa = Dp[a], pb = Dp[b];
-        if (pa != pb) return pa > pb;
-        const i64 qa = Dq[a], qb = Dq[b];
-        if (qa != qb) return qa > qb;
-        return a < b;
+        const int ia = a < 0 ? 0 : a, ib = b < 0 ? 0 : b;
+        const i64 pa = Dp[ia], pb = Dp[ib], qa = Dq[ia], qb = Dq[ib];
+        const bool first = pa > pb || (pa == pb && (qa > qb || (qa == qb && a < b)));
+        return a >= 0 && (b < 0 || first);
     };
     for (int k = 2; k <= N; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
@@ -642,6 +641,7 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
     const unsigned char* dom = book.q != nullptr ? book.dom : ev.domestic + e0;
     double R = 0.0;
     i64 exq = 0; double exv = 0.0;
+    bool sorted_sums = false;
     if (X.q <= 0) {
         cx.foreach(n, [&](int i) {
             const i64 at = ring_slot_last(ev.rings, slotw[i]);
@@ -730,6 +730,7 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
                 ordered_range_sums(cx, n, Dq, Dp, cutoff, h, (int)dt_.rcnt, PermGlobal{ev.sort_scratch + 2 * (i64)e0}, rs);
             rq_f = rs[0]; rv_f = rs[1];
             exact = true;                                             // ... and the shipments are written once more
+            sorted_sums = true;
         }
         if (dt_.rcnt > 0 && prorata) R = dt_.fv + st_.rev;            // :214,225
         else R = X.v;                                                 // :231,241
@@ -744,6 +745,7 @@ ACC_HD void seller_phase1(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
         fv.sumD_q[f] = tot.sq; fv.sumD_v[f] = tot.sv;
         fv.bk_sq[f] = tot.sq; fv.bk_sv[f] = tot.sv; fv.bk_cnt[f] = tot.cnt; fv.bk_pmax[f] = tot.pmax; fv.bk_pmin[f] = tot.pmin;
         fv.exp_q[f] = exq; fv.exp_v[f] = exv;
+        if (fv.sorted != nullptr) fv.sorted[f] = sorted_sums ? 1 : 0;
     }
 }
 
