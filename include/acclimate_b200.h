@@ -261,7 +261,11 @@ int acc_observe(acc_engine* e, const char* group, const char* variable, const in
 int acc_firm_incoming_demand_static(acc_engine* e, double* out_quantity, double* out_value, size_t cap, size_t* n);
 
 /* Raw state for parity checks: int64 / f64 arrays named like the oracle's per-step dump
- * (oracle/ref_harness/harness.cpp dump_step).  is_f64 tells which type was written to dst. */
+ * (oracle/ref_harness/harness.cpp dump_step).  is_f64 tells which type was written to dst.
+ * Three names have no counterpart in the dump (diagnostics): "sto_solver_iters" / "sto_solver_evals" (SQP iterations and objective
+ * evaluations of every purchasing manager's last solve), "consumer_solver_ret" (return code of every consumer's last utility
+ * optimisation, csrc/sqp_core.h) and "firm_sorted_sums" (1 for the firms whose last pro-rata distribution took its demand sums in
+ * the reference's sorted order, csrc/model_core.cuh ordered_range_sums). */
 int acc_read_state(acc_engine* e, const char* name, void* dst, size_t cap_bytes, size_t* n, int* is_f64);
 
 /* counters */
