@@ -218,7 +218,10 @@ int acc_step(acc_engine* e);
 /* the same, split by phase as ModelRun::run calls them */
 enum { ACC_PHASE_CONSUMPTION_AND_PRODUCTION = 0, ACC_PHASE_EXPECTATION = 1, ACC_PHASE_PURCHASE = 2, ACC_PHASE_TICK = 3 };
 int acc_phase(acc_engine* e, int phase);
-/* block until the device has finished all queued phases */
+/* block until the device has finished all queued phases -- including the consumers' utility optimisation of the NEXT step, which
+ * the engine starts on a side stream as soon as this step's storages are final (it only reads model state; its results are applied
+ * at the start of the next step, and dropped if acc_load_state replaces the state in between).  Raises the error the reference
+ * ends a run with when a consumer's optimisation failed outright (src/model/Consumer.cpp:505-512). */
 int acc_sync(acc_engine* e);
 
 /* replaces ModelRun::event (src/ModelRun.cpp:255-275): *n receives the number of pending events; up to cap of them
