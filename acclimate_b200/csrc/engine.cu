@@ -879,6 +879,7 @@ struct acc_engine {
     PeerTable h_peers;
     unsigned long long barrier_epoch = 0;
     bool flag_barrier = false;
+    bool peer_sellers = false;  // the sellers' records travel by peer stores too (no collective in the step)
     std::vector<void*> ipc_opened;
 #ifndef ACC_HOST_EMU
     NcclApi::comm_t comm = nullptr;
@@ -963,6 +964,7 @@ struct acc_engine {
         FirmView v;
         v.pub = pub.p;
         v.pubT = seller_table();
+        v.peers = (peer_stores && peer_sellers) ? peer_table.p : nullptr; v.n_parts = comm_world; v.my_part = comm_rank;
         v.Xstar_q = f_Xstar_q.p; v.Xstar_v = f_Xstar_v.p; v.beta = a_beta.p; v.lambda = a_lambda.p; v.sector = a_sector.p; v.region = a_region.p;
         v.type = a_type.p; v.markup_eff = f_markup_eff.p; v.var_costs = f_var_costs.p; v.st_off = a_st_off.p; v.st_list = a_st_list.p;
         v.cap_q = f_cap_q.p; v.cap_v = f_cap_v.p; v.Xhat_q = f_Xhat_q.p; v.Xhat_v = f_Xhat_v.p; v.est_q = f_est_q.p; v.est_v = f_est_v.p;
@@ -1225,14 +1227,19 @@ struct acc_engine {
             launch_delivery(owned.p);
             SellerExpectation k{firm_view(), edge_view(), storage_view(), mp, sectors.p, sink(), firm_ids.p};
             timed("seller_expectation", [&] { launch_warp(stream, nF, 0, k); });
-            PackSellerRows pk{pub.p, firm_ids.p, comm_rows_send.p};
-            timed("pack_sellers", [&] { launch_thread(stream, nF, pk); });
+            if (!(peer_stores && peer_sellers)) {
+                PackSellerRows pk{pub.p, firm_ids.p, comm_rows_send.p};
+                timed("pack_sellers", [&] { launch_thread(stream, nF, pk); });
+            }
         }
-        timed_comm("exchange_sellers", [&] {
-            ACC_NCCL(nc.AllGather(comm_rows_send.p, comm_rows_recv.p, (size_t)comm_max_rows * ACC_SELLER_WORDS, NcclApi::Int64, comm, stream));
-            ++collectives;
-        });
-        {
+        if (peer_stores && peer_sellers) {
+            // the expectation pass has stored every owned firm's record into the other parts' tables: all of them have landed
+            timed_comm("barrier_sellers", [&] { cross_barrier(); });
+        } else {
+            timed_comm("exchange_sellers", [&] {
+                ACC_NCCL(nc.AllGather(comm_rows_send.p, comm_rows_recv.p, (size_t)comm_max_rows * ACC_SELLER_WORDS, NcclApi::Int64, comm, stream));
+                ++collectives;
+            });
             UnpackSellerRows k{pub.p, seller_table(), comm_part_firms.p, comm_part_off.p, comm_world, comm_rank, comm_max_rows, comm_rows_recv.p};
             timed("unpack_sellers", [&] { launch_thread(stream, comm_world * comm_max_rows, k); });
         }
@@ -2550,7 +2557,7 @@ int acc_comm_enable_peer_stores(acc_engine* e) {
     // every part tells the others where its two receive buffers are (IPC handles) and how its halo lists split over the parts:
     // the k-th entry this part sends to part p is the k-th entry p receives from it (both lists are in global order), so its
     // position in p's buffer is p's offset for this part + k -- no per-connection id has to travel
-    struct Hello { i64 send_cnt[ACC_MAX_PARTS], recv_cnt[ACC_MAX_PARTS]; cudaIpcMemHandle_t h[3]; };
+    struct Hello { i64 send_cnt[ACC_MAX_PARTS], recv_cnt[ACC_MAX_PARTS]; cudaIpcMemHandle_t h[5]; };
     static_assert(sizeof(Hello) % 8 == 0, "exchanged as int64 words");
     Hello mine;
     std::memset(&mine, 0, sizeof mine);
@@ -2558,8 +2565,8 @@ int acc_comm_enable_peer_stores(acc_engine* e) {
     e->barrier_flags.alloc(ACC_MAX_PARTS); e->barrier_flags.zero(s);
     e->barrier_timeout.alloc(1); e->barrier_timeout.zero(s);
     dev_sync(s);
-    void* arrays[3] = {e->own_flow_recv.p, e->own_dem_recv.p, e->barrier_flags.p};
-    for (int k = 0; k < 3; ++k) ACC_CUDA(cudaIpcGetMemHandle(&mine.h[k], arrays[k]));
+    void* arrays[5] = {e->own_flow_recv.p, e->own_dem_recv.p, e->barrier_flags.p, e->pub.p, e->pubT.p};
+    for (int k = 0; k < 5; ++k) ACC_CUDA(cudaIpcGetMemHandle(&mine.h[k], arrays[k]));
     DBuf<i64> d_hello, d_all;
     const size_t words = sizeof(Hello) / 8;
     d_hello.alloc(words); d_all.alloc(words * world);
@@ -2574,14 +2581,15 @@ int acc_comm_enable_peer_stores(acc_engine* e) {
     for (int p = 0; p < world; ++p) {
         if (all[p].recv_cnt[rank] != e->comm_send_cnt[p] || all[p].send_cnt[rank] != e->comm_recv_cnt[p])
             fail("acc_comm_enable_peer_stores: the parts' halo lists do not match");
-        void* ptr[3];
-        for (int k = 0; k < 3; ++k) {
+        void* ptr[5];
+        for (int k = 0; k < 5; ++k) {
             if (p == rank) { ptr[k] = arrays[k]; continue; }
             ACC_CUDA(cudaIpcOpenMemHandle(&ptr[k], all[p].h[k], cudaIpcMemLazyEnablePeerAccess));
             e->ipc_opened.push_back(ptr[k]);
         }
         pt.flow_recv[p] = static_cast<i64*>(ptr[0]); pt.dem_recv[p] = static_cast<i64*>(ptr[1]);
         pt.flags[p] = static_cast<unsigned long long*>(ptr[2]);
+        pt.pub[p] = static_cast<SellerPub*>(ptr[3]); pt.pubT[p] = static_cast<double*>(ptr[4]);
     }
     std::vector<i64> hs = e->halo_send.download(s), hr = e->halo_recv.download(s);
     std::vector<signed char> xp((size_t)e->nE, (signed char)-1);
@@ -2605,6 +2613,7 @@ int acc_comm_enable_peer_stores(acc_engine* e) {
     dev_sync(s);
     e->h_peers = pt;
     e->flag_barrier = std::getenv("ACC_NCCL_BARRIER") == nullptr;  // ACC_NCCL_BARRIER=1: one-word all-reduces instead (for comparison)
+    e->peer_sellers = std::getenv("ACC_NCCL_SELLERS") == nullptr;  // ACC_NCCL_SELLERS=1: the sellers' records by ncclAllGather instead (for comparison)
     e->peer_stores = true;
 #endif
     return 0;

@@ -334,8 +334,11 @@ ACC_HD void publish_seller(const SellerTable& t, int agent, const SellerPub& pb)
 // ------------------------------------------------------------------------------------------------
 // Per-firm state
 // ------------------------------------------------------------------------------------------------
+struct PeerTable;
 struct FirmView {
     SellerPub* pub;                 // published after the expectation phase, read by the purchasing phase
+    // peer stores (null: none): the other parts' copies of both seller tables; an owned firm's record goes straight into them
+    const PeerTable* peers; int n_parts, my_part;
     SellerTable pubT;               // ... and its field-major twin
     const i64* Xstar_q; const double* Xstar_v; const double* beta; const double* lambda; const int* sector; const int* region; const int* type;
     const i64* markup_eff; const i64* var_costs;  // SalesManager::get_initial_markup / get_initial_unit_variable_production_costs
@@ -365,7 +368,18 @@ struct PeerTable {
     i64* flow_recv[ACC_MAX_PARTS];  // [n_recv_p][2] shipments (quantity, value bits) part p receives
     i64* dem_recv[ACC_MAX_PARTS];   // [n_send_p][2] demand requests (quantity, price) part p receives
     unsigned long long* flags[ACC_MAX_PARTS];  // [ACC_MAX_PARTS] arrival counters of part p, one per announcing part (cross-part barrier)
+    SellerPub* pub[ACC_MAX_PARTS];  // part p's seller records (FirmView::pub) ...
+    double* pubT[ACC_MAX_PARTS];    // ... and their field-major twin (SellerTable::f; rows and stride are the same on every part)
 };
+// an owned firm's new record, stored into every other part's tables (the purchasing managers there read it after the next barrier)
+ACC_HD void peer_publish_seller(const FirmView& fv, int f, int p) {
+    if (p == fv.my_part) return;
+    const SellerPub pb = fv.pub[f];
+    fv.peers->pub[p][f] = pb;
+    SellerTable t = fv.pubT;
+    t.f = fv.peers->pubT[p];
+    publish_seller(t, f, pb);
+}
 struct alignas(16) HaloEntry {
     i64 a, b;
 };
@@ -856,6 +870,10 @@ ACC_HD void seller_phase2(Ctx& cx, int f, const FirmView& fv, const EdgeView& ev
         pb.n_co = (pb.Xf <= pb.lamXf) ? ncf : ncf + pb.c2 * (pb.Xf - pb.lamXf);
         fv.pub[f] = pb;
         publish_seller(fv.pubT, f, pb);
+    }
+    if (fv.peers != nullptr) {
+        cx.sync();  // the record is in this part's table: one lane per other part copies it over
+        cx.foreach(fv.n_parts, [&](int p) { peer_publish_seller(fv, f, p); });
     }
     // Firm::iterate_expectation, Firm.cpp:65-73: sum_demand_requests_D was zeroed two lines earlier
     // (SalesManager.cpp:623), so the desired production is the expected production
