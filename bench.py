@@ -481,7 +481,7 @@ def main():
             pk = sum(v[0] for k, v in ktimes.items() if k.startswith("pack_") or k.startswith("unpack_")) / args.steps
             line["partition"] = {"collective_ms": exchange_ms, "pack_ms": pk, "halo_bytes_per_step_this_rank": E.halo_bytes_per_step(),
                                  "data_plane": ("acc_step_partitioned (C++): halos stored into the peers' memory by the producing kernels over NVLink (CUDA IPC), "
-                                                "2 cross-part barriers over the same peer memory + 1 NCCL all-gather of seller records per step" if getattr(E, "peer_stores", False)
+                                                "the sellers' records likewise from the expectation pass, 3 cross-part barrier kernels over the same peer memory and no collective per step" if not os.environ.get("ACC_NCCL_SELLERS") else "2 cross-part barriers over the same peer memory + 1 NCCL all-gather of seller records per step" if getattr(E, "peer_stores", False)
                                                 else "acc_step_partitioned (C++, NCCL send/recv groups)") if nccl_plane else "acc_stage + torch.distributed"}
         print(json.dumps(line))
     E.close()
