@@ -4,11 +4,12 @@
 //   * BusinessConnections are stored once, CSR by seller (the file order of the snapshot).  Per
 //     connection: Z* (int64), last demand request D as (quantity, price) int64 pair, delay tau (u8),
 //     domestic flag (u8), geo entity (int32).
-//   * TransportChainLink delay queues are a "conveyor": T = max(tau)+1 planes of [n_edges] (quantity
-//     int64 plane + value f64 plane).  The shipment of step t on a connection with delay tau is written
-//     to plane (t + tau) mod T and arrives when plane t mod T is read -- every connection advances by
-//     exactly one slot per step (reference TransportChainLink.cpp:69-71), so the ring shift is pure
-//     index arithmetic, arrivals of a step are ONE contiguous plane, and nothing is ever moved.
+//   * TransportChainLink delay queues are a "conveyor": every connection owns a ring of tau + 1 slots (int64
+//     quantity + f64 value); connections of equal delay form a ring group stored plane by plane (model_core.cuh
+//     ConveyorRings).  The shipment of step t on a connection with delay tau is written to slot (t + tau) mod
+//     (tau + 1) and arrives when slot t mod (tau + 1) is read -- every connection advances by exactly one slot per
+//     step (reference TransportChainLink.cpp:69-71), so the ring shift is pure index arithmetic and nothing is ever
+//     moved.
 //   * Buyer side: storages are numbered sector-major / buyer-minor so that neighbouring storages read
 //     neighbouring connections; incoming connections are listed per storage (CSC) twice: sliced-ELL
 //     (k-major in slices of 32 storages) for the thread-per-storage delivery pass and storage-major
@@ -17,7 +18,9 @@
 // Kernels of one step (reference phase they implement):
 //   seller_production          CapacityManager::get_possible_production_X_hat (one warp, while the demand book is staged),
 //                              SalesManager::calc_production_X + distribute              (phase 1)
-//   consumer_utility           Consumer::iterate_consumption_and_production, side stream (phase 1)
+//   consumer_utility           Consumer::iterate_consumption_and_production: the optimisation, on a side stream, started
+//                              behind storage_delivery of the step BEFORE (it only reads state)       (phase 1)
+//   consumer_apply             ... its results become the step's desired use                           (phase 1)
 //   storage_delivery           Firm/Consumer input use, Storage::calc_content_S, TransportChainLink::push_flow_Z
 //                              arrivals, Storage::push_flow_Z accumulation               (phase 1)
 //   seller_expectation         SalesManager::iterate_expectation, Firm::iterate_expectation (phase 2)
